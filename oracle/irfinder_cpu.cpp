@@ -1,0 +1,554 @@
+// oracle/irfinder_cpu.cpp — CPU restatement of IRFinder 1.x's BAM -> intron-retention counting core.
+//
+// *** TEST INFRASTRUCTURE, NOT PRODUCT. ***  Only tests/, __graft_entry__.smoke() and bench.py's
+// cpu_baseline / --impl reference legs may build or execute this file.  The product library
+// (irfinder_b200/csrc) never includes, links or calls anything under oracle/.
+//
+// *** PARITY UNPINNED. ***  /root/reference holds only a redirect README (README.md:1-7); no
+// IRFinder source, test, fixture or golden vector exists offline.  This file
+// therefore follows the behavioural specification in SURVEY.md Appendix B (recalled upstream files
+// src/irfinder/{BAM2blocks,FragmentBlocks,ReadBlockProcessor,ReadBlockProcessor_CoverageBlocks,
+// CoverageBlock,irfinder}.cpp).  Every behaviour that SURVEY.md Appendix C lists as uncertain is
+// isolated in one named constant or one small function tagged [C-n] so it can be corrected in one
+// place once real source is available.  Parity claims read "identical to the in-repo CPU
+// restatement", not "identical to IRFinder".
+//
+// Deliberately naive and single-threaded: std::map / std::upper_bound, one record at a time, the
+// same shape as the reference (BAM2blocks producer -> FragmentBlocks -> ReadBlockProcessor
+// callbacks), so it can be diffed function by function against upstream.
+//
+// usage: irfinder_cpu <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|-> [--dump-fragments FILE]
+//   <bam> may be BGZF/gzip (inflated through zlib, which is what the reference's `gzip -cd |` pipe does)
+//   or an already-inflated BAM byte stream.  Records must be mate-adjacent.
+//   env IRF_TRIM_CENTER overrides the trimmed-mean centre percentage [C-2].
+#include <zlib.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <functional>
+#include <iostream>
+#include <map>
+#include <sstream>
+#include <string>
+#include <vector>
+
+using std::string;
+using std::vector;
+
+// ---------------------------------------------------------------------------------------------
+// Disputed constants.  One place each.
+static unsigned TRIM_CENTER_PERCENT = 40;        // [C-2] central band kept by the trimmed mean (40 => ranks 30%..70%)
+static const int JUNC_MIN_FLANK = 5;             // [C-3] both flanking blocks must be >= 5 bp
+static const unsigned SPAN_OVERHANG_LEFT = 5;    // [C-4]
+static const unsigned SPAN_OVERHANG_RIGHT = 4;   // [C-4]
+static const unsigned DIR_MIN_TOTAL = 8;         // [C-11] junction considered when total > 8
+static const unsigned DIR_RATIO = 4;             // [C-11] one strand > 4x the other
+static const unsigned DIR_DECISIVE = 100;        // [C-11] agree > 100x oppose
+static const unsigned EDGE_WINDOW_OFFSET = 5;    // [C-13] first/last-50bp windows start 5 bp inside the intron
+static const unsigned EDGE_WINDOW_LEN = 50;      // [C-13]
+static const char* HDR_IR = "Chr\tStart\tEnd\tName\tNull\tStrand\tExcludedBases\tCoverage\tIntronDepth\tIntronDepth25Percentile\tIntronDepth50Percentile\tIntronDepth75Percentile\tExonToIntronReadsLeft\tExonToIntronReadsRight\tIntronDepthFirst50bp\tIntronDepthLast50bp\tSpliceLeft\tSpliceRight\tSpliceExact\tIRratio\tWarnings\n";
+static const char* HDR_JC = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";   // [C-15]
+static const char* HDR_SP = "SP_seqname\tcoord\ttotal\tpos\tneg\n";                 // [C-15]
+static const char* HDR_ROI = "ROI_Name\ttotal\tpos\tneg\n";                          // [C-15]
+static const char* HDR_CHR = "ChrCoverage_RName\ttotal\tpos\tneg\n";                 // [C-15]
+
+// ---------------------------------------------------------------------------------------------
+// FragmentBlocks (upstream FragmentBlocks.h)
+struct FragmentBlocks {
+  string readName;
+  vector<int> rStarts[2];   // block starts relative to readStart
+  vector<int> rLens[2];
+  unsigned readStart[2] = {0, 0};
+  unsigned readEnd[2] = {0, 0};
+  int readCount = 0;        // 1 or 2
+  unsigned chr_id = 0;
+  bool direction = false;   // [C-8] 1 = first mate (or the single read) maps forward
+};
+
+// ReadBlockProcessor (row a6; upstream ReadBlockProcessor.h)
+class ReadBlockProcessor {
+ public:
+  virtual void ProcessBlocks(const FragmentBlocks& fragblock) = 0;
+  virtual void ChrMapUpdate(const vector<string>& chrmap) = 0;
+  virtual ~ReadBlockProcessor() {}
+};
+
+static vector<string> split_tabs(const string& line) {
+  vector<string> f; size_t p = 0;
+  for (;;) { size_t q = line.find('\t', p); if (q == string::npos) { f.push_back(line.substr(p)); break; } f.push_back(line.substr(p, q - p)); p = q + 1; }
+  if (!f.empty() && !f.back().empty() && f.back().back() == '\r') f.back().pop_back();
+  return f;
+}
+
+// ---------------------------------------------------------------------------------------------
+// JunctionCount (row a7; upstream ReadBlockProcessor.cpp)
+class JunctionCount : public ReadBlockProcessor {
+  // count[0] = direction 0 ("neg"), count[1] = direction 1 ("pos"), count[2] = annotated strand bits (1 '-', 2 '+')
+  typedef std::map<std::pair<unsigned, unsigned>, unsigned[3]> JMap;
+  std::map<string, JMap> chrName_junc_count;
+  std::map<string, std::map<unsigned, unsigned[2]>> chrName_juncLeft_count, chrName_juncRight_count;
+  vector<JMap*> chrID_junc_count;
+  vector<std::map<unsigned, unsigned[2]>*> chrID_juncLeft_count, chrID_juncRight_count;
+
+ public:
+  void loadRef(std::istream& IN) {
+    string line;
+    while (std::getline(IN, line)) {
+      if (line.empty()) continue;
+      auto f = split_tabs(line); if (f.size() < 4) continue;
+      unsigned s = (unsigned)std::stoul(f[1]), e = (unsigned)std::stoul(f[2]);
+      unsigned* c = chrName_junc_count[f[0]][std::make_pair(s, e)];
+      if (f[3] == "-") c[2] |= 1; else if (f[3] == "+") c[2] |= 2;
+    }
+  }
+  void ChrMapUpdate(const vector<string>& chrmap) override {
+    chrID_junc_count.clear(); chrID_juncLeft_count.clear(); chrID_juncRight_count.clear();
+    for (auto& n : chrmap) { chrID_junc_count.push_back(&chrName_junc_count[n]); chrID_juncLeft_count.push_back(&chrName_juncLeft_count[n]); chrID_juncRight_count.push_back(&chrName_juncRight_count[n]); }
+  }
+  void ProcessBlocks(const FragmentBlocks& b) override {
+    for (int r = 0; r < b.readCount; r++)
+      for (size_t j = 1; j < b.rLens[r].size(); j++)
+        if (b.rLens[r][j - 1] >= JUNC_MIN_FLANK && b.rLens[r][j] >= JUNC_MIN_FLANK) {
+          unsigned left = b.readStart[r] + b.rStarts[r][j - 1] + b.rLens[r][j - 1];
+          unsigned right = b.readStart[r] + b.rStarts[r][j];
+          (*chrID_junc_count.at(b.chr_id))[std::make_pair(left, right)][b.direction]++;
+          (*chrID_juncLeft_count.at(b.chr_id))[left][b.direction]++;
+          (*chrID_juncRight_count.at(b.chr_id))[right][b.direction]++;
+        }
+  }
+  // dir: -1 both strands summed, else 0/1
+  unsigned lookup(const string& chr, unsigned l, unsigned r, int dir) const {
+    auto c = chrName_junc_count.find(chr); if (c == chrName_junc_count.end()) return 0;
+    auto j = c->second.find(std::make_pair(l, r)); if (j == c->second.end()) return 0;
+    return dir < 0 ? j->second[0] + j->second[1] : j->second[dir];
+  }
+  static unsigned side(const std::map<string, std::map<unsigned, unsigned[2]>>& m, const string& chr, unsigned p, int dir) {
+    auto c = m.find(chr); if (c == m.end()) return 0; auto j = c->second.find(p); if (j == c->second.end()) return 0;
+    return dir < 0 ? j->second[0] + j->second[1] : j->second[dir];
+  }
+  unsigned lookupLeft(const string& chr, unsigned p, int dir) const { return side(chrName_juncLeft_count, chr, p, dir); }
+  unsigned lookupRight(const string& chr, unsigned p, int dir) const { return side(chrName_juncRight_count, chr, p, dir); }
+
+  // [C-11] strandedness call from annotated, well-covered junctions.  Returns -1 / 0 / +1.
+  int Directional(std::ostream* os) const {
+    unsigned long long dir_same = 0, dir_diff = 0, dir_ev = 0, nondir_ev = 0, dir_ev_known = 0, nondir_ev_known = 0;
+    for (auto& c : chrName_junc_count)
+      for (auto& j : c.second) {
+        const unsigned* v = j.second;
+        if (v[0] + v[1] > DIR_MIN_TOTAL) {
+          if (v[0] > v[1] * DIR_RATIO) { dir_ev++; if (v[2]) dir_ev_known++; if (v[2] == 1) dir_same++; else if (v[2] == 2) dir_diff++; }
+          else if (v[1] > v[0] * DIR_RATIO) { dir_ev++; if (v[2]) dir_ev_known++; if (v[2] == 2) dir_same++; else if (v[2] == 1) dir_diff++; }
+          else { nondir_ev++; if (v[2]) nondir_ev_known++; }
+        }
+      }
+    *os << "Directionality: Dir evidence:\t" << dir_ev << "\n";
+    *os << "Directionality: Nondir evidence:\t" << nondir_ev << "\n";
+    *os << "Directionality: Dir evidence known junctions:\t" << dir_ev_known << "\n";
+    *os << "Directionality: Nondir evidence known junctions:\t" << nondir_ev_known << "\n";
+    *os << "Directionality: Dir matches ref:\t" << dir_same << "\n";
+    *os << "Directionality: Dir opposed to ref:\t" << dir_diff << "\n";
+    *os << "Directionality: Dir score all (0-10000):\t" << (dir_ev * 10000 / (dir_ev + nondir_ev + 1)) << "\n";
+    *os << "Directionality: Dir score known junctions (0-10000):\t" << (dir_ev_known * 10000 / (dir_ev_known + nondir_ev_known + 1)) << "\n";
+    if (dir_same > dir_diff * DIR_DECISIVE && dir_ev_known > nondir_ev_known * DIR_DECISIVE) return 1;
+    if (dir_diff > dir_same * DIR_DECISIVE && dir_ev_known > nondir_ev_known * DIR_DECISIVE) return -1;
+    return 0;
+  }
+  int WriteOutput(std::ostream* os) const {  // [C-16] chromosome names in std::map (lexicographic) order
+    *os << HDR_JC;
+    for (auto& c : chrName_junc_count)
+      for (auto& j : c.second)
+        *os << c.first << "\t" << j.first.first << "\t" << j.first.second << "\t" << (j.second[2] == 1 ? "-" : j.second[2] == 2 ? "+" : ".")
+            << "\t" << (j.second[0] + j.second[1]) << "\t" << j.second[1] << "\t" << j.second[0] << "\n";
+    return 0;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// SpansPoint (row a8)
+class SpansPoint : public ReadBlockProcessor {
+  unsigned overhangLeft = 0, overhangRight = 0, overhangTotal = 0;
+  std::map<string, vector<unsigned>> chrName_pos;
+  std::map<string, vector<unsigned>> chrName_count[2];
+  vector<vector<unsigned>*> chrID_pos, chrID_count[2];
+
+ public:
+  void setSpanLength(unsigned l, unsigned r) { overhangLeft = l; overhangRight = r; overhangTotal = l + r; }
+  void loadRef(std::istream& IN) {  // [C-9] the strand column is read and ignored
+    string line;
+    while (std::getline(IN, line)) { if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 2) continue; chrName_pos[f[0]].push_back((unsigned)std::stoul(f[1])); }
+    for (auto& c : chrName_pos) { std::sort(c.second.begin(), c.second.end()); chrName_count[0][c.first].assign(c.second.size(), 0); chrName_count[1][c.first].assign(c.second.size(), 0); }
+  }
+  void ChrMapUpdate(const vector<string>& chrmap) override {
+    chrID_pos.clear(); chrID_count[0].clear(); chrID_count[1].clear();
+    for (auto& n : chrmap) { chrID_pos.push_back(&chrName_pos[n]); chrID_count[0].push_back(&chrName_count[0][n]); chrID_count[1].push_back(&chrName_count[1][n]); }
+  }
+  void ProcessBlocks(const FragmentBlocks& b) override {  // [C-4] strict inequalities: start+L < p < end-R
+    for (int r = 0; r < b.readCount; r++)
+      for (size_t j = 0; j < b.rLens[r].size(); j++)
+        if ((unsigned)b.rLens[r][j] > overhangTotal) {
+          unsigned start = b.readStart[r] + b.rStarts[r][j] + overhangLeft;
+          unsigned end = b.readStart[r] + b.rStarts[r][j] + b.rLens[r][j] - overhangRight;
+          vector<unsigned>& pos = *chrID_pos.at(b.chr_id);
+          auto it = std::upper_bound(pos.begin(), pos.end(), start);
+          while (it != pos.end() && *it < end) { (*chrID_count[b.direction].at(b.chr_id))[it - pos.begin()]++; ++it; }
+        }
+  }
+  unsigned lookup(const string& chr, unsigned p, int dir) const {
+    auto c = chrName_pos.find(chr); if (c == chrName_pos.end()) return 0;
+    auto it = std::lower_bound(c->second.begin(), c->second.end(), p); if (it == c->second.end() || *it != p) return 0;
+    size_t i = it - c->second.begin();
+    unsigned n = chrName_count[0].at(chr)[i], q = chrName_count[1].at(chr)[i];
+    return dir < 0 ? n + q : (dir ? q : n);
+  }
+  int WriteOutput(std::ostream* os) const {
+    *os << HDR_SP;
+    for (auto& c : chrName_pos) { auto& n = chrName_count[0].at(c.first); auto& p = chrName_count[1].at(c.first);
+      for (size_t i = 0; i < c.second.size(); i++) *os << c.first << "\t" << c.second[i] << "\t" << (n[i] + p[i]) << "\t" << p[i] << "\t" << n[i] << "\n"; }
+    return 0;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// FragmentsInChr / FragmentsInROI (row a13)
+class FragmentsInChr : public ReadBlockProcessor {
+  std::map<string, vector<unsigned>> chrName_count; vector<vector<unsigned>*> chrID_count;
+ public:
+  void ChrMapUpdate(const vector<string>& chrmap) override { chrID_count.clear(); for (auto& n : chrmap) { chrName_count[n].resize(2, 0); chrID_count.push_back(&chrName_count[n]); } }
+  void ProcessBlocks(const FragmentBlocks& b) override { (*chrID_count.at(b.chr_id))[b.direction]++; }
+  int WriteOutput(std::ostream* os) const { *os << HDR_CHR; for (auto& c : chrName_count) *os << c.first << "\t" << (c.second[0] + c.second[1]) << "\t" << c.second[1] << "\t" << c.second[0] << "\n"; return 0; }
+};
+
+class FragmentsInROI : public ReadBlockProcessor {
+  struct Roi { unsigned start, end; string name; unsigned count[2]; };
+  std::map<string, vector<Roi>> chrName_ROI; vector<vector<Roi>*> chrID_ROI;
+ public:
+  void loadRef(std::istream& IN) {
+    string line;
+    while (std::getline(IN, line)) { if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) continue;
+      chrName_ROI[f[0]].push_back(Roi{(unsigned)std::stoul(f[1]), (unsigned)std::stoul(f[2]), f[3], {0, 0}}); }
+    for (auto& c : chrName_ROI) std::stable_sort(c.second.begin(), c.second.end(), [](const Roi& a, const Roi& b) { return a.end < b.end; });
+  }
+  void ChrMapUpdate(const vector<string>& chrmap) override { chrID_ROI.clear(); for (auto& n : chrmap) chrID_ROI.push_back(&chrName_ROI[n]); }
+  void ProcessBlocks(const FragmentBlocks& b) override {
+    unsigned fs = b.readStart[0], fe = b.readEnd[0];
+    if (b.readCount > 1 && b.readEnd[1] > fe) fe = b.readEnd[1];
+    vector<Roi>& v = *chrID_ROI.at(b.chr_id);
+    // first ROI whose end lies beyond the fragment start; the fragment counts if it sits wholly inside it
+    auto it = std::upper_bound(v.begin(), v.end(), fs, [](unsigned p, const Roi& r) { return p < r.end; });
+    if (it != v.end() && it->start <= fs && fe <= it->end) it->count[b.direction]++;
+  }
+  int WriteOutput(std::ostream* os) const { *os << HDR_ROI; for (auto& c : chrName_ROI) for (auto& r : c.second) *os << r.name << "\t" << (r.count[0] + r.count[1]) << "\t" << r.count[1] << "\t" << r.count[0] << "\n"; return 0; }
+};
+
+// ---------------------------------------------------------------------------------------------
+// CoverageBlock / CoverageBlocks / CoverageBlocksIRFinder (rows a9-a12)
+// One CoverageBlock = one contiguous measured segment with per-strand start/stop difference counters.
+// (Upstream packs the counters 8-bit with a 32-bit upgrade path; that is a memory trick, not behaviour.)
+struct CoverageBlock {
+  unsigned blockStart, blockEnd;
+  vector<int> diff[2];  // len+1 each; prefix-summed into depth by finalise()
+  bool finalised = false;
+  CoverageBlock(unsigned s, unsigned e) : blockStart(s), blockEnd(e) { diff[0].assign(e - s + 1, 0); diff[1].assign(e - s + 1, 0); }
+  void RecordCover(unsigned readStart, unsigned readEnd, bool dir) {  // half-open [readStart, readEnd), clipped to the segment
+    unsigned a = std::max(readStart, blockStart), b = std::min(readEnd, blockEnd);
+    if (a >= b) return;
+    diff[dir][a - blockStart]++; diff[dir][b - blockStart]--;
+  }
+  void finalise() { if (finalised) return; for (int d = 0; d < 2; d++) { int run = 0; for (auto& x : diff[d]) { run += x; x = run; } } finalised = true; }
+  // dir: -1 = both strands summed
+  void updateCoverageHist(std::map<unsigned, unsigned>& hist, unsigned start, unsigned end, int dir) const {
+    unsigned a = std::max(start, blockStart), b = std::min(end, blockEnd);
+    for (unsigned p = a; p < b; p++) { unsigned i = p - blockStart; unsigned depth = dir < 0 ? (unsigned)(diff[0][i] + diff[1][i]) : (unsigned)diff[dir][i]; hist[depth]++; }
+  }
+};
+
+class CoverageBlocks : public ReadBlockProcessor {
+ protected:
+  struct BEDrecord { string chrName, name; unsigned start, end; bool direction; vector<std::pair<unsigned, unsigned>> blocks; };
+  vector<BEDrecord> BEDrecords;
+  std::map<string, vector<CoverageBlock>> chrName_CoverageBlocks;
+  vector<vector<CoverageBlock>*> chrID_CoverageBlocks;
+
+ public:
+  void loadRef(std::istream& IN) {
+    string line; std::map<string, vector<std::pair<unsigned, unsigned>>> raw;
+    while (std::getline(IN, line)) {
+      if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 12) continue;
+      BEDrecord r; r.chrName = f[0]; r.start = (unsigned)std::stoul(f[1]); r.end = (unsigned)std::stoul(f[2]); r.name = f[3]; r.direction = (f[5] == "+");
+      std::istringstream ls(f[10]), os(f[11]); string a, b;
+      while (std::getline(ls, a, ',') && std::getline(os, b, ',')) { if (a.empty() || b.empty()) break; unsigned len = (unsigned)std::stoul(a), off = (unsigned)std::stoul(b);
+        r.blocks.push_back({r.start + off, r.start + off + len}); raw[r.chrName].push_back(r.blocks.back()); }
+      BEDrecords.push_back(r);
+    }
+    // measured segments = union of all blocks per chromosome, merged into sorted disjoint intervals
+    for (auto& c : raw) {
+      std::sort(c.second.begin(), c.second.end()); auto& out = chrName_CoverageBlocks[c.first];
+      unsigned cs = 0, ce = 0; bool open = false;
+      for (auto& b : c.second) { if (b.first >= b.second) continue;
+        if (open && b.first <= ce) ce = std::max(ce, b.second); else { if (open) out.emplace_back(cs, ce); cs = b.first; ce = b.second; open = true; } }
+      if (open) out.emplace_back(cs, ce);
+    }
+  }
+  void ChrMapUpdate(const vector<string>& chrmap) override { chrID_CoverageBlocks.clear(); for (auto& n : chrmap) chrID_CoverageBlocks.push_back(&chrName_CoverageBlocks[n]); }
+  void ProcessBlocks(const FragmentBlocks& b) override {
+    for (int r = 0; r < b.readCount; r++)
+      for (size_t j = 0; j < b.rLens[r].size(); j++) {
+        unsigned start = b.readStart[r] + b.rStarts[r][j], end = start + b.rLens[r][j];
+        vector<CoverageBlock>& v = *chrID_CoverageBlocks.at(b.chr_id);
+        auto it = std::upper_bound(v.begin(), v.end(), start, [](unsigned p, const CoverageBlock& cb) { return p < cb.blockEnd; });
+        while (it != v.end() && it->blockStart < end) { it->RecordCover(start, end, b.direction); ++it; }
+      }
+  }
+  void finalise() { for (auto& c : chrName_CoverageBlocks) for (auto& cb : c.second) cb.finalise(); }
+  void fillHist(std::map<unsigned, unsigned>& hist, const string& chr, const vector<std::pair<unsigned, unsigned>>& blocks, int dir) const {
+    auto c = chrName_CoverageBlocks.find(chr); if (c == chrName_CoverageBlocks.end()) return; const vector<CoverageBlock>& v = c->second;
+    for (auto& bd : blocks) {
+      auto it = std::upper_bound(v.begin(), v.end(), bd.first, [](unsigned p, const CoverageBlock& cb) { return p < cb.blockEnd; });
+      while (it != v.end() && it->blockStart < bd.second) { it->updateCoverageHist(hist, bd.first, bd.second, dir); ++it; }
+    }
+  }
+  static unsigned long long histPositions(const std::map<unsigned, unsigned>& h) { unsigned long long n = 0; for (auto& x : h) n += x.second; return n; }
+  static double meanFromHist(const std::map<unsigned, unsigned>& h) {
+    unsigned long long total = 0, n = 0; for (auto& x : h) { total += (unsigned long long)x.first * x.second; n += x.second; }
+    return n ? (double)total / (double)n : 0.0;
+  }
+  static double coverageFromHist(const std::map<unsigned, unsigned>& h) {
+    unsigned long long n = histPositions(h); if (!n) return 0.0; auto z = h.find(0); unsigned long long zero = z == h.end() ? 0 : z->second;
+    return (double)(n - zero) / (double)n;
+  }
+  // [C-12] smallest depth whose cumulative count exceeds p% of positions; exactly on the boundary -> midpoint with the next depth
+  static double percentileFromHist(const std::map<unsigned, unsigned>& h, unsigned percentile) {
+    unsigned long long n = histPositions(h); if (!n) return 0.0;
+    unsigned long long target100 = n * percentile;  // compare 100*cum against n*percentile: exact integers
+    unsigned long long cum = 0;
+    for (auto it = h.begin(); it != h.end(); ++it) {
+      cum += it->second;
+      if (cum * 100 > target100) return it->first;
+      if (cum * 100 == target100) { auto nx = std::next(it); return nx == h.end() ? (double)it->first : ((double)it->first + (double)nx->first) / 2.0; }
+    }
+    return (double)h.rbegin()->first;
+  }
+  // [C-2][C-12] mean over ranks [lo, n-lo) of the sorted depths, lo = floor(n * (100-centre)/200)
+  static double trimmedMeanFromHist(const std::map<unsigned, unsigned>& h, unsigned centerPercent) {
+    unsigned long long n = histPositions(h); if (!n) return 0.0;
+    unsigned long long lo = n * (100 - centerPercent) / 200, hi = n - lo; if (hi <= lo) return 0.0;
+    unsigned long long cum = 0, total = 0;
+    for (auto& x : h) { unsigned long long a = std::max(cum, lo), b = std::min(cum + x.second, hi); if (b > a) total += (b - a) * x.first; cum += x.second; }
+    return (double)total / (double)(hi - lo);
+  }
+};
+
+class CoverageBlocksIRFinder : public CoverageBlocks {
+ public:
+  // directionality: 0 = nondir table; +1/-1 = dir table (measured strand follows/opposes the annotated strand)
+  int WriteOutput(std::ostream* os, const JunctionCount& JC, const SpansPoint& SP, int directionality) const {
+    *os << HDR_IR;
+    for (auto& rec : BEDrecords) {
+      int dir = -1;
+      if (directionality != 0) { bool measureDir = rec.direction; if (directionality < 0) measureDir = !measureDir; dir = measureDir ? 1 : 0; }
+      std::map<unsigned, unsigned> hist, hf, hl;
+      fillHist(hist, rec.chrName, rec.blocks, dir);
+      unsigned long long positions = histPositions(hist);
+      long long excluded = (long long)(rec.end - rec.start) - (long long)positions;  // [C-5]
+      double coverage = coverageFromHist(hist), depth = trimmedMeanFromHist(hist, TRIM_CENTER_PERCENT);
+      // [C-13] windows just inside each end; only measured positions contribute
+      unsigned ws = rec.start + EDGE_WINDOW_OFFSET, we = rec.end > EDGE_WINDOW_OFFSET ? rec.end - EDGE_WINDOW_OFFSET : 0;
+      fillHist(hf, rec.chrName, {{ws, std::min(ws + EDGE_WINDOW_LEN, rec.end)}}, dir);
+      fillHist(hl, rec.chrName, {{we > EDGE_WINDOW_LEN && we - EDGE_WINDOW_LEN > rec.start ? we - EDGE_WINDOW_LEN : rec.start, we}}, dir);
+      unsigned SPleft = SP.lookup(rec.chrName, rec.start, dir), SPright = SP.lookup(rec.chrName, rec.end, dir);
+      unsigned JCleft = JC.lookupLeft(rec.chrName, rec.start, dir), JCright = JC.lookupRight(rec.chrName, rec.end, dir), JCexact = JC.lookup(rec.chrName, rec.start, rec.end, dir);
+      unsigned JCmax = std::max(JCleft, JCright);
+      *os << rec.chrName << "\t" << rec.start << "\t" << rec.end << "\t" << rec.name << "\t0\t" << (rec.direction ? "+" : "-") << "\t" << excluded << "\t"
+          << coverage << "\t" << depth << "\t" << percentileFromHist(hist, 25) << "\t" << percentileFromHist(hist, 50) << "\t" << percentileFromHist(hist, 75) << "\t"
+          << SPleft << "\t" << SPright << "\t" << meanFromHist(hf) << "\t" << meanFromHist(hl) << "\t" << JCleft << "\t" << JCright << "\t" << JCexact << "\t";
+      if (depth == 0 && JCmax == 0) *os << "0\t"; else *os << (depth / (depth + JCmax)) << "\t";
+      *os << warning(depth, JCexact, JCmax, SPleft, SPright) << "\n";
+    }
+    return 0;
+  }
+  // [C-14]
+  static const char* warning(double depth, unsigned JCexact, unsigned JCmax, unsigned SPleft, unsigned SPright) {
+    double spmax = std::max(SPleft, SPright), spmin = std::min(SPleft, SPright);
+    if (JCexact + depth < 10) return "LowCover";
+    if (JCexact < 4) return "LowSplicing";
+    if (JCexact < JCmax * 0.33333) return "MinorIsoform";
+    if ((spmax > depth + 4 && spmax > depth * 1.5) || (spmin + 4 < depth && spmin * 1.5 < depth)) return "NonUniformIntronCover";
+    return "-";
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+// BAM2blocks (rows a1-a4; upstream BAM2blocks.cpp)
+struct ByteSource {   // inflated BAM bytes, from gz/BGZF or raw input (zlib's gzread is transparent for raw)
+  gzFile gz = nullptr;
+  bool open(const char* path) { gz = (strcmp(path, "-") == 0 || strcmp(path, "/dev/stdin") == 0) ? gzdopen(0, "rb") : gzopen(path, "rb"); if (gz) gzbuffer(gz, 1 << 20); return gz != nullptr; }
+  bool read(void* dst, size_t n) { uint8_t* p = (uint8_t*)dst; while (n) { int k = gzread(gz, p, (unsigned)std::min<size_t>(n, 1u << 30)); if (k <= 0) return false; p += k; n -= k; } return true; }
+  bool skip(size_t n) { static uint8_t tmp[65536]; while (n) { size_t k = std::min(n, sizeof tmp); if (!read(tmp, k)) return false; n -= k; } return true; }
+  bool eof_clean() { int c = gzgetc(gz); if (c < 0) return true; gzungetc(c, gz); return false; }
+};
+
+struct bam_read_core { int32_t block_size, refID, pos; uint8_t l_read_name, mapq; uint16_t bin, n_cigar_op, flag; int32_t l_seq, next_refID, next_pos, tlen; };
+struct BamRead { bam_read_core core; char read_name[256]; vector<uint32_t> cigar; };
+
+class BAM2blocks {
+  FragmentBlocks oBlocks;
+  vector<std::function<void(const vector<string>&)>> callbacksChrMappingChange;
+  vector<std::function<void(const FragmentBlocks&)>> callbacksProcessBlocks;
+  ByteSource* IN = nullptr;
+ public:
+  vector<string> chr_names; vector<int> chr_lens;
+  unsigned long long cShortPairs = 0, cIntersectPairs = 0, cLongPairs = 0, cSingleReads = 0, cPairedReads = 0, cErrorReads = 0, cSkippedReads = 0, totalNucleotides = 0;
+  FILE* dump = nullptr;
+
+  void registerCallbackChrMappingChange(std::function<void(const vector<string>&)> cb) { callbacksChrMappingChange.push_back(cb); }
+  void registerCallbackProcessBlocks(std::function<void(const FragmentBlocks&)> cb) { callbacksProcessBlocks.push_back(cb); }
+  bool openFile(ByteSource* in) { IN = in; return readBamHeader(); }
+
+  bool readBamHeader() {  // row a1
+    char magic[4]; int32_t l_text, n_ref;
+    if (!IN->read(magic, 4) || memcmp(magic, "BAM\1", 4) != 0) { std::cerr << "Not a BAM stream\n"; return false; }
+    if (!IN->read(&l_text, 4) || !IN->skip(l_text) || !IN->read(&n_ref, 4)) return false;
+    for (int i = 0; i < n_ref; i++) { int32_t l_name, l_ref; if (!IN->read(&l_name, 4)) return false; string nm(l_name, '\0'); if (!IN->read(&nm[0], l_name) || !IN->read(&l_ref, 4)) return false;
+      nm.resize(l_name ? l_name - 1 : 0); chr_names.push_back(nm); chr_lens.push_back(l_ref); }
+    for (auto& cb : callbacksChrMappingChange) cb(chr_names);
+    return true;
+  }
+
+  // row a3.  M,D,=,X extend the current block; N closes it and skips; I,S,H,P are ignored.
+  static void cigar2block(const uint32_t* cigar, unsigned n, vector<int>& starts, vector<int>& lens, int& genome_len) {
+    bool inBlock = true; int relpos = 0; starts.assign(1, 0); lens.assign(1, 0);
+    for (unsigned i = 0; i < n; i++) {
+      int op = cigar[i] & 15, len = (int)(cigar[i] >> 4);
+      if (op == 0 || op == 2 || op == 7 || op == 8) { if (!inBlock) { inBlock = true; } lens.back() += len; relpos += len; }
+      else if (op == 3) { relpos += len; if (inBlock) { starts.push_back(relpos); lens.push_back(0); inBlock = false; } else starts.back() = relpos; }
+    }
+    genome_len = relpos;
+  }
+
+  void emit() {
+    unsigned total = 0; for (int r = 0; r < oBlocks.readCount; r++) for (int l : oBlocks.rLens[r]) total += l;
+    totalNucleotides += total;
+    if (dump) {  // one line per fragment: chr dir readCount | blocks of read 0 | blocks of read 1
+      fprintf(dump, "%u\t%d\t%d", oBlocks.chr_id, (int)oBlocks.direction, oBlocks.readCount);
+      for (int r = 0; r < oBlocks.readCount; r++) { fputc('\t', dump); for (size_t j = 0; j < oBlocks.rLens[r].size(); j++) fprintf(dump, "%s%u-%u", j ? "," : "", oBlocks.readStart[r] + oBlocks.rStarts[r][j], oBlocks.readStart[r] + oBlocks.rStarts[r][j] + oBlocks.rLens[r][j]); }
+      fputc('\n', dump);
+    }
+    for (auto& cb : callbacksProcessBlocks) cb(oBlocks);
+  }
+
+  void processSingle(const BamRead& r) {  // row a4
+    int glen; oBlocks.direction = !(r.core.flag & 0x10);
+    cigar2block(r.cigar.data(), r.core.n_cigar_op, oBlocks.rStarts[0], oBlocks.rLens[0], glen);
+    oBlocks.readCount = 1; oBlocks.chr_id = r.core.refID; oBlocks.readStart[0] = r.core.pos; oBlocks.readEnd[0] = r.core.pos + glen;
+    oBlocks.readName.assign(r.read_name);
+    emit();
+  }
+
+  // read1 is left of (or level with) read2.  [C-10]
+  void processPair(const BamRead& read1, const BamRead& read2) {
+    int len1, len2;
+    if (read1.core.flag & 0x40) oBlocks.direction = !(read1.core.flag & 0x10); else oBlocks.direction = !(read1.core.flag & 0x20);
+    cigar2block(read1.cigar.data(), read1.core.n_cigar_op, oBlocks.rStarts[0], oBlocks.rLens[0], len1);
+    cigar2block(read2.cigar.data(), read2.core.n_cigar_op, oBlocks.rStarts[1], oBlocks.rLens[1], len2);
+    int r1pos = read1.core.pos, r2pos = read2.core.pos;
+    if (r1pos + len1 < r2pos) { cLongPairs++; oBlocks.readCount = 2; }
+    else if (r1pos + len1 >= r2pos + len2) { cShortPairs++; oBlocks.readCount = 1; }
+    else {
+      cIntersectPairs++; oBlocks.readCount = 1; bool goodPair = true;
+      for (size_t i = 0; i < oBlocks.rStarts[0].size(); i++) {
+        if (r1pos + oBlocks.rStarts[0][i] + oBlocks.rLens[0][i] >= r2pos) {
+          if (r1pos + oBlocks.rStarts[0][i] <= r2pos) {
+            // read 2 starts inside (or right at the end of) this block: stretch it to the end of read 2's first block, then append the rest of read 2
+            oBlocks.rLens[0][i] = r2pos - r1pos - oBlocks.rStarts[0][i] + oBlocks.rLens[1][0];
+            size_t n2 = oBlocks.rStarts[1].size();
+            oBlocks.rStarts[0].resize(i + n2); oBlocks.rLens[0].resize(i + n2);
+            for (size_t j = 1; j < n2; j++) { i++; oBlocks.rLens[0][i] = oBlocks.rLens[1][j]; oBlocks.rStarts[0][i] = oBlocks.rStarts[1][j] + r2pos - r1pos; }
+            len1 = r2pos - r1pos + len2;
+            break;
+          } else { goodPair = false; }  // read 2 starts in a gap of read 1: structures disagree, keep both reads
+        }
+      }
+      if (!goodPair) oBlocks.readCount = 2;
+    }
+    oBlocks.chr_id = read1.core.refID; oBlocks.readStart[0] = r1pos; oBlocks.readEnd[0] = r1pos + len1;
+    oBlocks.readStart[1] = r2pos; oBlocks.readEnd[1] = r2pos + len2; oBlocks.readName.assign(read1.read_name);
+    emit();
+  }
+
+  bool readRecord(BamRead& r, bool& eof) {
+    eof = false;
+    if (IN->eof_clean()) { eof = true; return true; }
+    if (!IN->read(&r.core, 36)) return false;
+    if (r.core.block_size < 32 + r.core.l_read_name + 4 * (int)r.core.n_cigar_op) return false;
+    if (!IN->read(r.read_name, r.core.l_read_name)) return false; r.read_name[r.core.l_read_name ? r.core.l_read_name - 1 : 0] = 0;
+    r.cigar.resize(r.core.n_cigar_op); if (r.core.n_cigar_op && !IN->read(r.cigar.data(), 4 * (size_t)r.core.n_cigar_op)) return false;
+    return IN->skip((size_t)r.core.block_size - 32 - r.core.l_read_name - 4 * (size_t)r.core.n_cigar_op);
+  }
+
+  // [C-6][C-7] a record is a pair candidate when it is paired, mapped, its mate is mapped and on the same reference;
+  // paired records that fail the mate tests are handled as singles; unmapped records are skipped.
+  static bool pairCandidate(const bam_read_core& c) { return (c.flag & 0x1) && !(c.flag & 0x8) && c.next_refID == c.refID; }
+
+  int processAll() {  // row a2
+    BamRead reads[2]; int held = -1;  // index of a buffered first mate
+    for (;;) {
+      int idx = held == 0 ? 1 : 0; bool eof;
+      if (!readRecord(reads[idx], eof)) { cErrorReads++; std::cerr << "Input error: truncated or malformed BAM record\n"; return 1; }
+      if (eof) break;
+      const bam_read_core& c = reads[idx].core;
+      if ((c.flag & 0x4) || c.refID < 0) { cSkippedReads++; continue; }
+      if (!pairCandidate(c)) { cSingleReads++; processSingle(reads[idx]); continue; }
+      if (held < 0) { held = idx; continue; }
+      BamRead& a = reads[held]; BamRead& b = reads[idx];
+      if (a.core.refID == b.core.refID && a.core.l_read_name == b.core.l_read_name && strcmp(a.read_name, b.read_name) == 0) {
+        if (a.core.pos <= b.core.pos) processPair(a, b); else processPair(b, a);
+        cPairedReads++; held = -1;
+      } else { cErrorReads++; held = idx; }  // not mates: drop the held record, hold the new one
+    }
+    if (held >= 0) cErrorReads++;
+    return 0;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
+int main(int argc, char** argv) {
+  if (argc < 7) { std::cerr << "Usage: irfinder_cpu <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|-> [--dump-fragments FILE]\n"; return 1; }
+  if (const char* t = getenv("IRF_TRIM_CENTER")) TRIM_CENTER_PERCENT = (unsigned)atoi(t);
+  string outdir = argv[1];
+  CoverageBlocksIRFinder oCov; JunctionCount oJC; SpansPoint oSP; FragmentsInChr oChr; FragmentsInROI oROI; bool haveROI = strcmp(argv[5], "NULL") != 0;
+  { std::ifstream f(argv[2]); if (!f) { std::cerr << "cannot open " << argv[2] << "\n"; return 1; } oCov.loadRef(f); }
+  { std::ifstream f(argv[3]); if (!f) { std::cerr << "cannot open " << argv[3] << "\n"; return 1; } oJC.loadRef(f); }
+  { std::ifstream f(argv[4]); if (!f) { std::cerr << "cannot open " << argv[4] << "\n"; return 1; } oSP.setSpanLength(SPAN_OVERHANG_LEFT, SPAN_OVERHANG_RIGHT); oSP.loadRef(f); }
+  if (haveROI) { std::ifstream f(argv[5]); if (!f) { std::cerr << "cannot open " << argv[5] << "\n"; return 1; } oROI.loadRef(f); }
+  BAM2blocks BB;
+  for (int i = 7; i + 1 < argc; i += 2) if (!strcmp(argv[i], "--dump-fragments")) BB.dump = fopen(argv[i + 1], "w");
+  using namespace std::placeholders;
+  BB.registerCallbackChrMappingChange(std::bind(&JunctionCount::ChrMapUpdate, &oJC, _1)); BB.registerCallbackProcessBlocks(std::bind(&JunctionCount::ProcessBlocks, &oJC, _1));
+  BB.registerCallbackChrMappingChange(std::bind(&SpansPoint::ChrMapUpdate, &oSP, _1)); BB.registerCallbackProcessBlocks(std::bind(&SpansPoint::ProcessBlocks, &oSP, _1));
+  BB.registerCallbackChrMappingChange(std::bind(&FragmentsInChr::ChrMapUpdate, &oChr, _1)); BB.registerCallbackProcessBlocks(std::bind(&FragmentsInChr::ProcessBlocks, &oChr, _1));
+  if (haveROI) { BB.registerCallbackChrMappingChange(std::bind(&FragmentsInROI::ChrMapUpdate, &oROI, _1)); BB.registerCallbackProcessBlocks(std::bind(&FragmentsInROI::ProcessBlocks, &oROI, _1)); }
+  BB.registerCallbackChrMappingChange(std::bind(&CoverageBlocks::ChrMapUpdate, &oCov, _1)); BB.registerCallbackProcessBlocks(std::bind(&CoverageBlocks::ProcessBlocks, &oCov, _1));
+  ByteSource src; if (!src.open(argv[6])) { std::cerr << "cannot open " << argv[6] << "\n"; return 1; }
+  if (!BB.openFile(&src)) return 1;
+  int rc = BB.processAll();
+  if (BB.dump) fclose(BB.dump);
+  if (rc) return rc;
+  oCov.finalise();
+  int directionality = oJC.Directional(&std::cout);
+  std::cout << "Directionality:\t" << directionality << "\n";
+  { std::ofstream o(outdir + "/IRFinder-IR-nondir.txt"); oCov.WriteOutput(&o, oJC, oSP, 0); }
+  if (directionality != 0) { std::ofstream o(outdir + "/IRFinder-IR-dir.txt"); oCov.WriteOutput(&o, oJC, oSP, directionality); }
+  { std::ofstream o(outdir + "/IRFinder-JuncCount.txt"); oJC.WriteOutput(&o); }
+  { std::ofstream o(outdir + "/IRFinder-SpansPoint.txt"); oSP.WriteOutput(&o); }
+  { std::ofstream o(outdir + "/IRFinder-ChrCoverage.txt"); oChr.WriteOutput(&o); }
+  if (haveROI) { std::ofstream o(outdir + "/IRFinder-ROI.txt"); oROI.WriteOutput(&o); }
+  std::cout << "Total reads processed\t" << (BB.cSingleReads + BB.cPairedReads) << "\n" << "Total nucleotides\t" << BB.totalNucleotides << "\n"
+            << "Total singles processed\t" << BB.cSingleReads << "\n" << "Total pairs processed\t" << BB.cPairedReads << "\n"
+            << "Short pairs\t" << BB.cShortPairs << "\n" << "Intersect pairs\t" << BB.cIntersectPairs << "\n" << "Long pairs\t" << BB.cLongPairs << "\n"
+            << "Skipped reads\t" << BB.cSkippedReads << "\n" << "Error reads\t" << BB.cErrorReads << "\n";
+  return 0;
+}
