@@ -1,0 +1,109 @@
+/* irfinder_b200.h — C ABI of the B200-native IRFinder BAM -> intron-retention counting core.
+ *
+ * The reference exposes this path only as a process boundary:
+ *     irfinder <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|/dev/stdin>
+ * (upstream src/irfinder/irfinder.cpp main(); the mounted /root/reference holds only README.md:1-7, so no
+ * file:line inside it can be cited — SURVEY.md §0).  Each entry point below names the reference routine it
+ * stands in for.  Conventions: every call returns 0 or a negative IRF_E* code; no C++ exception crosses
+ * the ABI; the caller owns every pointer it passes; memory returned by irf_get_table belongs to the
+ * context until the next run or irf_destroy; one context drives ONE GPU and is used from one host thread
+ * at a time (multi-GPU = one process and one context per GPU).
+ */
+#ifndef IRFINDER_B200_H
+#define IRFINDER_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct irf_ctx irf_ctx;
+
+enum { IRF_OK = 0, IRF_EINVAL = -1, IRF_EIO = -2, IRF_EFORMAT = -3, IRF_ECUDA = -4, IRF_ESTATE = -5, IRF_ECAPACITY = -6 };
+
+/* which-codes of irf_get_table / irf_get_device_table */
+enum {
+  IRF_T_STATS = 0,        /* uint64[9]: singles, pairs, short, intersect, long, skipped, error, nucleotides, records (reference: stdout counters) */
+  IRF_T_SPANS = 1,        /* uint32[2][n_points]: [0]=neg/dir0, [1]=pos/dir1, chromosome-name order (SpansPoint counts) */
+  IRF_T_ROI = 2,          /* uint32[2][n_roi] (FragmentsInROI counts) */
+  IRF_T_CHR = 3,          /* uint32[2][n_ref], BAM header order (FragmentsInChr counts) */
+  IRF_T_JUNCTIONS = 4,    /* struct {int32 refid; uint32 start, end, neg, pos;}[n] counted junctions (JunctionCount map) */
+  IRF_T_DEPTH = 5,        /* int32[2][P] per-base depth over the compact measured space (CoverageBlock counters after scan) */
+  IRF_T_ROWS_NONDIR = 6,  /* irf_intron_row[n_introns], ref-cover.bed order (IRFinder-IR-nondir.txt, numeric) */
+  IRF_T_ROWS_DIR = 7,     /* same for IRFinder-IR-dir.txt; n = 0 when the library is unstranded */
+  IRF_T_FRAGMENTS = 8,    /* uint32 words of the FragmentBlocks dump (option dump_fragments=1): per fragment
+                             [n_words, chr, dir, readCount, nblk0, nblk1, (start,end)*] */
+  IRF_T_TIMING = 9,       /* double[10] of the last run: ms h2d+inflate, ms inflate kernels, ms framing, ms counting, ms finalize, ms count total, ms host BGZF scan, ms output formatting, kernels launched since irf_reset, inflate launches */
+  IRF_T_DIFF = 10         /* device only: int32[2][P] difference counters before irf_finalize */
+};
+
+typedef struct irf_intron_row {
+  long long excluded; unsigned long long positions;
+  double coverage, depth, p25, p50, p75, first50, last50, irratio;
+  uint32_t sp_left, sp_right, jc_left, jc_right, jc_exact; int32_t warning; /* 0 -, 1 LowCover, 2 LowSplicing, 3 MinorIsoform, 4 NonUniformIntronCover */
+} irf_intron_row;
+
+/* Creates a context on device_ids[0] (n_devices must be 1).  Stands in for process start of `irfinder`. */
+int irf_create(irf_ctx** out, const int* device_ids, int n_devices);
+void irf_destroy(irf_ctx* ctx);
+const char* irf_last_error(irf_ctx* ctx);
+
+/* Options (strings): "trim_center" (default 40), "dump_fragments" (0/1), "inflate_variant" (0-6),
+ * "junc_capacity_log2" (default 24), "require_eof" (default 1).  Must be set before irf_load_ref / the first run. */
+int irf_set_option(irf_ctx* ctx, const char* key, const char* value);
+
+/* Replaces CoverageBlocksIRFinder::loadRef, JunctionCount::loadRef, SpansPoint::setSpanLength(5,4)+loadRef and
+ * FragmentsInROI::loadRef (irfinder.cpp main).  roi_bed may be NULL or "NULL". */
+int irf_load_ref(irf_ctx* ctx, const char* cover_bed, const char* sj_ref, const char* read_continues_ref, const char* roi_bed);
+
+/* Replaces BAM2blocks::openFile + processAll over a whole BGZF BAM file, followed by the output-side statistics
+ * (everything of main() between loadRef and the file writers).  bai_path is accepted for CLI compatibility and ignored:
+ * record framing needs no index.  Mates may be in any order (coordinate-sorted or mate-adjacent). */
+int irf_run_bam(irf_ctx* ctx, const char* bam_path, const char* bai_path);
+/* Same, from a host buffer holding the BGZF bytes (pinned memory copies fastest). */
+int irf_run_buffer(irf_ctx* ctx, const void* bgzf, size_t nbytes);
+/* Reference-compatible stdin mode: fd delivers BGZF/gzip bytes (inflated = 0) or an already-inflated BAM stream (inflated = 1). */
+int irf_run_stream(irf_ctx* ctx, int fd, int inflated);
+
+/* Replaces the six file writers at the end of main(): IRFinder-IR-nondir.txt, IRFinder-IR-dir.txt (stranded libraries only),
+ * IRFinder-JuncCount.txt, IRFinder-SpansPoint.txt, IRFinder-ChrCoverage.txt, IRFinder-ROI.txt (when an ROI file was loaded). */
+int irf_write_outputs(irf_ctx* ctx, const char* outdir);
+/* The stdout block of the reference (directionality evidence + read counters) as one NUL-terminated string. */
+const char* irf_stdout_text(irf_ctx* ctx);
+/* +1 / 0 / -1 as returned by JunctionCount::Directional. */
+int irf_directionality(irf_ctx* ctx);
+
+/* Raw tables for tests and embedding (host copies). */
+int irf_get_table(irf_ctx* ctx, int which, const void** host_ptr, size_t* n_elems);
+
+/* ---- staged operation: the same pipeline in separately timed / separately sharded steps ---- */
+/* Zeroes every counter (keeps the loaded references). */
+int irf_reset(irf_ctx* ctx);
+/* Parses the BAM header (BAM2blocks::readBamHeader + every ChrMapUpdate) from the first bytes of a BGZF BAM. */
+int irf_read_header(irf_ctx* ctx, const void* bgzf_prefix, size_t nbytes);
+/* Copies BGZF bytes to the GPU.  Records that START in the first nbytes_own bytes' blocks are this context's to count;
+ * the bytes up to nbytes_total are look-ahead so a record straddling the shard end can be read.  has_header = 1 when the
+ * buffer starts at the beginning of the file.  The staged bytes stay resident until the next irf_stage, so irf_reset +
+ * irf_count + irf_finalize can be repeated on them. */
+int irf_stage(irf_ctx* ctx, const void* bgzf, size_t nbytes_own, size_t nbytes_total, int has_header);
+/* Inflate + record framing + per-fragment counting of the staged bytes, device only. */
+int irf_count(irf_ctx* ctx);
+/* Framing hand-shake between neighbouring shards: entry = inflated offset of the first record counted here,
+ * exit = inflated offset (relative to the end of the own bytes) where the next shard's first record starts. */
+int irf_frame_info(irf_ctx* ctx, uint64_t* entry0, uint64_t* exit_rel);
+/* Depth scan, junction merge, directionality and per-intron statistics on the (possibly all-reduced) tables. */
+int irf_finalize(irf_ctx* ctx);
+/* Device pointers of the additive tables, for an NCCL all-reduce by the caller (IRF_T_SPANS, _ROI, _CHR, _STATS, _DIFF). */
+int irf_get_device_table(irf_ctx* ctx, int which, void** dev_ptr, size_t* n_elems, int* elem_bytes);
+/* Junction tables as dense device arrays (keys uint64, counts uint32[n][2]); which = 0 exact, 1 left ends, 2 right ends. */
+int irf_export_junctions(irf_ctx* ctx, int which, void** dev_keys, void** dev_counts, size_t* n);
+int irf_import_junctions(irf_ctx* ctx, int which, const void* dev_keys, const void* dev_counts, size_t n);
+/* Records whose mate was not seen in this shard, trimmed to fixed part + name + CIGAR, and their byte offsets. */
+int irf_export_halo(irf_ctx* ctx, void** dev_bytes, size_t* nbytes, void** dev_offsets, size_t* nrec);
+/* Pairs the gathered halo records of all shards; this context counts the pairs whose key hash % n_owners == owner. */
+int irf_import_halo(irf_ctx* ctx, const void* dev_bytes, size_t nbytes, const void* dev_offsets, size_t nrec, int owner, int n_owners);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,79 @@
+// common.cuh — shared types of the B200 BAM->IR counting path.
+// Names follow the reference's domain: FragmentBlocks, JunctionCount, SpansPoint,
+// CoverageBlocks, FragmentsInChr/ROI, ChrMapUpdate.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+
+namespace irf {
+
+typedef unsigned long long u64;
+typedef uint32_t u32;
+
+// ---- disputed behavioural constants; the oracle holds its own copy on purpose
+constexpr int JUNC_MIN_FLANK = 5;          // [C-3]
+constexpr u32 SPAN_OVERHANG_LEFT = 5;      // [C-4]
+constexpr u32 SPAN_OVERHANG_RIGHT = 4;     // [C-4]
+constexpr u32 EDGE_WINDOW_OFFSET = 5;      // [C-13]
+constexpr u32 EDGE_WINDOW_LEN = 50;        // [C-13]
+
+// ---- junction key: 36-bit concatenated-genome coordinate of the left end, 28-bit gap (CIGAR op lengths are 28-bit)
+constexpr int JKEY_GAP_BITS = 28;
+constexpr u64 JKEY_EMPTY = ~0ull;
+__host__ __device__ inline u64 jkey_make(u64 gleft, u64 gap) { return (gleft << JKEY_GAP_BITS) | gap; }
+
+// ---- error bits set by kernels in DevTables::err
+enum DevErr : int {
+  DERR_INFLATE = 1, DERR_TRUNCATED = 2, DERR_BAD_RECORD = 4, DERR_JUNC_FULL = 8, DERR_JKEY_RANGE = 16,
+  DERR_PAIR_FULL = 32, DERR_REFID = 64, DERR_DUMP_FULL = 128,
+};
+
+// ---- counters (the reference prints these on stdout; SURVEY.md §5 "Metrics")
+enum Stat : int { ST_SINGLE = 0, ST_PAIRED, ST_SHORT, ST_INTERSECT, ST_LONG, ST_SKIPPED, ST_ERROR, ST_NUCLEOTIDES, ST_RECORDS, ST_COUNT };
+
+struct Range { u32 begin, end; };
+
+// Device-side view of every processor's tables after ChrMapUpdate (indexed by BAM refID).
+struct DevTables {
+  int n_ref;
+  const int32_t* ref_len;   // [n_ref]
+  const u64* chr_goff;      // [n_ref + 1] offset of each BAM reference in the concatenated coordinate space
+  // SpansPoint
+  const u32* sp_pos; const Range* sp_range; u32* sp_count; u32 n_sp;          // sp_count[dir * n_sp + i]
+  // CoverageBlocks: measured segments (sorted, disjoint), compact depth space with one sentinel slot per segment
+  const u32* seg_start; const u32* seg_end; const u64* seg_coff; const Range* seg_range; int32_t* diff; u64 P;  // diff[dir * P + c]
+  // FragmentsInROI
+  const u32* roi_start; const u32* roi_end; const Range* roi_range; u32* roi_count; u32 n_roi;  // roi_count[dir * n_roi + i]
+  // FragmentsInChr
+  u32* chr_count;           // [dir * n_ref + refID]
+  // JunctionCount: open-addressing tables, keys + counts[slot * 2 + dir]
+  u64* jc_keys; u32* jc_cnt; u32 jc_mask;
+  u64* jl_keys; u32* jl_cnt; u32 jl_mask;   // left ends (key = concatenated coordinate)
+  u64* jr_keys; u32* jr_cnt; u32 jr_mask;   // right ends
+  u64* stats;               // [ST_COUNT]
+  int* err;
+  // optional fragment dump (tests): words appended at dump[atomicAdd(dump_cursor, n)]
+  u32* dump; u64* dump_cursor; u64 dump_cap;
+};
+
+// One row of IRFinder-IR-*.txt in numeric form; text formatting happens on the host.
+struct IntronRow {
+  long long excluded; u64 positions;
+  double coverage, depth, p25, p50, p75, first50, last50, irratio;
+  u32 sp_left, sp_right, jc_left, jc_right, jc_exact; int warning;
+};
+enum Warning : int { W_NONE = 0, W_LOWCOVER, W_LOWSPLICING, W_MINORISOFORM, W_NONUNIFORM };
+
+// Device description of one ref-cover.bed record.
+struct IntronDesc {
+  u32 blk_begin, blk_main_end, blk_first_end, blk_last_end;  // [begin,main_end) measured blocks, then first-50 pieces, then last-50 pieces
+  u32 start, end; int refid;                                  // refid = -1 when the chromosome is absent from the BAM
+  int sp_left, sp_right;                                      // indices into sp arrays or -1
+  u32 plus;                                                   // annotated strand
+};
+struct IntronBlock { u64 c0; u32 len; u32 pad; };            // compact range [c0, c0+len)
+
+#define IRF_CUDA(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) throw std::string(#call) + ": " + cudaGetErrorString(e_); } while (0)
+
+}  // namespace irf

@@ -1,0 +1,565 @@
+// context.cu — irf_ctx and the C ABI declared in include/irfinder_b200.h.
+//
+// Host side of the path: BGZF block scan, pinned/async host->device streaming in batches that overlap the
+// inflate kernels, BAM header parse (BAM2blocks::readBamHeader) from device-inflated bytes, ChrMapUpdate
+// (binding name-keyed reference tables to BAM refIDs), kernel orchestration and result download.
+// There is no CPU implementation of any counting step in this library: without a CUDA device every entry
+// point fails with IRF_ECUDA.
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <string>
+#include <vector>
+
+#include "../../include/irfinder_b200.h"
+#include "common.cuh"
+#include "kernels.h"
+#include "refs.h"
+
+using namespace irf;
+using std::string;
+using std::vector;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr; size_t cap = 0;
+  void ensure(size_t n) { n += 256; if (n > cap) { if (p) cudaFree(p); p = nullptr; cap = 0; IRF_CUDA(cudaMalloc(&p, n)); cap = n; } }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return (T*)p; }
+};
+template <class T> static void upload(DevBuf& b, const vector<T>& v, cudaStream_t s) {
+  b.ensure(v.size() * sizeof(T)); if (!v.empty()) IRF_CUDA(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+}
+struct Blk { u64 c_off; u32 c_len; u32 isize; u64 file_off; };
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std::min<u64>(p, 1ull << 31); }
+
+}  // namespace
+
+struct irf_ctx {
+  int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr;
+  // options
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1;
+  // references (host)
+  CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
+  // BAM header
+  vector<string> chr_names; vector<int32_t> chr_lens; vector<u64> chr_goff; bool have_header = false, bound = false; u64 rec0 = 0;
+  // device reference tables
+  DevBuf d_ref_len, d_chr_goff, d_sp_pos, d_sp_range, d_sp_count, d_seg_start, d_seg_end, d_seg_coff, d_seg_range, d_diff, d_roi_start, d_roi_end, d_roi_range, d_roi_count, d_chr_count;
+  DevBuf d_jc_keys, d_jc_cnt, d_jl_keys, d_jl_cnt, d_jr_keys, d_jr_cnt, d_annot_keys; u64 n_annot = 0; u32 jc_slots = 0, jside_slots = 0;
+  DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
+  DevBuf d_exp_keys[3], d_exp_cnt[3];
+  // staged input
+  DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab;
+  const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
+  vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
+  u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
+  void* pinned = nullptr; size_t pinned_cap = 0;
+  // results
+  vector<u64> h_stats; vector<u32> h_sp, h_roi, h_chr, h_dump; vector<JuncEntry> h_junc; vector<IntronRow> rows_nondir, rows_dir; vector<int32_t> h_depth;
+  struct JuncOut { int32_t refid; u32 start, end, neg, pos; }; vector<JuncOut> h_junc_out;
+  int directionality = 0; string stdout_text, dir_log; double timing[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
+  bool counted = false, finalized = false;
+  string err;
+
+  DevTables T{};
+
+  // ---------------------------------------------------------------- set-up
+  void init(int dev) {
+    int n = 0; cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) throw string("no CUDA device: this library has no CPU path (") + cudaGetErrorString(e) + ")";
+    device = dev; IRF_CUDA(cudaSetDevice(dev));
+    IRF_CUDA(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_copy, cudaStreamNonBlocking));
+    d_stats.ensure(ST_COUNT * 8); d_err.ensure(4); d_small.ensure(256);
+  }
+  void sync() { IRF_CUDA(cudaStreamSynchronize(s_compute)); }
+
+  void load_ref(const char* cover, const char* sj, const char* rc, const char* roi_path) {
+    { std::ifstream f(cover); if (!f) throw string("cannot open ") + cover; cov.loadRef(f); }
+    { std::ifstream f(sj); if (!f) throw string("cannot open ") + sj; jref.loadRef(f); }
+    { std::ifstream f(rc); if (!f) throw string("cannot open ") + rc; sp.loadRef(f); }   // SpansPoint::setSpanLength(5,4) is compiled in (common.cuh)
+    roi = RoiRef();
+    if (roi_path && strcmp(roi_path, "NULL") != 0 && roi_path[0]) { std::ifstream f(roi_path); if (!f) throw string("cannot open ") + roi_path; roi.loadRef(f); }
+    refs_loaded = true; bound = false;
+    // chromosome-independent device tables
+    upload(d_sp_pos, sp.pos, s_compute); upload(d_seg_start, cov.seg_start, s_compute); upload(d_seg_end, cov.seg_end, s_compute); upload(d_seg_coff, cov.seg_coff, s_compute);
+    vector<u32> rs, re; for (auto& r : roi.rois) { rs.push_back(r.start); re.push_back(r.end); }
+    upload(d_roi_start, rs, s_compute); upload(d_roi_end, re, s_compute);
+    d_sp_count.ensure(sp.pos.size() * 8); d_roi_count.ensure(roi.rois.size() * 8); d_diff.ensure(cov.P * 8); d_tile_sums.ensure(depth_scan_tiles(cov.P * 2) * 4);
+    jc_slots = 1u << junc_cap_log2; jside_slots = jc_slots >> 1;
+    if ((u64)jc_slots < 4 * jref.size()) jc_slots = next_pow2(4 * jref.size()), jside_slots = jc_slots >> 1;
+    d_jc_keys.ensure((u64)jc_slots * 8); d_jc_cnt.ensure((u64)jc_slots * 8); d_jl_keys.ensure((u64)jside_slots * 8); d_jl_cnt.ensure((u64)jside_slots * 8);
+    d_jr_keys.ensure((u64)jside_slots * 8); d_jr_cnt.ensure((u64)jside_slots * 8);
+    sync();
+  }
+
+  // every processor's ChrMapUpdate: bind name-keyed tables to the BAM's refID order
+  void chr_map_update() {
+    if (!refs_loaded) throw string("irf_load_ref must be called before a run");
+    int n = (int)chr_names.size();
+    chr_goff.assign(n + 1, 0); for (int i = 0; i < n; i++) chr_goff[i + 1] = chr_goff[i] + (u64)std::max(chr_lens[i], 0) + 1;
+    if (chr_goff[n] >= (1ull << 36)) throw string("genome larger than 2^36 bases is not supported by the junction key");
+    vector<Range> spr(n), sgr(n), ror(n);
+    for (int i = 0; i < n; i++) {
+      auto a = sp.chr_range.find(chr_names[i]); spr[i] = a == sp.chr_range.end() ? Range{0, 0} : a->second;
+      auto b = cov.chr_range.find(chr_names[i]); sgr[i] = b == cov.chr_range.end() ? Range{0, 0} : b->second;
+      auto c = roi.chr_range.find(chr_names[i]); ror[i] = c == roi.chr_range.end() ? Range{0, 0} : c->second;
+    }
+    upload(d_ref_len, chr_lens, s_compute); upload(d_chr_goff, chr_goff, s_compute); upload(d_sp_range, spr, s_compute); upload(d_seg_range, sgr, s_compute); upload(d_roi_range, ror, s_compute);
+    d_chr_count.ensure((size_t)n * 8);
+    // annotated junction keys (JunctionCount::loadRef entries on chromosomes present in the BAM)
+    std::map<string, int> id; for (int i = n - 1; i >= 0; i--) id[chr_names[i]] = i;
+    vector<u64> keys;
+    for (auto& c : jref.chr_junc) { auto it = id.find(c.first); if (it == id.end()) continue; u64 base = chr_goff[it->second];
+      for (auto& j : c.second) { u64 gap = (u64)j.first.second - j.first.first; if (j.first.second >= j.first.first && gap < (1ull << JKEY_GAP_BITS)) keys.push_back(jkey_make(base + j.first.first, gap)); } }
+    n_annot = keys.size(); upload(d_annot_keys, keys, s_compute);
+    // intron descriptors
+    vector<IntronDesc> descs; vector<IntronBlock> ib; descs.reserve(cov.BEDrecords.size());
+    for (auto& rec : cov.BEDrecords) {
+      IntronDesc d; d.blk_begin = (u32)ib.size();
+      for (auto& b : rec.blocks) cov.pieces(rec.chrName, b.first, b.second, ib);
+      d.blk_main_end = (u32)ib.size();
+      u32 ws = rec.start + EDGE_WINDOW_OFFSET, we = rec.end > EDGE_WINDOW_OFFSET ? rec.end - EDGE_WINDOW_OFFSET : 0;
+      cov.pieces(rec.chrName, ws, std::min(ws + EDGE_WINDOW_LEN, rec.end), ib); d.blk_first_end = (u32)ib.size();
+      cov.pieces(rec.chrName, (we > EDGE_WINDOW_LEN && we - EDGE_WINDOW_LEN > rec.start) ? we - EDGE_WINDOW_LEN : rec.start, we, ib); d.blk_last_end = (u32)ib.size();
+      d.start = rec.start; d.end = rec.end; auto it = id.find(rec.chrName); d.refid = it == id.end() ? -1 : it->second;
+      d.sp_left = sp.lookup_index(rec.chrName, rec.start); d.sp_right = sp.lookup_index(rec.chrName, rec.end); d.plus = rec.direction ? 1 : 0;
+      descs.push_back(d);
+    }
+    upload(d_introns, descs, s_compute); upload(d_iblocks, ib, s_compute); d_rows.ensure(descs.size() * sizeof(IntronRow));
+    if (dump_fragments) { dump_cap = 1ull << 26; d_dump.ensure(dump_cap * 4); d_dump_cursor.ensure(8); }
+    T.n_ref = n; T.ref_len = d_ref_len.as<int32_t>(); T.chr_goff = d_chr_goff.as<u64>();
+    T.sp_pos = d_sp_pos.as<u32>(); T.sp_range = d_sp_range.as<Range>(); T.sp_count = d_sp_count.as<u32>(); T.n_sp = (u32)sp.pos.size();
+    T.seg_start = d_seg_start.as<u32>(); T.seg_end = d_seg_end.as<u32>(); T.seg_coff = d_seg_coff.as<u64>(); T.seg_range = d_seg_range.as<Range>(); T.diff = d_diff.as<int32_t>(); T.P = cov.P;
+    T.roi_start = d_roi_start.as<u32>(); T.roi_end = d_roi_end.as<u32>(); T.roi_range = d_roi_range.as<Range>(); T.roi_count = d_roi_count.as<u32>(); T.n_roi = (u32)roi.rois.size();
+    T.chr_count = d_chr_count.as<u32>();
+    T.jc_keys = d_jc_keys.as<u64>(); T.jc_cnt = d_jc_cnt.as<u32>(); T.jc_mask = jc_slots - 1;
+    T.jl_keys = d_jl_keys.as<u64>(); T.jl_cnt = d_jl_cnt.as<u32>(); T.jl_mask = jside_slots - 1;
+    T.jr_keys = d_jr_keys.as<u64>(); T.jr_cnt = d_jr_cnt.as<u32>(); T.jr_mask = jside_slots - 1;
+    T.stats = d_stats.as<u64>(); T.err = d_err.as<int>();
+    T.dump = dump_fragments ? d_dump.as<u32>() : nullptr; T.dump_cursor = dump_fragments ? d_dump_cursor.as<u64>() : nullptr; T.dump_cap = dump_cap;
+    bound = true; sync();
+    reset();
+  }
+
+  void reset() {
+    if (!bound) { counted = finalized = false; return; }
+    cudaStream_t s = s_compute;
+    IRF_CUDA(cudaMemsetAsync(d_sp_count.p, 0, sp.pos.size() * 8, s)); IRF_CUDA(cudaMemsetAsync(d_roi_count.p, 0, roi.rois.size() * 8, s));
+    IRF_CUDA(cudaMemsetAsync(d_chr_count.p, 0, chr_names.size() * 8, s)); IRF_CUDA(cudaMemsetAsync(d_diff.p, 0, cov.P * 8, s));
+    IRF_CUDA(cudaMemsetAsync(d_jc_keys.p, 0xff, (u64)jc_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jc_cnt.p, 0, (u64)jc_slots * 8, s));
+    IRF_CUDA(cudaMemsetAsync(d_jl_keys.p, 0xff, (u64)jside_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jl_cnt.p, 0, (u64)jside_slots * 8, s));
+    IRF_CUDA(cudaMemsetAsync(d_jr_keys.p, 0xff, (u64)jside_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jr_cnt.p, 0, (u64)jside_slots * 8, s));
+    IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_COUNT * 8, s)); IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
+    if (dump_fragments) IRF_CUDA(cudaMemsetAsync(d_dump_cursor.p, 0, 8, s));
+    launch_ht_insert_keys(T.jc_keys, T.jc_mask, d_annot_keys.as<u64>(), n_annot, T.err, s);
+    counted = finalized = false; sharded = false; halo_leftover = 0; launches0 = launch_counter();
+  }
+
+  // ---------------------------------------------------------------- BGZF scan (SAM v1 §4.1)
+  void scan_bgzf(const uint8_t* p, size_t n_own, size_t n_total) {
+    blks.clear(); nblk_own = 0; size_t off = 0;
+    while (off < n_total) {
+      if (off + 18 > n_total) { if (off >= n_own) break; throw string("truncated BGZF block header"); }
+      const uint8_t* h = p + off;
+      if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) throw string("not a BGZF block at offset ") + std::to_string(off);
+      u32 xlen = h[10] | (u32)h[11] << 8; if (off + 12 + xlen > n_total) { if (off >= n_own) break; throw string("truncated BGZF extra field"); }
+      int bsize = -1; for (u32 x = 0; x + 4 <= xlen;) { const uint8_t* sf = h + 12 + x; u32 slen = sf[2] | (u32)sf[3] << 8; if (sf[0] == 'B' && sf[1] == 'C' && slen == 2) { bsize = sf[4] | (int)sf[5] << 8; break; } x += 4 + slen; }
+      if (bsize < 0) throw string("BGZF block without BC subfield at offset ") + std::to_string(off);
+      size_t total = (size_t)bsize + 1; if (total < 12 + xlen + 8) throw string("bad BGZF BSIZE");
+      if (off + total > n_total) { if (off >= n_own) break; throw string("truncated BGZF block (file cut short)"); }
+      Blk b; b.file_off = off; b.c_off = off + 12 + xlen; b.c_len = (u32)(total - 12 - xlen - 8); memcpy(&b.isize, p + off + total - 4, 4);
+      if (b.isize > 65536) throw string("BGZF ISIZE > 64 KiB");
+      if (off < n_own) nblk_own++;
+      blks.push_back(b); off += total;
+    }
+  }
+
+  void stage(const void* src, size_t n_own, size_t n_total, int has_header, bool copy_now) {
+    if (n_own > n_total) throw string("nbytes_own > nbytes_total");
+    double t0 = now_ms();
+    inflated_input = false; scan_bgzf((const uint8_t*)src, n_own, n_total);
+    if (require_eof && has_header && n_own == n_total) { if (blks.empty() || blks.back().isize != 0) throw string("BGZF EOF marker missing (truncated file?)"); }
+    timing[6] = now_ms() - t0;
+    h_src = (const uint8_t*)src; src_total = blks.empty() ? 0 : (size_t)(blks.back().c_off + blks.back().c_len + 8);
+    vector<u64> c_off(blks.size()), u_off(blks.size()); vector<u32> c_len(blks.size()), u_len(blks.size()); u64 u = 0;
+    for (size_t i = 0; i < blks.size(); i++) { c_off[i] = blks[i].c_off; c_len[i] = blks[i].c_len; u_off[i] = u; u_len[i] = blks[i].isize; u += blks[i].isize; }
+    Uend = u;
+    upload(d_c_off, c_off, s_compute); upload(d_c_len, c_len, s_compute); upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute);
+    d_comp.ensure(src_total + 64); d_U.ensure(Uend + 64);
+    size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
+    sync();  // the host vectors above go out of scope
+    resident = false; staged = true; staged_has_header = has_header != 0;
+    if (copy_now) { if (src_total) IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); sync(); resident = true; h_src = nullptr; }
+  }
+  void stage_inflated(const void* src, size_t n) {  // reference stdin mode with an already-inflated stream
+    inflated_input = true; blks.clear(); const u32 CH = 65536; size_t nb = (n + CH - 1) / CH; vector<u64> u_off(nb); vector<u32> u_len(nb);
+    for (size_t i = 0; i < nb; i++) { u_off[i] = (u64)i * CH; u_len[i] = (u32)std::min<size_t>(CH, n - i * CH); blks.push_back(Blk{0, 0, u_len[i], 0}); }
+    nblk_own = (int)nb; Uend = n; upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute); d_U.ensure(n + 64);
+    IRF_CUDA(cudaMemcpyAsync(d_U.p, src, n, cudaMemcpyHostToDevice, s_compute));
+    d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
+    sync(); staged = true; staged_has_header = true; resident = true;
+  }
+
+  // S1: copy (when not resident) and inflate in batches so the copy of batch i+1 overlaps the inflate of batch i
+  void inflate_all() {
+    if (inflated_input) return;
+    size_t nb = blks.size(); if (!nb) return;
+    IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
+    const size_t target = std::max<size_t>(768ull << 20, src_total / 8 + 1);
+    cudaEvent_t ev_k0, ev_k1; IRF_CUDA(cudaEventCreate(&ev_k0)); IRF_CUDA(cudaEventCreate(&ev_k1));
+    vector<cudaEvent_t> copied; size_t b0 = 0; double kernel_ms = 0; vector<std::pair<cudaEvent_t, cudaEvent_t>> kev;
+    while (b0 < nb) {
+      size_t b1 = b0; u64 begin = blks[b0].file_off, end = begin;
+      while (b1 < nb && (end - begin) < target) { end = blks[b1].c_off + blks[b1].c_len + 8; b1++; }
+      if (!resident) {
+        if (b1 == nb) end = src_total;
+        IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + begin, h_src + begin, end - begin, cudaMemcpyHostToDevice, s_copy));
+        cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev, 0)); copied.push_back(ev);
+      }
+      InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>() + b0, d_c_len.as<u32>() + b0, d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, (int)(b1 - b0), d_status.as<int>() + b0, T.err ? T.err : d_err.as<int>()};
+      cudaEvent_t k0, k1; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1));
+      IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute)); kev.push_back({k0, k1});
+      b0 = b1;
+    }
+    IRF_CUDA(cudaGetLastError()); sync();
+    for (auto& k : kev) { float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k.first, k.second)); kernel_ms += ms; cudaEventDestroy(k.first); cudaEventDestroy(k.second); }
+    for (auto e : copied) cudaEventDestroy(e);
+    cudaEventDestroy(ev_k0); cudaEventDestroy(ev_k1);
+    timing[1] = kernel_ms; n_inflate_launches = (int)kev.size();
+    if (!resident) { resident = true; }
+  }
+  int n_inflate_launches = 0;
+
+  int dev_err() { int e = 0; IRF_CUDA(cudaMemcpyAsync(&e, d_err.p, 4, cudaMemcpyDeviceToHost, s_compute)); sync(); return e; }
+  void check_dev_err(const char* stage_name) {
+    int e = dev_err(); if (!e) return;
+    string m = string(stage_name) + ":";
+    if (e & DERR_INFLATE) m += " corrupt DEFLATE data in a BGZF block;"; if (e & DERR_TRUNCATED) m += " truncated BAM record stream;"; if (e & DERR_BAD_RECORD) m += " malformed BAM record / unframeable stream;";
+    if (e & DERR_JUNC_FULL) m += " junction table full (raise junc_capacity_log2);"; if (e & DERR_JKEY_RANGE) m += " junction outside the supported key range;";
+    if (e & DERR_PAIR_FULL) m += " pairing table full;"; if (e & DERR_REFID) m += " record refID beyond the header's reference list;"; if (e & DERR_DUMP_FULL) m += " fragment dump buffer full;";
+    throw m;
+  }
+
+  // BAM2blocks::readBamHeader on device-inflated bytes
+  void parse_header_from_device() {
+    size_t have = 0; vector<uint8_t> h;
+    auto fetch = [&](size_t want) { want = std::min<size_t>(want, Uend); if (want <= have) return; h.resize(want); IRF_CUDA(cudaMemcpyAsync(h.data() + have, d_U.as<uint8_t>() + have, want - have, cudaMemcpyDeviceToHost, s_compute)); sync(); have = want; };
+    fetch(1 << 16);
+    auto need = [&](size_t n) { if (n > have) fetch(std::max(n, have * 2)); if (n > have) throw string("BAM header truncated"); };
+    need(12); if (memcmp(h.data(), "BAM\1", 4) != 0) throw string("not a BAM stream (bad magic)");
+    int32_t l_text; memcpy(&l_text, &h[4], 4); if (l_text < 0) throw string("bad BAM header");
+    size_t p = 8 + (size_t)l_text; need(p + 4); int32_t n_ref; memcpy(&n_ref, &h[p], 4); p += 4; if (n_ref < 0) throw string("bad BAM header");
+    vector<string> names; vector<int32_t> lens;
+    for (int i = 0; i < n_ref; i++) { need(p + 4); int32_t l_name; memcpy(&l_name, &h[p], 4); p += 4; if (l_name < 1) throw string("bad BAM header"); need(p + l_name + 4);
+      names.emplace_back((const char*)&h[p], (size_t)l_name - 1); p += l_name; int32_t l_ref; memcpy(&l_ref, &h[p], 4); p += 4; lens.push_back(l_ref); }
+    rec0 = p;
+    if (!have_header || names != chr_names || lens != chr_lens || !bound) { chr_names = names; chr_lens = lens; have_header = true; chr_map_update(); }
+  }
+
+  // S2 + S3
+  void count() {
+    if (!staged) throw string("nothing staged");
+    cudaEvent_t e0, e1, e2, e3; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventCreate(&e2)); IRF_CUDA(cudaEventCreate(&e3));
+    IRF_CUDA(cudaEventRecord(e0, s_compute));
+    if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
+    inflate_all();
+    check_dev_err("inflate");
+    IRF_CUDA(cudaEventRecord(e1, s_compute));
+    if (staged_has_header) parse_header_from_device();
+    else if (!have_header) throw string("no BAM header: call irf_read_header before staging a shard without one");
+    if (!bound) chr_map_update();
+    int nb = (int)blks.size();
+    FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), nb, Uend, rec0, staged_has_header ? 1 : 0, T.n_ref, T.ref_len,
+                 d_entry.as<u64>(), d_exit.as<u64>(), d_nrec.as<u32>(), d_ncand.as<u32>(), d_ferr.as<uint8_t>(), T.err};
+    if (!staged_has_header && entry0_override >= 0) { fa.rec0 = (u64)entry0_override; fa.rec0_valid = 1; }
+    launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
+    u32* n_bad = d_small.as<u32>(); int rounds = 0;
+    for (;;) {
+      IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mask.as<uint8_t>(), n_bad, s_compute);
+      u32 hb = 0; IRF_CUDA(cudaMemcpyAsync(&hb, n_bad, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
+      if (!hb) break; if (++rounds > nb + 2) throw string("record framing did not converge");
+      launch_walk_count(fa, d_mask.as<uint8_t>(), s_compute);
+    }
+    frame_rounds = rounds;
+    u64* totals = (u64*)(d_small.as<uint8_t>() + 16); IRF_CUDA(cudaMemsetAsync(totals, 0, 16, s_compute));
+    FrameArgs own = fa; own.nblk = nblk_own; launch_frame_totals(own, totals, s_compute);
+    u64 ht[2] = {0, 0}; IRF_CUDA(cudaMemcpyAsync(ht, totals, 16, cudaMemcpyDeviceToHost, s_compute));
+    u64 fe[2] = {0, 0}; if (nblk_own > 0) { IRF_CUDA(cudaMemcpyAsync(&fe[0], d_entry.as<u64>(), 8, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(&fe[1], d_exit.as<u64>() + (nblk_own - 1), 8, cudaMemcpyDeviceToHost, s_compute)); }
+    sync(); n_rec = ht[0]; n_cand = ht[1];
+    u64 own_end = 0; for (int i = 0; i < nblk_own; i++) own_end += blks[i].isize;
+    frame_entry0 = fe[0]; frame_exit_rel = fe[1] >= own_end ? fe[1] - own_end : 0;
+    check_dev_err("record framing");
+    if (nblk_own == nb && nb > 0 && fe[1] != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
+    IRF_CUDA(cudaEventRecord(e2, s_compute));
+    pslots = next_pow2(std::max<u64>(1024, n_cand + n_cand / 2)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
+    launch_walk_process(T, own, d_ptab.as<u64>(), (u32)(pslots - 1), s_compute);
+    IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaGetLastError());
+    check_dev_err("fragment counting");
+    float a, b, c; IRF_CUDA(cudaEventElapsedTime(&a, e0, e1)); IRF_CUDA(cudaEventElapsedTime(&b, e1, e2)); IRF_CUDA(cudaEventElapsedTime(&c, e2, e3));
+    timing[0] = a; timing[2] = b; timing[3] = c; timing[5] = a + b + c;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
+    counted = true; finalized = false;
+  }
+  int frame_rounds = 0;
+
+  u64 count_leftovers(u64* fill, u64 cap) {
+    u64* n_left = (u64*)(d_small.as<uint8_t>() + 64); IRF_CUDA(cudaMemsetAsync(n_left, 0, 8, s_compute));
+    launch_pair_leftover(d_ptab.as<u64>(), pslots, n_left, fill, cap, s_compute);
+    u64 h = 0; IRF_CUDA(cudaMemcpyAsync(&h, n_left, 8, cudaMemcpyDeviceToHost, s_compute)); sync(); return h;
+  }
+
+  u64 export_table(int which) {   // compact the counted entries of one junction table into dense device arrays
+    u64* keys = which == 0 ? T.jc_keys : which == 1 ? T.jl_keys : T.jr_keys; u32* cnt = which == 0 ? T.jc_cnt : which == 1 ? T.jl_cnt : T.jr_cnt; u64 slots = which == 0 ? jc_slots : jside_slots;
+    u64* cur = (u64*)(d_small.as<uint8_t>() + 96);
+    IRF_CUDA(cudaMemsetAsync(cur, 0, 8, s_compute)); launch_ht_compact(keys, cnt, slots, nullptr, nullptr, cur, 0, 1, s_compute);
+    u64 n = 0; IRF_CUDA(cudaMemcpyAsync(&n, cur, 8, cudaMemcpyDeviceToHost, s_compute)); sync();
+    d_exp_keys[which].ensure(n * 8); d_exp_cnt[which].ensure(n * 8);
+    IRF_CUDA(cudaMemsetAsync(cur, 0, 8, s_compute)); launch_ht_compact(keys, cnt, slots, d_exp_keys[which].as<u64>(), d_exp_cnt[which].as<u32>(), cur, n, 1, s_compute); sync();
+    return n;
+  }
+
+  // S4 + output-side statistics
+  void finalize() {
+    if (!counted) throw string("irf_count has not run");
+    if (finalized) return;
+    cudaEvent_t e0, e1; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventRecord(e0, s_compute));
+    u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0);
+    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute);
+    // junctions -> host (JunctionCount map contents)
+    u64 nj = export_table(0); vector<u64> k(nj); vector<u32> c(nj * 2);
+    if (nj) { IRF_CUDA(cudaMemcpyAsync(k.data(), d_exp_keys[0].p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(c.data(), d_exp_cnt[0].p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); sync(); }
+    h_junc.resize(nj);
+    for (u64 i = 0; i < nj; i++) { u64 gl = k[i] >> JKEY_GAP_BITS, gap = k[i] & ((1ull << JKEY_GAP_BITS) - 1); int rid = (int)(std::upper_bound(chr_goff.begin(), chr_goff.end(), gl) - chr_goff.begin()) - 1;
+      h_junc[i] = JuncEntry{rid, (u32)(gl - chr_goff[rid]), (u32)(gl - chr_goff[rid] + gap), {c[2 * i], c[2 * i + 1]}}; }
+    std::sort(h_junc.begin(), h_junc.end(), [](const JuncEntry& a, const JuncEntry& b) { if (a.refid != b.refid) return a.refid < b.refid; if (a.start != b.start) return a.start < b.start; return a.end < b.end; });
+    h_junc_out.resize(nj); for (u64 i = 0; i < nj; i++) h_junc_out[i] = JuncOut{h_junc[i].refid, h_junc[i].start, h_junc[i].end, h_junc[i].cnt[0], h_junc[i].cnt[1]};
+    dir_log.clear(); directionality = directional(jref, chr_names, h_junc, dir_log);
+    // per-intron statistics
+    u32* dmax = d_small.as<u32>() + 2; IRF_CUDA(cudaMemsetAsync(dmax, 0, 4, s_compute)); launch_max_depth(T.diff, cov.P, dmax, s_compute);
+    u32 hmax = 0; IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
+    u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
+    u32 bins = hmax >= 8192 ? hmax + 1 : 1; d_scratch.ensure((u64)grid * bins * 4);
+    launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
+    rows_nondir.resize(n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
+    rows_dir.clear();
+    if (directionality != 0) {
+      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, directionality, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
+      rows_dir.resize(n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
+    }
+    h_stats.assign(ST_COUNT, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
+    IRF_CUDA(cudaMemcpyAsync(h_stats.data(), d_stats.p, ST_COUNT * 8, cudaMemcpyDeviceToHost, s_compute));
+    if (!h_sp.empty()) IRF_CUDA(cudaMemcpyAsync(h_sp.data(), d_sp_count.p, h_sp.size() * 4, cudaMemcpyDeviceToHost, s_compute));
+    if (!h_roi.empty()) IRF_CUDA(cudaMemcpyAsync(h_roi.data(), d_roi_count.p, h_roi.size() * 4, cudaMemcpyDeviceToHost, s_compute));
+    if (!h_chr.empty()) IRF_CUDA(cudaMemcpyAsync(h_chr.data(), d_chr_count.p, h_chr.size() * 4, cudaMemcpyDeviceToHost, s_compute));
+    IRF_CUDA(cudaEventRecord(e1, s_compute)); sync();
+    check_dev_err("finalize");
+    h_stats[ST_ERROR] += errors;
+    float ms; IRF_CUDA(cudaEventElapsedTime(&ms, e0, e1)); timing[4] = ms; cudaEventDestroy(e0); cudaEventDestroy(e1);
+    h_dump.clear(); h_depth.clear();
+    if (dump_fragments) { u64 n = 0; IRF_CUDA(cudaMemcpy(&n, d_dump_cursor.p, 8, cudaMemcpyDeviceToHost)); n = std::min(n, dump_cap); h_dump.resize(n); if (n) IRF_CUDA(cudaMemcpy(h_dump.data(), d_dump.p, n * 4, cudaMemcpyDeviceToHost)); }
+    // the reference's stdout block
+    stdout_text = dir_log + "Directionality:\t" + std::to_string(directionality) + "\n";
+    auto line = [&](const char* key, u64 v) { stdout_text += key; stdout_text += '\t'; stdout_text += std::to_string(v); stdout_text += '\n'; };
+    line("Total reads processed", h_stats[ST_SINGLE] + h_stats[ST_PAIRED]); line("Total nucleotides", h_stats[ST_NUCLEOTIDES]); line("Total singles processed", h_stats[ST_SINGLE]);
+    line("Total pairs processed", h_stats[ST_PAIRED]); line("Short pairs", h_stats[ST_SHORT]); line("Intersect pairs", h_stats[ST_INTERSECT]); line("Long pairs", h_stats[ST_LONG]);
+    line("Skipped reads", h_stats[ST_SKIPPED]); line("Error reads", h_stats[ST_ERROR]);
+    finalized = true;
+  }
+
+  void write_outputs(const char* outdir) {
+    if (!finalized) throw string("no finished run to write");
+    double t0 = now_ms(); string d = outdir;
+    auto put = [&](const char* name, const string& s) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; size_t w = fwrite(s.data(), 1, s.size(), f); int rc = fclose(f); if (w != s.size() || rc) throw string("short write to ") + p; };
+    put("IRFinder-IR-nondir.txt", format_ir_table(cov, rows_nondir));
+    if (directionality != 0) put("IRFinder-IR-dir.txt", format_ir_table(cov, rows_dir));
+    put("IRFinder-JuncCount.txt", format_junctions(jref, chr_names, h_junc));
+    put("IRFinder-SpansPoint.txt", format_spans(sp, h_sp));
+    put("IRFinder-ChrCoverage.txt", format_chr(chr_names, h_chr));
+    if (roi.present) put("IRFinder-ROI.txt", format_roi(roi, h_roi));
+    timing[7] = now_ms() - t0;
+  }
+
+  void run_host_buffer(const void* p, size_t n) {
+    stage(p, n, n, 1, false);
+    if (bound) reset();
+    count(); finalize();
+  }
+  void* pinned_buf(size_t n) { if (n > pinned_cap) { if (pinned) cudaFreeHost(pinned); pinned = nullptr; IRF_CUDA(cudaMallocHost(&pinned, n + 64)); pinned_cap = n; } return pinned; }
+  size_t read_fd_all(int fd, size_t hint) {
+    size_t cap = std::max<size_t>(hint, 1 << 20), n = 0; vector<uint8_t> tmp; uint8_t* dst = (uint8_t*)pinned_buf(cap);
+    for (;;) {
+      if (n == cap) { tmp.assign(dst, dst + n); cap *= 2; dst = (uint8_t*)pinned_buf(cap); memcpy(dst, tmp.data(), n); }
+      ssize_t k = read(fd, dst + n, std::min<size_t>(cap - n, 1u << 30)); if (k < 0) throw string("read error"); if (k == 0) break; n += (size_t)k;
+    }
+    return n;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------ C ABI
+#define IRF_TRY(ctx, ...) do { if (!(ctx)) return IRF_EINVAL; try { cudaSetDevice((ctx)->device); __VA_ARGS__; return IRF_OK; } catch (const string& e_) { (ctx)->err = e_; return classify(e_); } catch (const std::exception& e_) { (ctx)->err = e_.what(); return IRF_EINVAL; } } while (0)
+static int classify(const string& e) {
+  if (e.find("cuda") != string::npos || e.find("CUDA") != string::npos) return IRF_ECUDA;
+  if (e.find("cannot open") != string::npos || e.find("cannot write") != string::npos || e.find("read error") != string::npos || e.find("short write") != string::npos) return IRF_EIO;
+  if (e.find("full") != string::npos) return IRF_ECAPACITY;
+  if (e.find("must be called") != string::npos || e.find("has not run") != string::npos || e.find("nothing staged") != string::npos || e.find("no finished run") != string::npos || e.find("no BAM header") != string::npos) return IRF_ESTATE;
+  return IRF_EFORMAT;
+}
+
+extern "C" {
+
+int irf_create(irf_ctx** out, const int* device_ids, int n_devices) {
+  if (!out || n_devices != 1 || !device_ids) return IRF_EINVAL;
+  irf_ctx* c = new irf_ctx();
+  try { c->init(device_ids[0]); } catch (const string& e) { fprintf(stderr, "irf_create: %s\n", e.c_str()); delete c; *out = nullptr; return IRF_ECUDA; }
+  *out = c; return IRF_OK;
+}
+void irf_destroy(irf_ctx* c) {
+  if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
+  DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
+                   &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_stats, &c->d_err, &c->d_introns,
+                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
+                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2]};
+  for (auto b : all) b->release();
+  if (c->pinned) cudaFreeHost(c->pinned);
+  if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy);
+  delete c;
+}
+const char* irf_last_error(irf_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int irf_set_option(irf_ctx* c, const char* key, const char* value) {
+  if (!c || !key || !value) return IRF_EINVAL; string k = key; long long v = atoll(value);
+  if (k == "trim_center") { if (v < 1 || v > 100) return IRF_EINVAL; c->trim_center = (u32)v; }
+  else if (k == "dump_fragments") { c->dump_fragments = v != 0; c->bound = false; }
+  else if (k == "inflate_variant") c->inflate_variant = (int)v;
+  else if (k == "junc_capacity_log2") { if (v < 10 || v > 30) return IRF_EINVAL; c->junc_cap_log2 = (int)v; }
+  else if (k == "require_eof") c->require_eof = v != 0;
+  else if (k == "entry0") c->entry0_override = v;
+  else { c->err = "unknown option " + k; return IRF_EINVAL; }
+  return IRF_OK;
+}
+int irf_load_ref(irf_ctx* c, const char* cover, const char* sj, const char* rc, const char* roi) { if (!cover || !sj || !rc) return IRF_EINVAL; IRF_TRY(c, c->load_ref(cover, sj, rc, roi)); }
+
+int irf_run_buffer(irf_ctx* c, const void* bgzf, size_t n) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->run_host_buffer(bgzf, n)); }
+int irf_run_bam(irf_ctx* c, const char* path, const char* /*bai_path*/) {
+  if (!path) return IRF_EINVAL;
+  IRF_TRY(c, {
+    int fd = open(path, O_RDONLY); if (fd < 0) throw string("cannot open ") + path;
+    struct stat st; size_t hint = 0; if (fstat(fd, &st) == 0 && st.st_size > 0) hint = (size_t)st.st_size + 1;
+    size_t n = 0; try { n = c->read_fd_all(fd, hint); } catch (...) { close(fd); throw; } close(fd);
+    c->run_host_buffer(c->pinned, n);
+  });
+}
+int irf_run_stream(irf_ctx* c, int fd, int inflated) {
+  IRF_TRY(c, {
+    size_t n = c->read_fd_all(fd, 64 << 20);
+    if (!inflated) c->run_host_buffer(c->pinned, n);
+    else { c->stage_inflated(c->pinned, n); if (c->bound) c->reset(); c->count(); c->finalize(); }
+  });
+}
+int irf_write_outputs(irf_ctx* c, const char* outdir) { if (!outdir) return IRF_EINVAL; IRF_TRY(c, c->write_outputs(outdir)); }
+const char* irf_stdout_text(irf_ctx* c) { return c ? c->stdout_text.c_str() : ""; }
+int irf_directionality(irf_ctx* c) { return c ? c->directionality : 0; }
+
+int irf_get_table(irf_ctx* c, int which, const void** p, size_t* n) {
+  if (!c || !p || !n) return IRF_EINVAL;
+  IRF_TRY(c, {
+    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; *p = c->timing; *n = 10; }
+    else {
+      if (!c->finalized) throw string("no finished run to read tables from");
+      switch (which) {
+        case IRF_T_STATS: *p = c->h_stats.data(); *n = c->h_stats.size(); break;
+        case IRF_T_SPANS: *p = c->h_sp.data(); *n = c->h_sp.size(); break;
+        case IRF_T_ROI: *p = c->h_roi.data(); *n = c->h_roi.size(); break;
+        case IRF_T_CHR: *p = c->h_chr.data(); *n = c->h_chr.size(); break;
+        case IRF_T_JUNCTIONS: *p = c->h_junc_out.data(); *n = c->h_junc_out.size(); break;
+        case IRF_T_ROWS_NONDIR: *p = c->rows_nondir.data(); *n = c->rows_nondir.size(); break;
+        case IRF_T_ROWS_DIR: *p = c->rows_dir.data(); *n = c->rows_dir.size(); break;
+        case IRF_T_FRAGMENTS: *p = c->h_dump.data(); *n = c->h_dump.size(); break;
+        case IRF_T_DEPTH:
+          if (c->h_depth.empty() && c->cov.P) { c->h_depth.resize(c->cov.P * 2); IRF_CUDA(cudaMemcpy(c->h_depth.data(), c->d_diff.p, c->cov.P * 8, cudaMemcpyDeviceToHost)); }
+          *p = c->h_depth.data(); *n = c->h_depth.size(); break;
+        default: throw string("unknown table code");
+      }
+    }
+  });
+}
+
+int irf_reset(irf_ctx* c) { IRF_TRY(c, c->reset()); }
+int irf_read_header(irf_ctx* c, const void* prefix, size_t n) {
+  if (!prefix) return IRF_EINVAL;
+  IRF_TRY(c, {
+    // inflate just the leading blocks that hold the header, through the same device path as a run
+    bool req = c->require_eof; c->require_eof = false;
+    try { c->stage(prefix, 0, n, 1, false); } catch (...) { c->require_eof = req; throw; } c->require_eof = req;
+    if (!c->bound) IRF_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4, c->s_compute));
+    c->inflate_all(); c->check_dev_err("inflate"); c->parse_header_from_device(); c->staged = false;
+  });
+}
+int irf_stage(irf_ctx* c, const void* bgzf, size_t own, size_t total, int has_header) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->stage(bgzf, own, total, has_header, true)); }
+int irf_count(irf_ctx* c) { IRF_TRY(c, c->count()); }
+int irf_frame_info(irf_ctx* c, uint64_t* entry0, uint64_t* exit_rel) { if (!c || !c->counted) return IRF_ESTATE; if (entry0) *entry0 = c->frame_entry0; if (exit_rel) *exit_rel = c->frame_exit_rel; return IRF_OK; }
+int irf_finalize(irf_ctx* c) { IRF_TRY(c, c->finalize()); }
+
+int irf_get_device_table(irf_ctx* c, int which, void** dp, size_t* n, int* eb) {
+  if (!c || !dp || !n || !eb || !c->bound) return c ? IRF_ESTATE : IRF_EINVAL;
+  switch (which) {
+    case IRF_T_STATS: *dp = c->d_stats.p; *n = ST_COUNT; *eb = 8; break;
+    case IRF_T_SPANS: *dp = c->d_sp_count.p; *n = c->sp.pos.size() * 2; *eb = 4; break;
+    case IRF_T_ROI: *dp = c->d_roi_count.p; *n = c->roi.rois.size() * 2; *eb = 4; break;
+    case IRF_T_CHR: *dp = c->d_chr_count.p; *n = c->chr_names.size() * 2; *eb = 4; break;
+    case IRF_T_DIFF: *dp = c->d_diff.p; *n = c->cov.P * 2; *eb = 4; break;
+    default: return IRF_EINVAL;
+  }
+  return IRF_OK;
+}
+int irf_export_junctions(irf_ctx* c, int which, void** keys, void** counts, size_t* n) {
+  if (!keys || !counts || !n || which < 0 || which > 2) return IRF_EINVAL;
+  IRF_TRY(c, { if (!c->counted) throw string("irf_count has not run"); u64 k = c->export_table(which); *keys = c->d_exp_keys[which].p; *counts = c->d_exp_cnt[which].p; *n = (size_t)k; });
+}
+int irf_import_junctions(irf_ctx* c, int which, const void* keys, const void* counts, size_t n) {
+  if (which < 0 || which > 2) return IRF_EINVAL;
+  IRF_TRY(c, {
+    if (!c->bound) throw string("irf_count has not run");
+    u64* tk = which == 0 ? c->T.jc_keys : which == 1 ? c->T.jl_keys : c->T.jr_keys; u32* tc = which == 0 ? c->T.jc_cnt : which == 1 ? c->T.jl_cnt : c->T.jr_cnt; u32 mask = which == 0 ? c->T.jc_mask : c->T.jl_mask;
+    launch_ht_add(tk, tc, mask, (const u64*)keys, (const u32*)counts, n, c->T.err, c->s_compute); c->sync(); c->check_dev_err("junction merge");
+  });
+}
+int irf_export_halo(irf_ctx* c, void** bytes, size_t* nbytes, void** offsets, size_t* nrec) {
+  if (!bytes || !nbytes || !offsets || !nrec) return IRF_EINVAL;
+  IRF_TRY(c, {
+    if (!c->counted) throw string("irf_count has not run");
+    u64 n = c->count_leftovers(nullptr, 0); c->d_left.ensure(n * 8); if (n) c->count_leftovers(c->d_left.as<u64>(), n);
+    // each trimmed record is at most 4 + 32 + 255 + 4 * 65535 bytes; typical ones are < 100
+    u64 cap = n * 320 + 1024; for (;;) {
+      c->d_halo.ensure(cap + 64); c->d_halo_off.ensure(n * 8); u64* cur = (u64*)(c->d_small.as<uint8_t>() + 128); IRF_CUDA(cudaMemsetAsync(cur, 0, 8, c->s_compute));
+      launch_halo_pack(c->d_U.as<uint8_t>(), c->d_left.as<u64>(), n, c->d_halo.as<uint8_t>(), c->d_halo_off.as<u64>(), cur, cap, c->s_compute);
+      u64 used = 0; IRF_CUDA(cudaMemcpyAsync(&used, cur, 8, cudaMemcpyDeviceToHost, c->s_compute)); c->sync();
+      if (used <= cap) { *nbytes = (size_t)used; break; } cap = used + 1024;
+    }
+    *bytes = c->d_halo.p; *offsets = c->d_halo_off.p; *nrec = (size_t)n; c->sharded = true;
+  });
+}
+int irf_import_halo(irf_ctx* c, const void* bytes, size_t nbytes, const void* offsets, size_t nrec, int owner, int n_owners) {
+  if (n_owners < 1 || owner < 0 || owner >= n_owners) return IRF_EINVAL;
+  IRF_TRY(c, {
+    if (!c->bound) throw string("irf_count has not run");
+    c->sharded = true; c->halo_leftover = 0; if (!nrec) return IRF_OK;
+    u64 slots = next_pow2(std::max<u64>(1024, 2 * nrec)); c->d_hptab.ensure(slots * 8); IRF_CUDA(cudaMemsetAsync(c->d_hptab.p, 0, slots * 8, c->s_compute));
+    launch_halo_process(c->T, (const uint8_t*)bytes, nbytes, (const u64*)offsets, nrec, c->d_hptab.as<u64>(), (u32)(slots - 1), (u32)owner, (u32)n_owners, c->s_compute);
+    u64* n_left = (u64*)(c->d_small.as<uint8_t>() + 64); IRF_CUDA(cudaMemsetAsync(n_left, 0, 8, c->s_compute));
+    launch_pair_leftover(c->d_hptab.as<u64>(), slots, n_left, nullptr, 0, c->s_compute);
+    u64 h = 0; IRF_CUDA(cudaMemcpyAsync(&h, n_left, 8, cudaMemcpyDeviceToHost, c->s_compute)); c->sync(); c->check_dev_err("halo pairing");
+    if (owner == 0) c->halo_leftover = h;   // templates whose mate is in no shard: error reads, counted once
+  });
+}
+
+}  // extern "C"

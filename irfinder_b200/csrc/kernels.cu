@@ -1,0 +1,615 @@
+// kernels.cu — sm_100a kernels of the BAM -> intron-retention counting path.
+//
+// Stage map:  S1 inflate_kernel  ->  S2 frame_guess / walk_count / frame_mark+rewalk (record
+// framing)  ->  S3 walk_process_kernel (record decode, CIGAR -> blocks, mate pairing by device hash,
+// FragmentBlocks formation and every ReadBlockProcessor's ProcessBlocks)  ->  S4 scan + intron_stats_kernel.
+// Each device function that restates a reference routine names it (upstream file per SURVEY.md §8a; the
+// mounted /root/reference has no source to cite by line).
+#include "common.cuh"
+#include "inflate_core.cuh"
+#include "kernels.h"
+
+namespace irf {
+
+static unsigned long long g_launches = 0;  // kernels launched by this library (bench.py reports it as gpu_launches)
+unsigned long long launch_counter() { return g_launches; }
+#define IRF_LAUNCHED() (++g_launches)
+
+// ------------------------------------------------------------------------------------------------
+// small device helpers
+__device__ __forceinline__ u32 ld32(const uint8_t* p) {  // unaligned little-endian load from two aligned words
+  uintptr_t a = (uintptr_t)p; u32 sh = (u32)(a & 3) * 8; const u32* w = (const u32*)(a & ~(uintptr_t)3);
+  u32 lo = w[0]; if (!sh) return lo;
+  return __funnelshift_r(lo, w[1], sh);
+}
+__device__ __forceinline__ u64 mix64(u64 x) { x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33; return x; }
+
+struct Core {  // the fields of a BAM record's fixed part that this path reads (SAM v1 §4.2)
+  int block_size, refID, pos, l_seq, next_refID, next_pos; u32 l_read_name, n_cigar_op, flag;
+};
+__device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
+  const uint8_t* p = U + off; uintptr_t a = (uintptr_t)p; u32 sh = (u32)(a & 3) * 8; const u32* w = (const u32*)(a & ~(uintptr_t)3);
+  u32 x[10];
+#pragma unroll
+  for (int i = 0; i < 10; i++) x[i] = w[i];
+  u32 f[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) f[i] = sh ? __funnelshift_r(x[i], x[i + 1], sh) : x[i];
+  c.block_size = (int)f[0]; c.refID = (int)f[1]; c.pos = (int)f[2]; c.l_read_name = f[3] & 255u; c.n_cigar_op = f[4] & 0xffffu; c.flag = f[4] >> 16;
+  c.l_seq = (int)f[5]; c.next_refID = (int)f[6]; c.next_pos = (int)f[7];
+}
+
+// ------------------------------------------------------------------------------------------------
+// S1: BGZF / DEFLATE inflate, one lane per BGZF block
+template <int WARPS, int LB, int DB>
+__global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
+                                                             uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
+                                                             int* __restrict__ status, int* __restrict__ err) {
+  extern __shared__ uint16_t smem_tables[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint16_t* lit = smem_tables + (size_t)warp * (((1 << LB) + (1 << DB)) * 32);
+  uint16_t* dst = lit + (1 << LB) * 32;
+  int b = blockIdx.x * (WARPS * 32) + threadIdx.x;
+  if (b >= nblk) return;
+  u32 n = u_len[b];
+  if (!n && c_len[b] <= 2) return;  // the 28-byte EOF marker / empty block
+  int st = inflate_block<32, LB, DB>(comp + c_off[b], c_len[b], U + u_off[b], n, lit, dst, lane);
+  if (st) { status[b] = st; atomicOr(err, DERR_INFLATE); }
+}
+
+template <int WARPS, int LB, int DB>
+static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
+  size_t smem = (size_t)WARPS * (((1 << LB) + (1 << DB)) * 32) * sizeof(uint16_t);
+  static bool attr_done = false;
+  if (!attr_done) { IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
+  int grid = (a.nblk + WARPS * 32 - 1) / (WARPS * 32);
+  if (grid > 0) { inflate_kernel<WARPS, LB, DB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err); IRF_LAUNCHED(); }
+}
+void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
+  switch (variant) {
+    case 1: launch_inflate_t<1, 9, 6>(a, s); break;
+    case 2: launch_inflate_t<2, 8, 6>(a, s); break;
+    case 3: launch_inflate_t<1, 8, 6>(a, s); break;
+    case 4: launch_inflate_t<2, 10, 6>(a, s); break;
+    case 5: launch_inflate_t<1, 10, 7>(a, s); break;
+    case 6: launch_inflate_t<4, 9, 6>(a, s); break;
+    default: launch_inflate_t<2, 9, 6>(a, s); break;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// S2: record framing.  Records straddle BGZF blocks and each starts with its own block_size, so record
+// starts form a serial chain.  We guess each block's entry (first record start at
+// or after the block's first inflated byte) from the record layout, walk all blocks in parallel, then check
+// exit[b] == entry[b+1]; with entry[0] exact this proves the whole chain by induction.  Wrong or missing
+// guesses are repaired from the predecessor's exit and re-walked until none remain.
+__device__ bool plausible_record(const uint8_t* U, u64 off, u64 Uend, int n_ref, const int32_t* ref_len, u64& next) {
+  if (off + 36 > Uend) return false;
+  Core c; load_core(U, off, c);
+  if (c.block_size < 32 || c.block_size >= (1 << 26)) return false;
+  next = off + 4 + (u64)c.block_size;
+  if (next > Uend) return false;
+  if (c.refID < -1 || c.refID >= n_ref || c.next_refID < -1 || c.next_refID >= n_ref) return false;
+  if (c.pos < -1 || c.next_pos < -1 || c.l_seq < 0 || c.l_read_name < 1) return false;
+  if (c.refID >= 0 && c.pos > ref_len[c.refID]) return false;
+  u64 need = 32ull + c.l_read_name + 4ull * c.n_cigar_op + (u64)(c.l_seq + 1) / 2 + (u64)c.l_seq;
+  if (need > (u64)c.block_size) return false;
+  const uint8_t* nm = U + off + 36;
+  if (nm[c.l_read_name - 1] != 0) return false;
+  for (u32 i = 0; i + 1 < c.l_read_name; i++) { uint8_t ch = nm[i]; if (ch < 33 || ch > 126) return false; }
+  const uint8_t* cg = nm + c.l_read_name;
+  for (u32 i = 0; i < c.n_cigar_op && i < 8; i++) if ((ld32(cg + 4 * i) & 15u) > 8u) return false;
+  return true;
+}
+
+__global__ void frame_guess_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk, u64 Uend, u64 rec0, int rec0_valid,
+                                   int n_ref, const int32_t* __restrict__ ref_len, u64* __restrict__ entry) {
+  int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (b >= nblk) return;
+  u64 o = u_off[b], e = o + u_len[b];
+  if (rec0_valid && o <= rec0) { if (lane == 0) entry[b] = rec0; return; }
+  u64 found = ~0ull;
+  for (u64 base = o; base < e; base += 32) {
+    u64 c = base + lane, nx = 0, nx2 = 0;
+    bool ok = c < e && plausible_record(U, c, Uend, n_ref, ref_len, nx);
+    if (ok && nx != Uend) ok = plausible_record(U, nx, Uend, n_ref, ref_len, nx2);
+    u32 m = __ballot_sync(0xffffffffu, ok);
+    if (m) { found = base + (u64)(__ffs(m) - 1); break; }
+  }
+  if (lane == 0) entry[b] = found;
+}
+
+// Walks the records that start inside block b; exit = first record start at or beyond the block end.
+__device__ void walk_count_block(const uint8_t* U, u64 e, u64 blk_end, u64 Uend, u64& exit_off, u32& n_rec, u32& n_cand, int& ferr) {
+  n_rec = 0; n_cand = 0; ferr = 0;
+  while (e < blk_end) {
+    if (e + 36 > Uend) { ferr = DERR_TRUNCATED; e = Uend; break; }
+    Core c; load_core(U, e, c);
+    if (c.block_size < 32 || e + 4 + (u64)c.block_size > Uend) { ferr = c.block_size < 32 ? DERR_BAD_RECORD : DERR_TRUNCATED; e = Uend; break; }
+    n_rec++;
+    if (!(c.flag & 0x4) && c.refID >= 0 && (c.flag & 0x1) && !(c.flag & 0x8) && c.next_refID == c.refID) n_cand++;
+    e += 4 + (u64)c.block_size;
+  }
+  exit_off = e;
+}
+__global__ void walk_count_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk, u64 Uend,
+                                  const u64* __restrict__ entry, u64* __restrict__ exit_off, u32* __restrict__ n_rec, u32* __restrict__ n_cand,
+                                  const uint8_t* __restrict__ mask, uint8_t* __restrict__ ferr) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nblk || (mask && !mask[b])) return;
+  u64 e = entry[b];
+  if (e == ~0ull) { exit_off[b] = ~0ull; n_rec[b] = 0; n_cand[b] = 0; ferr[b] = 0; return; }
+  u64 x; u32 nr, nc; int fe; walk_count_block(U, e, u_off[b] + u_len[b], Uend, x, nr, nc, fe);
+  exit_off[b] = x; n_rec[b] = nr; n_cand[b] = nc; ferr[b] = (uint8_t)fe;
+}
+__global__ void frame_mark_kernel(int nblk, u64* __restrict__ entry, const u64* __restrict__ exit_off, uint8_t* __restrict__ mask, u32* __restrict__ n_bad) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nblk) return;
+  uint8_t m = 0;
+  if (b >= 1) { u64 want = exit_off[b - 1]; if (want != ~0ull && entry[b] != want) { entry[b] = want; m = 1; atomicAdd(n_bad, 1u); } }
+  mask[b] = m;
+}
+__global__ void frame_totals_kernel(int nblk, const u32* __restrict__ n_rec, const u32* __restrict__ n_cand, const uint8_t* __restrict__ ferr, const u64* __restrict__ exit_off, int* __restrict__ err, u64* __restrict__ totals) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  u64 r = b < nblk ? n_rec[b] : 0, c = b < nblk ? n_cand[b] : 0;
+  if (b < nblk && ferr[b]) atomicOr(err, (int)ferr[b]);
+  if (b < nblk && exit_off[b] == ~0ull) atomicOr(err, DERR_BAD_RECORD);  // chain never reached this block
+  for (int o = 16; o; o >>= 1) { r += __shfl_down_sync(0xffffffffu, r, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+  if ((threadIdx.x & 31) == 0) { if (r) atomicAdd(&totals[0], r); if (c) atomicAdd(&totals[1], c); }
+}
+
+void launch_frame_guess(const FrameArgs& a, cudaStream_t s) {
+  long threads = (long)a.nblk * 32; int grid = (int)((threads + 255) / 256);
+  if (grid) { frame_guess_kernel<<<grid, 256, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.rec0, a.rec0_valid, a.n_ref, a.ref_len, a.entry); IRF_LAUNCHED(); }
+}
+void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s) {
+  int grid = (a.nblk + 127) / 128;
+  if (grid) { walk_count_kernel<<<grid, 128, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.entry, a.exit_off, a.n_rec, a.n_cand, mask, a.ferr); IRF_LAUNCHED(); }
+}
+void launch_frame_mark(const FrameArgs& a, uint8_t* mask, u32* n_bad, cudaStream_t s) {
+  int grid = (a.nblk + 255) / 256;
+  if (grid) { frame_mark_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, mask, n_bad); IRF_LAUNCHED(); }
+}
+void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s) {
+  int grid = (a.nblk + 255) / 256;
+  if (grid) { frame_totals_kernel<<<grid, 256, 0, s>>>(a.nblk, a.n_rec, a.n_cand, a.ferr, a.exit_off, a.err, totals); IRF_LAUNCHED(); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// S3: per-fragment processing
+__device__ __forceinline__ u32 ht_hash(u64 k) { return (u32)(mix64(k) >> 17); }
+// insert-or-find in a keys-only open-addressing table; returns the slot or 0xffffffff when full
+__device__ u32 ht_upsert(u64* keys, u32 mask, u64 key, int* err) {
+  u32 s = ht_hash(key) & mask;
+  for (u32 probe = 0; probe < 4096; probe++) {
+    u64 k = keys[s];
+    if (k == key) return s;
+    if (k == JKEY_EMPTY) { u64 old = atomicCAS(&keys[s], JKEY_EMPTY, key); if (old == JKEY_EMPTY || old == key) return s; }
+    s = (s + 1) & mask;
+  }
+  atomicOr(err, DERR_JUNC_FULL); return 0xffffffffu;
+}
+__device__ u32 ht_find(const u64* keys, u32 mask, u64 key) {
+  u32 s = ht_hash(key) & mask;
+  for (u32 probe = 0; probe < 4096; probe++) { u64 k = keys[s]; if (k == key) return s; if (k == JKEY_EMPTY) return 0xffffffffu; s = (s + 1) & mask; }
+  return 0xffffffffu;
+}
+
+// cigar2block as a streaming iterator (upstream BAM2blocks::cigar2block): M,D,=,X extend the
+// current block; N closes it and skips; I,S,H,P are ignored.  Yields exactly the (start,len) pairs the
+// reference's rStarts/rLens vectors would hold, including a zero-length first/last block around a leading/trailing N.
+struct BlockIter {
+  const uint8_t* cig; u32 n, i; int relpos, cur_start, cur_len; bool inBlock, done;
+  __device__ void init(const uint8_t* c, u32 n_) { cig = c; n = n_; i = 0; relpos = 0; cur_start = 0; cur_len = 0; inBlock = true; done = false; }
+  __device__ bool next(int& s, int& l) {
+    if (done) return false;
+    while (i < n) {
+      u32 c = ld32(cig + 4ull * i); i++; int op = (int)(c & 15u), len = (int)(c >> 4);
+      if (op == 0 || op == 2 || op == 7 || op == 8) { cur_len += len; relpos += len; inBlock = true; }
+      else if (op == 3) {
+        relpos += len;
+        if (inBlock) { s = cur_start; l = cur_len; cur_start = relpos; cur_len = 0; inBlock = false; return true; }
+        cur_start = relpos;
+      }
+    }
+    done = true; s = cur_start; l = cur_len; return true;
+  }
+};
+__device__ void cigar_scan(const uint8_t* cig, u32 n, int& genome_len, int& first_len) {
+  BlockIter it; it.init(cig, n); int s, l; bool first = true; first_len = 0;
+  while (it.next(s, l)) { if (first) { first_len = l; first = false; } }
+  genome_len = it.relpos;
+}
+
+// Receives the blocks of one FragmentBlocks value in order and applies every processor's ProcessBlocks.
+struct FragSink {
+  const DevTables& T; int chr, dir; u32 read_start; bool have_prev; u32 prev_end; int prev_len; u64 nuc;
+  u32* dump_base; u32 dump_n, dump_nb[2]; int dump_read;
+  __device__ FragSink(const DevTables& t) : T(t), nuc(0), dump_base(nullptr) {}
+  __device__ void begin_fragment(int chr_, int dir_, u32 reserve_blocks) {
+    chr = chr_; dir = dir_; dump_base = nullptr;
+    if (T.dump) {
+      u64 words = 6 + 2ull * reserve_blocks; u64 at = atomicAdd(T.dump_cursor, words);
+      if (at + words <= T.dump_cap) { dump_base = T.dump + at; dump_base[0] = (u32)words; dump_n = 6; dump_nb[0] = dump_nb[1] = 0; dump_read = -1; for (u64 w = 1; w < words; w++) dump_base[w] = 0; }
+      else atomicOr(T.err, DERR_DUMP_FULL);
+    }
+  }
+  __device__ void begin_read(u32 rs) { read_start = rs; have_prev = false; dump_read++; }
+  __device__ void end_fragment(int readCount) { if (dump_base) { dump_base[1] = (u32)chr; dump_base[2] = (u32)dir; dump_base[3] = (u32)readCount; dump_base[4] = dump_nb[0]; dump_base[5] = dump_nb[1]; } }
+
+  // JunctionCount::ProcessBlocks (upstream ReadBlockProcessor.cpp)
+  __device__ void junction(u32 left, u32 right) {
+    u64 base = T.chr_goff[chr]; u64 gl = base + left, gr = base + right; u64 gap = (u64)right - (u64)left;
+    if (right < left || gap >= (1ull << JKEY_GAP_BITS) || gr >= (1ull << 36)) { atomicOr(T.err, DERR_JKEY_RANGE); return; }
+    u32 s = ht_upsert(T.jc_keys, T.jc_mask, jkey_make(gl, gap), T.err); if (s != 0xffffffffu) atomicAdd(&T.jc_cnt[2ull * s + dir], 1u);
+    s = ht_upsert(T.jl_keys, T.jl_mask, gl, T.err); if (s != 0xffffffffu) atomicAdd(&T.jl_cnt[2ull * s + dir], 1u);
+    s = ht_upsert(T.jr_keys, T.jr_mask, gr, T.err); if (s != 0xffffffffu) atomicAdd(&T.jr_cnt[2ull * s + dir], 1u);
+  }
+  // SpansPoint::ProcessBlocks (row a8): points p with start < p < end
+  __device__ void spans(u32 start, u32 end) {
+    Range r = T.sp_range[chr]; u32 lo = r.begin, hi = r.end;
+    while (lo < hi) { u32 mid = (lo + hi) >> 1; if (T.sp_pos[mid] <= start) lo = mid + 1; else hi = mid; }  // upper_bound(start)
+    for (; lo < r.end && T.sp_pos[lo] < end; lo++) atomicAdd(&T.sp_count[(u64)dir * T.n_sp + lo], 1u);
+  }
+  // CoverageBlocks::ProcessBlocks + CoverageBlock::RecordCover (row a9): +1 at start, -1 at end, clipped per measured segment
+  __device__ void coverage(u32 start, u32 end) {
+    Range r = T.seg_range[chr]; u32 lo = r.begin, hi = r.end;
+    while (lo < hi) { u32 mid = (lo + hi) >> 1; if (T.seg_end[mid] <= start) lo = mid + 1; else hi = mid; }  // first segment with end > start
+    for (; lo < r.end; lo++) {
+      u32 ss = T.seg_start[lo]; if (ss >= end) break;
+      u32 a = max(start, ss), b = min(end, T.seg_end[lo]);
+      if (a < b) { int32_t* d = T.diff + (u64)dir * T.P + T.seg_coff[lo]; atomicAdd(d + (a - ss), 1); atomicAdd(d + (b - ss), -1); }
+    }
+  }
+  __device__ void block(int s, int l) {
+    u32 a = read_start + (u32)s, e = a + (u32)l;
+    nuc += (u32)l;
+    if (have_prev && prev_len >= JUNC_MIN_FLANK && l >= JUNC_MIN_FLANK) junction(prev_end, a);
+    have_prev = true; prev_end = e; prev_len = l;
+    if ((u32)l > SPAN_OVERHANG_LEFT + SPAN_OVERHANG_RIGHT) spans(a + SPAN_OVERHANG_LEFT, e - SPAN_OVERHANG_RIGHT);
+    if (l > 0) coverage(a, e);
+    if (dump_base && dump_n + 2 <= dump_base[0]) { dump_base[dump_n++] = a; dump_base[dump_n++] = e; dump_nb[dump_read]++; }
+  }
+  // FragmentsInChr / FragmentsInROI ::ProcessBlocks (row a13)
+  __device__ void fragment_counts(u32 fs, u32 fe) {
+    atomicAdd(&T.chr_count[(u64)dir * T.n_ref + chr], 1u);
+    Range r = T.roi_range[chr]; u32 lo = r.begin, hi = r.end;
+    while (lo < hi) { u32 mid = (lo + hi) >> 1; if (T.roi_end[mid] <= fs) lo = mid + 1; else hi = mid; }  // first ROI with end > fs
+    if (lo < r.end && T.roi_start[lo] <= fs && fe <= T.roi_end[lo]) atomicAdd(&T.roi_count[(u64)dir * T.n_roi + lo], 1u);
+  }
+};
+
+struct LocalStats { u32 single, paired, shortp, inter, longp, skipped, error; };
+
+// BAM2blocks::processSingle (row a4)
+__device__ void process_single(const DevTables& T, const uint8_t* U, u64 off, const Core& c, FragSink& sink) {
+  int dir = !(c.flag & 0x10);
+  const uint8_t* cig = U + off + 36 + c.l_read_name;
+  sink.begin_fragment(c.refID, dir, c.n_cigar_op + 1); sink.begin_read((u32)c.pos);
+  BlockIter it; it.init(cig, c.n_cigar_op); int s, l;
+  while (it.next(s, l)) sink.block(s, l);
+  sink.end_fragment(1);
+  sink.fragment_counts((u32)c.pos, (u32)(c.pos + it.relpos));
+}
+
+// BAM2blocks::processPair (row a4; merge rule [C-10]).  Record 1 is the left mate (or level, earlier in the file).
+__device__ void process_pair(const DevTables& T, const uint8_t* U, u64 off1, const Core& c1, u64 off2, const Core& c2, FragSink& sink, LocalStats& st) {
+  int dir = (c1.flag & 0x40) ? !(c1.flag & 0x10) : !(c1.flag & 0x20);
+  const uint8_t* cig1 = U + off1 + 36 + c1.l_read_name; const uint8_t* cig2 = U + off2 + 36 + c2.l_read_name;
+  int len1, len2, fb1, fb2; cigar_scan(cig1, c1.n_cigar_op, len1, fb1); cigar_scan(cig2, c2.n_cigar_op, len2, fb2);
+  int r1pos = c1.pos, r2pos = c2.pos; int readCount; int merge_at = -1;
+  if (r1pos + len1 < r2pos) { st.longp++; readCount = 2; }
+  else if (r1pos + len1 >= r2pos + len2) { st.shortp++; readCount = 1; }
+  else {
+    st.inter++; readCount = 1;
+    BlockIter it; it.init(cig1, c1.n_cigar_op); int s, l, i = 0;
+    while (it.next(s, l)) { if (r1pos + s + l >= r2pos) { if (r1pos + s <= r2pos) merge_at = i; else readCount = 2; break; } i++; }
+  }
+  sink.begin_fragment(c1.refID, dir, c1.n_cigar_op + c2.n_cigar_op + 2);
+  sink.begin_read((u32)r1pos);
+  BlockIter it; it.init(cig1, c1.n_cigar_op); int s, l, i = 0;
+  if (merge_at < 0) { while (it.next(s, l)) sink.block(s, l); }
+  else {
+    while (it.next(s, l)) { if (i == merge_at) { sink.block(s, r2pos - r1pos - s + fb2); break; } sink.block(s, l); i++; }
+    BlockIter it2; it2.init(cig2, c2.n_cigar_op); bool first = true;
+    while (it2.next(s, l)) { if (first) { first = false; continue; } sink.block(s + r2pos - r1pos, l); }
+    len1 = r2pos - r1pos + len2;
+  }
+  u32 fe = (u32)(r1pos + len1);
+  if (readCount == 2) {
+    sink.begin_read((u32)r2pos);
+    BlockIter it2; it2.init(cig2, c2.n_cigar_op);
+    while (it2.next(s, l)) sink.block(s, l);
+    if ((u32)(r2pos + len2) > fe) fe = (u32)(r2pos + len2);
+  }
+  sink.end_fragment(readCount);
+  sink.fragment_counts((u32)r1pos, fe);
+}
+
+// Mate pairing by device hash keyed on read name (+ reference and the two mate positions so multi-mapped
+// templates keep their loci apart).  One 64-bit word per waiting record: tag(24) | record offset + 1 (40).
+constexpr u64 PAIR_EMPTY = 0ull, PAIR_TOMB = ~0ull;
+__device__ u64 pair_key(const uint8_t* U, u64 off, const Core& c) {
+  u32 lo = (u32)min(c.pos, c.next_pos), hi = (u32)max(c.pos, c.next_pos);
+  u64 h = mix64(((u64)lo << 32 | hi) ^ ((u64)(u32)c.refID * 0x9E3779B97F4A7C15ull));
+  const uint8_t* nm = U + off + 36; u32 n = c.l_read_name - 1, i = 0;
+  for (; i + 4 <= n; i += 4) h = (h ^ ld32(nm + i)) * 0x100000001b3ull + 0x632be59bd9b4e019ull;
+  u32 tail = 0; for (u32 j = 0; i + j < n; j++) tail |= (u32)nm[i + j] << (8 * j);
+  return mix64(h ^ tail ^ ((u64)n << 56));
+}
+__device__ bool is_mate(const uint8_t* U, u64 off, const Core& c, u64 off2, Core& c2) {
+  load_core(U, off2, c2);
+  if (c2.refID != c.refID || c2.l_read_name != c.l_read_name || c2.pos != c.next_pos || c2.next_pos != c.pos) return false;
+  const uint8_t* a = U + off + 36; const uint8_t* b = U + off2 + 36;
+  for (u32 i = 0; i + 1 < c.l_read_name; i++) if (a[i] != b[i]) return false;
+  return true;
+}
+// Returns true and the mate's offset when this record completes a pair; otherwise the record is left waiting.
+__device__ bool pair_lookup_or_wait(const DevTables& T, u64* ptab, u32 pmask, const uint8_t* U, u64 off, const Core& c, u64& mate_off, Core& mate) {
+  u64 h = pair_key(U, off, c); u64 mine = ((h >> 40) << 40) | (off + 1); if (mine == PAIR_TOMB) mine ^= 1ull << 40;
+  u32 s = (u32)h & pmask;
+  for (u32 probe = 0; probe < (1u << 20); probe++) {
+    u64 cur = ptab[s];
+    for (;;) {
+      if (cur == PAIR_EMPTY) { u64 old = atomicCAS(&ptab[s], PAIR_EMPTY, mine); if (old == PAIR_EMPTY) return false; cur = old; continue; }
+      if (cur != PAIR_TOMB && (cur >> 40) == (mine >> 40)) {
+        u64 o2 = (cur & ((1ull << 40) - 1)) - 1;
+        if (o2 != off && is_mate(U, off, c, o2, mate)) { u64 old = atomicCAS(&ptab[s], cur, PAIR_TOMB); if (old == cur) { mate_off = o2; return true; } cur = old; continue; }
+      }
+      break;
+    }
+    s = (s + 1) & pmask;
+  }
+  atomicOr(T.err, DERR_PAIR_FULL); return false;
+}
+
+// BAM2blocks::processAll (row a2), one lane per BGZF block: every record that starts inside the block.
+__global__ void __launch_bounds__(128) walk_process_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
+                                                            u64 Uend, const u64* __restrict__ entry, u64* __restrict__ ptab, u32 pmask) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nblk) return;
+  u64 e = entry[b], blk_end = u_off[b] + u_len[b];
+  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0}; u32 nrec = 0;
+  while (e < blk_end) {
+    Core c; load_core(U, e, c); nrec++;
+    u64 next = e + 4 + (u64)c.block_size;
+    if ((c.flag & 0x4) || c.refID < 0) st.skipped++;                       // [C-6] only unmapped records are skipped
+    else if (c.refID >= T.n_ref) { atomicOr(T.err, DERR_REFID); }
+    else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) { st.single++; process_single(T, U, e, c, sink); }  // [C-7]
+    else {
+      u64 mo; Core m;
+      if (pair_lookup_or_wait(T, ptab, pmask, U, e, c, mo, m)) {
+        st.paired++;
+        bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);
+        if (first_is_me) process_pair(T, U, e, c, mo, m, sink, st); else process_pair(T, U, mo, m, e, c, sink, st);
+      }
+    }
+    e = next;
+  }
+  if (st.single) atomicAdd(&T.stats[ST_SINGLE], (u64)st.single);
+  if (st.paired) atomicAdd(&T.stats[ST_PAIRED], (u64)st.paired);
+  if (st.shortp) atomicAdd(&T.stats[ST_SHORT], (u64)st.shortp);
+  if (st.inter) atomicAdd(&T.stats[ST_INTERSECT], (u64)st.inter);
+  if (st.longp) atomicAdd(&T.stats[ST_LONG], (u64)st.longp);
+  if (st.skipped) atomicAdd(&T.stats[ST_SKIPPED], (u64)st.skipped);
+  if (sink.nuc) atomicAdd(&T.stats[ST_NUCLEOTIDES], sink.nuc);
+  if (nrec) atomicAdd(&T.stats[ST_RECORDS], (u64)nrec);
+}
+void launch_walk_process(const DevTables& T, const FrameArgs& a, u64* ptab, u32 pmask, cudaStream_t s) {
+  int grid = (a.nblk + 127) / 128;
+  if (grid) { walk_process_kernel<<<grid, 128, 0, s>>>(T, a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.entry, ptab, pmask); IRF_LAUNCHED(); }
+}
+
+// Records still waiting in the pair table never met a mate: error reads on one GPU, halo candidates when sharded.
+__global__ void pair_leftover_kernel(const u64* __restrict__ ptab, u64 nslots, u64* __restrict__ n_left, u64* __restrict__ left_off, u64 left_cap) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nslots) return;
+  u64 v = ptab[i];
+  if (v != PAIR_EMPTY && v != PAIR_TOMB) { u64 at = atomicAdd(n_left, 1ull); if (left_off && at < left_cap) left_off[at] = (v & ((1ull << 40) - 1)) - 1; }
+}
+void launch_pair_leftover(const u64* ptab, u64 nslots, u64* n_left, u64* left_off, u64 left_cap, cudaStream_t s) {
+  u64 grid = (nslots + 255) / 256; if (grid) { pair_leftover_kernel<<<(unsigned)grid, 256, 0, s>>>(ptab, nslots, n_left, left_off, left_cap); IRF_LAUNCHED(); }
+}
+
+// Copies each leftover record's fixed part + name + CIGAR into a dense halo buffer: [u32 bytes][record bytes padded to 4].
+__global__ void halo_pack_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ left_off, u64 n, uint8_t* __restrict__ out, u64* __restrict__ rec_off, u64* __restrict__ cursor, u64 cap) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+  u64 off = left_off[i]; Core c; load_core(U, off, c);
+  u32 keep = 36 + c.l_read_name + 4 * c.n_cigar_op; u32 padded = (keep + 3) & ~3u;
+  u64 at = atomicAdd(cursor, (u64)padded); rec_off[i] = at; if (at + padded > cap) return;
+  for (u32 k = 0; k < keep; k++) out[at + k] = U[off + k];
+  for (u32 k = keep; k < padded; k++) out[at + k] = 0;
+  int bs = (int)padded - 4; out[at] = (uint8_t)bs; out[at + 1] = (uint8_t)(bs >> 8); out[at + 2] = (uint8_t)(bs >> 16); out[at + 3] = (uint8_t)(bs >> 24);  // shrink block_size: seq/qual/tags dropped
+  // l_seq must stay consistent with the shortened record
+  out[at + 20] = out[at + 21] = out[at + 22] = out[at + 23] = 0;
+}
+void launch_halo_pack(const uint8_t* U, const u64* left_off, u64 n, uint8_t* out, u64* rec_off, u64* cursor, u64 cap, cudaStream_t s) {
+  u64 grid = (n + 127) / 128; if (grid) { halo_pack_kernel<<<(unsigned)grid, 128, 0, s>>>(U, left_off, n, out, rec_off, cursor, cap); IRF_LAUNCHED(); }
+}
+
+// Halo pass: the gathered leftovers of all shards form one small record stream; every rank sees the same stream and
+// processes the pairs whose key hash it owns, so each cross-shard pair is counted exactly once.
+__global__ void halo_process_kernel(DevTables T, const uint8_t* __restrict__ H, u64 Hend, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask, u32 owner, u32 nowners) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i >= nrec) return;
+  u64 e = rec_off[i]; Core c; load_core(H, e, c);
+  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
+  u64 mo; Core m;
+  if (pair_lookup_or_wait(T, ptab, pmask, H, e, c, mo, m)) {
+    if ((u32)(pair_key(H, e, c) >> 8) % nowners == owner) {
+      st.paired++;
+      bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);
+      if (first_is_me) process_pair(T, H, e, c, mo, m, sink, st); else process_pair(T, H, mo, m, e, c, sink, st);
+    }
+  }
+  if (st.paired) atomicAdd(&T.stats[ST_PAIRED], (u64)st.paired);
+  if (st.shortp) atomicAdd(&T.stats[ST_SHORT], (u64)st.shortp);
+  if (st.inter) atomicAdd(&T.stats[ST_INTERSECT], (u64)st.inter);
+  if (st.longp) atomicAdd(&T.stats[ST_LONG], (u64)st.longp);
+  if (sink.nuc) atomicAdd(&T.stats[ST_NUCLEOTIDES], sink.nuc);
+}
+void launch_halo_process(const DevTables& T, const uint8_t* H, u64 Hend, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u32 owner, u32 nowners, cudaStream_t s) {
+  u64 grid = (nrec + 127) / 128; if (grid) { halo_process_kernel<<<(unsigned)grid, 128, 0, s>>>(T, H, Hend, rec_off, nrec, ptab, pmask, owner, nowners); IRF_LAUNCHED(); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// JunctionCount table maintenance
+__global__ void ht_insert_keys_kernel(u64* keys, u32 mask, const u64* __restrict__ in, u64 n, int* err) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i < n) ht_upsert(keys, mask, in[i], err);
+}
+__global__ void ht_add_kernel(u64* keys, u32* cnt, u32 mask, const u64* __restrict__ in_keys, const u32* __restrict__ in_cnt, u64 n, int* err) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+  u32 s = ht_upsert(keys, mask, in_keys[i], err); if (s == 0xffffffffu) return;
+  if (in_cnt[2 * i]) atomicAdd(&cnt[2ull * s], in_cnt[2 * i]); if (in_cnt[2 * i + 1]) atomicAdd(&cnt[2ull * s + 1], in_cnt[2 * i + 1]);
+}
+__global__ void ht_compact_kernel(const u64* __restrict__ keys, const u32* __restrict__ cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i >= nslots) return;
+  u64 k = keys[i]; if (k == JKEY_EMPTY) return;
+  u32 a = cnt[2 * i], b = cnt[2 * i + 1]; if (only_counted && !a && !b) return;
+  u64 at = atomicAdd(cursor, 1ull); if (at < cap) { out_keys[at] = k; out_cnt[2 * at] = a; out_cnt[2 * at + 1] = b; }
+}
+void launch_ht_insert_keys(u64* keys, u32 mask, const u64* in, u64 n, int* err, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { ht_insert_keys_kernel<<<(unsigned)g, 256, 0, s>>>(keys, mask, in, n, err); IRF_LAUNCHED(); } }
+void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32* in_cnt, u64 n, int* err, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { ht_add_kernel<<<(unsigned)g, 256, 0, s>>>(keys, cnt, mask, in_keys, in_cnt, n, err); IRF_LAUNCHED(); } }
+void launch_ht_compact(const u64* keys, const u32* cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted, cudaStream_t s) {
+  u64 g = (nslots + 255) / 256; if (g) { ht_compact_kernel<<<(unsigned)g, 256, 0, s>>>(keys, cnt, nslots, out_keys, out_cnt, cursor, cap, only_counted); IRF_LAUNCHED(); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// S4a: difference counters -> per-base depth.  In-place inclusive scan over both strands at once (every
+// segment's counters sum to zero at its sentinel slot, so no segment boundaries need handling).
+constexpr int SCAN_THREADS = 256, SCAN_ITEMS = 16, SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+__global__ void __launch_bounds__(SCAN_THREADS) scan_tile_sums_kernel(const int32_t* __restrict__ d, u64 n, int32_t* __restrict__ sums) {
+  u64 base = (u64)blockIdx.x * SCAN_TILE; int acc = 0;
+  for (int k = 0; k < SCAN_ITEMS; k++) { u64 i = base + (u64)k * SCAN_THREADS + threadIdx.x; if (i < n) acc += d[i]; }
+  __shared__ int sh[SCAN_THREADS / 32];
+  for (int o = 16; o; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < SCAN_THREADS / 32; w++) t += sh[w]; sums[blockIdx.x] = t; }
+}
+__global__ void __launch_bounds__(1024) scan_sums_kernel(int32_t* sums, u64 nt) {  // exclusive scan, single CTA
+  __shared__ int sh[1024]; __shared__ int carry; if (threadIdx.x == 0) carry = 0; __syncthreads();
+  for (u64 base = 0; base < nt; base += 1024) {
+    u64 i = base + threadIdx.x; int v = i < nt ? sums[i] : 0; sh[threadIdx.x] = v; __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) { int t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0; __syncthreads(); sh[threadIdx.x] += t; __syncthreads(); }
+    int incl = sh[threadIdx.x], c = carry; if (i < nt) sums[i] = c + incl - v; __syncthreads();
+    if (threadIdx.x == 1023) carry = c + incl; __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(int32_t* __restrict__ d, u64 n, const int32_t* __restrict__ sums) {
+  // each thread owns SCAN_ITEMS consecutive elements (vector loads), warp + CTA prefix over thread totals
+  u64 base = (u64)blockIdx.x * SCAN_TILE + (u64)threadIdx.x * SCAN_ITEMS; int v[SCAN_ITEMS]; int tot = 0;
+  if (base + SCAN_ITEMS <= n) { const int4* p = (const int4*)(d + base);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS / 4; k++) { int4 q = p[k]; v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w; } }
+  else { for (int k = 0; k < SCAN_ITEMS; k++) v[k] = base + k < n ? d[base + k] : 0; }
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) { tot += v[k]; v[k] = tot; }
+  int incl = tot; const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  __shared__ int wsum[SCAN_THREADS / 32];
+  if (lane == 31) wsum[warp] = incl; __syncthreads();
+  int off = sums[blockIdx.x] + incl - tot; for (int w = 0; w < warp; w++) off += wsum[w];
+  if (base + SCAN_ITEMS <= n) { int4* p = (int4*)(d + base);
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS / 4; k++) p[k] = make_int4(v[4 * k] + off, v[4 * k + 1] + off, v[4 * k + 2] + off, v[4 * k + 3] + off); }
+  else { for (int k = 0; k < SCAN_ITEMS; k++) if (base + k < n) d[base + k] = v[k] + off; }
+}
+void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s) {
+  if (!n) return; u64 nt = (n + SCAN_TILE - 1) / SCAN_TILE;
+  { scan_tile_sums_kernel<<<(unsigned)nt, SCAN_THREADS, 0, s>>>(d, n, tile_sums); IRF_LAUNCHED(); }
+  { scan_sums_kernel<<<1, 1024, 0, s>>>(tile_sums, nt); IRF_LAUNCHED(); }
+  { scan_apply_kernel<<<(unsigned)nt, SCAN_THREADS, 0, s>>>(d, n, tile_sums); IRF_LAUNCHED(); }
+}
+u64 depth_scan_tiles(u64 n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
+
+__global__ void max_depth_kernel(const int32_t* __restrict__ depth, u64 P, u32* __restrict__ out) {
+  u32 m = 0;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < P; i += (u64)gridDim.x * blockDim.x) m = max(m, (u32)(depth[i] + depth[P + i]));
+  for (int o = 16; o; o >>= 1) m = max(m, __shfl_down_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s) { if (P) { max_depth_kernel<<<148 * 8, 256, 0, s>>>(depth, P, out); IRF_LAUNCHED(); } }
+
+// ------------------------------------------------------------------------------------------------
+// S4b: CoverageBlocks::fillHist + *FromHist + CoverageBlocksIRFinder::WriteOutput's numeric part (rows a10-a12).
+// One CTA per ref-cover.bed record.  The depth histogram lives in shared memory when the intron's maximum depth
+// fits, otherwise in the CTA's slice of a global scratch histogram.
+constexpr int IS_THREADS = 256, IS_SMEM_BINS = 8192;
+__device__ __forceinline__ u32 depth_at(const int32_t* depth, u64 P, u64 c, int sel) { return sel < 0 ? (u32)(depth[c] + depth[P + c]) : (u32)depth[(u64)sel * P + c]; }
+
+__global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, const int32_t* __restrict__ depth, const IntronDesc* __restrict__ introns, const IntronBlock* __restrict__ blocks,
+                                                                   u32 n_introns, int directionality, u32 trim_center, u32* __restrict__ scratch, u32 scratch_bins, IntronRow* __restrict__ rows) {
+  __shared__ u32 sh_hist[IS_SMEM_BINS]; __shared__ u32 sh_red[IS_THREADS / 32]; __shared__ u32 sh_max; __shared__ u64 sh_edge[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  u32* ghist = scratch + (u64)blockIdx.x * scratch_bins;
+  for (u32 it = blockIdx.x; it < n_introns; it += gridDim.x) {
+    const IntronDesc in = introns[it];
+    int sel = -1;
+    if (directionality != 0) { bool measureDir = in.plus != 0; if (directionality < 0) measureDir = !measureDir; sel = measureDir ? 1 : 0; }
+    // pass 1: maximum depth and number of positions
+    u32 mx = 0; u64 npos = 0;
+    for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { IntronBlock bl = blocks[b]; npos += bl.len; for (u32 p = tid; p < bl.len; p += IS_THREADS) mx = max(mx, depth_at(depth, T.P, bl.c0 + p, sel)); }
+    for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_down_sync(0xffffffffu, mx, o));
+    if (lane == 0) sh_red[warp] = mx; __syncthreads();
+    if (tid == 0) { u32 m = 0; for (int w = 0; w < IS_THREADS / 32; w++) m = max(m, sh_red[w]); sh_max = m; } __syncthreads();
+    mx = sh_max; const bool in_smem = mx < IS_SMEM_BINS; u32* hist = in_smem ? sh_hist : ghist;
+    if (!in_smem && mx >= scratch_bins) { if (tid == 0) atomicOr(T.err, DERR_BAD_RECORD); __syncthreads(); continue; }
+    for (u32 i = tid; i <= mx; i += IS_THREADS) hist[i] = 0;
+    __syncthreads();
+    // pass 2: histogram
+    for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { IntronBlock bl = blocks[b]; for (u32 p = tid; p < bl.len; p += IS_THREADS) atomicAdd(&hist[depth_at(depth, T.P, bl.c0 + p, sel)], 1u); }
+    // edge windows (mean depth over measured positions): warps 1 and 2
+    if (warp == 1 || warp == 2) {
+      u32 b0 = warp == 1 ? in.blk_main_end : in.blk_first_end, b1 = warp == 1 ? in.blk_first_end : in.blk_last_end; u64 tot = 0, cnt = 0;
+      for (u32 b = b0; b < b1; b++) { IntronBlock bl = blocks[b]; cnt += bl.len; for (u32 p = lane; p < bl.len; p += 32) tot += depth_at(depth, T.P, bl.c0 + p, sel); }
+      for (int o = 16; o; o >>= 1) tot += __shfl_down_sync(0xffffffffu, tot, o);
+      if (lane == 0) { sh_edge[(warp - 1) * 2] = tot; sh_edge[(warp - 1) * 2 + 1] = cnt; }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      IntronRow r; r.positions = npos; r.excluded = (long long)(in.end - in.start) - (long long)npos;
+      // coverageFromHist / percentileFromHist / trimmedMeanFromHist, one ascending walk ([C-2][C-12])
+      u64 n = npos, lo = n * (100 - trim_center) / 200, hi = n - lo, cum = 0, total = 0; double pct[3] = {0, 0, 0}; int pstate[3] = {0, 0, 0}; u32 pdepth[3] = {0, 0, 0};
+      const u32 pp[3] = {25, 50, 75};
+      for (u32 d = 0; d <= mx && n; d++) {
+        u32 h = hist[d]; if (!h) continue;
+        for (int q = 0; q < 3; q++) if (pstate[q] == 1) { pct[q] = ((double)pdepth[q] + (double)d) / 2.0; pstate[q] = 2; }
+        u64 a = max(cum, lo), b = min(cum + h, hi); if (b > a) total += (b - a) * d;
+        cum += h;
+        for (int q = 0; q < 3; q++) if (pstate[q] == 0) { if (cum * 100 > n * pp[q]) { pct[q] = d; pstate[q] = 2; } else if (cum * 100 == n * pp[q]) { pdepth[q] = d; pct[q] = d; pstate[q] = 1; } }
+      }
+      r.coverage = n ? (double)(n - hist[0]) / (double)n : 0.0;
+      r.depth = (n && hi > lo) ? (double)total / (double)(hi - lo) : 0.0;
+      r.p25 = pct[0]; r.p50 = pct[1]; r.p75 = pct[2];
+      r.first50 = sh_edge[1] ? (double)sh_edge[0] / (double)sh_edge[1] : 0.0;
+      r.last50 = sh_edge[3] ? (double)sh_edge[2] / (double)sh_edge[3] : 0.0;
+      // SpansPoint::lookup and JunctionCount::lookup{Left,Right,}
+      auto pick = [&](const u32* cnt, u64 stride2, u64 i) -> u32 { return sel < 0 ? cnt[i] + cnt[i + stride2] : cnt[i + (sel ? stride2 : 0)]; };
+      r.sp_left = in.sp_left >= 0 ? pick(T.sp_count, T.n_sp, (u64)in.sp_left) : 0; r.sp_right = in.sp_right >= 0 ? pick(T.sp_count, T.n_sp, (u64)in.sp_right) : 0;
+      r.jc_left = r.jc_right = r.jc_exact = 0;
+      if (in.refid >= 0) {
+        u64 base = T.chr_goff[in.refid];
+        auto jl = [&](const u64* keys, const u32* cnt, u32 mask, u64 key) -> u32 { u32 s = ht_find(keys, mask, key); if (s == 0xffffffffu) return 0; return sel < 0 ? cnt[2ull * s] + cnt[2ull * s + 1] : cnt[2ull * s + sel]; };
+        r.jc_left = jl(T.jl_keys, T.jl_cnt, T.jl_mask, base + in.start); r.jc_right = jl(T.jr_keys, T.jr_cnt, T.jr_mask, base + in.end);
+        if (in.end >= in.start && (u64)(in.end - in.start) < (1ull << JKEY_GAP_BITS)) r.jc_exact = jl(T.jc_keys, T.jc_cnt, T.jc_mask, jkey_make(base + in.start, in.end - in.start));
+      }
+      u32 jmax = max(r.jc_left, r.jc_right);
+      r.irratio = (r.depth == 0 && jmax == 0) ? 0.0 : r.depth / (r.depth + (double)jmax);
+      // warnings [C-14]
+      double spmax = max(r.sp_left, r.sp_right), spmin = min(r.sp_left, r.sp_right);
+      if ((double)r.jc_exact + r.depth < 10) r.warning = W_LOWCOVER;
+      else if (r.jc_exact < 4) r.warning = W_LOWSPLICING;
+      else if ((double)r.jc_exact < (double)jmax * 0.33333) r.warning = W_MINORISOFORM;
+      else if ((spmax > r.depth + 4 && spmax > r.depth * 1.5) || (spmin + 4 < r.depth && spmin * 1.5 < r.depth)) r.warning = W_NONUNIFORM;
+      else r.warning = W_NONE;
+      rows[it] = r;
+    }
+    __syncthreads();
+  }
+}
+void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
+                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s) {
+  if (n_introns) { intron_stats_kernel<<<grid, IS_THREADS, 0, s>>>(T, depth, introns, blocks, n_introns, directionality, trim_center, scratch, scratch_bins, rows); IRF_LAUNCHED(); }
+}
+
+}  // namespace irf

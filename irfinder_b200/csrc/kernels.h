@@ -1,0 +1,37 @@
+// kernels.h — host-callable launchers of kernels.cu (all asynchronous on the given stream).
+#pragma once
+#include "common.cuh"
+
+namespace irf {
+
+struct InflateArgs {
+  const uint8_t* comp; const u64* c_off; const u32* c_len;   // compressed bytes, per-block CDATA offset / length
+  uint8_t* U; const u64* u_off; const u32* u_len;            // inflated bytes, per-block offset / ISIZE
+  int nblk; int* status; int* err;
+};
+struct FrameArgs {
+  const uint8_t* U; const u64* u_off; const u32* u_len; int nblk; u64 Uend; u64 rec0; int rec0_valid;  // rec0: inflated offset of the first record when known exactly
+  int n_ref; const int32_t* ref_len;
+  u64* entry; u64* exit_off; u32* n_rec; u32* n_cand; uint8_t* ferr; int* err;  // ferr: per-block framing error of the latest walk
+};
+
+void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
+void launch_frame_guess(const FrameArgs& a, cudaStream_t s);
+void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s);
+void launch_frame_mark(const FrameArgs& a, uint8_t* mask, u32* n_bad, cudaStream_t s);
+void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s);
+void launch_walk_process(const DevTables& T, const FrameArgs& a, u64* ptab, u32 pmask, cudaStream_t s);
+void launch_pair_leftover(const u64* ptab, u64 nslots, u64* n_left, u64* left_off, u64 left_cap, cudaStream_t s);
+void launch_halo_pack(const uint8_t* U, const u64* left_off, u64 n, uint8_t* out, u64* rec_off, u64* cursor, u64 cap, cudaStream_t s);
+unsigned long long launch_counter();
+void launch_halo_process(const DevTables& T, const uint8_t* H, u64 Hend, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u32 owner, u32 nowners, cudaStream_t s);
+void launch_ht_insert_keys(u64* keys, u32 mask, const u64* in, u64 n, int* err, cudaStream_t s);
+void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32* in_cnt, u64 n, int* err, cudaStream_t s);
+void launch_ht_compact(const u64* keys, const u32* cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted, cudaStream_t s);
+void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s);
+u64 depth_scan_tiles(u64 n);
+void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s);
+void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
+                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s);
+
+}  // namespace irf

@@ -1,0 +1,181 @@
+// refs.cpp — loadRef parsers and WriteOutput formatters (host side of the reference's processors).
+#include "refs.h"
+
+#include <algorithm>
+#include <charconv>
+#include <cstring>
+#include <sstream>
+#include <thread>
+
+namespace irf {
+
+static std::vector<std::string> split_tabs(const std::string& line) {
+  std::vector<std::string> f; size_t p = 0;
+  for (;;) { size_t q = line.find('\t', p); if (q == std::string::npos) { f.push_back(line.substr(p)); break; } f.push_back(line.substr(p, q - p)); p = q + 1; }
+  if (!f.empty() && !f.back().empty() && f.back().back() == '\r') f.back().pop_back();
+  return f;
+}
+
+// SpansPoint::loadRef — "chr pos strand"; the strand column is not used at lookup time [C-9]
+void SpansPointRef::loadRef(std::istream& in) {
+  std::map<std::string, std::vector<u32>> by_chr; std::string line;
+  while (std::getline(in, line)) { if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 2) continue; by_chr[f[0]].push_back((u32)std::stoul(f[1])); }
+  pos.clear(); chr_range.clear();
+  for (auto& c : by_chr) { std::sort(c.second.begin(), c.second.end()); Range r; r.begin = (u32)pos.size(); pos.insert(pos.end(), c.second.begin(), c.second.end()); r.end = (u32)pos.size(); chr_range[c.first] = r; }
+}
+int SpansPointRef::lookup_index(const std::string& chr, u32 p) const {
+  auto c = chr_range.find(chr); if (c == chr_range.end()) return -1;
+  auto b = pos.begin() + c->second.begin, e = pos.begin() + c->second.end; auto it = std::lower_bound(b, e, p);
+  return (it == e || *it != p) ? -1 : (int)(it - pos.begin());
+}
+
+// JunctionCount::loadRef — "chr start end strand"
+void JunctionRef::loadRef(std::istream& in) {
+  std::string line;
+  while (std::getline(in, line)) {
+    if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) continue;
+    u32& bits = chr_junc[f[0]][std::make_pair((u32)std::stoul(f[1]), (u32)std::stoul(f[2]))];
+    if (f[3] == "-") bits |= 1; else if (f[3] == "+") bits |= 2;
+  }
+}
+
+// FragmentsInROI::loadRef — "chr start end name", kept sorted by end
+void RoiRef::loadRef(std::istream& in) {
+  std::map<std::string, std::vector<Roi>> by_chr; std::string line;
+  while (std::getline(in, line)) { if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) continue; by_chr[f[0]].push_back(Roi{(u32)std::stoul(f[1]), (u32)std::stoul(f[2]), f[3]}); }
+  rois.clear(); chr_range.clear(); present = true;
+  for (auto& c : by_chr) {
+    std::stable_sort(c.second.begin(), c.second.end(), [](const Roi& a, const Roi& b) { return a.end < b.end; });
+    Range r; r.begin = (u32)rois.size(); rois.insert(rois.end(), c.second.begin(), c.second.end()); r.end = (u32)rois.size(); chr_range[c.first] = r;
+  }
+}
+
+// CoverageBlocks::loadRef — BED12; measured segments are the union of every record's blocks
+void CoverageRef::loadRef(std::istream& in) {
+  std::map<std::string, std::vector<std::pair<u32, u32>>> raw; std::string line;
+  BEDrecords.clear();
+  while (std::getline(in, line)) {
+    if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 12) continue;
+    BEDrecord r; r.chrName = f[0]; r.start = (u32)std::stoul(f[1]); r.end = (u32)std::stoul(f[2]); r.name = f[3]; r.direction = (f[5] == "+");
+    std::istringstream ls(f[10]), os(f[11]); std::string a, b;
+    while (std::getline(ls, a, ',') && std::getline(os, b, ',')) {
+      if (a.empty() || b.empty()) break; u32 len = (u32)std::stoul(a), off = (u32)std::stoul(b);
+      r.blocks.push_back({r.start + off, r.start + off + len}); raw[r.chrName].push_back(r.blocks.back());
+    }
+    BEDrecords.push_back(std::move(r));
+  }
+  seg_start.clear(); seg_end.clear(); seg_coff.clear(); chr_range.clear(); P = 0;
+  for (auto& c : raw) {
+    std::sort(c.second.begin(), c.second.end()); Range rg; rg.begin = (u32)seg_start.size();
+    u32 cs = 0, ce = 0; bool open = false;
+    auto close = [&]() { seg_start.push_back(cs); seg_end.push_back(ce); seg_coff.push_back(P); P += (u64)(ce - cs) + 1; };
+    for (auto& b : c.second) { if (b.first >= b.second) continue; if (open && b.first <= ce) ce = std::max(ce, b.second); else { if (open) close(); cs = b.first; ce = b.second; open = true; } }
+    if (open) close();
+    rg.end = (u32)seg_start.size(); chr_range[c.first] = rg;
+  }
+}
+void CoverageRef::pieces(const std::string& chr, u32 s, u32 e, std::vector<IntronBlock>& out) const {
+  auto c = chr_range.find(chr); if (c == chr_range.end() || s >= e) return;
+  u32 lo = c->second.begin, hi = c->second.end;
+  u32 i = (u32)(std::upper_bound(seg_end.begin() + lo, seg_end.begin() + hi, s) - seg_end.begin());  // first segment with end > s
+  for (; i < hi && seg_start[i] < e; i++) { u32 a = std::max(s, seg_start[i]), b = std::min(e, seg_end[i]); if (a < b) out.push_back(IntronBlock{seg_coff[i] + (a - seg_start[i]), b - a, 0}); }
+}
+
+// ---------------------------------------------------------------------------------------------
+// formatting: std::ostream << (default precision 6) == printf("%g") == to_chars(general, 6)
+static inline void put_u(std::string& s, unsigned long long v) { char b[24]; auto r = std::to_chars(b, b + sizeof b, v); s.append(b, r.ptr); }
+static inline void put_i(std::string& s, long long v) { char b[24]; auto r = std::to_chars(b, b + sizeof b, v); s.append(b, r.ptr); }
+static inline void put_g(std::string& s, double v) { char b[40]; auto r = std::to_chars(b, b + sizeof b, v, std::chars_format::general, 6); s.append(b, r.ptr); }
+
+static const char* HDR_IR = "Chr\tStart\tEnd\tName\tNull\tStrand\tExcludedBases\tCoverage\tIntronDepth\tIntronDepth25Percentile\tIntronDepth50Percentile\tIntronDepth75Percentile\tExonToIntronReadsLeft\tExonToIntronReadsRight\tIntronDepthFirst50bp\tIntronDepthLast50bp\tSpliceLeft\tSpliceRight\tSpliceExact\tIRratio\tWarnings\n";
+static const char* WARN[5] = {"-", "LowCover", "LowSplicing", "MinorIsoform", "NonUniformIntronCover"};
+
+static void format_ir_rows(const CoverageRef& cov, const std::vector<IntronRow>& rows, size_t a, size_t b, std::string& s) {
+  for (size_t i = a; i < b; i++) {
+    const auto& rec = cov.BEDrecords[i]; const IntronRow& r = rows[i];
+    s += rec.chrName; s += '\t'; put_u(s, rec.start); s += '\t'; put_u(s, rec.end); s += '\t'; s += rec.name; s += "\t0\t"; s += rec.direction ? '+' : '-'; s += '\t';
+    put_i(s, r.excluded); s += '\t'; put_g(s, r.coverage); s += '\t'; put_g(s, r.depth); s += '\t'; put_g(s, r.p25); s += '\t'; put_g(s, r.p50); s += '\t'; put_g(s, r.p75); s += '\t';
+    put_u(s, r.sp_left); s += '\t'; put_u(s, r.sp_right); s += '\t'; put_g(s, r.first50); s += '\t'; put_g(s, r.last50); s += '\t';
+    put_u(s, r.jc_left); s += '\t'; put_u(s, r.jc_right); s += '\t'; put_u(s, r.jc_exact); s += '\t';
+    if (r.depth == 0 && std::max(r.jc_left, r.jc_right) == 0) s += '0'; else put_g(s, r.irratio);
+    s += '\t'; s += WARN[r.warning]; s += '\n';
+  }
+}
+std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>& rows) {
+  size_t n = cov.BEDrecords.size(); unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+  if (n < 20000) nt = 1;
+  std::vector<std::string> parts(nt); std::vector<std::thread> th;
+  for (unsigned t = 0; t < nt; t++) { size_t a = n * t / nt, b = n * (t + 1) / nt; parts[t].reserve((b - a) * 160);
+    if (nt == 1) format_ir_rows(cov, rows, a, b, parts[t]); else th.emplace_back([&, a, b, t]() { format_ir_rows(cov, rows, a, b, parts[t]); }); }
+  for (auto& t : th) t.join();
+  std::string out = HDR_IR; size_t tot = out.size(); for (auto& p : parts) tot += p.size(); out.reserve(tot); for (auto& p : parts) out += p;
+  return out;
+}
+
+struct JRow { u32 start, end, bits, c0, c1; };
+// per-chromosome rows in (start,end) order: annotated junctions (possibly uncounted) merged with counted ones
+static std::map<std::string, std::vector<JRow>> merged_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
+  std::map<std::string, std::vector<JRow>> out;
+  for (auto& c : ref.chr_junc) { auto& v = out[c.first]; v.reserve(c.second.size()); for (auto& j : c.second) v.push_back(JRow{j.first.first, j.first.second, j.second, 0, 0}); }
+  std::map<std::string, std::vector<JRow>> extra;
+  for (auto& e : counted) { if (e.refid < 0 || e.refid >= (int)chr_names.size()) continue; extra[chr_names[e.refid]].push_back(JRow{e.start, e.end, 0, e.cnt[0], e.cnt[1]}); }
+  for (auto& x : extra) {
+    auto& v = x.second; std::sort(v.begin(), v.end(), [](const JRow& a, const JRow& b) { return a.start != b.start ? a.start < b.start : a.end < b.end; });
+    auto& base = out[x.first]; std::vector<JRow> m; m.reserve(base.size() + v.size()); size_t i = 0, j = 0;
+    while (i < base.size() || j < v.size()) {
+      bool takeA = j >= v.size() || (i < base.size() && (base[i].start < v[j].start || (base[i].start == v[j].start && base[i].end <= v[j].end)));
+      if (takeA) { JRow r = base[i++]; if (j < v.size() && v[j].start == r.start && v[j].end == r.end) { r.c0 += v[j].c0; r.c1 += v[j].c1; j++; } m.push_back(r); }
+      else { if (!m.empty() && m.back().start == v[j].start && m.back().end == v[j].end) { m.back().c0 += v[j].c0; m.back().c1 += v[j].c1; } else m.push_back(v[j]); j++; }
+    }
+    base.swap(m);
+  }
+  return out;
+}
+std::string format_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
+  auto m = merged_junctions(ref, chr_names, counted); std::string s = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";
+  for (auto& c : m) for (auto& r : c.second) {
+    s += c.first; s += '\t'; put_u(s, r.start); s += '\t'; put_u(s, r.end); s += '\t'; s += r.bits == 1 ? '-' : r.bits == 2 ? '+' : '.'; s += '\t';
+    put_u(s, (unsigned long long)r.c0 + r.c1); s += '\t'; put_u(s, r.c1); s += '\t'; put_u(s, r.c0); s += '\n';
+  }
+  return s;
+}
+int directional(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted, std::string& log) {
+  auto m = merged_junctions(ref, chr_names, counted);
+  unsigned long long same = 0, diff = 0, ev = 0, nev = 0, evk = 0, nevk = 0;
+  for (auto& c : m) for (auto& r : c.second) {  // thresholds [C-11]
+    if (r.c0 + r.c1 > 8) {
+      if (r.c0 > r.c1 * 4) { ev++; if (r.bits) evk++; if (r.bits == 1) same++; else if (r.bits == 2) diff++; }
+      else if (r.c1 > r.c0 * 4) { ev++; if (r.bits) evk++; if (r.bits == 2) same++; else if (r.bits == 1) diff++; }
+      else { nev++; if (r.bits) nevk++; }
+    }
+  }
+  auto line = [&](const char* k, unsigned long long v) { log += k; put_u(log, v); log += '\n'; };
+  line("Directionality: Dir evidence:\t", ev); line("Directionality: Nondir evidence:\t", nev);
+  line("Directionality: Dir evidence known junctions:\t", evk); line("Directionality: Nondir evidence known junctions:\t", nevk);
+  line("Directionality: Dir matches ref:\t", same); line("Directionality: Dir opposed to ref:\t", diff);
+  line("Directionality: Dir score all (0-10000):\t", ev * 10000 / (ev + nev + 1)); line("Directionality: Dir score known junctions (0-10000):\t", evk * 10000 / (evk + nevk + 1));
+  if (same > diff * 100 && evk > nevk * 100) return 1;
+  if (diff > same * 100 && evk > nevk * 100) return -1;
+  return 0;
+}
+std::string format_spans(const SpansPointRef& ref, const std::vector<u32>& count) {
+  std::string s = "SP_seqname\tcoord\ttotal\tpos\tneg\n"; size_t n = ref.pos.size();
+  for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) {
+    u32 neg = count[i], pos = count[n + i]; s += c.first; s += '\t'; put_u(s, ref.pos[i]); s += '\t'; put_u(s, (unsigned long long)neg + pos); s += '\t'; put_u(s, pos); s += '\t'; put_u(s, neg); s += '\n'; }
+  return s;
+}
+std::string format_roi(const RoiRef& ref, const std::vector<u32>& count) {
+  std::string s = "ROI_Name\ttotal\tpos\tneg\n"; size_t n = ref.rois.size();
+  for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) {
+    u32 neg = count[i], pos = count[n + i]; s += ref.rois[i].name; s += '\t'; put_u(s, (unsigned long long)neg + pos); s += '\t'; put_u(s, pos); s += '\t'; put_u(s, neg); s += '\n'; }
+  return s;
+}
+std::string format_chr(const std::vector<std::string>& chr_names, const std::vector<u32>& count) {
+  std::map<std::string, std::pair<unsigned long long, unsigned long long>> m; size_t n = chr_names.size();
+  for (size_t i = 0; i < n; i++) { auto& e = m[chr_names[i]]; e.first += count[i]; e.second += count[n + i]; }
+  std::string s = "ChrCoverage_RName\ttotal\tpos\tneg\n";
+  for (auto& c : m) { s += c.first; s += '\t'; put_u(s, c.second.first + c.second.second); s += '\t'; put_u(s, c.second.second); s += '\t'; put_u(s, c.second.first); s += '\n'; }
+  return s;
+}
+
+}  // namespace irf

@@ -1,0 +1,35 @@
+// Host-side emulation harness (TEST ONLY): runs irfinder_b200/csrc/inflate_core.cuh — the exact routine the
+// GPU lanes execute — on the CPU over every BGZF block of a file and compares each block with zlib.
+// usage: inflate_emu <file.bam> [LIT_BITS variant: 8|9|10]
+#include <zlib.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include "../../irfinder_b200/csrc/inflate_core.cuh"
+
+template <int LB, int DB>
+static int run(const std::vector<uint8_t>& f) {
+  std::vector<uint16_t> lit(1 << LB), dist(1 << (DB < 7 ? 7 : DB));
+  size_t off = 0; long nblk = 0, bad = 0; std::vector<uint8_t> a(65536 + 16), b(65536 + 16);
+  while (off + 18 <= f.size()) {
+    const uint8_t* h = &f[off];
+    if (h[0] != 31 || h[1] != 139 || h[12] != 'B' || h[13] != 'C') { fprintf(stderr, "bad BGZF header at %zu\n", off); return 2; }
+    uint32_t bsize = (h[16] | h[17] << 8) + 1u, clen = bsize - 26, isize; memcpy(&isize, &f[off + bsize - 4], 4);
+    std::fill(a.begin(), a.end(), 0xAA);
+    int st = irf::inflate_block<1, LB, DB>(&f[off + 18], clen, a.data() + (nblk & 3), isize, lit.data(), dist.data(), 0);  // vary output alignment
+    z_stream zs; memset(&zs, 0, sizeof zs); inflateInit2(&zs, -15); zs.next_in = (Bytef*)&f[off + 18]; zs.avail_in = clen; zs.next_out = b.data(); zs.avail_out = 65536;
+    int zr = inflate(&zs, Z_FINISH); inflateEnd(&zs);
+    if (st != 0 || zr != Z_STREAM_END || zs.total_out != isize || memcmp(a.data() + (nblk & 3), b.data(), isize) != 0 || a[(nblk & 3) + isize] != 0xAA) {
+      if (bad < 5) fprintf(stderr, "block %ld at %zu: status %d zlib %d isize %u\n", nblk, off, st, zr, isize); bad++; }
+    off += bsize; nblk++;
+  }
+  printf("blocks %ld bad %ld\n", nblk, bad); return bad ? 1 : 0;
+}
+int main(int argc, char** argv) {
+  FILE* fp = fopen(argv[1], "rb"); if (!fp) return 2; std::vector<uint8_t> f; uint8_t buf[1 << 16]; size_t n;
+  while ((n = fread(buf, 1, sizeof buf, fp)) > 0) f.insert(f.end(), buf, buf + n); fclose(fp); f.resize(f.size() + 16);
+  f.resize(f.size() - 16);
+  int v = argc > 2 ? atoi(argv[2]) : 9;
+  if (v == 8) return run<8, 6>(f); if (v == 10) return run<10, 7>(f); if (v == 7) return run<7, 5>(f); return run<9, 6>(f);
+}

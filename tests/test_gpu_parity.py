@@ -1,0 +1,192 @@
+"""GPU parity: the CUDA path through the C ABI vs the CPU restatement (oracle/) on the same seeded inputs.
+
+Integer tables must be bit-exact and the text tables byte-identical (the floating columns are printed with
+6 significant digits, so byte identity is stricter than BASELINE.json's 1e-6 relative tolerance).
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, assert_same_outputs, run_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _core(**opt):
+    from irfinder_b200 import IRFinderCore
+    return IRFinderCore(0, **opt)
+
+
+def _gen(tmp, name, **kw):
+    from irfinder_b200 import synth
+    return synth.generate(os.path.join(str(tmp), name), **kw)
+
+
+def _gpu_run(meta, outdir, bam=None, roi=True, **opt):
+    c = _core(**opt)
+    c.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"] if roi else None)
+    c.run_bam(bam or meta["sorted"])
+    c.write_outputs(outdir)
+    return c
+
+
+def _stats_from_stdout(text):
+    return {l.split("\t")[0]: l.split("\t")[1] for l in text.strip().split("\n") if "\t" in l}
+
+
+@pytest.fixture(scope="module")
+def tiny(built, tmp_path_factory):
+    tmp = tmp_path_factory.mktemp("tiny")
+    meta = _gen(tmp, "w", genome="tiny", introns=300, pairs=30000, readlen=100, seed=11, chunks=7)
+    meta["oracle_out"] = os.path.join(str(tmp), "oracle")
+    meta["oracle_stdout"] = run_oracle(built, meta, meta["oracle_out"], dump=os.path.join(str(tmp), "frags.txt"))
+    meta["oracle_frags"] = os.path.join(str(tmp), "frags.txt")
+    return meta
+
+
+def test_sorted_bam_matches_oracle(tiny, tmp_path):
+    c = _gpu_run(tiny, str(tmp_path / "gpu"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "gpu"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+
+
+def test_collated_bam_matches_oracle(tiny, tmp_path):
+    c = _gpu_run(tiny, str(tmp_path / "gpu"), bam=tiny["collated"])
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "gpu"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+
+
+def test_fragment_blocks_stream(tiny, tmp_path):
+    """FragmentBlocks values, element for element (order-free): chr, direction, readCount and every block."""
+    c = _core(dump_fragments=1)
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    c.run_bam(tiny["sorted"])
+    w = c.table("fragments")
+    got, i = [], 0
+    while i < len(w):
+        n, chr_, d, rc, n0, n1 = (int(x) for x in w[i:i + 6])
+        blocks = w[i + 6:i + 6 + 2 * (n0 + n1)].reshape(-1, 2)
+        reads = [blocks[:n0], blocks[n0:n0 + n1]][:rc]
+        got.append("%d\t%d\t%d\t%s" % (chr_, d, rc, "\t".join(",".join("%d-%d" % (a, b) for a, b in r) for r in reads)))
+        i += n
+    with open(tiny["oracle_frags"]) as f:
+        want = [l.rstrip("\n") for l in f]
+    assert sorted(got) == sorted(want)
+
+
+def test_integer_tables_bit_exact(tiny, built, tmp_path):
+    c = _core()
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    c.run_bam(tiny["sorted"])
+    st = c.stats()
+    o = _stats_from_stdout(tiny["oracle_stdout"])
+    assert st["pairs"] == int(o["Total pairs processed"]) and st["singles"] == int(o["Total singles processed"])
+    assert st["nucleotides"] == int(o["Total nucleotides"]) and st["skipped"] == int(o["Skipped reads"]) and st["error"] == int(o["Error reads"])
+    # junction table against the oracle's JuncCount file (counted rows)
+    j = c.table("junctions")
+    want = {}
+    with open(os.path.join(tiny["oracle_out"], "IRFinder-JuncCount.txt")) as f:
+        next(f)
+        for l in f:
+            ch, s, e, _, tot, pos, neg = l.rstrip("\n").split("\t")
+            if int(tot):
+                want[(ch, int(s), int(e))] = (int(neg), int(pos))
+    names = ["chrA", "chrB", "chrEmpty"]
+    got = {(names[r["refid"]], int(r["start"]), int(r["end"])): (int(r["neg"]), int(r["pos"])) for r in j}
+    assert got == want
+    # depth: sentinel slot of every measured segment is zero and depth is never negative
+    d = c.table("depth")
+    assert d.min() >= 0
+
+
+def test_stranded_library_writes_dir_table(built, tmp_path):
+    meta = _gen(tmp_path, "s", genome="tiny", introns=300, pairs=40000, readlen=100, seed=12, stranded=-1, chunks=5)
+    out = run_oracle(built, meta, str(tmp_path / "o"))
+    assert "Directionality:\t-1" in out
+    c = _gpu_run(meta, str(tmp_path / "g"))
+    assert c.directionality == -1 and os.path.exists(str(tmp_path / "g" / "IRFinder-IR-dir.txt"))
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+    meta2 = _gen(tmp_path, "s2", genome="tiny", introns=300, pairs=40000, readlen=100, seed=13, stranded=1, chunks=5)
+    out2 = run_oracle(built, meta2, str(tmp_path / "o2"))
+    assert "Directionality:\t1" in out2
+    _gpu_run(meta2, str(tmp_path / "g2"))
+    assert_same_outputs(str(tmp_path / "o2"), str(tmp_path / "g2"))
+
+
+def test_single_end_dense_introns(built, tmp_path):
+    meta = _gen(tmp_path, "se", genome="tiny", introns=200, pairs=60000, readlen=75, seed=14, single=True, intronic=0.4, hot_introns=50, chunks=3)
+    run_oracle(built, meta, str(tmp_path / "o"))
+    _gpu_run(meta, str(tmp_path / "g"))
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+
+
+def test_trim_band_option_and_no_roi(built, tiny, tmp_path):
+    run_oracle(built, tiny, str(tmp_path / "o"), env={"IRF_TRIM_CENTER": "60"}, roi=False)
+    _gpu_run(tiny, str(tmp_path / "g"), roi=False, trim_center=60)
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+    assert not os.path.exists(str(tmp_path / "g" / "IRFinder-ROI.txt"))
+
+
+def test_record_aligned_blocks_and_inflated_stream(built, tmp_path):
+    meta = _gen(tmp_path, "al", genome="tiny", introns=150, pairs=8000, readlen=100, seed=15, align_records=True, chunks=2)
+    run_oracle(built, meta, str(tmp_path / "o"))
+    _gpu_run(meta, str(tmp_path / "g"))
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+    # reference-style stdin mode: `gzip -cd < bam | irfinder ... /dev/stdin`
+    import gzip
+    raw = str(tmp_path / "inflated.bam")
+    with gzip.open(meta["sorted"], "rb") as f, open(raw, "wb") as o:
+        o.write(f.read())
+    c = _core()
+    c.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])
+    fd = os.open(raw, os.O_RDONLY)
+    try:
+        c.run_stream(fd, True)
+    finally:
+        os.close(fd)
+    c.write_outputs(str(tmp_path / "g2"))
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g2"))
+
+
+def test_cli_shim_matches_reference_invocation(built, tiny, tmp_path):
+    exe = os.path.join(ROOT, "bin", "irfinder")
+    out = str(tmp_path / "cli")
+    os.makedirs(out)
+    r = subprocess.run([exe, out, tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"], tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 0, r.stderr
+    assert_same_outputs(tiny["oracle_out"], out)
+    assert _stats_from_stdout(r.stdout) == _stats_from_stdout(tiny["oracle_stdout"])
+    bad = subprocess.run([exe, out], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert bad.returncode != 0
+
+
+def test_repeated_runs_are_idempotent(tiny, tmp_path):
+    c = _core()
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    c.run_bam(tiny["sorted"])
+    a = c.table("rows_nondir").tobytes(), c.table("spans").tobytes(), c.table("junctions").tobytes()
+    c.run_bam(tiny["collated"])
+    b = c.table("rows_nondir").tobytes(), c.table("spans").tobytes(), c.table("junctions").tobytes()
+    assert a == b
+
+
+def test_bad_inputs_fail_loudly(tiny, tmp_path):
+    from irfinder_b200 import IRFError
+    data = open(tiny["sorted"], "rb").read()
+    c = _core()
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    with pytest.raises(IRFError):   # cut mid-block
+        c.run_bytes(data[: len(data) // 2])
+    with pytest.raises(IRFError):   # EOF marker missing
+        c.run_bytes(data[:-28])
+    corrupt = bytearray(data)
+    for k in range(40000, 40064):
+        corrupt[k] ^= 0x5A           # damage DEFLATE payload
+    with pytest.raises(IRFError):
+        c.run_bytes(bytes(corrupt))
+    with pytest.raises(IRFError):
+        c.run_bytes(b"this is not a BAM file at all, not even gzip")
+    c.run_bytes(data)               # the context stays usable afterwards
+    assert c.stats()["pairs"] > 0
