@@ -1,0 +1,311 @@
+#!/usr/bin/env python
+"""bench.py — BAM -> IR table throughput of the B200 path (BASELINE.json metric) and the CPU reference arm.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--pairs P]
+
+A "step" is one complete pass of the hot path over the workload: BGZF inflate, record framing, mate
+pairing, every ProcessBlocks, depth scan and per-intron statistics.
+  value : million read pairs / s with the compressed BAM already resident in HBM (irf_reset + irf_count + irf_finalize)
+  e2e   : the same through the reference-facing call with HOST buffers: irf_run_buffer (pinned host BGZF bytes ->
+          device in the timed region) + irf_write_outputs (result tables device -> host, six text tables formatted)
+  roofline : dominant kernel = inflate_kernel; algorithmic bytes = compressed in + inflated out
+  cpu_baseline : the CPU restatement in oracle/ (the mounted reference has no source) on one host core,
+          bounded sample of the same workload
+Workload: BASELINE.json configs[1] (50M pairs 2x150, GRCh38-shaped, ~200k introns); inputs (10 GB) exceed L2.
+"""
+import argparse
+import json
+import os
+import shutil
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "M read pairs/sec BAM->IR table"
+UNIT = "M read pairs/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--pairs", type=int, default=50_000_000, help="read pairs per GPU (configs[1] = 50M)")
+    ap.add_argument("--introns", type=int, default=200_000)
+    ap.add_argument("--genome", default="grch38")
+    ap.add_argument("--readlen", type=int, default=150)
+    ap.add_argument("--workdir", default=os.environ.get("IRF_BENCH_DIR", "/tmp/irf_bench"))
+    ap.add_argument("--cpu-sample-pairs", type=int, default=1_000_000)
+    ap.add_argument("--inflate-variant", type=int, default=-1)
+    return ap.parse_args()
+
+
+def workload_name(a, total_pairs):
+    return f"configs[1]-shaped: {total_pairs / 1e6:g}M pairs 2x{a.readlen} unstranded, coordinate-sorted BGZF BAM (zlib level 1), synthetic {a.genome} genome, {a.introns} target introns"
+
+
+def gen_cached(outdir, **kw):
+    """Generates a workload once per (directory, parameters); both arms and repeated runs on one box share it."""
+    from irfinder_b200 import synth
+    key = json.dumps(kw, sort_keys=True)
+    kp = os.path.join(outdir, "key.json")
+    if os.path.exists(kp) and open(kp).read() == key and os.path.exists(os.path.join(outdir, "meta.json")):
+        return synth.describe(outdir)
+    shutil.rmtree(outdir, ignore_errors=True)
+    meta = synth.generate(outdir, **kw)
+    with open(kp, "w") as f:
+        f.write(key)
+    return meta
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.p = [], None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def oracle_run(oracle, meta, bam, outdir):
+    os.makedirs(outdir, exist_ok=True)
+    t = time.perf_counter()
+    r = subprocess.run([oracle, outdir, meta["cover"], meta["sj"], meta["rc"], meta["roi"], bam], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True)
+    dt = time.perf_counter() - t
+    if r.returncode != 0:
+        raise RuntimeError("oracle failed: " + r.stderr[-500:])
+    return dt
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def run_reference(a):
+    """CPU arm: the reference's own implementation is absent from /root/reference (README.md only), so this times the
+    in-repo CPU restatement (oracle/irfinder_cpu, kind "port"), one single-threaded process per host core, each on its
+    own region-shaped shard of the same workload, gzip inflate included (as the reference's `gzip -cd |` pipe is)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from irfinder_b200 import build
+    oracle = build.build_oracle()
+    build.build_tools()
+    cores = os.cpu_count() or 1
+    shard_pairs = max(100_000, min(2_000_000, a.pairs // max(cores, 1)))
+    wd = os.path.join(a.workdir, "ref_arm")
+    metas = []
+    t0 = time.perf_counter()
+    for s in range(cores):  # one independent BAM (own seed) per host core
+        m = gen_cached(os.path.join(wd, f"s{s}"), genome=a.genome, introns=a.introns, pairs=shard_pairs, readlen=a.readlen, seed=2 + s, sorted_bam=False, chunks=16)
+        metas.append(m)
+    gen_s = time.perf_counter() - t0
+    pairs_total = sum(m["pairs"] + m["singles"] for m in metas)
+
+    def one_step():
+        res = [None] * cores
+
+        def work(i):
+            res[i] = oracle_run(oracle, metas[i], metas[i]["collated"], os.path.join(wd, f"out{i}"))
+        th = [threading.Thread(target=work, args=(i,)) for i in range(cores)]
+        t = time.perf_counter()
+        [x.start() for x in th]
+        [x.join() for x in th]
+        return time.perf_counter() - t
+    for _ in range(a.warmup):
+        one_step()
+    times = [one_step() for _ in range(a.steps)]
+    dt = sum(times)
+    value = pairs_total * a.steps / dt / 1e6
+    sample = f"{cores} processes x {shard_pairs / 1e6:g}M-pair shards of the workload per step (collated BAM, gzip inflate + reference load included)"
+    line = {"metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(dt / a.steps * 1e3, 2),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32/u32 counts + f64 ratios", "data": "synthetic", "impl": "reference",
+            "config": {"workload": workload_name(a, a.pairs * a.gpus), "sampled": sample, "generation_s": round(gen_s, 1)},
+            "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def run_b200(a):
+    import numpy as np
+    import torch
+    from irfinder_b200 import IRFinderCore, build
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    total_pairs = a.pairs * world
+    wd = os.path.join(a.workdir, f"w{world}")
+    t0 = time.perf_counter()
+    if rank == 0:
+        build.build_tools()
+        meta = gen_cached(wd, genome=a.genome, introns=a.introns, pairs=total_pairs, readlen=a.readlen, seed=2, collated=False, chunks=max(256, 64 * world))
+    if world > 1:
+        dist.barrier()
+    if rank != 0:
+        meta = gen_cached(wd, genome=a.genome, introns=a.introns, pairs=total_pairs, readlen=a.readlen, seed=2, collated=False, chunks=max(256, 64 * world))
+    gen_s = time.perf_counter() - t0
+    n_units = meta["pairs"] + meta["singles"]   # fragments (pairs; a few orphans count as one unit each)
+    fsize = os.path.getsize(meta["sorted"])
+    host = torch.empty(fsize + 64, dtype=torch.uint8, pin_memory=True)   # pinned host copy of the BGZF bytes
+    hv = host.numpy()
+    with open(meta["sorted"], "rb") as f:
+        f.readinto(memoryview(hv)[:fsize])
+    opts = {} if a.inflate_variant < 0 else {"inflate_variant": a.inflate_variant}
+    core = IRFinderCore(local, **opts)
+    t1 = time.perf_counter()
+    core.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])
+    ref_s = time.perf_counter() - t1
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    # ---------------- value: inputs resident in HBM
+    inflate_ms, launches, inflate_launches, stage_t = [], 0, 0, {}
+    if world == 1:
+        core.stage(hv.ctypes.data, fsize)
+
+        def step():
+            core.reset(); core.count(); core.finalize()
+    else:
+        from irfinder_b200.distributed import run_sharded
+
+        def step():   # sharded steps re-stage their byte range: the copy is part of the multi-GPU step
+            run_sharded(core, hv[:fsize], rank, world, device=torch.device("cuda", local))
+    for _ in range(a.warmup):
+        step()
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    t = time.perf_counter()
+    for _ in range(a.steps):
+        step()
+        tm = core.timing()
+        inflate_ms.append(tm["inflate_kernel_ms"]); launches += int(tm["launches"]); inflate_launches += int(tm["inflate_launches"]); stage_t = tm
+    barrier()
+    dt = time.perf_counter() - t
+    if world > 1:
+        v = torch.tensor([dt], dtype=torch.float64, device="cuda"); dist.all_reduce(v, op=dist.ReduceOp.MAX); dt = float(v.item())
+    value = n_units * a.steps / dt / 1e6
+    stats = core.stats()
+
+    # ---------------- e2e: host buffer in, six text tables out
+    outdir = os.path.join("/dev/shm" if os.path.isdir("/dev/shm") else wd, f"irf_bench_out_{rank}")
+    if world == 1:
+        def e2e_step():
+            core.run_buffer(hv.ctypes.data, fsize); core.write_outputs(outdir)
+    else:
+        def e2e_step():
+            run_sharded(core, hv[:fsize], rank, world, device=torch.device("cuda", local))
+            if rank == 0:
+                core.write_outputs(outdir)
+    for _ in range(min(a.warmup, 2)):
+        e2e_step()
+    barrier()
+    t = time.perf_counter()
+    for _ in range(a.steps):
+        e2e_step()
+    barrier()
+    dte = time.perf_counter() - t
+    if world > 1:
+        v = torch.tensor([dte], dtype=torch.float64, device="cuda"); dist.all_reduce(v, op=dist.ReduceOp.MAX); dte = float(v.item())
+    e2e_value = n_units * a.steps / dte / 1e6
+    clocks = sampler.stop() if sampler else None
+    d2h = sum(core.table(x).nbytes for x in ("rows_nondir", "rows_dir", "spans", "roi", "chr", "junctions", "stats"))
+    out_bytes = sum(os.path.getsize(os.path.join(outdir, f)) for f in os.listdir(outdir)) if (rank == 0 and os.path.isdir(outdir)) else 0
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier(); dist.destroy_process_group()
+        return
+    # ---------------- roofline of the dominant kernel (inflate): algorithmic bytes = compressed in + inflated out
+    peak, peak_src = measured_peak()
+    share = (fsize / world if world > 1 else fsize)
+    alg_bytes = (meta["compressed_bytes"] + meta["inflated_bytes"]) / world
+    avg_inflate_ms = sum(inflate_ms) / max(len(inflate_ms), 1)
+    achieved = alg_bytes / (avg_inflate_ms * 1e-3) / 1e9 if avg_inflate_ms > 0 else 0.0
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "inflate_traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("dram_bytes_per_algorithmic_byte")
+            traffic = None if traffic is None else traffic * alg_bytes / max(inflate_launches / a.steps, 1)
+        except Exception:
+            traffic = None
+    # ---------------- CPU baseline on a bounded sample (rank 0, N = 1 only)
+    cpu = None
+    if world == 1:
+        try:
+            oracle = build.build_oracle()
+            sm = gen_cached(os.path.join(a.workdir, "cpu_sample"), genome=a.genome, introns=a.introns, pairs=a.cpu_sample_pairs, readlen=a.readlen, seed=2, sorted_bam=False, chunks=16)
+            sec = oracle_run(oracle, sm, sm["collated"], os.path.join(a.workdir, "cpu_sample", "out"))
+            cpu = {"value": round((sm["pairs"] + sm["singles"]) / sec / 1e6, 4), "unit": UNIT, "cores": 1, "kind": "port",
+                   "sample": f"{a.cpu_sample_pairs / 1e6:g}M-pair collated BAM of the same workload shape, one process, gzip inflate + reference load included ({sec:.1f} s)"}
+        except Exception as e:  # the baseline is reporting only; never let it kill the bench line
+            cpu = {"value": None, "unit": UNIT, "cores": 1, "kind": "port", "sample": f"failed: {e}"}
+    line = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(dt / a.steps * 1e3, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 bytes -> int32/u32 counts, f64 ratios", "data": "synthetic",
+            "config": {"workload": workload_name(a, total_pairs), "fragments": n_units, "records": meta["records"], "compressed_bytes": meta["compressed_bytes"],
+                       "inflated_bytes": meta["inflated_bytes"], "l2": "inputs larger than L2 (no flush needed)", "sharding": "one BGZF byte range per rank" if world > 1 else "single GPU",
+                       "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
+            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(fsize), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes)},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": "inflate_kernel", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic,
+                         "peak_source": peak_src, "algorithmic_bytes_per_step": int(alg_bytes), "launches_per_step": inflate_launches / max(a.steps, 1), "avg_ms_per_step": round(avg_inflate_ms, 3)},
+            "cpu_baseline": cpu, "clocks": clocks}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier(); dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

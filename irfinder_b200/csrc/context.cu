@@ -57,7 +57,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3];
   // staged input
-  DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab;
+  DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -279,7 +279,7 @@ struct irf_ctx {
     int nb = (int)blks.size();
     FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), nb, Uend, rec0, staged_has_header ? 1 : 0, T.n_ref, T.ref_len,
                  d_entry.as<u64>(), d_exit.as<u64>(), d_nrec.as<u32>(), d_ncand.as<u32>(), d_ferr.as<uint8_t>(), T.err};
-    if (!staged_has_header && entry0_override >= 0) { fa.rec0 = (u64)entry0_override; fa.rec0_valid = 1; }
+    if (!staged_has_header && entry0_override >= 0) { fa.rec0 = (u64)entry0_override; fa.rec0_valid = 1; entry0_override = -1; }
     launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
     u32* n_bad = d_small.as<u32>(); int rounds = 0;
     for (;;) {
@@ -300,7 +300,10 @@ struct irf_ctx {
     if (nblk_own == nb && nb > 0 && fe[1] != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
     IRF_CUDA(cudaEventRecord(e2, s_compute));
     pslots = next_pow2(std::max<u64>(1024, n_cand + n_cand / 2)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
-    launch_walk_process(T, own, d_ptab.as<u64>(), (u32)(pslots - 1), s_compute);
+    d_rec_base.ensure((size_t)nblk_own * 8); d_rec_off.ensure(n_rec * 8);
+    launch_scan_counts(d_nrec.as<u32>(), d_rec_base.as<u64>(), nblk_own, s_compute);
+    launch_walk_list(own, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
+    launch_process_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), s_compute);
     IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaGetLastError());
     check_dev_err("fragment counting");
     float a, b, c; IRF_CUDA(cudaEventElapsedTime(&a, e0, e1)); IRF_CUDA(cudaEventElapsedTime(&b, e1, e2)); IRF_CUDA(cudaEventElapsedTime(&c, e2, e3));
@@ -426,7 +429,7 @@ void irf_destroy(irf_ctx* c) {
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
-                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
+                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2]};
   for (auto b : all) b->release();
   if (c->pinned) cudaFreeHost(c->pinned);
@@ -558,7 +561,7 @@ int irf_import_halo(irf_ctx* c, const void* bytes, size_t nbytes, const void* of
     u64* n_left = (u64*)(c->d_small.as<uint8_t>() + 64); IRF_CUDA(cudaMemsetAsync(n_left, 0, 8, c->s_compute));
     launch_pair_leftover(c->d_hptab.as<u64>(), slots, n_left, nullptr, 0, c->s_compute);
     u64 h = 0; IRF_CUDA(cudaMemcpyAsync(&h, n_left, 8, cudaMemcpyDeviceToHost, c->s_compute)); c->sync(); c->check_dev_err("halo pairing");
-    if (owner == 0) c->halo_leftover = h;   // templates whose mate is in no shard: error reads, counted once
+    c->halo_leftover = h;   // templates whose mate is in no shard: error reads (every rank sees the same gathered set, so the same number)
   });
 }
 

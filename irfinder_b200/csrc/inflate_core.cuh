@@ -11,8 +11,8 @@
 //    interleaved by lane (word index * LANES + lane) so a warp's 32 random lookups never bank-conflict.
 //    Codes longer than the LUT width (rare) fall back to a canonical bit-serial walk over the
 //    code-length histogram, held in per-lane local memory.
-//  * Output bytes go through a 4-byte accumulator so literal runs leave as aligned 32-bit stores;
-//    LZ77 copies load up to 8 source bytes before storing any, so their latencies overlap.
+//  * Literals go through a 4-byte accumulator so literal runs leave as aligned 32-bit stores; LZ77 copies
+//    load up to 8 source bytes before storing any, so their latencies overlap.
 //
 // The routine is __host__ __device__ so tests/emu can run the very same code on the CPU against
 // zlib; the shipped library only ever instantiates it inside kernels.
@@ -49,20 +49,21 @@ struct LaneTable {
 };
 
 struct BitReader {
-  const uint32_t* wp;
+  const uint32_t* wp;    // next word to load into `ahead`
   const uint32_t* wend;  // first word that lies wholly beyond the input
   uint64_t bb;
+  uint32_t ahead;        // word loaded one refill early, so the load latency overlaps decoding
   int bc;
   IRF_HD void init(const uint8_t* p, uint32_t len) {
     uintptr_t a = (uintptr_t)p; int mis = (int)(a & 3);
     wp = (const uint32_t*)(a - mis); wend = (const uint32_t*)((a + len + 3) & ~(uintptr_t)3);
-    bb = (uint64_t)(*wp++) >> (8 * mis); bc = 32 - 8 * mis;
+    bb = (uint64_t)(*wp++) >> (8 * mis); bc = 32 - 8 * mis; ahead = *wp++;
   }
-  IRF_HD void refill() { if (bc <= 32) { bb |= (uint64_t)(*wp++) << bc; bc += 32; } }  // afterwards bc >= 33
+  IRF_HD void refill() { if (bc <= 32) { bb |= (uint64_t)ahead << bc; bc += 32; ahead = *wp++; } }  // afterwards bc >= 33
   IRF_HD uint32_t peek(int n) const { return (uint32_t)bb & ((1u << n) - 1u); }
   IRF_HD void drop(int n) { bb >>= n; bc -= n; }
   IRF_HD uint32_t take(int n) { uint32_t v = peek(n); drop(n); return v; }
-  IRF_HD bool overrun() const { return wp > wend + 2; }  // two words of look-ahead are legitimate
+  IRF_HD bool overrun() const { return wp > wend + 3; }  // three words of look-ahead are legitimate
 };
 
 // Output cursor with a 4-byte accumulator.
@@ -86,29 +87,32 @@ struct OutCursor {
   }
 };
 
-// Per-lane Huffman set: LUT in LaneTable + canonical fallback arrays in local memory.
+// Per-lane Huffman set: a BITS-wide LUT plus, for the rare longer codes, the canonical-code limits.
+// aux[l] (l = 1..15) = upper bound of the length-l codes, left-justified to 15 bits; aux[16 + l] = index of the
+// first length-l symbol in `symbol` minus the first length-l code.  `symbol` (ordered by length, value) stays in
+// per-lane local memory: it is touched once per long code.
 template <int LANES, int BITS, int MAXSYM>
 struct Huff {
   LaneTable<LANES> lut;          // entry = sym << 4 | len (len 1..BITS); 0 => long code or invalid
-  uint16_t count[16];            // codes per length
-  uint16_t symbol[MAXSYM];       // symbols ordered by (length, value)
-  bool has_long;
+  LaneTable<LANES> aux;          // 32 entries per lane
+  uint16_t* symbol;              // MAXSYM entries in the lane's local memory (kept outside this struct so its scalars stay in registers)
 
   // lens[0..n): code lengths.  Returns false on an over-subscribed set, or an incomplete one
   // (allowed only for a single-code set, as in zlib).
   IRF_HD bool build(const uint8_t* lens, int n) {
+    uint16_t count[16];
     for (int i = 0; i < 16; i++) count[i] = 0;
     for (int i = 0; i < n; i++) count[lens[i]]++;
     for (uint32_t i = 0; i < (1u << BITS); i++) lut.set(i, 0);
-    if (count[0] == n) { has_long = false; return true; }  // no codes: any use is an error later
+    for (int i = 0; i < 32; i++) aux.set(i, 0);
+    if (count[0] == n) return true;  // no codes: any use is an error later
     int left = 1;
     for (int l = 1; l < 16; l++) { left <<= 1; left -= count[l]; if (left < 0) return false; }
     if (left > 0 && (n - count[0]) != 1) return false;
-    uint16_t offs[16]; offs[1] = 0;
+    uint16_t offs[16], next_code[16]; offs[1] = 0;
     for (int l = 1; l < 15; l++) offs[l + 1] = offs[l] + count[l];
-    uint16_t next_code[16];
-    { uint32_t code = 0; for (int l = 1; l < 16; l++) { code = (code + (l > 1 ? count[l - 1] : 0)) << 1; next_code[l] = (uint16_t)code; } }
-    has_long = false;
+    { uint32_t code = 0; for (int l = 1; l < 16; l++) { code = (code + (l > 1 ? count[l - 1] : 0)) << 1; next_code[l] = (uint16_t)code;
+        aux.set(l, (uint16_t)((code + count[l]) << (15 - l) > 0xffffu ? 0xffffu : (code + count[l]) << (15 - l))); aux.set(16 + l, (uint16_t)(offs[l] - code)); } }
     for (int s = 0; s < n; s++) {
       int l = lens[s]; if (!l) continue;
       symbol[offs[l]++] = (uint16_t)s;
@@ -117,140 +121,193 @@ struct Huff {
         uint32_t rev = 0; for (int b = 0; b < l; b++) rev |= ((code >> b) & 1u) << (l - 1 - b);
         uint16_t e = (uint16_t)(s << 4 | l);
         for (uint32_t i = rev; i < (1u << BITS); i += (1u << l)) lut.set(i, e);
-      } else has_long = true;
+      }
     }
     return true;
   }
-  // canonical bit-serial decode (used when the LUT entry is empty); returns -1 on an invalid code
+  // codes longer than BITS bits; returns -1 on an invalid code
   IRF_HD int slow(BitReader& br) const {
-    int code = 0, first = 0, index = 0;
-    for (int l = 1; l < 16; l++) {
-      code |= (int)((br.bb >> (l - 1)) & 1u);
-      int c = count[l];
-      if (code - c < first) { br.drop(l); return symbol[index + (code - first)]; }
-      index += c; first += c; first <<= 1; code <<= 1;
-    }
-    return -1;
+    uint32_t x = (uint32_t)br.bb & 0x7fffu, code15 = 0;
+    for (int b = 0; b < 15; b++) code15 |= ((x >> b) & 1u) << (14 - b);
+    return slow15(br, code15);
+  }
+  IRF_HD int slow15(BitReader& br, uint32_t code15) const {
+    uint32_t lim[16];
+#pragma unroll
+    for (int l = BITS + 1; l < 16; l++) lim[l] = aux.get(l);
+    int len = 0;
+#pragma unroll
+    for (int l = 15; l > BITS; l--) if (code15 < lim[l]) len = l;
+    if (!len) return -1;
+    uint32_t idx = (uint32_t)(uint16_t)((code15 >> (15 - len)) + aux.get(16 + len));
+    if (idx >= (uint32_t)MAXSYM) return -1;
+    br.drop(len);
+    return symbol[idx];
   }
   IRF_HD int decode(BitReader& br) const {
     uint16_t e = lut.get(br.peek(BITS));
     int l = e & 15;
     if (l) { br.drop(l); return e >> 4; }
+#ifdef __CUDA_ARCH__
+    return slow15(br, __brev((uint32_t)br.bb) >> 17);
+#else
     return slow(br);
+#endif
   }
 };
 
-// Decodes one raw DEFLATE stream of `clen` bytes at `cdata` into exactly `isize` bytes at `out`.
-// Both buffers need 8 readable bytes of slack after their ends (the caller pads its allocations).
+// One lane's decoder as a state machine.  A GPU warp advances all 32 lanes one step() at a time under a
+// warp-wide vote, so the lanes re-converge every iteration instead of drifting into 32 serialised
+// instruction streams (the first version of this kernel did exactly that and ran ~50x slower).
+// Per step a lane decodes one symbol and/or copies up to 8 bytes of a pending LZ77 match; block headers
+// (Huffman table builds) are a third, rarer state.
+enum LaneState : int { LS_HEADER = 0, LS_SYMBOL = 1, LS_COPY = 2, LS_FINISH = 3, LS_DONE = 4 };
+
 template <int LANES, int LIT_BITS, int DIST_BITS>
-IRF_HD int inflate_block(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize,
-                         uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane) {
-  BitReader br; br.init(cdata, clen);
-  OutCursor oc; oc.init(out, isize);
-  Huff<LANES, LIT_BITS, 288> hl; hl.lut.base = lit_lut_base; hl.lut.lane = lane;
-  Huff<LANES, DIST_BITS, 32> hd; hd.lut.base = dist_lut_base; hd.lut.lane = lane;
-  uint8_t lens[320];
-  int bfinal;
-  do {
+struct InflateLane {
+  BitReader br; OutCursor oc;
+  Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32> hd;
+  int state, status, bfinal; uint32_t copy_len, copy_dist, isize;
+
+  // sym_store: 320 uint16 of lane-private scratch (288 literal/length symbols + 32 distance symbols)
+  IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize_, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store) {
+    hl.symbol = sym_store; hd.symbol = sym_store + 288;
+    br.init(cdata, clen); oc.init(out, isize_); isize = isize_;
+    hl.lut.base = lit_lut_base; hl.lut.lane = lane; hd.lut.base = dist_lut_base; hd.lut.lane = lane;
+    // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][lit aux (32)][dist aux (32)], all lane-interleaved
+    hd.aux.base = dist_lut_base + (size_t)(1u << DIST_BITS) * LANES; hd.aux.lane = lane; hl.aux.base = hd.aux.base + 32 * LANES; hl.aux.lane = lane;
+    state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = copy_dist = 0;
+  }
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; }
+  IRF_HD bool done() const { return state == LS_DONE; }
+  IRF_HD void fail(int code) { status = code; state = LS_DONE; }
+
+  IRF_HD void header() {
+    uint8_t lens[320];
     br.refill();
     bfinal = (int)br.take(1); int btype = (int)br.take(2);
-    if (btype == 0) {
+    if (btype == 0) {  // stored block: rare in BAM, copied here in one go
       br.drop(br.bc & 7); br.refill();
       uint32_t len = br.take(16); br.refill(); uint32_t nlen = br.take(16);
-      if ((len ^ nlen) != 0xffffu) return INF_ERR_STORED;
-      if (oc.op + len > oc.cap) return INF_ERR_OVERRUN_OUT;
-      for (uint32_t i = 0; i < len; i++) { br.refill(); oc.emit(br.take(8)); if (br.overrun()) return INF_ERR_OVERRUN_IN; }
-      continue;
+      if ((len ^ nlen) != 0xffffu) return fail(INF_ERR_STORED);
+      if (oc.op + len > oc.cap) return fail(INF_ERR_OVERRUN_OUT);
+      for (uint32_t i = 0; i < len; i++) { br.refill(); oc.emit(br.take(8)); if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); }
+      state = bfinal ? LS_FINISH : LS_HEADER; return;
     }
-    if (btype == 3) return INF_ERR_BTYPE;
+    if (btype == 3) return fail(INF_ERR_BTYPE);
     if (btype == 1) {
       int i = 0;
       for (; i < 144; i++) lens[i] = 8; for (; i < 256; i++) lens[i] = 9; for (; i < 280; i++) lens[i] = 7; for (; i < 288; i++) lens[i] = 8;
-      if (!hl.build(lens, 288)) return INF_ERR_CODELEN;
+      if (!hl.build(lens, 288)) return fail(INF_ERR_CODELEN);
       for (i = 0; i < 32; i++) lens[i] = 5;  // 30 and 31 complete the code but never occur
-      if (!hd.build(lens, 32)) return INF_ERR_CODELEN;
+      if (!hd.build(lens, 32)) return fail(INF_ERR_CODELEN);
     } else {
       br.refill();
       int hlit = (int)br.take(5) + 257, hdist = (int)br.take(5) + 1, hclen = (int)br.take(4) + 4;
-      if (hlit > 286 || hdist > 30) return INF_ERR_CODELEN;
+      if (hlit > 286 || hdist > 30) return fail(INF_ERR_CODELEN);
       const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
       for (int i = 0; i < 19; i++) lens[i] = 0;
       for (int i = 0; i < hclen; i++) { br.refill(); lens[order[i]] = (uint8_t)br.take(3); }
-      // the code-length code (<= 7 bits) borrows the distance LUT when it is wide enough, else decodes bit-serially
-      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.lut.base = dist_lut_base; hc.lut.lane = lane;
-      if (!hc.build(lens, 19)) return INF_ERR_CODELEN;
+      // the code-length code (<= 7 bits) borrows the distance LUT region
+      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.lut.lane = hd.lut.lane; hc.aux.base = hd.aux.base; hc.aux.lane = hd.aux.lane;
+      if (!hc.build(lens, 19)) return fail(INF_ERR_CODELEN);
       int idx = 0;
       while (idx < hlit + hdist) {
         br.refill();
         int sym = hc.decode(br);
-        if (sym < 0) return INF_ERR_CODELEN;
+        if (sym < 0) return fail(INF_ERR_CODELEN);
         if (sym < 16) lens[idx++] = (uint8_t)sym;
         else {
           int rep, val = 0;
-          if (sym == 16) { if (idx == 0) return INF_ERR_CODELEN; val = lens[idx - 1]; rep = 3 + (int)br.take(2); }
+          if (sym == 16) { if (idx == 0) return fail(INF_ERR_CODELEN); val = lens[idx - 1]; rep = 3 + (int)br.take(2); }
           else if (sym == 17) rep = 3 + (int)br.take(3);
           else rep = 11 + (int)br.take(7);
-          if (idx + rep > hlit + hdist) return INF_ERR_CODELEN;
+          if (idx + rep > hlit + hdist) return fail(INF_ERR_CODELEN);
           while (rep--) lens[idx++] = (uint8_t)val;
         }
-        if (br.overrun()) return INF_ERR_OVERRUN_IN;
+        if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
       }
-      if (lens[256] == 0) return INF_ERR_CODELEN;
-      if (!hl.build(lens, hlit)) return INF_ERR_CODELEN;
-      if (!hd.build(lens + hlit, hdist)) return INF_ERR_CODELEN;
+      if (lens[256] == 0) return fail(INF_ERR_CODELEN);
+      if (!hl.build(lens, hlit)) return fail(INF_ERR_CODELEN);
+      if (!hd.build(lens + hlit, hdist)) return fail(INF_ERR_CODELEN);
     }
-    // ---- symbol loop
-    for (;;) {
-      br.refill();
-      int sym = hl.decode(br);
-      if (sym < 256) {
-        if (sym < 0) return INF_ERR_SYMBOL;
-        if (oc.op >= oc.cap) return INF_ERR_OVERRUN_OUT;
-        oc.emit((uint32_t)sym);
-        continue;
-      }
-      if (sym == 256) break;
-      if (sym > 285) return INF_ERR_SYMBOL;
-      uint32_t len;
-      if (sym < 265) len = (uint32_t)sym - 254u;
-      else if (sym == 285) len = 258;
-      else { int xb = (sym - 261) >> 2; len = ((4u + ((uint32_t)(sym - 261) & 3u)) << xb) + 3u + br.take(xb); }
-      br.refill();
-      int ds = hd.decode(br);
-      if (ds < 0 || ds > 29) return INF_ERR_SYMBOL;
-      uint32_t dist;
-      if (ds < 4) dist = (uint32_t)ds + 1u;
-      else { int xb = (ds >> 1) - 1; dist = ((2u + ((uint32_t)ds & 1u)) << xb) + 1u + br.take(xb); }
-      if (dist > oc.op) return INF_ERR_DIST;
-      if (oc.op + len > oc.cap) return INF_ERR_OVERRUN_OUT;
-      if (br.overrun()) return INF_ERR_OVERRUN_IN;
-      // ---- LZ77 copy
-      if (dist >= 8) {
-        while (len) {
-          oc.flush_bytes();
-          const uint8_t* src = oc.out + oc.op - dist;
-          uint32_t k = len < 8 ? len : 8;
-          uint8_t t[8];
+    state = LS_SYMBOL;
+  }
+
+  IRF_HD void symbol() {
+    br.refill();  // >= 33 bits: enough for three LUT-resolved literals, or one length code + extra bits
+    uint16_t e = 0; int l = 0, nlit = 0;
 #pragma unroll
-          for (int j = 0; j < 8; j++) t[j] = (uint32_t)j < k ? src[j] : (uint8_t)0;
-#pragma unroll
-          for (int j = 0; j < 8; j++) if ((uint32_t)j < k) oc.emit(t[j]);
-          len -= k;
-        }
-      } else {
-        oc.flush_bytes();
-        const uint8_t* src = oc.out + oc.op - dist;
-        uint64_t pat = 0;
-#pragma unroll
-        for (int j = 0; j < 7; j++) if ((uint32_t)j < dist) pat |= (uint64_t)src[j] << (8 * j);
-        uint32_t ph = 0;
-        for (uint32_t i = 0; i < len; i++) { oc.emit((uint32_t)(pat >> (8 * ph)) & 255u); ph++; if (ph == dist) ph = 0; }
-      }
+    for (int r = 0; r < 3; r++) {
+      e = hl.lut.get(br.peek(LIT_BITS)); l = e & 15;
+      if (l && (e >> 4) < 256 && oc.op < oc.cap) { br.drop(l); oc.emit((uint32_t)(e >> 4)); nlit++; } else break;
     }
-    if (br.overrun()) return INF_ERR_OVERRUN_IN;
-  } while (!bfinal);
-  oc.flush_bytes();
-  return oc.op == isize ? INF_OK : INF_ERR_ISIZE;
+    if (nlit) return;
+    int sym;
+    if (l) { br.drop(l); sym = e >> 4; }
+    else {
+#ifdef __CUDA_ARCH__
+      sym = hl.slow15(br, __brev((uint32_t)br.bb) >> 17);
+#else
+      sym = hl.slow(br);
+#endif
+    }
+    if (sym < 256) {
+      if (sym < 0) return fail(INF_ERR_SYMBOL);
+      if (oc.op >= oc.cap) return fail(INF_ERR_OVERRUN_OUT);
+      oc.emit((uint32_t)sym);
+      return;
+    }
+    if (sym == 256) { if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); state = bfinal ? LS_FINISH : LS_HEADER; return; }
+    if (sym > 285) return fail(INF_ERR_SYMBOL);
+    uint32_t len;
+    if (sym < 265) len = (uint32_t)sym - 254u;
+    else if (sym == 285) len = 258;
+    else { int xb = (sym - 261) >> 2; len = ((4u + ((uint32_t)(sym - 261) & 3u)) << xb) + 3u + br.take(xb); }
+    br.refill();
+    int ds = hd.decode(br);
+    if (ds < 0 || ds > 29) return fail(INF_ERR_SYMBOL);
+    uint32_t dist;
+    if (ds < 4) dist = (uint32_t)ds + 1u;
+    else { int xb = (ds >> 1) - 1; dist = ((2u + ((uint32_t)ds & 1u)) << xb) + 1u + br.take(xb); }
+    if (dist > oc.op) return fail(INF_ERR_DIST);
+    if (oc.op + len > oc.cap) return fail(INF_ERR_OVERRUN_OUT);
+    if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
+    copy_len = len; copy_dist = dist; state = LS_COPY;
+  }
+
+  // up to 8 bytes of the pending match; sources are read before anything is stored.  For dist < 8 the
+  // source index wraps inside the period so overlapping (run-length) matches need no reload.
+  IRF_HD void copy_chunk() {
+    oc.flush_bytes();
+    uint8_t* dst = oc.out + oc.op; const uint8_t* src = dst - copy_dist;
+    uint32_t k = copy_len < 8 ? copy_len : 8;
+    uint8_t t[8]; uint32_t w = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) { t[j] = (uint32_t)j < k ? src[w] : (uint8_t)0; w++; if (w == copy_dist) w = 0; }
+#pragma unroll
+    for (int j = 0; j < 8; j++) if ((uint32_t)j < k) dst[j] = t[j];
+    oc.op += k; copy_len -= k;
+    if (!copy_len) state = LS_SYMBOL;
+  }
+
+  IRF_HD void step() {
+    if (state == LS_HEADER) header();
+    if (state == LS_SYMBOL) symbol();
+    if (state == LS_COPY) copy_chunk();
+    if (state == LS_FINISH) { oc.flush_bytes(); status = oc.op == isize ? INF_OK : INF_ERR_ISIZE; state = LS_DONE; }
+  }
+};
+
+// Decodes one raw DEFLATE stream of `clen` bytes at `cdata` into exactly `isize` bytes at `out` (scalar driver,
+// used by the host emulation in tests/emu).  Both buffers need 8 readable bytes of slack after their ends.
+template <int LANES, int LIT_BITS, int DIST_BITS>
+IRF_HD int inflate_block(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize,
+                         uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane) {
+  InflateLane<LANES, LIT_BITS, DIST_BITS> L; uint16_t sym_store[320];
+  L.start(cdata, clen, out, isize, lit_lut_base, dist_lut_base, lane, sym_store);
+  while (!L.done()) L.step();
+  return L.status;
 }
 
 }  // namespace irf

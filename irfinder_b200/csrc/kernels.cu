@@ -47,33 +47,37 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
                                                              int* __restrict__ status, int* __restrict__ err) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint16_t* lit = smem_tables + (size_t)warp * (((1 << LB) + (1 << DB)) * 32);
+  uint16_t* lit = smem_tables + (size_t)warp * (((1 << LB) + (1 << DB) + 64) * 32);  // [lit LUT][dist LUT][2 x 32 canonical-limit entries], lane-interleaved
   uint16_t* dst = lit + (1 << LB) * 32;
   int b = blockIdx.x * (WARPS * 32) + threadIdx.x;
-  if (b >= nblk) return;
-  u32 n = u_len[b];
-  if (!n && c_len[b] <= 2) return;  // the 28-byte EOF marker / empty block
-  int st = inflate_block<32, LB, DB>(comp + c_off[b], c_len[b], U + u_off[b], n, lit, dst, lane);
-  if (st) { status[b] = st; atomicOr(err, DERR_INFLATE); }
+  InflateLane<32, LB, DB> L; uint16_t sym_store[320];
+  bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
+  if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
+  // all 32 lanes vote every iteration: this is what keeps the warp converged (see InflateLane)
+  while (__any_sync(0xffffffffu, !L.done())) L.step();
+  if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
 }
 
 template <int WARPS, int LB, int DB>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
-  size_t smem = (size_t)WARPS * (((1 << LB) + (1 << DB)) * 32) * sizeof(uint16_t);
+  size_t smem = (size_t)WARPS * (((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
   static bool attr_done = false;
   if (!attr_done) { IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
   int grid = (a.nblk + WARPS * 32 - 1) / (WARPS * 32);
   if (grid > 0) { inflate_kernel<WARPS, LB, DB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err); IRF_LAUNCHED(); }
 }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
-  switch (variant) {
-    case 1: launch_inflate_t<1, 9, 6>(a, s); break;
-    case 2: launch_inflate_t<2, 8, 6>(a, s); break;
-    case 3: launch_inflate_t<1, 8, 6>(a, s); break;
-    case 4: launch_inflate_t<2, 10, 6>(a, s); break;
-    case 5: launch_inflate_t<1, 10, 7>(a, s); break;
-    case 6: launch_inflate_t<4, 9, 6>(a, s); break;
-    default: launch_inflate_t<2, 9, 6>(a, s); break;
+  switch (variant) {   // (warps per CTA, literal LUT bits, distance LUT bits); shared memory per warp = (2^LB + 2^DB + 64) * 64 B
+    case 1: launch_inflate_t<2, 8, 6>(a, s); break;
+    case 2: launch_inflate_t<2, 10, 6>(a, s); break;
+    case 3: launch_inflate_t<4, 9, 6>(a, s); break;
+    case 4: launch_inflate_t<2, 9, 6>(a, s); break;
+    case 5: launch_inflate_t<2, 9, 7>(a, s); break;
+    case 6: launch_inflate_t<8, 8, 6>(a, s); break;
+    case 7: launch_inflate_t<4, 7, 6>(a, s); break;
+    case 8: launch_inflate_t<4, 7, 5>(a, s); break;
+    case 9: launch_inflate_t<8, 7, 6>(a, s); break;
+    default: launch_inflate_t<4, 8, 6>(a, s); break;
   }
 }
 
@@ -363,16 +367,31 @@ __device__ bool pair_lookup_or_wait(const DevTables& T, u64* ptab, u32 pmask, co
   atomicOr(T.err, DERR_PAIR_FULL); return false;
 }
 
-// BAM2blocks::processAll (row a2), one lane per BGZF block: every record that starts inside the block.
-__global__ void __launch_bounds__(128) walk_process_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
-                                                            u64 Uend, const u64* __restrict__ entry, u64* __restrict__ ptab, u32 pmask) {
+// Second framing pass: every lane re-walks its BGZF block and lists the record offsets at rec_base[b] + i.
+__global__ void walk_list_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk, const u64* __restrict__ entry,
+                                 const u64* __restrict__ rec_base, u64* __restrict__ rec_off) {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= nblk) return;
-  u64 e = entry[b], blk_end = u_off[b] + u_len[b];
-  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0}; u32 nrec = 0;
-  while (e < blk_end) {
-    Core c; load_core(U, e, c); nrec++;
-    u64 next = e + 4 + (u64)c.block_size;
+  u64 e = entry[b], blk_end = u_off[b] + u_len[b], at = rec_base[b];
+  while (e < blk_end) { rec_off[at++] = e; e += 4 + (u64)ld32(U + e); }
+}
+// exclusive scan of per-block record counts (single CTA; a few hundred thousand values at most)
+__global__ void __launch_bounds__(1024) scan_counts_kernel(const u32* __restrict__ in, u64* __restrict__ out, int n) {
+  __shared__ u64 sh[1024]; __shared__ u64 carry; if (threadIdx.x == 0) carry = 0; __syncthreads();
+  for (int base = 0; base < n; base += 1024) {
+    int i = base + threadIdx.x; u64 v = i < n ? in[i] : 0; sh[threadIdx.x] = v; __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) { u64 t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0; __syncthreads(); sh[threadIdx.x] += t; __syncthreads(); }
+    u64 incl = sh[threadIdx.x], c = carry; if (i < n) out[i] = c + incl - v; __syncthreads();
+    if (threadIdx.x == 1023) carry = c + incl; __syncthreads();
+  }
+}
+
+// BAM2blocks::processAll (row a2), one lane per record: skip / single / pair decision, mate pairing, fragment processing.
+__global__ void __launch_bounds__(128) process_records_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
+  if (i < nrec) {
+    u64 e = rec_off[i]; Core c; load_core(U, e, c);
     if ((c.flag & 0x4) || c.refID < 0) st.skipped++;                       // [C-6] only unmapped records are skipped
     else if (c.refID >= T.n_ref) { atomicOr(T.err, DERR_REFID); }
     else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) { st.single++; process_single(T, U, e, c, sink); }  // [C-7]
@@ -384,20 +403,21 @@ __global__ void __launch_bounds__(128) walk_process_kernel(DevTables T, const ui
         if (first_is_me) process_pair(T, U, e, c, mo, m, sink, st); else process_pair(T, U, mo, m, e, c, sink, st);
       }
     }
-    e = next;
   }
-  if (st.single) atomicAdd(&T.stats[ST_SINGLE], (u64)st.single);
-  if (st.paired) atomicAdd(&T.stats[ST_PAIRED], (u64)st.paired);
-  if (st.shortp) atomicAdd(&T.stats[ST_SHORT], (u64)st.shortp);
-  if (st.inter) atomicAdd(&T.stats[ST_INTERSECT], (u64)st.inter);
-  if (st.longp) atomicAdd(&T.stats[ST_LONG], (u64)st.longp);
-  if (st.skipped) atomicAdd(&T.stats[ST_SKIPPED], (u64)st.skipped);
-  if (sink.nuc) atomicAdd(&T.stats[ST_NUCLEOTIDES], sink.nuc);
-  if (nrec) atomicAdd(&T.stats[ST_RECORDS], (u64)nrec);
+  // warp-aggregate the counters: one atomic per warp and counter
+  u64 v[8] = {st.single, st.paired, st.shortp, st.inter, st.longp, st.skipped, 0, sink.nuc};
+#pragma unroll
+  for (int k = 0; k < 8; k++) { if (k == 6) continue; u64 x = v[k]; for (int o = 16; o; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o); if ((threadIdx.x & 31) == 0 && x) atomicAdd(&T.stats[k], x); }
+  if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
 }
-void launch_walk_process(const DevTables& T, const FrameArgs& a, u64* ptab, u32 pmask, cudaStream_t s) {
+void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s) {
   int grid = (a.nblk + 127) / 128;
-  if (grid) { walk_process_kernel<<<grid, 128, 0, s>>>(T, a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.entry, ptab, pmask); IRF_LAUNCHED(); }
+  if (grid) { walk_list_kernel<<<grid, 128, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.entry, rec_base, rec_off); IRF_LAUNCHED(); }
+}
+void launch_scan_counts(const u32* in, u64* out, int n, cudaStream_t s) { if (n) { scan_counts_kernel<<<1, 1024, 0, s>>>(in, out, n); IRF_LAUNCHED(); } }
+void launch_process_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, cudaStream_t s) {
+  u64 grid = (nrec + 127) / 128;
+  if (grid) { process_records_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, rec_off, nrec, ptab, pmask); IRF_LAUNCHED(); }
 }
 
 // Records still waiting in the pair table never met a mate: error reads on one GPU, halo candidates when sharded.

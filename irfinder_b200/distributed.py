@@ -1,0 +1,171 @@
+"""Region-sharded multi-GPU run: one process and one irf_ctx per GPU, torch.distributed for the exchange.
+
+SURVEY.md §8e.  A coordinate-sorted BAM is cut at BGZF block boundaries into `world` byte ranges of equal
+compressed size; BGZF offsets order records by coordinate, so each range is a genomic region.  No BAI is
+needed: record framing inside a shard is speculative + verified (kernels.cu, S2) and the first record of
+shard r is cross-checked against the last record of shard r-1 (`frame handshake`).
+
+Exchange steps (all integer, so outputs are identical for every GPU count):
+  1. halo:      records whose mate lies in another shard are trimmed to fixed part + name + CIGAR and
+                all-gathered; every rank pairs the gathered set and counts the pairs whose key it owns.
+  2. junctions: the three JunctionCount hash tables are exported as dense (key, counts) lists, all-gathered
+                and re-inserted (slot positions differ between ranks, so they cannot be reduced in place).
+  3. additive:  depth difference counters, span-point, ROI, chromosome and read counters are all-reduced
+                (SUM) in place on the library's device buffers (NCCL over NVLink).
+Afterwards every rank holds the complete tables and runs irf_finalize; rank 0 writes the files.
+"""
+import numpy as np
+
+_BGZF_MAGIC = bytes([31, 139, 8, 4])
+
+
+def _is_block_start(buf, off):
+    """True when a BGZF block header with a BC subfield starts at buf[off]; returns (ok, block_size)."""
+    if off + 18 > len(buf) or bytes(buf[off:off + 4]) != _BGZF_MAGIC:
+        return False, 0
+    xlen = int(buf[off + 10]) | int(buf[off + 11]) << 8
+    x = 0
+    while x + 4 <= xlen and off + 12 + x + 6 <= len(buf):
+        si1, si2 = int(buf[off + 12 + x]), int(buf[off + 13 + x])
+        slen = int(buf[off + 14 + x]) | int(buf[off + 15 + x]) << 8
+        if si1 == 66 and si2 == 67 and slen == 2:
+            return True, (int(buf[off + 16 + x]) | int(buf[off + 17 + x]) << 8) + 1
+        x += 4 + slen
+    return False, 0
+
+
+def find_block_start(buf, approx, hops=3):
+    """First BGZF block start at or after `approx`, verified by following `hops` BSIZE links (SAM v1 §4.1)."""
+    n = len(buf)
+    off = int(approx)
+    while off + 18 <= n:
+        j = off
+        view = bytes(buf[off:min(n, off + (1 << 17))])
+        k = view.find(_BGZF_MAGIC)
+        if k < 0:
+            off += max(1, len(view) - 3)
+            continue
+        j = off + k
+        ok, cur = True, j
+        for _ in range(hops):
+            good, bs = _is_block_start(buf, cur)
+            if not good:
+                ok = False
+                break
+            cur += bs
+            if cur >= n:
+                break
+        if ok:
+            return j
+        off = j + 1
+    return n
+
+
+def shard_cuts(buf, world):
+    """Byte offsets [0, c1, ..., len(buf)]: BGZF-block-aligned cuts that balance compressed bytes."""
+    n = len(buf)
+    cuts = [0]
+    for r in range(1, world):
+        c = find_block_start(buf, n * r // world)
+        cuts.append(max(c, cuts[-1]))
+    cuts.append(n)
+    return cuts
+
+
+class _DevArray:
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = dict(shape=(int(n),), typestr=typestr, data=(int(ptr), False), version=3)
+
+
+def _wrap(ptr, n, typestr, device):
+    import torch
+    if n == 0 or not ptr:
+        return torch.zeros(0, dtype={"<i4": torch.int32, "<i8": torch.int64, "|u1": torch.uint8}[typestr], device=device)
+    return torch.as_tensor(_DevArray(ptr, n, typestr), device=device)
+
+
+def _all_gather_var(t, group, dist):
+    """all_gather of 1-D tensors with per-rank lengths; returns (list of tensors, lengths)."""
+    import torch
+    world = dist.get_world_size(group)
+    n = torch.tensor([t.numel()], dtype=torch.int64, device=t.device)
+    ns = [torch.zeros_like(n) for _ in range(world)]
+    dist.all_gather(ns, n, group=group)
+    lens = [int(x.item()) for x in ns]
+    m = max(max(lens), 1)
+    pad = torch.zeros(m, dtype=t.dtype, device=t.device)
+    pad[: t.numel()] = t
+    outs = [torch.zeros_like(pad) for _ in range(world)]
+    dist.all_gather(outs, pad, group=group)
+    return [o[:l] for o, l in zip(outs, lens)], lens
+
+
+def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 18, header_probe=1 << 20):
+    """Counts `buf` (the whole BGZF BAM, host memory, same bytes on every rank) across `world` ranks.
+
+    `core` is an IRFinderCore with references loaded.  Returns a dict of bookkeeping numbers; the merged tables are
+    in `core` after this returns (finalized on every rank).
+    """
+    import torch
+    import torch.distributed as dist
+    dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+    base = arr.ctypes.data
+    n = arr.size
+    cuts = shard_cuts(arr, world)
+    probe = header_probe
+    while True:  # the header can span many blocks; grow the probe until it parses
+        try:
+            core.read_header(base, min(n, probe))
+            break
+        except Exception:
+            if probe >= n:
+                raise
+            probe *= 4
+    lo, hi = cuts[rank], cuts[rank + 1]
+    hi_look = hi if rank == world - 1 else min(n, find_block_start(arr, min(n, hi + lookahead)))
+    core.reset()
+    core.stage(base + lo, hi - lo, hi_look - lo, has_header=(rank == 0))
+    core.count()
+    info = dict(cuts=cuts, recount=0)
+    if world > 1:
+        # ---- frame handshake: my first record must be where my left neighbour's last record ends
+        e0, ex = core.frame_info()
+        mine = torch.tensor([e0, ex], dtype=torch.int64, device=dev)
+        allv = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allv, mine, group=group)
+        if rank > 0 and int(allv[rank][0]) != int(allv[rank - 1][1]):
+            core.set_option("entry0", int(allv[rank - 1][1]))
+            core.reset()
+            core.count()
+            info["recount"] = 1
+        # ---- 1. halo
+        hb, hnb, ho, hnr = core.export_halo()
+        torch.cuda.synchronize()
+        parts, blens = _all_gather_var(_wrap(hb, hnb, "|u1", dev), group, dist)
+        offs, olens = _all_gather_var(_wrap(ho, hnr, "<i8", dev), group, dist)
+        starts = np.concatenate([[0], np.cumsum(blens)[:-1]]).astype(np.int64)
+        all_bytes = torch.cat(parts + [torch.zeros(64, dtype=torch.uint8, device=dev)])
+        all_offs = torch.cat([o + int(s) for o, s in zip(offs, starts)]) if sum(olens) else torch.zeros(0, dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
+        core.import_halo(all_bytes.data_ptr(), int(sum(blens)), all_offs.data_ptr() if all_offs.numel() else 0, int(all_offs.numel()), rank, world)
+        info["halo_records"] = int(all_offs.numel())
+        # ---- 2. junction tables
+        for which in range(3):
+            kp, cp, nk = core.export_junctions(which)
+            torch.cuda.synchronize()
+            keys, klens = _all_gather_var(_wrap(kp, nk, "<i8", dev), group, dist)
+            cnts, _ = _all_gather_var(_wrap(cp, nk * 2, "<i4", dev), group, dist)
+            torch.cuda.synchronize()
+            for r in range(world):
+                if r != rank and klens[r]:
+                    k, c = keys[r].contiguous(), cnts[r].contiguous()
+                    core.import_junctions(which, k.data_ptr(), c.data_ptr(), klens[r])
+        # ---- 3. additive tables, in place on the library's buffers
+        for name, typestr in (("diff", "<i4"), ("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
+            p, cnt, _ = core.device_table(name)
+            if cnt:
+                dist.all_reduce(_wrap(p, cnt, typestr, dev), op=dist.ReduceOp.SUM, group=group)
+        torch.cuda.synchronize()
+    core.finalize()
+    return info

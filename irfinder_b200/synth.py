@@ -32,6 +32,11 @@ def generate(outdir, genome="chr22", introns=5000, pairs=100_000, readlen=100, s
         cmd.append("--refs-only")
     os.makedirs(outdir, exist_ok=True)
     subprocess.run(cmd, check=True)
+    return describe(outdir)
+
+
+def describe(outdir):
+    """Paths and counts of a generated workload directory."""
     meta = {}
     mp = os.path.join(outdir, "meta.json")
     if os.path.exists(mp):

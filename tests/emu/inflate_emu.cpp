@@ -10,7 +10,7 @@
 
 template <int LB, int DB>
 static int run(const std::vector<uint8_t>& f) {
-  std::vector<uint16_t> lit(1 << LB), dist(1 << (DB < 7 ? 7 : DB));
+  std::vector<uint16_t> lit(1 << LB), dist((1 << DB) + 64);  // dist LUT + the two 32-entry aux tables behind it
   size_t off = 0; long nblk = 0, bad = 0; std::vector<uint8_t> a(65536 + 16), b(65536 + 16);
   while (off + 18 <= f.size()) {
     const uint8_t* h = &f[off];
