@@ -78,10 +78,23 @@ class _DevArray:
 
 
 def _wrap(ptr, n, typestr, device):
+    """Zero-copy torch view of `n` elements at address `ptr` (device memory for a cuda device, host memory for cpu)."""
+    import ctypes
     import torch
+    tdt = {"<i4": torch.int32, "<i8": torch.int64, "|u1": torch.uint8}[typestr]
     if n == 0 or not ptr:
-        return torch.zeros(0, dtype={"<i4": torch.int32, "<i8": torch.int64, "|u1": torch.uint8}[typestr], device=device)
+        return torch.zeros(0, dtype=tdt, device=device)
+    if torch.device(device).type == "cpu":   # the gloo tests drive this module with host-resident fake tables
+        ndt = {"<i4": np.int32, "<i8": np.int64, "|u1": np.uint8}[typestr]
+        raw = (ctypes.c_uint8 * (int(n) * np.dtype(ndt).itemsize)).from_address(int(ptr))
+        return torch.from_numpy(np.frombuffer(raw, dtype=ndt))
     return torch.as_tensor(_DevArray(ptr, n, typestr), device=device)
+
+
+def _sync(device):
+    import torch
+    if torch.device(device).type == "cuda":
+        torch.cuda.synchronize()
 
 
 def _all_gather_var(t, group, dist):
@@ -108,7 +121,7 @@ def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 
     """
     import torch
     import torch.distributed as dist
-    dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+    dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
     arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
     base = arr.ctypes.data
     n = arr.size
@@ -141,22 +154,22 @@ def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 
             info["recount"] = 1
         # ---- 1. halo
         hb, hnb, ho, hnr = core.export_halo()
-        torch.cuda.synchronize()
+        _sync(dev)
         parts, blens = _all_gather_var(_wrap(hb, hnb, "|u1", dev), group, dist)
         offs, olens = _all_gather_var(_wrap(ho, hnr, "<i8", dev), group, dist)
         starts = np.concatenate([[0], np.cumsum(blens)[:-1]]).astype(np.int64)
         all_bytes = torch.cat(parts + [torch.zeros(64, dtype=torch.uint8, device=dev)])
         all_offs = torch.cat([o + int(s) for o, s in zip(offs, starts)]) if sum(olens) else torch.zeros(0, dtype=torch.int64, device=dev)
-        torch.cuda.synchronize()
+        _sync(dev)
         core.import_halo(all_bytes.data_ptr(), int(sum(blens)), all_offs.data_ptr() if all_offs.numel() else 0, int(all_offs.numel()), rank, world)
         info["halo_records"] = int(all_offs.numel())
         # ---- 2. junction tables
         for which in range(3):
             kp, cp, nk = core.export_junctions(which)
-            torch.cuda.synchronize()
+            _sync(dev)
             keys, klens = _all_gather_var(_wrap(kp, nk, "<i8", dev), group, dist)
             cnts, _ = _all_gather_var(_wrap(cp, nk * 2, "<i4", dev), group, dist)
-            torch.cuda.synchronize()
+            _sync(dev)
             for r in range(world):
                 if r != rank and klens[r]:
                     k, c = keys[r].contiguous(), cnts[r].contiguous()
@@ -166,6 +179,6 @@ def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 
             p, cnt, _ = core.device_table(name)
             if cnt:
                 dist.all_reduce(_wrap(p, cnt, typestr, dev), op=dist.ReduceOp.SUM, group=group)
-        torch.cuda.synchronize()
+        _sync(dev)
     core.finalize()
     return info

@@ -190,3 +190,27 @@ def test_bad_inputs_fail_loudly(tiny, tmp_path):
         c.run_bytes(b"this is not a BAM file at all, not even gzip")
     c.run_bytes(data)               # the context stays usable afterwards
     assert c.stats()["pairs"] > 0
+
+
+def test_micro_fixture_by_hand_on_gpu(tmp_path):
+    """The hand-derived fixture of tests/micro_fixture.py (every cell computed by hand) through the CUDA path,
+    in both record orders; BGZF blocks of 700-900 bytes make nearly every record straddle a block boundary."""
+    import micro_fixture
+    p = micro_fixture.write(str(tmp_path / "m"))
+    for key in ("collated", "sorted"):
+        c = _core()
+        c.load_ref(p["cover"], p["sj"], p["rc"], p["roi"])
+        c.run_bam(p[key])
+        out = str(tmp_path / ("g_" + key))
+        c.write_outputs(out)
+        for name, want in micro_fixture.EXPECT.items():
+            assert open(os.path.join(out, name)).read() == want, (key, name)
+        st = _stats_from_stdout(c.stdout_text)
+        for k, v in micro_fixture.EXPECT_STATS.items():
+            assert st[k] == v, (key, k)
+
+
+def test_golden_vectors_on_gpu(built, tmp_path):
+    meta = _gen(tmp_path, "w", genome="tiny", introns=120, pairs=4000, readlen=100, seed=21, chunks=3)
+    _gpu_run(meta, str(tmp_path / "g"))
+    assert_same_outputs(os.path.join(ROOT, "tests", "golden", "tiny_seed21"), str(tmp_path / "g"))
