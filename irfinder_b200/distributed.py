@@ -182,3 +182,77 @@ def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 
         _sync(dev)
     core.finalize()
     return info
+
+
+def run_sharded_local(cores, buf, lookahead=1 << 18, header_probe=1 << 20):
+    """The same protocol with every "rank" a context in THIS process on the current GPU (no torch.distributed).
+
+    Used by the single-GPU tests to check that a sharded run is byte-identical to an unsharded one, and usable to walk a
+    BAM larger than device memory shard by shard.  `cores` are IRFinderCore objects with the same references loaded.
+    """
+    import torch
+    world = len(cores)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+    base, n = arr.ctypes.data, arr.size
+    cuts = shard_cuts(arr, world)
+    info = dict(cuts=cuts, recount=0, halo_records=0)
+    frames = []
+    for r, core in enumerate(cores):
+        probe = header_probe
+        while True:
+            try:
+                core.read_header(base, min(n, probe))
+                break
+            except Exception:
+                if probe >= n:
+                    raise
+                probe *= 4
+        lo, hi = cuts[r], cuts[r + 1]
+        hi_look = hi if r == world - 1 else min(n, find_block_start(arr, min(n, hi + lookahead)))
+        core.reset()
+        core.stage(base + lo, hi - lo, hi_look - lo, has_header=(r == 0))
+        core.count()
+        e0, ex = core.frame_info()
+        if r > 0 and e0 != frames[-1][1]:
+            core.set_option("entry0", frames[-1][1])
+            core.reset()
+            core.count()
+            e0, ex = core.frame_info()
+            info["recount"] += 1
+        frames.append((e0, ex))
+    if world > 1:
+        halos = [c.export_halo() for c in cores]
+        torch.cuda.synchronize()
+        parts = [_wrap(h[0], h[1], "|u1", dev).clone() for h in halos]
+        offs, start = [], 0
+        for h in halos:
+            offs.append(_wrap(h[2], h[3], "<i8", dev).clone() + start)
+            start += h[1]
+        all_bytes = torch.cat(parts + [torch.zeros(64, dtype=torch.uint8, device=dev)])
+        all_offs = torch.cat(offs)
+        torch.cuda.synchronize()
+        info["halo_records"] = int(all_offs.numel())
+        for r, core in enumerate(cores):
+            core.import_halo(all_bytes.data_ptr(), start, all_offs.data_ptr() if all_offs.numel() else 0, int(all_offs.numel()), r, world)
+        for which in range(3):
+            exp = []
+            for c in cores:
+                kp, cp, nk = c.export_junctions(which)
+                torch.cuda.synchronize()
+                exp.append((_wrap(kp, nk, "<i8", dev).clone(), _wrap(cp, nk * 2, "<i4", dev).clone(), nk))
+            torch.cuda.synchronize()
+            for r, core in enumerate(cores):
+                for q, (k, c, nk) in enumerate(exp):
+                    if q != r and nk:
+                        core.import_junctions(which, k.data_ptr(), c.data_ptr(), nk)
+        for name, typestr in (("diff", "<i4"), ("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
+            views = [_wrap(*c.device_table(name)[:2], typestr, dev) for c in cores]
+            if views[0].numel():
+                total = torch.stack(views).sum(0)
+                for v in views:
+                    v.copy_(total)
+        torch.cuda.synchronize()
+    for core in cores:
+        core.finalize()
+    return info
