@@ -178,22 +178,30 @@ def run_b200(a):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     total_pairs = a.pairs * world
-    wd = os.path.join(a.workdir, f"w{world}")
+    wd = os.path.join(a.workdir, f"w{world}_r{rank}")
     t0 = time.perf_counter()
     if rank == 0:
         build.build_tools()
-        meta = gen_cached(wd, genome=a.genome, introns=a.introns, pairs=total_pairs, readlen=a.readlen, seed=2, collated=False, chunks=max(256, 64 * world))
     if world > 1:
         dist.barrier()
-    if rank != 0:
-        meta = gen_cached(wd, genome=a.genome, introns=a.introns, pairs=total_pairs, readlen=a.readlen, seed=2, collated=False, chunks=max(256, 64 * world))
+    # One logical BAM of `total_pairs`; with N ranks each rank generates ONLY its own byte range of that file
+    # (`irf_synth --chunk-range`: the concatenation of the parts is byte-identical to the whole file), so no rank
+    # ever holds more than its shard and generation parallelises across the host cores.
+    nchunks = max(256, 64 * world)
+    clo, chi = nchunks * rank // world, nchunks * (rank + 1) // world
+    threads = max(1, (os.cpu_count() or 1) // world)
+    meta = gen_cached(wd, genome=a.genome, introns=a.introns, pairs=total_pairs, readlen=a.readlen, seed=2, collated=False, chunks=nchunks,
+                      chunk_range=(clo, chi) if world > 1 else None, threads=threads)
     gen_s = time.perf_counter() - t0
-    n_units = meta["pairs"] + meta["singles"]   # fragments (pairs; a few orphans count as one unit each)
     fsize = os.path.getsize(meta["sorted"])
-    host = torch.empty(fsize + 64, dtype=torch.uint8, pin_memory=True)   # pinned host copy of the BGZF bytes
+    host = torch.empty(fsize + 64, dtype=torch.uint8, pin_memory=True)   # pinned host copy of this rank's BGZF bytes
     hv = host.numpy()
     with open(meta["sorted"], "rb") as f:
         f.readinto(memoryview(hv)[:fsize])
+    counts = torch.tensor([meta["pairs"] + meta["singles"], meta["records"], meta["compressed_bytes"], meta["inflated_bytes"]], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(counts)
+    n_units, n_records, comp_bytes, infl_bytes = (int(x) for x in counts.tolist())   # fragments = pairs (a few orphans count as one unit each)
     opts = {} if a.inflate_variant < 0 else {"inflate_variant": a.inflate_variant}
     core = IRFinderCore(local, **opts)
     t1 = time.perf_counter()
@@ -214,10 +222,12 @@ def run_b200(a):
         def step():
             core.reset(); core.count(); core.finalize()
     else:
-        from irfinder_b200.distributed import run_sharded
+        from irfinder_b200.distributed import ShardPlan, run_plan
+        hdr = None if rank == 0 else np.fromfile(meta["sorted"] + ".header", dtype=np.uint8)
+        plan = ShardPlan.from_parts(hv[:fsize], hdr, rank, world, dist, torch.device("cuda", local))
 
-        def step():   # sharded steps re-stage their byte range: the copy is part of the multi-GPU step
-            run_sharded(core, hv[:fsize], rank, world, device=torch.device("cuda", local))
+        def step():   # sharded steps re-stage their byte range: the host->device copy is part of the multi-GPU step
+            run_plan(core, plan, device=torch.device("cuda", local))
     for _ in range(a.warmup):
         step()
     sampler = ClockSampler(local) if rank == 0 else None
@@ -241,7 +251,7 @@ def run_b200(a):
             core.run_buffer(hv.ctypes.data, fsize); core.write_outputs(outdir)
     else:
         def e2e_step():
-            run_sharded(core, hv[:fsize], rank, world, device=torch.device("cuda", local))
+            run_plan(core, plan, device=torch.device("cuda", local))
             if rank == 0:
                 core.write_outputs(outdir)
     for _ in range(min(a.warmup, 2)):
@@ -265,8 +275,7 @@ def run_b200(a):
         return
     # ---------------- roofline of the dominant kernel (inflate): algorithmic bytes = compressed in + inflated out
     peak, peak_src = measured_peak()
-    share = (fsize / world if world > 1 else fsize)
-    alg_bytes = (meta["compressed_bytes"] + meta["inflated_bytes"]) / world
+    alg_bytes = (comp_bytes + infl_bytes) / world   # per GPU
     avg_inflate_ms = sum(inflate_ms) / max(len(inflate_ms), 1)
     achieved = alg_bytes / (avg_inflate_ms * 1e-3) / 1e9 if avg_inflate_ms > 0 else 0.0
     traffic = None
@@ -290,10 +299,10 @@ def run_b200(a):
             cpu = {"value": None, "unit": UNIT, "cores": 1, "kind": "port", "sample": f"failed: {e}"}
     line = {"metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(dt / a.steps * 1e3, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 bytes -> int32/u32 counts, f64 ratios", "data": "synthetic",
-            "config": {"workload": workload_name(a, total_pairs), "fragments": n_units, "records": meta["records"], "compressed_bytes": meta["compressed_bytes"],
-                       "inflated_bytes": meta["inflated_bytes"], "l2": "inputs larger than L2 (no flush needed)", "sharding": "one BGZF byte range per rank" if world > 1 else "single GPU",
+            "config": {"workload": workload_name(a, total_pairs), "fragments": n_units, "records": n_records, "compressed_bytes": comp_bytes,
+                       "inflated_bytes": infl_bytes, "l2": "inputs larger than L2 (no flush needed)", "sharding": "one BGZF byte range (genomic region) of the BAM per rank; value at N>1 includes the per-step host->device copy" if world > 1 else "single GPU",
                        "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
-            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(fsize), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes)},
+            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes)},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "inflate_kernel", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic,
                          "peak_source": peak_src, "algorithmic_bytes_per_step": int(alg_bytes), "launches_per_step": inflate_launches / max(a.steps, 1), "avg_ms_per_step": round(avg_inflate_ms, 3)},

@@ -113,34 +113,67 @@ def _all_gather_var(t, group, dist):
     return [o[:l] for o, l in zip(outs, lens)], lens
 
 
-def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 18, header_probe=1 << 20):
-    """Counts `buf` (the whole BGZF BAM, host memory, same bytes on every rank) across `world` ranks.
+class ShardPlan:
+    """What one rank feeds its context: the BAM header prefix, its own BGZF byte range and some look-ahead bytes of the
+    right neighbour (so a record straddling the shard end can be read).  `data` holds own + look-ahead contiguously."""
 
-    `core` is an IRFinderCore with references loaded.  Returns a dict of bookkeeping numbers; the merged tables are
-    in `core` after this returns (finalized on every rank).
-    """
+    def __init__(self, header, data, n_own, rank, world, cuts=None):
+        self.header, self.data, self.n_own, self.rank, self.world, self.cuts = header, data, int(n_own), rank, world, cuts
+
+    @staticmethod
+    def from_buffer(buf, rank, world, lookahead=1 << 18, header_probe=1 << 22):
+        """Every rank sees the whole BAM (host memory or np.memmap); cuts balance compressed bytes."""
+        arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+        n = arr.size
+        cuts = shard_cuts(arr, world)
+        lo, hi = cuts[rank], cuts[rank + 1]
+        hi_look = hi if rank == world - 1 else min(n, hi + lookahead)
+        return ShardPlan(arr[: min(n, header_probe)], arr[lo:hi_look], hi - lo, rank, world, cuts)
+
+    @staticmethod
+    def from_parts(part, header, rank, world, dist, device, group=None, lookahead=1 << 18, pin=True):
+        """Every rank holds only ITS byte range of the BAM (`part`, e.g. produced by `irf_synth --chunk-range`); the
+        look-ahead bytes come from the right neighbour through one all_gather of `lookahead` bytes per rank."""
+        import torch
+        part = np.frombuffer(part, dtype=np.uint8) if not isinstance(part, np.ndarray) else part
+        head = torch.zeros(lookahead, dtype=torch.uint8)
+        k = min(lookahead, part.size)
+        head[:k] = torch.from_numpy(np.ascontiguousarray(part[:k]))
+        meta = torch.tensor([k], dtype=torch.int64)
+        dev = torch.device(device)
+        heads = [torch.zeros(lookahead, dtype=torch.uint8, device=dev) for _ in range(world)]
+        ks = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+        dist.all_gather(heads, head.to(dev), group=group)
+        dist.all_gather(ks, meta.to(dev), group=group)
+        extra = heads[rank + 1][: int(ks[rank + 1].item())].cpu().numpy() if rank + 1 < world else np.zeros(0, np.uint8)
+        buf = torch.empty(part.size + extra.size + 64, dtype=torch.uint8, pin_memory=pin and torch.cuda.is_available()).numpy()
+        buf[: part.size] = part
+        buf[part.size: part.size + extra.size] = extra
+        hdr = part if rank == 0 else (np.frombuffer(header, dtype=np.uint8) if not isinstance(header, np.ndarray) else header)
+        return ShardPlan(hdr[: 1 << 26], buf[: part.size + extra.size], part.size, rank, world)
+
+
+def run_plan(core, plan, device=None, group=None):
+    """Counts one ShardPlan per rank and merges; the merged, finalized tables are in `core` on every rank afterwards."""
     import torch
     import torch.distributed as dist
     dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
-    arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
-    base = arr.ctypes.data
-    n = arr.size
-    cuts = shard_cuts(arr, world)
-    probe = header_probe
+    rank, world = plan.rank, plan.world
+    hdr = np.ascontiguousarray(plan.header)
+    probe = min(hdr.size, 1 << 20)
     while True:  # the header can span many blocks; grow the probe until it parses
         try:
-            core.read_header(base, min(n, probe))
+            core.read_header(hdr.ctypes.data, probe)
             break
         except Exception:
-            if probe >= n:
+            if probe >= hdr.size:
                 raise
-            probe *= 4
-    lo, hi = cuts[rank], cuts[rank + 1]
-    hi_look = hi if rank == world - 1 else min(n, find_block_start(arr, min(n, hi + lookahead)))
+            probe = min(hdr.size, probe * 4)
+    data = plan.data if plan.data.flags["C_CONTIGUOUS"] else np.ascontiguousarray(plan.data)
     core.reset()
-    core.stage(base + lo, hi - lo, hi_look - lo, has_header=(rank == 0))
+    core.stage(data.ctypes.data, plan.n_own, data.size, has_header=(rank == 0))
     core.count()
-    info = dict(cuts=cuts, recount=0)
+    info = dict(cuts=plan.cuts, recount=0)
     if world > 1:
         # ---- frame handshake: my first record must be where my left neighbour's last record ends
         e0, ex = core.frame_info()
@@ -182,6 +215,13 @@ def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 
         _sync(dev)
     core.finalize()
     return info
+
+
+
+
+def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 18):
+    """Counts `buf` (the whole BGZF BAM in host memory, same bytes on every rank) across `world` ranks."""
+    return run_plan(core, ShardPlan.from_buffer(buf, rank, world, lookahead), device, group)
 
 
 def run_sharded_local(cores, buf, lookahead=1 << 18, header_probe=1 << 20):

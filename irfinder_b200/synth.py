@@ -16,7 +16,7 @@ CONFIGS = {
 
 
 def generate(outdir, genome="chr22", introns=5000, pairs=100_000, readlen=100, seed=1, single=False, stranded=0, intronic=0.05,
-             hot_introns=0, level=1, threads=0, chunks=256, sorted_bam=True, collated=True, align_records=False, refs_only=False):
+             hot_introns=0, level=1, threads=0, chunks=256, sorted_bam=True, collated=True, align_records=False, refs_only=False, chunk_range=None):
     exe = build_tools()
     cmd = [exe, "--out", outdir, "--genome", genome, "--introns", str(introns), "--pairs", str(pairs), "--readlen", str(readlen), "--seed", str(seed),
            "--stranded", str(stranded), "--intronic", str(intronic), "--hot-introns", str(hot_introns), "--level", str(level), "--threads", str(threads), "--chunks", str(chunks)]
@@ -30,6 +30,8 @@ def generate(outdir, genome="chr22", introns=5000, pairs=100_000, readlen=100, s
         cmd.append("--align-records")
     if refs_only:
         cmd.append("--refs-only")
+    if chunk_range is not None:   # only the byte range of chunks [a,b) of the whole file (header with a == 0, EOF marker with b == chunks)
+        cmd += ["--chunk-range", "%d:%d" % tuple(chunk_range)]
     os.makedirs(outdir, exist_ok=True)
     subprocess.run(cmd, check=True)
     return describe(outdir)

@@ -234,3 +234,17 @@ def test_region_sharded_run_is_byte_identical(tiny, tmp_path, world):
         c.write_outputs(out)
         assert_same_outputs(tiny["oracle_out"], out)
         assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+
+
+def test_wrapper_script_bam_mode(built, tiny, tmp_path):
+    """`IRFinder -m BAM -r <RefDir> -d <OutDir> <bam>`."""
+    exe = os.path.join(ROOT, "bin", "IRFinder")
+    out = str(tmp_path / "wrapped")
+    r = subprocess.run([exe, "-m", "BAM", "-r", tiny["ref_dir"], "-d", out, tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 0, r.stderr + open(os.path.join(out, "irfinder.stderr")).read()
+    assert_same_outputs(tiny["oracle_out"], out)
+    assert _stats_from_stdout(open(os.path.join(out, "irfinder.stdout")).read()) == _stats_from_stdout(tiny["oracle_stdout"])
+    again = subprocess.run([exe, "-m", "BAM", "-r", tiny["ref_dir"], "-d", out, tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert again.returncode != 0      # refuses to overwrite
+    other = subprocess.run([exe, "-m", "FastQ", "-r", tiny["ref_dir"], "-d", str(tmp_path / "x"), tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert other.returncode != 0

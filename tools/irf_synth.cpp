@@ -72,6 +72,7 @@ struct Opt {
   bool write_sorted = true, write_collated = true;
   bool align_records = false;  // htslib-style: never split a record across BGZF blocks
   bool refs_only = false;
+  int chunk_lo = 0, chunk_hi = -1;  // --chunk-range A:B writes only the BGZF streams of chunks [A,B): byte range of the whole file
 };
 
 static void die(const char* m) { fprintf(stderr, "irf_synth: %s\n", m); exit(2); }
@@ -425,6 +426,7 @@ int main(int argc, char** argv) {
     else if (a == "--chunks") o.chunks = std::stoi(val()); else if (a == "--no-sorted") o.write_sorted = false;
     else if (a == "--no-collated") o.write_collated = false; else if (a == "--align-records") o.align_records = true;
     else if (a == "--refs-only") o.refs_only = true;
+    else if (a == "--chunk-range") { string v = val(); size_t c = v.find(':'); if (c == string::npos) die("--chunk-range A:B"); o.chunk_lo = std::stoi(v.substr(0, c)); o.chunk_hi = std::stoi(v.substr(c + 1)); }
     else { fprintf(stderr, "unknown option %s\n", a.c_str()); return 2; }
   }
   if (o.threads <= 0) o.threads = std::max(1u, std::thread::hardware_concurrency());
@@ -446,11 +448,12 @@ int main(int argc, char** argv) {
   for (int c = 1; c <= C; c++) if (cb[c] < cb[c - 1]) cb[c] = cb[c - 1];
   cb[C] = U;
 
-  vector<Bgzf*> S(C, nullptr), K(C, nullptr); std::atomic<int> next(0);
+  int clo = std::max(0, o.chunk_lo), chi = o.chunk_hi < 0 ? C : std::min(C, o.chunk_hi);
+  vector<Bgzf*> S(C, nullptr), K(C, nullptr); std::atomic<int> next(clo);
   vector<Worker> workers; for (int t = 0; t < o.threads; t++) workers.emplace_back(o, A, nf, first_id);
   vector<std::thread> th;
   for (int t = 0; t < o.threads; t++) th.emplace_back([&, t]() {
-    for (;;) { int c = next.fetch_add(1); if (c >= C) break;
+    for (;;) { int c = next.fetch_add(1); if (c >= chi) break;
       if (o.write_sorted) S[c] = new Bgzf(o.level, o.align_records); if (o.write_collated) K[c] = new Bgzf(o.level, o.align_records);
       for (size_t u = cb[c]; u < cb[c + 1]; u++) workers[t].gen_unit(u, S[c], K[c], nullptr);
       if (S[c]) S[c]->flush_block(); if (K[c]) K[c]->flush_block(); }
@@ -463,17 +466,20 @@ int main(int argc, char** argv) {
     bool sorted = pass == 0; if (sorted ? !o.write_sorted : !o.write_collated) continue;
     string path = o.out + (sorted ? "/sorted.bam" : "/collated.bam"); FILE* f = fopen(path.c_str(), "wb"); if (!f) die("cannot open bam for write");
     Bgzf hb(o.level, false); auto h = bam_header(A, sorted); hb.write(h.data(), (int)h.size()); hb.flush_block();
-    fwrite(hb.out.data(), 1, hb.out.size(), f); u64 infl = hb.inflated, comp = hb.out.size();
+    u64 infl = 0, comp = 0;
+    if (clo == 0) { fwrite(hb.out.data(), 1, hb.out.size(), f); infl = hb.inflated; comp = hb.out.size(); }
+    else { FILE* hf = fopen((path + ".header").c_str(), "wb"); if (hf) { fwrite(hb.out.data(), 1, hb.out.size(), hf); fclose(hf); } }  // a later part: header kept beside it
     for (int c = 0; c < C; c++) { Bgzf* b = sorted ? S[c] : K[c]; if (!b) continue; fwrite(b->out.data(), 1, b->out.size(), f); infl += b->inflated; comp += b->out.size(); delete b; }
-    fwrite(BGZF_EOF, 1, 28, f); comp += 28; fclose(f);
+    if (chi == C) { fwrite(BGZF_EOF, 1, 28, f); comp += 28; }
+    fclose(f);
     if (sorted || !o.write_sorted) { infl_sorted = infl; comp_sorted = comp; }
   }
   FILE* m = fopen((o.out + "/meta.json").c_str(), "w");
   fprintf(m, "{\"seed\": %llu, \"genome\": \"%s\", \"introns\": %zu, \"units\": %zu, \"fragments\": %llu, \"records\": %llu, \"pairs\": %llu, "
-             "\"singles\": %llu, \"unmapped\": %llu, \"readlen\": %d, \"single_end\": %s, \"stranded\": %d, \"inflated_bytes\": %llu, \"compressed_bytes\": %llu, \"level\": %d}\n",
+             "\"singles\": %llu, \"unmapped\": %llu, \"readlen\": %d, \"single_end\": %s, \"stranded\": %d, \"inflated_bytes\": %llu, \"compressed_bytes\": %llu, \"level\": %d, \"chunks\": %d, \"chunk_lo\": %d, \"chunk_hi\": %d}\n",
           (unsigned long long)o.seed, o.genome.c_str(), A.introns.size(), U, (unsigned long long)acc, (unsigned long long)nrec, (unsigned long long)npairs,
           (unsigned long long)nsing, (unsigned long long)nunm, o.readlen, o.single ? "true" : "false", o.stranded, (unsigned long long)infl_sorted,
-          (unsigned long long)comp_sorted, o.level);
+          (unsigned long long)comp_sorted, o.level, C, clo, chi);
   fclose(m);
   return 0;
 }
