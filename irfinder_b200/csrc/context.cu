@@ -213,18 +213,25 @@ struct irf_ctx {
     if (inflated_input) return;
     size_t nb = blks.size(); if (!nb) return;
     IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
-    const size_t target = std::max<size_t>(768ull << 20, src_total / 8 + 1);
+    // Batches: resident input -> one launch.  Streaming from the host -> three batches of 1/8, 3/8 and 1/2 of the bytes,
+    // so the first inflate starts early and every later copy hides behind the previous batch's inflate; few launches
+    // because each launch ends with a tail of partly idle SMs.
+    const size_t min_batch = 256ull << 20;
+    size_t cut[3] = {resident ? src_total : std::max(min_batch, src_total / 8), resident ? src_total : std::max(2 * min_batch, src_total / 2), src_total};
+    vector<cudaEvent_t> copied; size_t b0 = 0; double kernel_ms = 0; vector<std::pair<cudaEvent_t, cudaEvent_t>> kev; int bi = 0;
     cudaEvent_t ev_k0, ev_k1; IRF_CUDA(cudaEventCreate(&ev_k0)); IRF_CUDA(cudaEventCreate(&ev_k1));
-    vector<cudaEvent_t> copied; size_t b0 = 0; double kernel_ms = 0; vector<std::pair<cudaEvent_t, cudaEvent_t>> kev;
     while (b0 < nb) {
       size_t b1 = b0; u64 begin = blks[b0].file_off, end = begin;
-      while (b1 < nb && (end - begin) < target) { end = blks[b1].c_off + blks[b1].c_len + 8; b1++; }
+      while (b1 < nb && (bi >= 2 || blks[b1].file_off < cut[bi])) { end = blks[b1].c_off + blks[b1].c_len + 8; b1++; }
+      if (b1 == b0) { end = blks[b1].c_off + blks[b1].c_len + 8; b1++; }
+      bi++;
       if (!resident) {
         if (b1 == nb) end = src_total;
         IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + begin, h_src + begin, end - begin, cudaMemcpyHostToDevice, s_copy));
         cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev, 0)); copied.push_back(ev);
       }
-      InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>() + b0, d_c_len.as<u32>() + b0, d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, (int)(b1 - b0), d_status.as<int>() + b0, T.err ? T.err : d_err.as<int>()};
+      InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>() + b0, d_c_len.as<u32>() + b0, d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, (int)(b1 - b0), d_status.as<int>() + b0, T.err ? T.err : d_err.as<int>(),
+                    (unsigned int*)(d_small.as<uint8_t>() + 160)};
       cudaEvent_t k0, k1; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1));
       IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute)); kev.push_back({k0, k1});
       b0 = b1;

@@ -11,8 +11,8 @@
 //    interleaved by lane (word index * LANES + lane) so a warp's 32 random lookups never bank-conflict.
 //    Codes longer than the LUT width (rare) fall back to a canonical bit-serial walk over the
 //    code-length histogram, held in per-lane local memory.
-//  * Literals go through a 4-byte accumulator so literal runs leave as aligned 32-bit stores; LZ77 copies
-//    load up to 8 source bytes before storing any, so their latencies overlap.
+//  * Output bytes are stored one by one; LZ77 copies load up to 8 source bytes in one step and store them in
+//    the next, so the load latency hides behind decode work.
 //
 // The routine is __host__ __device__ so tests/emu can run the very same code on the CPU against
 // zlib; the shipped library only ever instantiates it inside kernels.
@@ -39,13 +39,15 @@ enum InflateStatus : int {
   INF_ERR_ISIZE = 8,       // stream ended with output length != ISIZE
 };
 
-// Lane-interleaved table of 16-bit entries living in shared memory (LANES = 32) or a plain array (LANES = 1).
+// Lane-interleaved table of 16-bit entries living in shared memory (LANES = 32) or a plain array (LANES = 1):
+// entry idx of lane l sits at base[idx * LANES + l].  Two neighbouring lanes share a 4-byte bank, so a warp's 32 random
+// look-ups cost at most two wavefronts, and the address is one multiply-add.
 template <int LANES>
 struct LaneTable {
-  uint16_t* base;  // start of the warp's table region
-  int lane;
-  IRF_HD uint16_t get(uint32_t idx) const { return base[(((idx >> 1) * LANES + lane) << 1) | (idx & 1)]; }
-  IRF_HD void set(uint32_t idx, uint16_t v) const { base[(((idx >> 1) * LANES + lane) << 1) | (idx & 1)] = v; }
+  uint16_t* base;  // start of the warp's table region, already offset by the lane
+  IRF_HD void bind(uint16_t* region, int lane) { base = region + lane; }
+  IRF_HD uint16_t get(uint32_t idx) const { return base[idx * LANES]; }
+  IRF_HD void set(uint32_t idx, uint16_t v) const { base[idx * LANES] = v; }
 };
 
 struct BitReader {
@@ -66,25 +68,16 @@ struct BitReader {
   IRF_HD bool overrun() const { return wp > wend + 3; }  // three words of look-ahead are legitimate
 };
 
-// Output cursor with a 4-byte accumulator.
+// Output cursor.  Bytes are stored one by one: each lane writes its own stream, so wider stores would need per-lane
+// alignment bookkeeping that cost more instructions than the byte stores themselves (profiles/r1: the 4-byte accumulator
+// version spent 25 % of its instructions flushing).
 struct OutCursor {
   uint8_t* out;      // start of this block's output
-  uint32_t op;       // bytes produced so far (including those still in acc)
+  uint32_t op;       // bytes produced so far
   uint32_t cap;      // ISIZE
-  uint32_t acc; int nacc;
-  IRF_HD void init(uint8_t* o, uint32_t c) { out = o; op = 0; cap = c; acc = 0; nacc = 0; }
-  IRF_HD void flush_bytes() {
-    uint8_t* p = out + op - nacc;
-    for (int i = 0; i < nacc; i++) p[i] = (uint8_t)(acc >> (8 * i));
-    acc = 0; nacc = 0;
-  }
-  IRF_HD void emit(uint32_t byte) {
-    acc |= byte << (8 * nacc); nacc++; op++;
-    if ((((uintptr_t)out + op) & 3) == 0) {
-      if (nacc == 4) { *(uint32_t*)(out + op - 4) = acc; acc = 0; nacc = 0; }
-      else flush_bytes();
-    }
-  }
+  IRF_HD void init(uint8_t* o, uint32_t c) { out = o; op = 0; cap = c; }
+  IRF_HD void flush_bytes() {}
+  IRF_HD void emit(uint32_t byte) { out[op++] = (uint8_t)byte; }
 };
 
 // Per-lane Huffman set: a BITS-wide LUT plus, for the rare longer codes, the canonical-code limits.
@@ -125,13 +118,8 @@ struct Huff {
     }
     return true;
   }
-  // codes longer than BITS bits; returns -1 on an invalid code
-  IRF_HD int slow(BitReader& br) const {
-    uint32_t x = (uint32_t)br.bb & 0x7fffu, code15 = 0;
-    for (int b = 0; b < 15; b++) code15 |= ((x >> b) & 1u) << (14 - b);
-    return slow15(br, code15);
-  }
-  IRF_HD int slow15(BitReader& br, uint32_t code15) const {
+  // index into `symbol` of the long code at the head of the bit buffer (drops its bits); -1 on an invalid code
+  IRF_HD int slow_index(BitReader& br, uint32_t code15) const {
     uint32_t lim[16];
 #pragma unroll
     for (int l = BITS + 1; l < 16; l++) lim[l] = aux.get(l);
@@ -142,17 +130,23 @@ struct Huff {
     uint32_t idx = (uint32_t)(uint16_t)((code15 >> (15 - len)) + aux.get(16 + len));
     if (idx >= (uint32_t)MAXSYM) return -1;
     br.drop(len);
-    return symbol[idx];
+    return (int)idx;
+  }
+  IRF_HD int slow15(BitReader& br, uint32_t code15) const { int idx = slow_index(br, code15); return idx < 0 ? -1 : symbol[idx]; }
+  static IRF_HD uint32_t head15(const BitReader& br) {   // the next 15 bits, first bit most significant
+#ifdef __CUDA_ARCH__
+    return __brev((uint32_t)br.bb) >> 17;
+#else
+    uint32_t x = (uint32_t)br.bb & 0x7fffu, c = 0;
+    for (int b = 0; b < 15; b++) c |= ((x >> b) & 1u) << (14 - b);
+    return c;
+#endif
   }
   IRF_HD int decode(BitReader& br) const {
     uint16_t e = lut.get(br.peek(BITS));
     int l = e & 15;
     if (l) { br.drop(l); return e >> 4; }
-#ifdef __CUDA_ARCH__
-    return slow15(br, __brev((uint32_t)br.bb) >> 17);
-#else
-    return slow(br);
-#endif
+    return slow15(br, head15(br));
   }
 };
 
@@ -161,24 +155,26 @@ struct Huff {
 // instruction streams (the first version of this kernel did exactly that and ran ~50x slower).
 // Per step a lane decodes one symbol and/or copies up to 8 bytes of a pending LZ77 match; block headers
 // (Huffman table builds) are a third, rarer state.
-enum LaneState : int { LS_HEADER = 0, LS_SYMBOL = 1, LS_COPY = 2, LS_FINISH = 3, LS_DONE = 4 };
+enum LaneState : int { LS_HEADER = 0, LS_SYMBOL = 1, LS_COPY = 2, LS_FINISH = 3, LS_DONE = 4, LS_SLOWLIT = 5, LS_SLOWDIST = 6 };
 
 template <int LANES, int LIT_BITS, int DIST_BITS>
 struct InflateLane {
   BitReader br; OutCursor oc;
   Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32> hd;
   int state, status, bfinal; uint32_t copy_len, copy_dist, isize;
+  uint32_t pend_n; uint8_t pend[8];   // bytes of a match chunk loaded in the previous step (untouched until stored in this one)
+  uint16_t slow_sym;   // long-code symbol fetched from local memory in the previous step
 
   // sym_store: 320 uint16 of lane-private scratch (288 literal/length symbols + 32 distance symbols)
   IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize_, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store) {
     hl.symbol = sym_store; hd.symbol = sym_store + 288;
     br.init(cdata, clen); oc.init(out, isize_); isize = isize_;
-    hl.lut.base = lit_lut_base; hl.lut.lane = lane; hd.lut.base = dist_lut_base; hd.lut.lane = lane;
+    hl.lut.bind(lit_lut_base, lane); hd.lut.bind(dist_lut_base, lane);
     // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][lit aux (32)][dist aux (32)], all lane-interleaved
-    hd.aux.base = dist_lut_base + (size_t)(1u << DIST_BITS) * LANES; hd.aux.lane = lane; hl.aux.base = hd.aux.base + 32 * LANES; hl.aux.lane = lane;
-    state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = copy_dist = 0;
+    hd.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES, lane); hl.aux.bind(dist_lut_base + (size_t)((1u << DIST_BITS) + 32) * LANES, lane);
+    state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = copy_dist = 0; pend_n = 0; slow_sym = 0;
   }
-  IRF_HD void idle() { state = LS_DONE; status = INF_OK; }
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; pend_n = 0; }
   IRF_HD bool done() const { return state == LS_DONE; }
   IRF_HD void fail(int code) { status = code; state = LS_DONE; }
 
@@ -209,7 +205,7 @@ struct InflateLane {
       for (int i = 0; i < 19; i++) lens[i] = 0;
       for (int i = 0; i < hclen; i++) { br.refill(); lens[order[i]] = (uint8_t)br.take(3); }
       // the code-length code (<= 7 bits) borrows the distance LUT region
-      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.lut.lane = hd.lut.lane; hc.aux.base = hd.aux.base; hc.aux.lane = hd.aux.lane;
+      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.aux.base = hd.aux.base;
       if (!hc.build(lens, 19)) return fail(INF_ERR_CODELEN);
       int idx = 0;
       while (idx < hlit + hdist) {
@@ -234,26 +230,9 @@ struct InflateLane {
     state = LS_SYMBOL;
   }
 
-  IRF_HD void symbol() {
-    br.refill();  // >= 33 bits: enough for three LUT-resolved literals, or one length code + extra bits
-    uint16_t e = 0; int l = 0, nlit = 0;
-#pragma unroll
-    for (int r = 0; r < 3; r++) {
-      e = hl.lut.get(br.peek(LIT_BITS)); l = e & 15;
-      if (l && (e >> 4) < 256 && oc.op < oc.cap) { br.drop(l); oc.emit((uint32_t)(e >> 4)); nlit++; } else break;
-    }
-    if (nlit) return;
-    int sym;
-    if (l) { br.drop(l); sym = e >> 4; }
-    else {
-#ifdef __CUDA_ARCH__
-      sym = hl.slow15(br, __brev((uint32_t)br.bb) >> 17);
-#else
-      sym = hl.slow(br);
-#endif
-    }
+  // A literal/length symbol is in hand (from the LUT, or a long code resolved in the previous step).
+  IRF_HD void handle_litlen(int sym) {
     if (sym < 256) {
-      if (sym < 0) return fail(INF_ERR_SYMBOL);
       if (oc.op >= oc.cap) return fail(INF_ERR_OVERRUN_OUT);
       oc.emit((uint32_t)sym);
       return;
@@ -264,38 +243,69 @@ struct InflateLane {
     if (sym < 265) len = (uint32_t)sym - 254u;
     else if (sym == 285) len = 258;
     else { int xb = (sym - 261) >> 2; len = ((4u + ((uint32_t)(sym - 261) & 3u)) << xb) + 3u + br.take(xb); }
+    copy_len = len;
     br.refill();
-    int ds = hd.decode(br);
-    if (ds < 0 || ds > 29) return fail(INF_ERR_SYMBOL);
+    uint16_t e = hd.lut.get(br.peek(DIST_BITS)); int l = e & 15;
+    if (l) { br.drop(l); return handle_dist(e >> 4); }
+    int idx = hd.slow_index(br, hd.head15(br));
+    if (idx < 0) return fail(INF_ERR_SYMBOL);
+    slow_sym = hd.symbol[idx]; state = LS_SLOWDIST;   // local-memory load: consumed in the next step
+  }
+  IRF_HD void handle_dist(int ds) {
+    if (ds > 29) return fail(INF_ERR_SYMBOL);
     uint32_t dist;
     if (ds < 4) dist = (uint32_t)ds + 1u;
     else { int xb = (ds >> 1) - 1; dist = ((2u + ((uint32_t)ds & 1u)) << xb) + 1u + br.take(xb); }
     if (dist > oc.op) return fail(INF_ERR_DIST);
-    if (oc.op + len > oc.cap) return fail(INF_ERR_OVERRUN_OUT);
+    if (oc.op + copy_len > oc.cap) return fail(INF_ERR_OVERRUN_OUT);
     if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
-    copy_len = len; copy_dist = dist; state = LS_COPY;
+    copy_dist = dist; state = LS_COPY;
+  }
+  IRF_HD void symbol() {
+    br.refill();  // >= 33 bits: enough for three LUT-resolved literals, or one length code + extra bits
+    uint16_t e = 0; int l = 0, nlit = 0;
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+      e = hl.lut.get(br.peek(LIT_BITS)); l = e & 15;
+      if (l && (e >> 4) < 256 && oc.op < oc.cap) { br.drop(l); oc.emit((uint32_t)(e >> 4)); nlit++; } else break;
+    }
+    if (nlit) return;
+    if (l) { br.drop(l); return handle_litlen(e >> 4); }
+    int idx = hl.slow_index(br, hl.head15(br));
+    if (idx < 0) return fail(INF_ERR_SYMBOL);
+    slow_sym = hl.symbol[idx]; state = LS_SLOWLIT;      // local-memory load: consumed in the next step
   }
 
-  // up to 8 bytes of the pending match; sources are read before anything is stored.  For dist < 8 the
-  // source index wraps inside the period so overlapping (run-length) matches need no reload.
-  IRF_HD void copy_chunk() {
-    oc.flush_bytes();
-    uint8_t* dst = oc.out + oc.op; const uint8_t* src = dst - copy_dist;
-    uint32_t k = copy_len < 8 ? copy_len : 8;
-    uint8_t t[8]; uint32_t w = 0;
+  // LZ77 copy, software-pipelined across steps: copy_load() issues the loads of up to 8 source bytes into registers,
+  // copy_store() at the top of the NEXT step stores them, so the L2 latency of the loads hides behind the other lanes'
+  // (and this lane's) decode work instead of stalling the warp.  For dist < 8 the source index wraps inside the period,
+  // which makes overlapping (run-length) matches correct without reloading.
+  IRF_HD void copy_store() {
+    uint8_t* dst = oc.out + oc.op;
 #pragma unroll
-    for (int j = 0; j < 8; j++) { t[j] = (uint32_t)j < k ? src[w] : (uint8_t)0; w++; if (w == copy_dist) w = 0; }
-#pragma unroll
-    for (int j = 0; j < 8; j++) if ((uint32_t)j < k) dst[j] = t[j];
-    oc.op += k; copy_len -= k;
+    for (int j = 0; j < 8; j++) if ((uint32_t)j < pend_n) dst[j] = pend[j];
+    oc.op += pend_n; pend_n = 0;
     if (!copy_len) state = LS_SYMBOL;
+  }
+  IRF_HD void copy_load() {
+    const uint8_t* src = oc.out + oc.op - copy_dist;
+    uint32_t k = copy_len < 8 ? copy_len : 8, w = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+      if ((uint32_t)j < k) pend[j] = src[w];   // consumed only by copy_store() in the next step
+      w++; if (w == copy_dist) w = 0;
+    }
+    pend_n = k; copy_len -= k;
   }
 
   IRF_HD void step() {
+    if (pend_n) copy_store();
+    if (state == LS_SLOWLIT) { state = LS_SYMBOL; handle_litlen(slow_sym); }
+    else if (state == LS_SLOWDIST) handle_dist(slow_sym);
     if (state == LS_HEADER) header();
     if (state == LS_SYMBOL) symbol();
-    if (state == LS_COPY) copy_chunk();
-    if (state == LS_FINISH) { oc.flush_bytes(); status = oc.op == isize ? INF_OK : INF_ERR_ISIZE; state = LS_DONE; }
+    if (state == LS_COPY) copy_load();
+    if (state == LS_FINISH) { status = oc.op == isize ? INF_OK : INF_ERR_ISIZE; state = LS_DONE; }
   }
 };
 

@@ -5,6 +5,7 @@
 // FragmentBlocks formation and every ReadBlockProcessor's ProcessBlocks)  ->  S4 scan + intron_stats_kernel.
 // Each device function that restates a reference routine names it (upstream file per SURVEY.md §8a; the
 // mounted /root/reference has no source to cite by line).
+#include <algorithm>
 #include "common.cuh"
 #include "inflate_core.cuh"
 #include "kernels.h"
@@ -40,44 +41,61 @@ __device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// S1: BGZF / DEFLATE inflate, one lane per BGZF block
+// S1: BGZF / DEFLATE inflate, one lane per BGZF block.  Persistent CTAs: every warp claims the next 32 blocks from a
+// global counter until none are left, so a launch has one short tail instead of one per wave.
 template <int WARPS, int LB, int DB>
 __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                              uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
-                                                             int* __restrict__ status, int* __restrict__ err) {
+                                                             int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint16_t* lit = smem_tables + (size_t)warp * (((1 << LB) + (1 << DB) + 64) * 32);  // [lit LUT][dist LUT][2 x 32 canonical-limit entries], lane-interleaved
   uint16_t* dst = lit + (1 << LB) * 32;
-  int b = blockIdx.x * (WARPS * 32) + threadIdx.x;
-  InflateLane<32, LB, DB> L; uint16_t sym_store[320];
-  bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
-  if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
-  // all 32 lanes vote every iteration: this is what keeps the warp converged (see InflateLane)
-  while (__any_sync(0xffffffffu, !L.done())) L.step();
-  if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
+  uint16_t sym_store[320];
+  for (;;) {
+    unsigned int base = 0;
+    if (lane == 0) base = atomicAdd(next_block, 32u);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (base >= (unsigned int)nblk) break;
+    int b = (int)base + lane;
+    InflateLane<32, LB, DB> L;
+    bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
+    if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
+    // all 32 lanes vote every iteration: this is what keeps the warp converged (see InflateLane)
+    while (__any_sync(0xffffffffu, !L.done())) L.step();
+    if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
+  }
 }
 
 template <int WARPS, int LB, int DB>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   size_t smem = (size_t)WARPS * (((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
-  static bool attr_done = false;
-  if (!attr_done) { IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = true; }
-  int grid = (a.nblk + WARPS * 32 - 1) / (WARPS * 32);
-  if (grid > 0) { inflate_kernel<WARPS, LB, DB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err); IRF_LAUNCHED(); }
+  static int ctas_per_sm = 0, sms = 0;
+  if (!ctas_per_sm) {
+    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB>, WARPS * 32, smem));
+    int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+  }
+  int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
+  if (grid > 0) {
+    IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
+    inflate_kernel<WARPS, LB, DB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block); IRF_LAUNCHED();
+  }
 }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
   switch (variant) {   // (warps per CTA, literal LUT bits, distance LUT bits); shared memory per warp = (2^LB + 2^DB + 64) * 64 B
-    case 1: launch_inflate_t<2, 8, 6>(a, s); break;
+    case 1: launch_inflate_t<4, 8, 6>(a, s); break;
     case 2: launch_inflate_t<2, 10, 6>(a, s); break;
     case 3: launch_inflate_t<4, 9, 6>(a, s); break;
-    case 4: launch_inflate_t<2, 9, 6>(a, s); break;
-    case 5: launch_inflate_t<2, 9, 7>(a, s); break;
-    case 6: launch_inflate_t<8, 8, 6>(a, s); break;
+    case 4: launch_inflate_t<4, 6, 6>(a, s); break;
+    case 5: launch_inflate_t<4, 6, 5>(a, s); break;
+    case 6: launch_inflate_t<8, 6, 5>(a, s); break;
     case 7: launch_inflate_t<4, 7, 6>(a, s); break;
     case 8: launch_inflate_t<4, 7, 5>(a, s); break;
     case 9: launch_inflate_t<8, 7, 6>(a, s); break;
-    default: launch_inflate_t<4, 8, 6>(a, s); break;
+    case 10: launch_inflate_t<2, 7, 6>(a, s); break;
+    default: launch_inflate_t<4, 6, 5>(a, s); break;
   }
 }
 
