@@ -17,6 +17,7 @@ constexpr u32 SPAN_OVERHANG_LEFT = 5;      // [C-4]
 constexpr u32 SPAN_OVERHANG_RIGHT = 4;     // [C-4]
 constexpr u32 EDGE_WINDOW_OFFSET = 5;      // [C-13]
 constexpr u32 EDGE_WINDOW_LEN = 50;        // [C-13]
+constexpr int BUCKET_SHIFT = 10;
 
 // ---- junction key: 36-bit concatenated-genome coordinate of the left end, 28-bit gap (CIGAR op lengths are 28-bit)
 constexpr int JKEY_GAP_BITS = 28;
@@ -39,6 +40,11 @@ struct DevTables {
   int n_ref;
   const int32_t* ref_len;   // [n_ref]
   const u64* chr_goff;      // [n_ref + 1] offset of each BAM reference in the concatenated coordinate space
+  // coordinate buckets (1 << BUCKET_SHIFT bases): first table index whose key is >= / > the bucket start, so every
+  // upper_bound becomes one load + a short forward scan instead of a ~20-step binary search
+  const u64* bucket_base;   // [n_ref] first bucket of each reference
+  const u32* bucket_n;      // [n_ref] number of buckets of each reference
+  const u32* sp_bidx; const u32* seg_bidx; const u32* roi_bidx;
   // SpansPoint
   const u32* sp_pos; const Range* sp_range; u32* sp_count; u32 n_sp;          // sp_count[dir * n_sp + i]
   // CoverageBlocks: measured segments (sorted, disjoint), compact depth space with one sentinel slot per segment

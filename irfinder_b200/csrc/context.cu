@@ -15,6 +15,7 @@
 #include <cstring>
 #include <fstream>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/irfinder_b200.h"
@@ -54,8 +55,9 @@ struct irf_ctx {
   // device reference tables
   DevBuf d_ref_len, d_chr_goff, d_sp_pos, d_sp_range, d_sp_count, d_seg_start, d_seg_end, d_seg_coff, d_seg_range, d_diff, d_roi_start, d_roi_end, d_roi_range, d_roi_count, d_chr_count;
   DevBuf d_jc_keys, d_jc_cnt, d_jl_keys, d_jl_cnt, d_jr_keys, d_jr_cnt, d_annot_keys; u64 n_annot = 0; u32 jc_slots = 0, jside_slots = 0;
+  DevBuf d_bucket_base, d_bucket_n, d_sp_bidx, d_seg_bidx, d_roi_bidx;
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
-  DevBuf d_exp_keys[3], d_exp_cnt[3];
+  DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
   DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
@@ -114,6 +116,20 @@ struct irf_ctx {
     }
     upload(d_ref_len, chr_lens, s_compute); upload(d_chr_goff, chr_goff, s_compute); upload(d_sp_range, spr, s_compute); upload(d_seg_range, sgr, s_compute); upload(d_roi_range, ror, s_compute);
     d_chr_count.ensure((size_t)n * 8);
+    // coordinate-bucket indices (common.cuh BUCKET_SHIFT)
+    { vector<u64> bbase(n); vector<u32> bn(n); u64 tot = 0; for (int i = 0; i < n; i++) { bbase[i] = tot; bn[i] = (u32)((u64)std::max(chr_lens[i], 0) >> BUCKET_SHIFT) + 2; tot += bn[i]; }
+      vector<u32> spb(tot), sgb(tot), rob(tot);
+      for (int i = 0; i < n; i++) {
+        u32 a = spr[i].begin, b = sgr[i].begin, c = ror[i].begin;
+        for (u32 k = 0; k < bn[i]; k++) {
+          u64 start = (u64)k << BUCKET_SHIFT;
+          while (a < spr[i].end && sp.pos[a] < start) a++;                 // first point >= bucket start
+          while (b < sgr[i].end && cov.seg_end[b] <= start) b++;           // first segment with end > bucket start
+          while (c < ror[i].end && roi.rois[c].end <= start) c++;
+          spb[bbase[i] + k] = a; sgb[bbase[i] + k] = b; rob[bbase[i] + k] = c;
+        }
+      }
+      upload(d_bucket_base, bbase, s_compute); upload(d_bucket_n, bn, s_compute); upload(d_sp_bidx, spb, s_compute); upload(d_seg_bidx, sgb, s_compute); upload(d_roi_bidx, rob, s_compute); sync(); }
     // annotated junction keys (JunctionCount::loadRef entries on chromosomes present in the BAM)
     std::map<string, int> id; for (int i = n - 1; i >= 0; i--) id[chr_names[i]] = i;
     vector<u64> keys;
@@ -136,6 +152,7 @@ struct irf_ctx {
     upload(d_introns, descs, s_compute); upload(d_iblocks, ib, s_compute); d_rows.ensure(descs.size() * sizeof(IntronRow));
     if (dump_fragments) { dump_cap = 1ull << 26; d_dump.ensure(dump_cap * 4); d_dump_cursor.ensure(8); }
     T.n_ref = n; T.ref_len = d_ref_len.as<int32_t>(); T.chr_goff = d_chr_goff.as<u64>();
+    T.bucket_base = d_bucket_base.as<u64>(); T.bucket_n = d_bucket_n.as<u32>(); T.sp_bidx = d_sp_bidx.as<u32>(); T.seg_bidx = d_seg_bidx.as<u32>(); T.roi_bidx = d_roi_bidx.as<u32>();
     T.sp_pos = d_sp_pos.as<u32>(); T.sp_range = d_sp_range.as<Range>(); T.sp_count = d_sp_count.as<u32>(); T.n_sp = (u32)sp.pos.size();
     T.seg_start = d_seg_start.as<u32>(); T.seg_end = d_seg_end.as<u32>(); T.seg_coff = d_seg_coff.as<u64>(); T.seg_range = d_seg_range.as<Range>(); T.diff = d_diff.as<int32_t>(); T.P = cov.P;
     T.roi_start = d_roi_start.as<u32>(); T.roi_end = d_roi_end.as<u32>(); T.roi_range = d_roi_range.as<Range>(); T.roi_count = d_roi_count.as<u32>(); T.n_roi = (u32)roi.rois.size();
@@ -164,22 +181,57 @@ struct irf_ctx {
   }
 
   // ---------------------------------------------------------------- BGZF scan (SAM v1 §4.1)
-  void scan_bgzf(const uint8_t* p, size_t n_own, size_t n_total) {
-    blks.clear(); nblk_own = 0; size_t off = 0;
-    while (off < n_total) {
-      if (off + 18 > n_total) { if (off >= n_own) break; throw string("truncated BGZF block header"); }
-      const uint8_t* h = p + off;
-      if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) throw string("not a BGZF block at offset ") + std::to_string(off);
-      u32 xlen = h[10] | (u32)h[11] << 8; if (off + 12 + xlen > n_total) { if (off >= n_own) break; throw string("truncated BGZF extra field"); }
-      int bsize = -1; for (u32 x = 0; x + 4 <= xlen;) { const uint8_t* sf = h + 12 + x; u32 slen = sf[2] | (u32)sf[3] << 8; if (sf[0] == 'B' && sf[1] == 'C' && slen == 2) { bsize = sf[4] | (int)sf[5] << 8; break; } x += 4 + slen; }
-      if (bsize < 0) throw string("BGZF block without BC subfield at offset ") + std::to_string(off);
-      size_t total = (size_t)bsize + 1; if (total < 12 + xlen + 8) throw string("bad BGZF BSIZE");
-      if (off + total > n_total) { if (off >= n_own) break; throw string("truncated BGZF block (file cut short)"); }
-      Blk b; b.file_off = off; b.c_off = off + 12 + xlen; b.c_len = (u32)(total - 12 - xlen - 8); memcpy(&b.isize, p + off + total - 4, 4);
-      if (b.isize > 65536) throw string("BGZF ISIZE > 64 KiB");
-      if (off < n_own) nblk_own++;
-      blks.push_back(b); off += total;
+  // Parses one block header at `off`; returns false when the bytes there cannot be a complete block inside [0, n_total).
+  static bool parse_block(const uint8_t* p, size_t off, size_t n_total, Blk& b, size_t& total, string* why) {
+    if (off + 18 > n_total) { if (why) *why = "truncated BGZF block header"; return false; }
+    const uint8_t* h = p + off;
+    if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) { if (why) *why = string("not a BGZF block at offset ") + std::to_string(off); return false; }
+    u32 xlen = h[10] | (u32)h[11] << 8; if (off + 12 + xlen > n_total) { if (why) *why = "truncated BGZF extra field"; return false; }
+    int bsize = -1; for (u32 x = 0; x + 4 <= xlen;) { const uint8_t* sf = h + 12 + x; u32 slen = sf[2] | (u32)sf[3] << 8; if (sf[0] == 'B' && sf[1] == 'C' && slen == 2) { bsize = sf[4] | (int)sf[5] << 8; break; } x += 4 + slen; }
+    if (bsize < 0) { if (why) *why = string("BGZF block without BC subfield at offset ") + std::to_string(off); return false; }
+    total = (size_t)bsize + 1; if (total < 12 + xlen + 8) { if (why) *why = "bad BGZF BSIZE"; return false; }
+    if (off + total > n_total) { if (why) *why = "truncated BGZF block (file cut short)"; return false; }
+    b.file_off = off; b.c_off = off + 12 + xlen; b.c_len = (u32)(total - 12 - xlen - 8); memcpy(&b.isize, p + off + total - 4, 4);
+    if (b.isize > 65536) { if (why) *why = "BGZF ISIZE > 64 KiB"; return false; }
+    return true;
+  }
+  // Serial walk of the BSIZE chain from `off` to `stop` (exclusive); throws on a malformed block unless it lies in the look-ahead.
+  void scan_range(const uint8_t* p, size_t off, size_t stop, size_t n_own, size_t n_total, vector<Blk>& out, size_t& end_off) {
+    while (off < stop) {
+      Blk b; size_t total = 0; string why;
+      if (!parse_block(p, off, n_total, b, total, &why)) { if (off >= n_own && why.find("truncated") != string::npos) break; throw why; }
+      out.push_back(b); off += total;
     }
+    end_off = off;
+  }
+  // The chain is serial (each header gives the next offset) and latency-bound on a 10+ GB buffer, so large inputs are cut into
+  // segments: each worker finds a block start by magic + 3 verified hops, walks its segment, and the joins are checked
+  // (a worker must land exactly on the next worker's start); any disagreement falls back to the serial walk.
+  void scan_bgzf(const uint8_t* p, size_t n_own, size_t n_total) {
+    blks.clear(); nblk_own = 0;
+    unsigned nt = std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    bool done = false;
+    if (n_total >= (256ull << 20) && nt > 1) {
+      vector<size_t> start(nt + 1, n_total); start[0] = 0; bool ok = true;
+      for (unsigned t = 1; t < nt && ok; t++) {
+        size_t off = n_total / nt * t, lim = std::min(n_total, off + (1u << 20)); bool found = false;
+        for (; off + 18 <= lim; off++) {
+          if (p[off] != 31 || p[off + 1] != 139 || p[off + 2] != 8 || !(p[off + 3] & 4)) continue;
+          size_t cur = off; int hops = 0; for (; hops < 3 && cur < n_total; hops++) { Blk b; size_t total; if (!parse_block(p, cur, n_total, b, total, nullptr)) break; cur += total; }
+          if (hops == 3 || cur >= n_total) { found = true; break; }
+        }
+        if (!found) ok = false; else start[t] = off;
+      }
+      if (ok) {
+        vector<vector<Blk>> parts(nt); vector<size_t> ends(nt, 0); vector<string> errs(nt); vector<std::thread> th;
+        for (unsigned t = 0; t < nt; t++) th.emplace_back([&, t]() { try { scan_range(p, start[t], start[t + 1], n_own, n_total, parts[t], ends[t]); } catch (const string& e) { errs[t] = e; } });
+        for (auto& x : th) x.join();
+        for (unsigned t = 0; t < nt && ok; t++) { if (!errs[t].empty()) ok = false; else if (t + 1 < nt && ends[t] != start[t + 1]) ok = false; }
+        if (ok) { size_t tot = 0; for (auto& v : parts) tot += v.size(); blks.reserve(tot); for (auto& v : parts) blks.insert(blks.end(), v.begin(), v.end()); done = true; }
+      }
+    }
+    if (!done) { blks.clear(); size_t e = 0; scan_range(p, 0, n_total, n_own, n_total, blks, e); }
+    for (auto& b : blks) if (b.file_off < n_own) nblk_own++;
   }
 
   void stage(const void* src, size_t n_own, size_t n_total, int has_header, bool copy_now) {
@@ -341,36 +393,40 @@ struct irf_ctx {
     if (!counted) throw string("irf_count has not run");
     if (finalized) return;
     cudaEvent_t e0, e1; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventRecord(e0, s_compute));
-    u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0);
-    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute);
+    const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr; double tdbg = now_ms(); auto mark = [&](const char* what) { if (dbg) { sync(); double t = now_ms(); fprintf(stderr, "[finalize] %-22s %8.3f ms\n", what, t - tdbg); tdbg = t; } };
+    u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0); mark("leftovers");
+    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute); mark("depth scan");
     // junctions -> host (JunctionCount map contents)
     u64 nj = export_table(0); vector<u64> k(nj); vector<u32> c(nj * 2);
-    if (nj) { IRF_CUDA(cudaMemcpyAsync(k.data(), d_exp_keys[0].p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(c.data(), d_exp_cnt[0].p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); sync(); }
+    if (nj) {   // sort by key on the device: key order == (refID, start, end) order
+      size_t tb = junction_sort_temp_bytes(nj); d_sort_tmp.ensure(tb); d_sort_keys.ensure(nj * 8); d_sort_cnt.ensure(nj * 8);
+      launch_junction_sort(d_sort_tmp.p, tb, d_exp_keys[0].as<u64>(), d_sort_keys.as<u64>(), d_exp_cnt[0].as<u64>(), d_sort_cnt.as<u64>(), nj, s_compute);
+      IRF_CUDA(cudaMemcpyAsync(k.data(), d_sort_keys.p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(c.data(), d_sort_cnt.p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); sync();
+    }
     h_junc.resize(nj);
-    for (u64 i = 0; i < nj; i++) { u64 gl = k[i] >> JKEY_GAP_BITS, gap = k[i] & ((1ull << JKEY_GAP_BITS) - 1); int rid = (int)(std::upper_bound(chr_goff.begin(), chr_goff.end(), gl) - chr_goff.begin()) - 1;
-      h_junc[i] = JuncEntry{rid, (u32)(gl - chr_goff[rid]), (u32)(gl - chr_goff[rid] + gap), {c[2 * i], c[2 * i + 1]}}; }
-    std::sort(h_junc.begin(), h_junc.end(), [](const JuncEntry& a, const JuncEntry& b) { if (a.refid != b.refid) return a.refid < b.refid; if (a.start != b.start) return a.start < b.start; return a.end < b.end; });
+    { int rid = 0; for (u64 i = 0; i < nj; i++) { u64 gl = k[i] >> JKEY_GAP_BITS, gap = k[i] & ((1ull << JKEY_GAP_BITS) - 1); while (rid + 1 < (int)chr_goff.size() - 1 && gl >= chr_goff[rid + 1]) rid++;
+        h_junc[i] = JuncEntry{rid, (u32)(gl - chr_goff[rid]), (u32)(gl - chr_goff[rid] + gap), {c[2 * i], c[2 * i + 1]}}; } }
     h_junc_out.resize(nj); for (u64 i = 0; i < nj; i++) h_junc_out[i] = JuncOut{h_junc[i].refid, h_junc[i].start, h_junc[i].end, h_junc[i].cnt[0], h_junc[i].cnt[1]};
-    dir_log.clear(); directionality = directional(jref, chr_names, h_junc, dir_log);
+    mark("junction export+sort"); dir_log.clear(); directionality = directional(jref, chr_names, h_junc, dir_log); mark("directional");
     // per-intron statistics
     u32* dmax = d_small.as<u32>() + 2; IRF_CUDA(cudaMemsetAsync(dmax, 0, 4, s_compute)); launch_max_depth(T.diff, cov.P, dmax, s_compute);
     u32 hmax = 0; IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
-    u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
+    mark("max depth"); u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
     u32 bins = hmax >= 8192 ? hmax + 1 : 1; d_scratch.ensure((u64)grid * bins * 4);
     launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
     rows_nondir.resize(n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
-    rows_dir.clear();
+    mark("intron stats nondir"); rows_dir.clear();
     if (directionality != 0) {
       launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, directionality, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
       rows_dir.resize(n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
     }
-    h_stats.assign(ST_COUNT, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
+    mark("intron stats dir"); h_stats.assign(ST_COUNT, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
     IRF_CUDA(cudaMemcpyAsync(h_stats.data(), d_stats.p, ST_COUNT * 8, cudaMemcpyDeviceToHost, s_compute));
     if (!h_sp.empty()) IRF_CUDA(cudaMemcpyAsync(h_sp.data(), d_sp_count.p, h_sp.size() * 4, cudaMemcpyDeviceToHost, s_compute));
     if (!h_roi.empty()) IRF_CUDA(cudaMemcpyAsync(h_roi.data(), d_roi_count.p, h_roi.size() * 4, cudaMemcpyDeviceToHost, s_compute));
     if (!h_chr.empty()) IRF_CUDA(cudaMemcpyAsync(h_chr.data(), d_chr_count.p, h_chr.size() * 4, cudaMemcpyDeviceToHost, s_compute));
     IRF_CUDA(cudaEventRecord(e1, s_compute)); sync();
-    check_dev_err("finalize");
+    check_dev_err("finalize"); mark("tables d2h");
     h_stats[ST_ERROR] += errors;
     float ms; IRF_CUDA(cudaEventElapsedTime(&ms, e0, e1)); timing[4] = ms; cudaEventDestroy(e0); cudaEventDestroy(e1);
     h_dump.clear(); h_depth.clear();
@@ -434,10 +490,10 @@ int irf_create(irf_ctx** out, const int* device_ids, int n_devices) {
 void irf_destroy(irf_ctx* c) {
   if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
-                   &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_stats, &c->d_err, &c->d_introns,
+                   &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
-                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2]};
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy);

@@ -111,7 +111,11 @@ struct Huff {
       symbol[offs[l]++] = (uint16_t)s;
       uint32_t code = next_code[l]++;
       if (l <= BITS) {
+#ifdef __CUDA_ARCH__
+        uint32_t rev = __brev(code) >> (32 - l);
+#else
         uint32_t rev = 0; for (int b = 0; b < l; b++) rev |= ((code >> b) & 1u) << (l - 1 - b);
+#endif
         uint16_t e = (uint16_t)(s << 4 | l);
         for (uint32_t i = rev; i < (1u << BITS); i += (1u << l)) lut.set(i, e);
       }
@@ -298,11 +302,13 @@ struct InflateLane {
     pend_n = k; copy_len -= k;
   }
 
-  IRF_HD void step() {
+  // allow_header: the GPU driver loop batches header work (a table build costs thousands of instructions, and in lock-step
+  // every lane pays for it), so a lane waiting in LS_HEADER only proceeds when enough lanes wait with it.
+  IRF_HD void step(bool allow_header = true) {
     if (pend_n) copy_store();
     if (state == LS_SLOWLIT) { state = LS_SYMBOL; handle_litlen(slow_sym); }
     else if (state == LS_SLOWDIST) handle_dist(slow_sym);
-    if (state == LS_HEADER) header();
+    if (state == LS_HEADER && allow_header) header();
     if (state == LS_SYMBOL) symbol();
     if (state == LS_COPY) copy_load();
     if (state == LS_FINISH) { status = oc.op == isize ? INF_OK : INF_ERR_ISIZE; state = LS_DONE; }

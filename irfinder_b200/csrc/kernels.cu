@@ -6,6 +6,7 @@
 // Each device function that restates a reference routine names it (upstream file per SURVEY.md §8a; the
 // mounted /root/reference has no source to cite by line).
 #include <algorithm>
+#include <cub/device/device_radix_sort.cuh>
 #include "common.cuh"
 #include "inflate_core.cuh"
 #include "kernels.h"
@@ -43,7 +44,7 @@ __device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
 // ------------------------------------------------------------------------------------------------
 // S1: BGZF / DEFLATE inflate, one lane per BGZF block.  Persistent CTAs: every warp claims the next 32 blocks from a
 // global counter until none are left, so a launch has one short tail instead of one per wave.
-template <int WARPS, int LB, int DB>
+template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM>
 __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                              uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                              int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block) {
@@ -52,42 +53,71 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
   uint16_t* lit = smem_tables + (size_t)warp * (((1 << LB) + (1 << DB) + 64) * 32);  // [lit LUT][dist LUT][2 x 32 canonical-limit entries], lane-interleaved
   uint16_t* dst = lit + (1 << LB) * 32;
   uint16_t sym_store[320];
+  if (!LANE_CLAIM) {   // warp-granular claims: 32 consecutive blocks per warp, all lanes start together
+    for (;;) {
+      unsigned int base = 0;
+      if (lane == 0) base = atomicAdd(next_block, 32u);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (base >= (unsigned int)nblk) break;
+      int b = (int)base + lane;
+      InflateLane<32, LB, DB> L;
+      bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
+      if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
+      while (__any_sync(0xffffffffu, !L.done())) L.step();   // the vote keeps the warp converged (see InflateLane)
+      if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
+    }
+    return;
+  }
+  InflateLane<32, LB, DB> L; L.idle();
+  int b = -1; bool exhausted = false;
+  // HEADER_BATCH: lanes that must be waiting for a block header before the warp pays for one
   for (;;) {
-    unsigned int base = 0;
-    if (lane == 0) base = atomicAdd(next_block, 32u);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (base >= (unsigned int)nblk) break;
-    int b = (int)base + lane;
-    InflateLane<32, LB, DB> L;
-    bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
-    if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
-    // all 32 lanes vote every iteration: this is what keeps the warp converged (see InflateLane)
-    while (__any_sync(0xffffffffu, !L.done())) L.step();
-    if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
+    // lanes that finished their block report it and claim the next one (warp-aggregated counter bump): no lane idles
+    // while another lane of its warp still has half a block to go
+    bool need = L.done() && !exhausted;
+    if (need && b >= 0 && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
+    unsigned int m = __ballot_sync(0xffffffffu, need);
+    if (m) {
+      unsigned int base = 0; int leader = __ffs(m) - 1;
+      if (lane == leader) base = atomicAdd(next_block, (unsigned int)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (need) {
+        unsigned int nb = base + (unsigned int)__popc(m & ((1u << lane) - 1u));
+        if (nb < (unsigned int)nblk) { b = (int)nb; if (u_len[b] == 0 && c_len[b] <= 2) L.idle(); else L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); }
+        else { b = -1; exhausted = true; }
+      }
+    }
+    if (!__any_sync(0xffffffffu, !L.done() || !exhausted)) break;
+    unsigned int mh = __ballot_sync(0xffffffffu, L.state == LS_HEADER);
+    unsigned int mrun = __ballot_sync(0xffffffffu, !L.done() && L.state != LS_HEADER);
+    const bool allow_header = __popc(mh) >= HEADER_BATCH || mrun == 0;
+    // the bookkeeping votes above run once per 8 steps; inside the group a plain warp barrier keeps the lanes converged
+#pragma unroll 1
+    for (int k = 0; k < 8; k++) { L.step(allow_header); __syncwarp(); }
   }
 }
 
-template <int WARPS, int LB, int DB>
+template <int WARPS, int LB, int DB, int HB = 1, int LC = 0>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   size_t smem = (size_t)WARPS * (((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
   static int ctas_per_sm = 0, sms = 0;
   if (!ctas_per_sm) {
-    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB>, WARPS * 32, smem));
+    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB, HB, LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB, HB, LC>, WARPS * 32, smem));
     int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
   int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-    inflate_kernel<WARPS, LB, DB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block); IRF_LAUNCHED();
+    inflate_kernel<WARPS, LB, DB, HB, LC><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block); IRF_LAUNCHED();
   }
 }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
   switch (variant) {   // (warps per CTA, literal LUT bits, distance LUT bits); shared memory per warp = (2^LB + 2^DB + 64) * 64 B
-    case 1: launch_inflate_t<4, 8, 6>(a, s); break;
-    case 2: launch_inflate_t<2, 10, 6>(a, s); break;
-    case 3: launch_inflate_t<4, 9, 6>(a, s); break;
+    case 1: launch_inflate_t<4, 6, 5, 1, 1>(a, s); break;
+    case 2: launch_inflate_t<4, 6, 5, 4, 1>(a, s); break;
+    case 3: launch_inflate_t<4, 6, 5, 8, 1>(a, s); break;
     case 4: launch_inflate_t<4, 6, 6>(a, s); break;
     case 5: launch_inflate_t<4, 6, 5>(a, s); break;
     case 6: launch_inflate_t<8, 6, 5>(a, s); break;
@@ -256,6 +286,7 @@ struct FragSink {
       else atomicOr(T.err, DERR_DUMP_FULL);
     }
   }
+  __device__ __forceinline__ u64 bucket_of(u32 pos) const { u32 b = pos >> BUCKET_SHIFT, nb = T.bucket_n[chr]; return T.bucket_base[chr] + (b < nb ? b : nb - 1); }
   __device__ void begin_read(u32 rs) { read_start = rs; have_prev = false; dump_read++; }
   __device__ void end_fragment(int readCount) { if (dump_base) { dump_base[1] = (u32)chr; dump_base[2] = (u32)dir; dump_base[3] = (u32)readCount; dump_base[4] = dump_nb[0]; dump_base[5] = dump_nb[1]; } }
 
@@ -269,14 +300,16 @@ struct FragSink {
   }
   // SpansPoint::ProcessBlocks (row a8): points p with start < p < end
   __device__ void spans(u32 start, u32 end) {
-    Range r = T.sp_range[chr]; u32 lo = r.begin, hi = r.end;
-    while (lo < hi) { u32 mid = (lo + hi) >> 1; if (T.sp_pos[mid] <= start) lo = mid + 1; else hi = mid; }  // upper_bound(start)
+    Range r = T.sp_range[chr]; if (r.begin == r.end) return;
+    u32 lo = T.sp_bidx[bucket_of(start)];                                   // first point >= the bucket start
+    while (lo < r.end && T.sp_pos[lo] <= start) lo++;                        // upper_bound(start)
     for (; lo < r.end && T.sp_pos[lo] < end; lo++) atomicAdd(&T.sp_count[(u64)dir * T.n_sp + lo], 1u);
   }
   // CoverageBlocks::ProcessBlocks + CoverageBlock::RecordCover (row a9): +1 at start, -1 at end, clipped per measured segment
   __device__ void coverage(u32 start, u32 end) {
-    Range r = T.seg_range[chr]; u32 lo = r.begin, hi = r.end;
-    while (lo < hi) { u32 mid = (lo + hi) >> 1; if (T.seg_end[mid] <= start) lo = mid + 1; else hi = mid; }  // first segment with end > start
+    Range r = T.seg_range[chr]; if (r.begin == r.end) return;
+    u32 lo = T.seg_bidx[bucket_of(start)];                                  // first segment with end > the bucket start
+    while (lo < r.end && T.seg_end[lo] <= start) lo++;                       // first segment with end > start
     for (; lo < r.end; lo++) {
       u32 ss = T.seg_start[lo]; if (ss >= end) break;
       u32 a = max(start, ss), b = min(end, T.seg_end[lo]);
@@ -294,9 +327,11 @@ struct FragSink {
   }
   // FragmentsInChr / FragmentsInROI ::ProcessBlocks (row a13)
   __device__ void fragment_counts(u32 fs, u32 fe) {
-    atomicAdd(&T.chr_count[(u64)dir * T.n_ref + chr], 1u);
-    Range r = T.roi_range[chr]; u32 lo = r.begin, hi = r.end;
-    while (lo < hi) { u32 mid = (lo + hi) >> 1; if (T.roi_end[mid] <= fs) lo = mid + 1; else hi = mid; }  // first ROI with end > fs
+    { u32 key = (u32)dir * (u32)T.n_ref + (u32)chr; u32 act = __activemask(); u32 grp = __match_any_sync(act, key);   // neighbouring records share chromosome and strand
+      if ((int)(__ffs(grp) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&T.chr_count[key], (u32)__popc(grp)); }
+    Range r = T.roi_range[chr]; if (r.begin == r.end) return;
+    u32 lo = T.roi_bidx[bucket_of(fs)];
+    while (lo < r.end && T.roi_end[lo] <= fs) lo++;                          // first ROI with end > fs
     if (lo < r.end && T.roi_start[lo] <= fs && fe <= T.roi_end[lo]) atomicAdd(&T.roi_count[(u64)dir * T.n_roi + lo], 1u);
   }
 };
@@ -418,7 +453,8 @@ __global__ void __launch_bounds__(128) process_records_kernel(DevTables T, const
       if (pair_lookup_or_wait(T, ptab, pmask, U, e, c, mo, m)) {
         st.paired++;
         bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);
-        if (first_is_me) process_pair(T, U, e, c, mo, m, sink, st); else process_pair(T, U, mo, m, e, c, sink, st);
+        u64 o1 = first_is_me ? e : mo, o2 = first_is_me ? mo : e; Core c1 = first_is_me ? c : m, c2 = first_is_me ? m : c;
+        process_pair(T, U, o1, c1, o2, c2, sink, st);
       }
     }
   }
@@ -476,7 +512,8 @@ __global__ void halo_process_kernel(DevTables T, const uint8_t* __restrict__ H, 
     if ((u32)(pair_key(H, e, c) >> 8) % nowners == owner) {
       st.paired++;
       bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);
-      if (first_is_me) process_pair(T, H, e, c, mo, m, sink, st); else process_pair(T, H, mo, m, e, c, sink, st);
+      u64 o1 = first_is_me ? e : mo, o2 = first_is_me ? mo : e; Core c1 = first_is_me ? c : m, c2 = first_is_me ? m : c;
+      process_pair(T, H, o1, c1, o2, c2, sink, st);
     }
   }
   if (st.paired) atomicAdd(&T.stats[ST_PAIRED], (u64)st.paired);
@@ -504,6 +541,12 @@ __global__ void ht_compact_kernel(const u64* __restrict__ keys, const u32* __res
   u64 k = keys[i]; if (k == JKEY_EMPTY) return;
   u32 a = cnt[2 * i], b = cnt[2 * i + 1]; if (only_counted && !a && !b) return;
   u64 at = atomicAdd(cursor, 1ull); if (at < cap) { out_keys[at] = k; out_cnt[2 * at] = a; out_cnt[2 * at + 1] = b; }
+}
+// Sorts the exported (key, counts) list by key so the host can emit JuncCount rows without sorting: keys order like (refID, start, end).
+// CUB's radix sort is used for this small auxiliary step (a few hundred thousand entries once per run).
+size_t junction_sort_temp_bytes(u64 n) { size_t b = 0; cub::DeviceRadixSort::SortPairs(nullptr, b, (const u64*)nullptr, (u64*)nullptr, (const u64*)nullptr, (u64*)nullptr, (int)n); return b; }
+void launch_junction_sort(void* temp, size_t temp_bytes, const u64* keys_in, u64* keys_out, const u64* cnt_in, u64* cnt_out, u64 n, cudaStream_t s) {
+  if (n) { cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, cnt_in, cnt_out, (int)n, 0, 64, s); IRF_LAUNCHED(); }
 }
 void launch_ht_insert_keys(u64* keys, u32 mask, const u64* in, u64 n, int* err, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { ht_insert_keys_kernel<<<(unsigned)g, 256, 0, s>>>(keys, mask, in, n, err); IRF_LAUNCHED(); } }
 void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32* in_cnt, u64 n, int* err, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { ht_add_kernel<<<(unsigned)g, 256, 0, s>>>(keys, cnt, mask, in_keys, in_cnt, n, err); IRF_LAUNCHED(); } }

@@ -30,6 +30,8 @@ void launch_halo_process(const DevTables& T, const uint8_t* H, u64 Hend, const u
 void launch_ht_insert_keys(u64* keys, u32 mask, const u64* in, u64 n, int* err, cudaStream_t s);
 void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32* in_cnt, u64 n, int* err, cudaStream_t s);
 void launch_ht_compact(const u64* keys, const u32* cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted, cudaStream_t s);
+size_t junction_sort_temp_bytes(u64 n);
+void launch_junction_sort(void* temp, size_t temp_bytes, const u64* keys_in, u64* keys_out, const u64* cnt_in, u64* cnt_out, u64 n, cudaStream_t s);
 void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s);
 u64 depth_scan_tiles(u64 n);
 void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s);

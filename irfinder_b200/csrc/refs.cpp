@@ -37,6 +37,8 @@ void JunctionRef::loadRef(std::istream& in) {
     u32& bits = chr_junc[f[0]][std::make_pair((u32)std::stoul(f[1]), (u32)std::stoul(f[2]))];
     if (f[3] == "-") bits |= 1; else if (f[3] == "+") bits |= 2;
   }
+  flat.clear();
+  for (auto& c : chr_junc) { auto& v = flat[c.first]; v.reserve(c.second.size()); for (auto& j : c.second) v.push_back(JRow{j.first.first, j.first.second, j.second, 0, 0}); }
 }
 
 // FragmentsInROI::loadRef — "chr start end name", kept sorted by end
@@ -112,11 +114,9 @@ std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>
   return out;
 }
 
-struct JRow { u32 start, end, bits, c0, c1; };
 // per-chromosome rows in (start,end) order: annotated junctions (possibly uncounted) merged with counted ones
 static std::map<std::string, std::vector<JRow>> merged_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
-  std::map<std::string, std::vector<JRow>> out;
-  for (auto& c : ref.chr_junc) { auto& v = out[c.first]; v.reserve(c.second.size()); for (auto& j : c.second) v.push_back(JRow{j.first.first, j.first.second, j.second, 0, 0}); }
+  std::map<std::string, std::vector<JRow>> out = ref.flat;
   std::map<std::string, std::vector<JRow>> extra;
   for (auto& e : counted) { if (e.refid < 0 || e.refid >= (int)chr_names.size()) continue; extra[chr_names[e.refid]].push_back(JRow{e.start, e.end, 0, e.cnt[0], e.cnt[1]}); }
   for (auto& x : extra) {
@@ -140,14 +140,19 @@ std::string format_junctions(const JunctionRef& ref, const std::vector<std::stri
   return s;
 }
 int directional(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted, std::string& log) {
-  auto m = merged_junctions(ref, chr_names, counted);
+  // only counted junctions can pass the evidence threshold, so walk those and look the annotation up (no merged map needed)
   unsigned long long same = 0, diff = 0, ev = 0, nev = 0, evk = 0, nevk = 0;
-  for (auto& c : m) for (auto& r : c.second) {  // thresholds [C-11]
-    if (r.c0 + r.c1 > 8) {
-      if (r.c0 > r.c1 * 4) { ev++; if (r.bits) evk++; if (r.bits == 1) same++; else if (r.bits == 2) diff++; }
-      else if (r.c1 > r.c0 * 4) { ev++; if (r.bits) evk++; if (r.bits == 2) same++; else if (r.bits == 1) diff++; }
-      else { nev++; if (r.bits) nevk++; }
-    }
+  std::vector<const std::vector<JRow>*> by_id(chr_names.size(), nullptr);
+  for (size_t i = 0; i < chr_names.size(); i++) { auto it = ref.flat.find(chr_names[i]); if (it != ref.flat.end()) by_id[i] = &it->second; }
+  for (auto& e : counted) {  // thresholds [C-11]
+    u32 c0 = e.cnt[0], c1 = e.cnt[1]; if (c0 + c1 <= 8) continue;
+    u32 bits = 0;
+    if (e.refid >= 0 && e.refid < (int)by_id.size() && by_id[e.refid]) { auto& v = *by_id[e.refid];
+      auto it = std::lower_bound(v.begin(), v.end(), e, [](const JRow& r, const JuncEntry& k) { return r.start != k.start ? r.start < k.start : r.end < k.end; });
+      if (it != v.end() && it->start == e.start && it->end == e.end) bits = it->bits; }
+    if (c0 > c1 * 4) { ev++; if (bits) evk++; if (bits == 1) same++; else if (bits == 2) diff++; }
+    else if (c1 > c0 * 4) { ev++; if (bits) evk++; if (bits == 2) same++; else if (bits == 1) diff++; }
+    else { nev++; if (bits) nevk++; }
   }
   auto line = [&](const char* k, unsigned long long v) { log += k; put_u(log, v); log += '\n'; };
   line("Directionality: Dir evidence:\t", ev); line("Directionality: Nondir evidence:\t", nev);

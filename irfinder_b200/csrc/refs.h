@@ -20,8 +20,10 @@ struct SpansPointRef {
   void loadRef(std::istream& in);
   int lookup_index(const std::string& chr, u32 p) const;  // -1 when absent
 };
+struct JRow { u32 start, end, bits, c0, c1; };
 struct JunctionRef {
   std::map<std::string, std::map<std::pair<u32, u32>, u32>> chr_junc;  // value: annotated strand bits (1 '-', 2 '+')
+  std::map<std::string, std::vector<JRow>> flat;                        // the same, as (start,end)-sorted rows with zero counts
   void loadRef(std::istream& in);
   size_t size() const { size_t n = 0; for (auto& c : chr_junc) n += c.second.size(); return n; }
 };
