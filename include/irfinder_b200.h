@@ -103,6 +103,19 @@ int irf_export_halo(irf_ctx* ctx, void** dev_bytes, size_t* nbytes, void** dev_o
 /* Pairs the gathered halo records of all shards; this context counts the pairs whose key hash % n_owners == owner. */
 int irf_import_halo(irf_ctx* ctx, const void* dev_bytes, size_t nbytes, const void* dev_offsets, size_t nrec, int owner, int n_owners);
 
+/* No counterpart in the reference (it has no GPU path and therefore no allocation question).
+ * Depth scan for callers that must not allocate GPU memory: out[i] = in[0] + ... + in[i] over `n` int32 difference
+ * counters, the same operation irf_finalize applies to the CoverageBlocks counters.  `diff_dev` and `depth_dev` are the
+ * caller's device buffers (they may be the same buffer); `cuda_stream` is a cudaStream_t or NULL; the work is queued on
+ * that stream and the call returns without waiting for it.  The call performs no cudaMalloc/cudaFree: its scratch is
+ * a 128 KB array that is part of the library image on every GPU.  Consequences the caller must know:
+ *   - at most 2^27 counters (512 MB) per call; a larger n is refused with IRF_ECAPACITY and an explanatory message;
+ *   - all calls on a GPU share that array, so calls that overlap in time on one GPU corrupt each other: serialise them;
+ *   - the first call made with a given GPU current looks the array's address up in the CUDA runtime; make that first
+ *     call during set-up, before any stream capture starts.
+ * `errbuf` (optional) receives a NUL-terminated message on failure.  Returns IRF_OK or a negative IRF_E* code. */
+int irf_depth_scan_static(const int32_t* diff_dev, int32_t* depth_dev, size_t n, void* cuda_stream, char* errbuf, size_t errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -7,6 +7,6 @@ BuildRef-format reference files, run a BAM, write the six output tables.  It bin
 ctypes and never computes anything itself: if the library is missing or no GPU is present, every
 operation raises.
 """
-from .api import IRFinderCore, IRFError, lib_path, load_library, TABLES  # noqa: F401
+from .api import IRFinderCore, IRFError, depth_scan_static, lib_path, load_library, TABLES  # noqa: F401
 
-__all__ = ["IRFinderCore", "IRFError", "lib_path", "load_library", "TABLES"]
+__all__ = ["IRFinderCore", "IRFError", "depth_scan_static", "lib_path", "load_library", "TABLES"]

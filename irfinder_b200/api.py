@@ -53,6 +53,7 @@ SYMBOLS = {
     "irf_import_junctions": (_i, [_vp, _i, _vp, _vp, _sz]),
     "irf_export_halo": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz), C.POINTER(_vp), C.POINTER(_sz)]),
     "irf_import_halo": (_i, [_vp, _vp, _sz, _vp, _sz, _i, _i]),
+    "irf_depth_scan_static": (_i, [_vp, _vp, _sz, _vp, C.c_char_p, _sz]),
 }
 _lib = None
 
@@ -199,3 +200,14 @@ class IRFinderCore:
 
     def import_halo(self, bytes_ptr, nbytes, offsets_ptr, nrec, owner, n_owners):
         self._ck(self.lib.irf_import_halo(self.h, _vp(bytes_ptr), nbytes, _vp(offsets_ptr), nrec, owner, n_owners))
+
+
+def depth_scan_static(diff_ptr, depth_ptr, n, stream=None):
+    """Allocation-free depth scan (irf_depth_scan_static): for hosts whose GPU memory is fully pre-partitioned, or that
+    cannot afford the device-wide stall of cudaMalloc/cudaFree inside their loop.  Device pointers in, nothing returned;
+    the work is queued on `stream`.  At most 2**27 counters per call; calls on one GPU must not overlap (shared scratch)."""
+    lib = load_library()
+    err = C.create_string_buffer(512)
+    rc = lib.irf_depth_scan_static(_vp(diff_ptr), _vp(depth_ptr), int(n), _vp(stream) if stream else None, err, len(err))
+    if rc != 0:
+        raise IRFError(rc, err.value.decode(errors="replace"))
