@@ -44,14 +44,17 @@ __device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
 // ------------------------------------------------------------------------------------------------
 // S1: BGZF / DEFLATE inflate, one lane per BGZF block.  Persistent CTAs: every warp claims the next 32 blocks from a
 // global counter until none are left, so a launch has one short tail instead of one per wave.
-template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM>
+template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM, int RB, int PZ>
 __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                              uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                              int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint16_t* lit = smem_tables + (size_t)warp * (((1 << LB) + (1 << DB) + 64) * 32);  // [lit LUT][dist LUT][2 x 32 canonical-limit entries], lane-interleaved
+  // per warp: [lit LUT][dist LUT][2 x 32 canonical-limit entries] (16-bit, lane-interleaved) [output ring: 2^RB bytes per lane]
+  constexpr size_t WARP_U16 = ((1 << LB) + (1 << DB) + 64) * 32 + (RB ? ((1 << RB) * 32) / 2 : 0);
+  uint16_t* lit = smem_tables + (size_t)warp * WARP_U16;
   uint16_t* dst = lit + (1 << LB) * 32;
+  uint8_t* ring = RB ? (uint8_t*)(lit + ((1 << LB) + (1 << DB) + 64) * 32) : nullptr;
   uint16_t sym_store[320];
   if (!LANE_CLAIM) {   // warp-granular claims: 32 consecutive blocks per warp, all lanes start together
     for (;;) {
@@ -60,15 +63,15 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
       base = __shfl_sync(0xffffffffu, base, 0);
       if (base >= (unsigned int)nblk) break;
       int b = (int)base + lane;
-      InflateLane<32, LB, DB> L;
+      InflateLane<32, LB, DB, RB, PZ> L;
       bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
-      if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
+      if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, ring); else L.idle();
       while (__any_sync(0xffffffffu, !L.done())) L.step();   // the vote keeps the warp converged (see InflateLane)
       if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
     }
     return;
   }
-  InflateLane<32, LB, DB> L; L.idle();
+  InflateLane<32, LB, DB, RB, PZ> L; L.idle();
   int b = -1; bool exhausted = false;
   // HEADER_BATCH: lanes that must be waiting for a block header before the warp pays for one
   for (;;) {
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
       base = __shfl_sync(0xffffffffu, base, leader);
       if (need) {
         unsigned int nb = base + (unsigned int)__popc(m & ((1u << lane) - 1u));
-        if (nb < (unsigned int)nblk) { b = (int)nb; if (u_len[b] == 0 && c_len[b] <= 2) L.idle(); else L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); }
+        if (nb < (unsigned int)nblk) { b = (int)nb; if (u_len[b] == 0 && c_len[b] <= 2) L.idle(); else L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, ring); }
         else { b = -1; exhausted = true; }
       }
     }
@@ -97,35 +100,34 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
   }
 }
 
-template <int WARPS, int LB, int DB, int HB = 1, int LC = 0>
+template <int WARPS, int LB, int DB, int HB = 1, int LC = 0, int RB = 0, int PZ = 0>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
-  size_t smem = (size_t)WARPS * (((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
+  size_t smem = (size_t)WARPS * ((((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t) + (RB ? (size_t)(1 << RB) * 32 : 0));
   static int ctas_per_sm = 0, sms = 0;
   if (!ctas_per_sm) {
-    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB, HB, LC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB, HB, LC>, WARPS * 32, smem));
+    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ>, WARPS * 32, smem));
     int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
   int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-    inflate_kernel<WARPS, LB, DB, HB, LC><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block); IRF_LAUNCHED();
+    inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block); IRF_LAUNCHED();
   }
 }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
-  switch (variant) {   // (warps per CTA, literal LUT bits, distance LUT bits); shared memory per warp = (2^LB + 2^DB + 64) * 64 B
-    case 1: launch_inflate_t<4, 6, 5, 1, 1>(a, s); break;
-    case 2: launch_inflate_t<4, 6, 5, 4, 1>(a, s); break;
-    case 3: launch_inflate_t<4, 6, 5, 8, 1>(a, s); break;
-    case 4: launch_inflate_t<4, 6, 6>(a, s); break;
-    case 5: launch_inflate_t<4, 6, 5>(a, s); break;
-    case 6: launch_inflate_t<8, 6, 5>(a, s); break;
-    case 7: launch_inflate_t<4, 7, 6>(a, s); break;
-    case 8: launch_inflate_t<4, 7, 5>(a, s); break;
-    case 9: launch_inflate_t<8, 7, 6>(a, s); break;
-    case 10: launch_inflate_t<2, 7, 6>(a, s); break;
-    default: launch_inflate_t<4, 6, 5>(a, s); break;
+  switch (variant) {   // <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, output ring bits>
+    case 1: launch_inflate_t<4, 6, 5, 1, 0, 8>(a, s); break;    // shared memory per warp = (2^LB + 2^DB + 64) * 64 B + 2^RB * 32 B
+    case 2: launch_inflate_t<4, 6, 5, 1, 0, 0, 1>(a, s); break;   // pre-written output sectors
+    case 3: launch_inflate_t<4, 6, 6, 1, 0, 0, 1>(a, s); break;
+    case 4: launch_inflate_t<4, 6, 6, 1, 0, 0>(a, s); break;
+    case 5: launch_inflate_t<4, 7, 6, 1, 0, 0, 1>(a, s); break;
+    case 6: launch_inflate_t<8, 6, 5, 1, 0, 8>(a, s); break;
+    case 7: launch_inflate_t<4, 7, 6, 1, 0, 0>(a, s); break;
+    case 8: launch_inflate_t<4, 6, 5, 4, 1, 0>(a, s); break;    // lane-granular claims + header batching (measured slower, kept for A/B)
+    case 9: launch_inflate_t<4, 8, 6, 1, 0, 8>(a, s); break;
+    default: launch_inflate_t<4, 6, 5, 1, 0, 0>(a, s); break;
   }
 }
 
