@@ -59,7 +59,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
-  DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off;
+  DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -362,7 +362,12 @@ struct irf_ctx {
     d_rec_base.ensure((size_t)nblk_own * 8); d_rec_off.ensure(n_rec * 8);
     launch_scan_counts(d_nrec.as<u32>(), d_rec_base.as<u64>(), nblk_own, s_compute);
     launch_walk_list(own, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
-    launch_process_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), s_compute);
+    d_pair_list.ensure((n_cand / 2 + 1) * 16); d_single_list.ensure((n_rec - n_cand + 1) * 8);
+    u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192); IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
+    launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute);
+    u64 lc[2] = {0, 0}; IRF_CUDA(cudaMemcpyAsync(lc, list_counts, 16, cudaMemcpyDeviceToHost, s_compute)); sync();
+    launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), lc[0], s_compute);
+    launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), lc[1], s_compute);
     IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaGetLastError());
     check_dev_err("fragment counting");
     float a, b, c; IRF_CUDA(cudaEventElapsedTime(&a, e0, e1)); IRF_CUDA(cudaEventElapsedTime(&b, e1, e2)); IRF_CUDA(cudaEventElapsedTime(&c, e2, e3));
@@ -492,7 +497,7 @@ void irf_destroy(irf_ctx* c) {
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
-                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
+                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (c->pinned) cudaFreeHost(c->pinned);

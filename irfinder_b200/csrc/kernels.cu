@@ -441,40 +441,79 @@ __global__ void __launch_bounds__(1024) scan_counts_kernel(const u32* __restrict
   }
 }
 
-// BAM2blocks::processAll (row a2), one lane per record: skip / single / pair decision, mate pairing, fragment processing.
-__global__ void __launch_bounds__(128) process_records_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask) {
+// BAM2blocks::processAll (row a2) in two passes so that every warp does one kind of work:
+//   pass 1 (lane per record): skip / single / pair decision and mate pairing; completed pairs and singles are appended to
+//           dense work lists (warp-aggregated appends);
+//   pass 2 (lane per fragment): BAM2blocks::processPair / processSingle and every processor's ProcessBlocks.
+// (The first version did both in one kernel: half the lanes of a warp parked a mate and idled while the other half
+//  processed pairs, and the large divergent body thrashed the instruction cache — profiles/r1.)
+__device__ __forceinline__ u64 warp_append(u64* counter, bool want) {
+  u32 m = __ballot_sync(0xffffffffu, want); if (!m) return 0;
+  u32 lane = threadIdx.x & 31; int leader = __ffs(m) - 1; u64 base = 0;
+  if ((int)lane == leader) base = atomicAdd(counter, (u64)__popc(m));
+  base = __shfl_sync(0xffffffffu, base, leader);
+  return base + (u64)__popc(m & ((1u << lane) - 1u));
+}
+__device__ __forceinline__ void warp_add_stat(u64* slot, u64 v) {
+  for (int o = 16; o; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0 && v) atomicAdd(slot, v);
+}
+__global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask,
+                                                            u64* __restrict__ pair_list, u64* __restrict__ single_list, u64* __restrict__ list_counts) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
+  bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0;
   if (i < nrec) {
-    u64 e = rec_off[i]; Core c; load_core(U, e, c);
-    if ((c.flag & 0x4) || c.refID < 0) st.skipped++;                       // [C-6] only unmapped records are skipped
-    else if (c.refID >= T.n_ref) { atomicOr(T.err, DERR_REFID); }
-    else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) { st.single++; process_single(T, U, e, c, sink); }  // [C-7]
+    e = rec_off[i]; Core c; load_core(U, e, c);
+    if ((c.flag & 0x4) || c.refID < 0) skipped = 1;                          // [C-6] only unmapped records are skipped
+    else if (c.refID >= T.n_ref) atomicOr(T.err, DERR_REFID);
+    else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) is_single = true;   // [C-7]
     else {
       u64 mo; Core m;
       if (pair_lookup_or_wait(T, ptab, pmask, U, e, c, mo, m)) {
-        st.paired++;
-        bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);
-        u64 o1 = first_is_me ? e : mo, o2 = first_is_me ? mo : e; Core c1 = first_is_me ? c : m, c2 = first_is_me ? m : c;
-        process_pair(T, U, o1, c1, o2, c2, sink, st);
+        is_pair = true;
+        bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);       // read 1 = left mate; level starts: the earlier record
+        o1 = first_is_me ? e : mo; o2 = first_is_me ? mo : e;
       }
     }
   }
-  // warp-aggregate the counters: one atomic per warp and counter
-  u64 v[8] = {st.single, st.paired, st.shortp, st.inter, st.longp, st.skipped, 0, sink.nuc};
-#pragma unroll
-  for (int k = 0; k < 8; k++) { if (k == 6) continue; u64 x = v[k]; for (int o = 16; o; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o); if ((threadIdx.x & 31) == 0 && x) atomicAdd(&T.stats[k], x); }
+  u64 at = warp_append(&list_counts[0], is_pair); if (is_pair) { pair_list[2 * at] = o1; pair_list[2 * at + 1] = o2; }
+  at = warp_append(&list_counts[1], is_single); if (is_single) single_list[at] = e;
+  warp_add_stat(&T.stats[ST_SKIPPED], skipped);
   if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
+}
+__global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
+  if (i < npairs) {
+    u64 o1 = pair_list[2 * i], o2 = pair_list[2 * i + 1]; Core c1, c2; load_core(U, o1, c1); load_core(U, o2, c2);
+    st.paired = 1; process_pair(T, U, o1, c1, o2, c2, sink, st);
+  }
+  warp_add_stat(&T.stats[ST_PAIRED], st.paired); warp_add_stat(&T.stats[ST_SHORT], st.shortp); warp_add_stat(&T.stats[ST_INTERSECT], st.inter);
+  warp_add_stat(&T.stats[ST_LONG], st.longp); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
+}
+__global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ single_list, u64 nsingles) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  FragSink sink(T); u32 n = 0;
+  if (i < nsingles) { u64 e = single_list[i]; Core c; load_core(U, e, c); n = 1; process_single(T, U, e, c, sink); }
+  warp_add_stat(&T.stats[ST_SINGLE], n); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
+}
+void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s) {
+  u64 grid = (nrec + 255) / 256;
+  if (grid) { pair_records_kernel<<<(unsigned)grid, 256, 0, s>>>(T, U, rec_off, nrec, ptab, pmask, pair_list, single_list, list_counts); IRF_LAUNCHED(); }
+}
+void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s) {
+  u64 grid = (npairs + 127) / 128;
+  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs); IRF_LAUNCHED(); }
+}
+void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s) {
+  u64 grid = (nsingles + 127) / 128;
+  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, single_list, nsingles); IRF_LAUNCHED(); }
 }
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s) {
   int grid = (a.nblk + 127) / 128;
   if (grid) { walk_list_kernel<<<grid, 128, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.entry, rec_base, rec_off); IRF_LAUNCHED(); }
 }
 void launch_scan_counts(const u32* in, u64* out, int n, cudaStream_t s) { if (n) { scan_counts_kernel<<<1, 1024, 0, s>>>(in, out, n); IRF_LAUNCHED(); } }
-void launch_process_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, cudaStream_t s) {
-  u64 grid = (nrec + 127) / 128;
-  if (grid) { process_records_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, rec_off, nrec, ptab, pmask); IRF_LAUNCHED(); }
-}
 
 // Records still waiting in the pair table never met a mate: error reads on one GPU, halo candidates when sharded.
 __global__ void pair_leftover_kernel(const u64* __restrict__ ptab, u64 nslots, u64* __restrict__ n_left, u64* __restrict__ left_off, u64 left_cap) {
