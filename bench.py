@@ -262,6 +262,7 @@ def run_b200(a):
         e2e_step()
     barrier()
     dte = time.perf_counter() - t
+    e2e_stage = core.timing()
     if world > 1:
         v = torch.tensor([dte], dtype=torch.float64, device="cuda"); dist.all_reduce(v, op=dist.ReduceOp.MAX); dte = float(v.item())
     e2e_value = n_units * a.steps / dte / 1e6
@@ -302,7 +303,7 @@ def run_b200(a):
             "config": {"workload": workload_name(a, total_pairs), "fragments": n_units, "records": n_records, "compressed_bytes": comp_bytes,
                        "inflated_bytes": infl_bytes, "l2": "inputs larger than L2 (no flush needed)", "sharding": "one BGZF byte range (genomic region) of the BAM per rank; value at N>1 includes the per-step host->device copy" if world > 1 else "single GPU",
                        "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
-            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes)},
+            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes), "stage_ms": {k: round(v, 3) for k, v in e2e_stage.items()}},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "inflate_kernel", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic,
                          "peak_source": peak_src, "algorithmic_bytes_per_step": int(alg_bytes), "launches_per_step": inflate_launches / max(a.steps, 1), "avg_ms_per_step": round(avg_inflate_ms, 3)},

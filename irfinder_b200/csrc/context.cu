@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstring>
 #include <fstream>
+#include <functional>
 #include <string>
 #include <thread>
 #include <vector>
@@ -260,41 +261,40 @@ struct irf_ctx {
     sync(); staged = true; staged_has_header = true; resident = true;
   }
 
-  // S1: copy (when not resident) and inflate in batches so the copy of batch i+1 overlaps the inflate of batch i
+  // S1: one persistent inflate launch.  When the bytes are still on the host the copy runs beside it in 256 MB chunks on
+  // the copy stream, each followed by a tiny stream-ordered "watermark" copy that tells the kernel how many bytes have
+  // landed; warps whose next blocks lie beyond the watermark wait for it.  (Batched launches were tried first: every launch
+  // ends with tens of milliseconds of partly idle SMs because one lane needs ~40 ms per 64 KiB block.)
   void inflate_all() {
     if (inflated_input) return;
     size_t nb = blks.size(); if (!nb) return;
     IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
-    // Batches: resident input -> one launch.  Streaming from the host -> three batches of 1/8, 3/8 and 1/2 of the bytes,
-    // so the first inflate starts early and every later copy hides behind the previous batch's inflate; few launches
-    // because each launch ends with a tail of partly idle SMs.
-    const size_t min_batch = 256ull << 20;
-    size_t cut[3] = {resident ? src_total : std::max(min_batch, src_total / 8), resident ? src_total : std::max(2 * min_batch, src_total / 2), src_total};
-    vector<cudaEvent_t> copied; size_t b0 = 0; double kernel_ms = 0; vector<std::pair<cudaEvent_t, cudaEvent_t>> kev; int bi = 0;
-    cudaEvent_t ev_k0, ev_k1; IRF_CUDA(cudaEventCreate(&ev_k0)); IRF_CUDA(cudaEventCreate(&ev_k1));
-    while (b0 < nb) {
-      size_t b1 = b0; u64 begin = blks[b0].file_off, end = begin;
-      while (b1 < nb && (bi >= 2 || blks[b1].file_off < cut[bi])) { end = blks[b1].c_off + blks[b1].c_len + 8; b1++; }
-      if (b1 == b0) { end = blks[b1].c_off + blks[b1].c_len + 8; b1++; }
-      bi++;
-      if (!resident) {
-        if (b1 == nb) end = src_total;
-        IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + begin, h_src + begin, end - begin, cudaMemcpyHostToDevice, s_copy));
-        cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev, 0)); copied.push_back(ev);
+    unsigned long long* wm = (unsigned long long*)(d_small.as<uint8_t>() + 224);
+    const bool stream_in = !resident && inflate_variant != 8;
+    if (!resident && !stream_in) { IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); }
+    if (stream_in) IRF_CUDA(cudaMemsetAsync(wm, 0, 8, s_compute));
+    InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)nb, d_status.as<int>(), T.err ? T.err : d_err.as<int>(),
+                  (unsigned int*)(d_small.as<uint8_t>() + 160), stream_in ? wm : nullptr};
+    cudaEvent_t k0, k1, ready; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1)); IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+    if (stream_in) { IRF_CUDA(cudaEventRecord(ready, s_compute)); IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0)); }   // tables + zeroed watermark first
+    IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute));
+    if (stream_in) {
+      const size_t chunk = 256ull << 20; size_t nch = (src_total + chunk - 1) / chunk;
+      if (wm_host_cap < nch) { if (wm_host) cudaFreeHost(wm_host); IRF_CUDA(cudaMallocHost((void**)&wm_host, (nch + 8) * 8)); wm_host_cap = nch + 8; }
+      for (size_t i = 0; i < nch; i++) {
+        size_t lo = i * chunk, hi = std::min(src_total, lo + chunk);
+        IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
+        wm_host[i] = (i + 1 == nch) ? hi + 4096 : hi;   // the last mark also covers the kernel's look-ahead margin
+        IRF_CUDA(cudaMemcpyAsync(wm, &wm_host[i], 8, cudaMemcpyHostToDevice, s_copy));
       }
-      InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>() + b0, d_c_len.as<u32>() + b0, d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, (int)(b1 - b0), d_status.as<int>() + b0, T.err ? T.err : d_err.as<int>(),
-                    (unsigned int*)(d_small.as<uint8_t>() + 160)};
-      cudaEvent_t k0, k1; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1));
-      IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute)); kev.push_back({k0, k1});
-      b0 = b1;
+      IRF_CUDA(cudaStreamSynchronize(s_copy));
     }
     IRF_CUDA(cudaGetLastError()); sync();
-    for (auto& k : kev) { float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k.first, k.second)); kernel_ms += ms; cudaEventDestroy(k.first); cudaEventDestroy(k.second); }
-    for (auto e : copied) cudaEventDestroy(e);
-    cudaEventDestroy(ev_k0); cudaEventDestroy(ev_k1);
-    timing[1] = kernel_ms; n_inflate_launches = (int)kev.size();
-    if (!resident) { resident = true; }
+    float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k0, k1)); timing[1] = ms; n_inflate_launches = 1;
+    cudaEventDestroy(k0); cudaEventDestroy(k1); cudaEventDestroy(ready);
+    resident = true;
   }
+  unsigned long long* wm_host = nullptr; size_t wm_host_cap = 0;
   int n_inflate_launches = 0;
 
   int dev_err() { int e = 0; IRF_CUDA(cudaMemcpyAsync(&e, d_err.p, 4, cudaMemcpyDeviceToHost, s_compute)); sync(); return e; }
@@ -303,7 +303,7 @@ struct irf_ctx {
     string m = string(stage_name) + ":";
     if (e & DERR_INFLATE) m += " corrupt DEFLATE data in a BGZF block;"; if (e & DERR_TRUNCATED) m += " truncated BAM record stream;"; if (e & DERR_BAD_RECORD) m += " malformed BAM record / unframeable stream;";
     if (e & DERR_JUNC_FULL) m += " junction table full (raise junc_capacity_log2);"; if (e & DERR_JKEY_RANGE) m += " junction outside the supported key range;";
-    if (e & DERR_PAIR_FULL) m += " pairing table full;"; if (e & DERR_REFID) m += " record refID beyond the header's reference list;"; if (e & DERR_DUMP_FULL) m += " fragment dump buffer full;";
+    if (e & DERR_PAIR_FULL) m += " pairing table full;"; if (e & DERR_REFID) m += " record refID beyond the header's reference list;"; if (e & DERR_DUMP_FULL) m += " fragment dump buffer full;"; if (e & DERR_STARVED) m += " inflate kernel starved of input (host copy stalled);";
     throw m;
   }
 
@@ -393,6 +393,13 @@ struct irf_ctx {
     return n;
   }
 
+  // result rows are read back into page-locked memory (a pageable read-back of 20 MB costs ~10 ms on this host)
+  void pin_rows(vector<IntronRow>& v, size_t n) {
+    if (v.size() == n) return;
+    if (!v.empty()) cudaHostUnregister(v.data());
+    v.clear(); v.resize(n);
+    if (n && cudaHostRegister(v.data(), n * sizeof(IntronRow), cudaHostRegisterDefault) != cudaSuccess) cudaGetLastError();   // pageable still works, only slower
+  }
   // S4 + output-side statistics
   void finalize() {
     if (!counted) throw string("irf_count has not run");
@@ -419,11 +426,12 @@ struct irf_ctx {
     mark("max depth"); u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
     u32 bins = hmax >= 8192 ? hmax + 1 : 1; d_scratch.ensure((u64)grid * bins * 4);
     launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
-    rows_nondir.resize(n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
-    mark("intron stats nondir"); rows_dir.clear();
+    pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
+    mark("intron stats nondir");
+    if (directionality == 0 && !rows_dir.empty()) { cudaHostUnregister(rows_dir.data()); vector<IntronRow>().swap(rows_dir); }
     if (directionality != 0) {
       launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, directionality, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
-      rows_dir.resize(n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
+      pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
     }
     mark("intron stats dir"); h_stats.assign(ST_COUNT, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
     IRF_CUDA(cudaMemcpyAsync(h_stats.data(), d_stats.p, ST_COUNT * 8, cudaMemcpyDeviceToHost, s_compute));
@@ -449,12 +457,17 @@ struct irf_ctx {
     if (!finalized) throw string("no finished run to write");
     double t0 = now_ms(); string d = outdir;
     auto put = [&](const char* name, const string& s) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; size_t w = fwrite(s.data(), 1, s.size(), f); int rc = fclose(f); if (w != s.size() || rc) throw string("short write to ") + p; };
-    put("IRFinder-IR-nondir.txt", format_ir_table(cov, rows_nondir));
-    if (directionality != 0) put("IRFinder-IR-dir.txt", format_ir_table(cov, rows_dir));
-    put("IRFinder-JuncCount.txt", format_junctions(jref, chr_names, h_junc));
-    put("IRFinder-SpansPoint.txt", format_spans(sp, h_sp));
-    put("IRFinder-ChrCoverage.txt", format_chr(chr_names, h_chr));
-    if (roi.present) put("IRFinder-ROI.txt", format_roi(roi, h_roi));
+    // the six tables are independent: format and write them side by side
+    vector<std::function<void()>> jobs;
+    jobs.push_back([&]() { put("IRFinder-IR-nondir.txt", format_ir_table(cov, rows_nondir)); });
+    if (directionality != 0) jobs.push_back([&]() { put("IRFinder-IR-dir.txt", format_ir_table(cov, rows_dir)); });
+    jobs.push_back([&]() { put("IRFinder-JuncCount.txt", format_junctions(jref, chr_names, h_junc)); });
+    jobs.push_back([&]() { put("IRFinder-SpansPoint.txt", format_spans(sp, h_sp)); });
+    jobs.push_back([&]() { put("IRFinder-ChrCoverage.txt", format_chr(chr_names, h_chr)); if (roi.present) put("IRFinder-ROI.txt", format_roi(roi, h_roi)); });
+    vector<string> errs(jobs.size()); vector<std::thread> th;
+    for (size_t i = 0; i < jobs.size(); i++) th.emplace_back([&, i]() { try { jobs[i](); } catch (const string& e) { errs[i] = e; } catch (const std::exception& e) { errs[i] = e.what(); } });
+    for (auto& t : th) t.join();
+    for (auto& e : errs) if (!e.empty()) throw e;
     timing[7] = now_ms() - t0;
   }
 
@@ -500,7 +513,9 @@ void irf_destroy(irf_ctx* c) {
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
+  if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
+  if (c->wm_host) cudaFreeHost(c->wm_host);
   if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy);
   delete c;
 }

@@ -47,7 +47,7 @@ __device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
 template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM, int RB, int PZ>
 __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                              uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
-                                                             int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block) {
+                                                             int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // per warp: [lit LUT][dist LUT][2 x 32 canonical-limit entries] (16-bit, lane-interleaved) [output ring: 2^RB bytes per lane]
@@ -62,6 +62,20 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
       if (lane == 0) base = atomicAdd(next_block, 32u);
       base = __shfl_sync(0xffffffffu, base, 0);
       if (base >= (unsigned int)nblk) break;
+      if (watermark) {   // streaming input: wait until the host->device copy has passed the last byte these 32 blocks need
+        int lastb = min((int)base + 31, nblk - 1); u64 need = c_off[lastb] + c_len[lastb] + 160; bool starved = false;   // + the bit reader's look-ahead, rounded up to whole sectors:
+                                                                               // no lane may pull a not-yet-written sector into L1
+        if (lane == 0) {
+          long long t0 = clock64();
+          while (*(volatile const unsigned long long*)watermark < need) {
+            __nanosleep(500);
+            if (clock64() - t0 > 40000000000ll) { starved = true; break; }   // ~20 s without data: give up instead of hanging the GPU
+          }
+          __threadfence();
+        }
+        starved = __shfl_sync(0xffffffffu, (int)starved, 0) != 0;
+        if (starved) { if (lane == 0) atomicOr(err, DERR_STARVED); break; }
+      }
       int b = (int)base + lane;
       InflateLane<32, LB, DB, RB, PZ> L;
       bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
@@ -113,7 +127,7 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-    inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block); IRF_LAUNCHED();
+    inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark); IRF_LAUNCHED();
   }
 }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {

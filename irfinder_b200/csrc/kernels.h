@@ -8,6 +8,7 @@ struct InflateArgs {
   const uint8_t* comp; const u64* c_off; const u32* c_len;   // compressed bytes, per-block CDATA offset / length
   uint8_t* U; const u64* u_off; const u32* u_len;            // inflated bytes, per-block offset / ISIZE
   int nblk; int* status; int* err; unsigned int* next_block;   // next_block: device work counter, zeroed by the launcher
+  const unsigned long long* watermark;   // optional: bytes of `comp` that have landed so far (streaming from the host); null = all resident
 };
 struct FrameArgs {
   const uint8_t* U; const u64* u_off; const u32* u_len; int nblk; u64 Uend; u64 rec0; int rec0_valid;  // rec0: inflated offset of the first record when known exactly
