@@ -459,13 +459,16 @@ struct irf_ctx {
     auto put = [&](const char* name, const string& s) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; size_t w = fwrite(s.data(), 1, s.size(), f); int rc = fclose(f); if (w != s.size() || rc) throw string("short write to ") + p; };
     // the six tables are independent: format and write them side by side
     vector<std::function<void()>> jobs;
-    jobs.push_back([&]() { put("IRFinder-IR-nondir.txt", format_ir_table(cov, rows_nondir)); });
-    if (directionality != 0) jobs.push_back([&]() { put("IRFinder-IR-dir.txt", format_ir_table(cov, rows_dir)); });
-    jobs.push_back([&]() { put("IRFinder-JuncCount.txt", format_junctions(jref, chr_names, h_junc)); });
-    jobs.push_back([&]() { put("IRFinder-SpansPoint.txt", format_spans(sp, h_sp)); });
+    auto putv = [&](const char* name, const vector<string>& parts) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; bool ok = true;
+      for (auto& s : parts) ok &= fwrite(s.data(), 1, s.size(), f) == s.size(); if (fclose(f) || !ok) throw string("short write to ") + p; };
+    jobs.push_back([&]() { putv("IRFinder-IR-nondir.txt", format_ir_table_parts(cov, rows_nondir)); });
+    if (directionality != 0) jobs.push_back([&]() { putv("IRFinder-IR-dir.txt", format_ir_table_parts(cov, rows_dir)); });
+    jobs.push_back([&]() { putv("IRFinder-JuncCount.txt", format_junctions_parts(jref, chr_names, h_junc)); });
+    jobs.push_back([&]() { putv("IRFinder-SpansPoint.txt", format_spans_parts(sp, h_sp)); });
     jobs.push_back([&]() { put("IRFinder-ChrCoverage.txt", format_chr(chr_names, h_chr)); if (roi.present) put("IRFinder-ROI.txt", format_roi(roi, h_roi)); });
     vector<string> errs(jobs.size()); vector<std::thread> th;
-    for (size_t i = 0; i < jobs.size(); i++) th.emplace_back([&, i]() { try { jobs[i](); } catch (const string& e) { errs[i] = e; } catch (const std::exception& e) { errs[i] = e.what(); } });
+    const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr;
+    for (size_t i = 0; i < jobs.size(); i++) th.emplace_back([&, i]() { double tj = now_ms(); try { jobs[i](); if (dbg) fprintf(stderr, "[output] job %zu %8.3f ms\n", i, now_ms() - tj); } catch (const string& e) { errs[i] = e; } catch (const std::exception& e) { errs[i] = e.what(); } });
     for (auto& t : th) t.join();
     for (auto& e : errs) if (!e.empty()) throw e;
     timing[7] = now_ms() - t0;

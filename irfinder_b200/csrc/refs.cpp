@@ -2,6 +2,7 @@
 #include "refs.h"
 
 #include <algorithm>
+#include <atomic>
 #include <charconv>
 #include <cstring>
 #include <sstream>
@@ -87,7 +88,11 @@ void CoverageRef::pieces(const std::string& chr, u32 s, u32 e, std::vector<Intro
 // formatting: std::ostream << (default precision 6) == printf("%g") == to_chars(general, 6)
 static inline void put_u(std::string& s, unsigned long long v) { char b[24]; auto r = std::to_chars(b, b + sizeof b, v); s.append(b, r.ptr); }
 static inline void put_i(std::string& s, long long v) { char b[24]; auto r = std::to_chars(b, b + sizeof b, v); s.append(b, r.ptr); }
-static inline void put_g(std::string& s, double v) { char b[40]; auto r = std::to_chars(b, b + sizeof b, v, std::chars_format::general, 6); s.append(b, r.ptr); }
+static inline void put_g(std::string& s, double v) {
+  // %g prints integral values below 1e6 as plain integers; that covers most cells (0, 1, integer percentiles) without the general path
+  if (v >= 0 && v < 1e6) { unsigned long long u = (unsigned long long)v; if ((double)u == v) { put_u(s, u); return; } }
+  char b[40]; auto r = std::to_chars(b, b + sizeof b, v, std::chars_format::general, 6); s.append(b, r.ptr);
+}
 
 static const char* HDR_IR = "Chr\tStart\tEnd\tName\tNull\tStrand\tExcludedBases\tCoverage\tIntronDepth\tIntronDepth25Percentile\tIntronDepth50Percentile\tIntronDepth75Percentile\tExonToIntronReadsLeft\tExonToIntronReadsRight\tIntronDepthFirst50bp\tIntronDepthLast50bp\tSpliceLeft\tSpliceRight\tSpliceExact\tIRratio\tWarnings\n";
 static const char* WARN[5] = {"-", "LowCover", "LowSplicing", "MinorIsoform", "NonUniformIntronCover"};
@@ -103,16 +108,20 @@ static void format_ir_rows(const CoverageRef& cov, const std::vector<IntronRow>&
     s += '\t'; s += WARN[r.warning]; s += '\n';
   }
 }
-std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>& rows) {
-  size_t n = cov.BEDrecords.size(); unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
-  if (n < 20000) nt = 1;
-  std::vector<std::string> parts(nt); std::vector<std::thread> th;
-  for (unsigned t = 0; t < nt; t++) { size_t a = n * t / nt, b = n * (t + 1) / nt; parts[t].reserve((b - a) * 160);
-    if (nt == 1) format_ir_rows(cov, rows, a, b, parts[t]); else th.emplace_back([&, a, b, t]() { format_ir_rows(cov, rows, a, b, parts[t]); }); }
-  for (auto& t : th) t.join();
-  std::string out = HDR_IR; size_t tot = out.size(); for (auto& p : parts) tot += p.size(); out.reserve(tot); for (auto& p : parts) out += p;
-  return out;
+static unsigned fmt_threads(size_t n, unsigned cap = 6) { unsigned nt = std::max(1u, std::min(cap, std::thread::hardware_concurrency())); return n < 20000 ? 1 : nt; }
+template <class F> static void run_parts(unsigned nt, F f) {   // f(t) for t in [0, nt), on nt threads
+  if (nt == 1) { f(0); return; }
+  std::vector<std::thread> th; for (unsigned t = 0; t < nt; t++) th.emplace_back([&, t]() { f(t); }); for (auto& t : th) t.join();
 }
+static std::string join_parts(const std::vector<std::string>& parts) { size_t tot = 0; for (auto& p : parts) tot += p.size(); std::string out; out.reserve(tot); for (auto& p : parts) out += p; return out; }
+
+std::vector<std::string> format_ir_table_parts(const CoverageRef& cov, const std::vector<IntronRow>& rows) {
+  size_t n = cov.BEDrecords.size(); unsigned nt = fmt_threads(n, 16);
+  std::vector<std::string> parts(nt + 1); parts[0] = HDR_IR;
+  run_parts(nt, [&](unsigned t) { size_t a = n * t / nt, b = n * (t + 1) / nt; parts[t + 1].reserve((b - a) * 160); format_ir_rows(cov, rows, a, b, parts[t + 1]); });
+  return parts;
+}
+std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>& rows) { return join_parts(format_ir_table_parts(cov, rows)); }
 
 // per-chromosome rows in (start,end) order: annotated junctions (possibly uncounted) merged with counted ones
 static std::map<std::string, std::vector<JRow>> merged_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
@@ -131,14 +140,23 @@ static std::map<std::string, std::vector<JRow>> merged_junctions(const JunctionR
   }
   return out;
 }
-std::string format_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
-  auto m = merged_junctions(ref, chr_names, counted); std::string s = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";
-  for (auto& c : m) for (auto& r : c.second) {
-    s += c.first; s += '\t'; put_u(s, r.start); s += '\t'; put_u(s, r.end); s += '\t'; s += r.bits == 1 ? '-' : r.bits == 2 ? '+' : '.'; s += '\t';
+static void format_junction_rows(const std::string& chr, const std::vector<JRow>& rows, std::string& s) {
+  s.reserve(rows.size() * 40);
+  for (auto& r : rows) {
+    s += chr; s += '\t'; put_u(s, r.start); s += '\t'; put_u(s, r.end); s += '\t'; s += r.bits == 1 ? '-' : r.bits == 2 ? '+' : '.'; s += '\t';
     put_u(s, (unsigned long long)r.c0 + r.c1); s += '\t'; put_u(s, r.c1); s += '\t'; put_u(s, r.c0); s += '\n';
   }
-  return s;
 }
+std::vector<std::string> format_junctions_parts(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
+  auto m = merged_junctions(ref, chr_names, counted);
+  std::vector<std::pair<const std::string*, const std::vector<JRow>*>> chrs; for (auto& c : m) chrs.push_back({&c.first, &c.second});
+  std::vector<std::string> parts(chrs.size() + 1); parts[0] = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";
+  size_t total = 0; for (auto& c : chrs) total += c.second->size();
+  unsigned nt = fmt_threads(total); std::atomic<size_t> next(0);
+  run_parts(nt, [&](unsigned) { for (;;) { size_t i = next.fetch_add(1); if (i >= chrs.size()) break; format_junction_rows(*chrs[i].first, *chrs[i].second, parts[i + 1]); } });
+  return parts;
+}
+std::string format_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) { return join_parts(format_junctions_parts(ref, chr_names, counted)); }
 int directional(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted, std::string& log) {
   // only counted junctions can pass the evidence threshold, so walk those and look the annotation up (no merged map needed)
   unsigned long long same = 0, diff = 0, ev = 0, nev = 0, evk = 0, nevk = 0;
@@ -163,12 +181,15 @@ int directional(const JunctionRef& ref, const std::vector<std::string>& chr_name
   if (diff > same * 100 && evk > nevk * 100) return -1;
   return 0;
 }
-std::string format_spans(const SpansPointRef& ref, const std::vector<u32>& count) {
-  std::string s = "SP_seqname\tcoord\ttotal\tpos\tneg\n"; size_t n = ref.pos.size();
-  for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) {
-    u32 neg = count[i], pos = count[n + i]; s += c.first; s += '\t'; put_u(s, ref.pos[i]); s += '\t'; put_u(s, (unsigned long long)neg + pos); s += '\t'; put_u(s, pos); s += '\t'; put_u(s, neg); s += '\n'; }
-  return s;
+std::vector<std::string> format_spans_parts(const SpansPointRef& ref, const std::vector<u32>& count) {
+  size_t n = ref.pos.size(); unsigned nt = fmt_threads(n);
+  std::vector<const std::string*> name_of(n); for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) name_of[i] = &c.first;
+  std::vector<std::string> parts(nt + 1); parts[0] = "SP_seqname\tcoord\ttotal\tpos\tneg\n";
+  run_parts(nt, [&](unsigned t) { size_t a = n * t / nt, b = n * (t + 1) / nt; std::string& s = parts[t + 1]; s.reserve((b - a) * 32);
+    for (size_t i = a; i < b; i++) { u32 neg = count[i], pos = count[n + i]; s += *name_of[i]; s += '\t'; put_u(s, ref.pos[i]); s += '\t'; put_u(s, (unsigned long long)neg + pos); s += '\t'; put_u(s, pos); s += '\t'; put_u(s, neg); s += '\n'; } });
+  return parts;
 }
+std::string format_spans(const SpansPointRef& ref, const std::vector<u32>& count) { return join_parts(format_spans_parts(ref, count)); }
 std::string format_roi(const RoiRef& ref, const std::vector<u32>& count) {
   std::string s = "ROI_Name\ttotal\tpos\tneg\n"; size_t n = ref.rois.size();
   for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) {

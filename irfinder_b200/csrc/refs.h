@@ -48,7 +48,11 @@ struct CoverageRef {
 
 struct JuncEntry { int refid; u32 start, end; u32 cnt[2]; };
 
-// text writers (byte layout per SURVEY.md B.7 / B.8)
+// text writers (byte layout per SURVEY.md B.7 / B.8).  Large tables come back as consecutive pieces (formatted by several
+// threads) so the caller can write them without another copy.
+std::vector<std::string> format_ir_table_parts(const CoverageRef& cov, const std::vector<IntronRow>& rows);
+std::vector<std::string> format_junctions_parts(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted);
+std::vector<std::string> format_spans_parts(const SpansPointRef& ref, const std::vector<u32>& count);
 std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>& rows);
 std::string format_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted);
 std::string format_spans(const SpansPointRef& ref, const std::vector<u32>& count /* [2][n] */);
