@@ -243,6 +243,11 @@ def run_b200(a):
         v = torch.tensor([dt], dtype=torch.float64, device="cuda"); dist.all_reduce(v, op=dist.ReduceOp.MAX); dt = float(v.item())
     value = n_units * a.steps / dt / 1e6
     stats = core.stats()
+    # size-independent consistency checks at full size (the byte-level parity tests run at sizes the CPU oracle can handle)
+    chk = core.table("chr").astype(np.int64).sum()
+    checks = {"fragments == pairs + singles": int(stats["pairs"] + stats["singles"]) == n_units, "sum(ChrCoverage) == fragments": int(chk) == n_units,
+              "long + short + intersect == pairs": stats["long"] + stats["short"] + stats["intersect"] == stats["pairs"], "no error reads": stats["error"] == 0,
+              "records == generated": stats["records"] == n_records}
 
     # ---------------- e2e: host buffer in, six text tables out
     outdir = os.path.join("/dev/shm" if os.path.isdir("/dev/shm") else wd, f"irf_bench_out_{rank}")
@@ -302,7 +307,7 @@ def run_b200(a):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 bytes -> int32/u32 counts, f64 ratios", "data": "synthetic",
             "config": {"workload": workload_name(a, total_pairs), "fragments": n_units, "records": n_records, "compressed_bytes": comp_bytes,
                        "inflated_bytes": infl_bytes, "l2": "inputs larger than L2 (no flush needed)", "sharding": "one BGZF byte range (genomic region) of the BAM per rank; value at N>1 includes the per-step host->device copy" if world > 1 else "single GPU",
-                       "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
+                       "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "checks": "ok" if all(checks.values()) else {k: v for k, v in checks.items() if not v}, "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes), "stage_ms": {k: round(v, 3) for k, v in e2e_stage.items()}},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "inflate_kernel", "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic,

@@ -48,7 +48,7 @@ static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std:
 struct irf_ctx {
   int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr;
   // options
-  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1;
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0;
   // references (host)
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
@@ -276,9 +276,11 @@ struct irf_ctx {
     InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)nb, d_status.as<int>(), T.err ? T.err : d_err.as<int>(),
                   (unsigned int*)(d_small.as<uint8_t>() + 160), stream_in ? wm : nullptr};
     cudaEvent_t k0, k1, ready; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1)); IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
-    if (stream_in) { IRF_CUDA(cudaEventRecord(ready, s_compute)); IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0)); }   // tables + zeroed watermark first
-    IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute));
     if (stream_in) {
+      IRF_CUDA(cudaEventRecord(ready, s_compute)); IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0));   // tables + zeroed watermark first
+      // The copies are queued BEFORE the kernel is launched.  If the driver happens to map both streams onto one hardware
+      // queue the kernel then simply runs after the copies (no overlap, but no wait-for-ever either); with separate queues
+      // the copy engine and the kernel run side by side.
       const size_t chunk = 256ull << 20; size_t nch = (src_total + chunk - 1) / chunk;
       if (wm_host_cap < nch) { if (wm_host) cudaFreeHost(wm_host); IRF_CUDA(cudaMallocHost((void**)&wm_host, (nch + 8) * 8)); wm_host_cap = nch + 8; }
       for (size_t i = 0; i < nch; i++) {
@@ -287,10 +289,15 @@ struct irf_ctx {
         wm_host[i] = (i + 1 == nch) ? hi + 4096 : hi;   // the last mark also covers the kernel's look-ahead margin
         IRF_CUDA(cudaMemcpyAsync(wm, &wm_host[i], 8, cudaMemcpyHostToDevice, s_copy));
       }
-      IRF_CUDA(cudaStreamSynchronize(s_copy));
+    }
+    IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute));
+    if (stream_in) {
+      double tc0 = now_ms(); IRF_CUDA(cudaStreamSynchronize(s_copy));
+      if (getenv("IRF_DEBUG_TIMING")) fprintf(stderr, "[inflate] %zu bytes streamed, copies drained %.1f ms after the launch\n", src_total, now_ms() - tc0);
     }
     IRF_CUDA(cudaGetLastError()); sync();
     float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k0, k1)); timing[1] = ms; n_inflate_launches = 1;
+    if (getenv("IRF_DEBUG_TIMING")) fprintf(stderr, "[inflate] kernel %.1f ms\n", ms);
     cudaEventDestroy(k0); cudaEventDestroy(k1); cudaEventDestroy(ready);
     resident = true;
   }
@@ -532,6 +539,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "junc_capacity_log2") { if (v < 10 || v > 30) return IRF_EINVAL; c->junc_cap_log2 = (int)v; }
   else if (k == "require_eof") c->require_eof = v != 0;
   else if (k == "entry0") c->entry0_override = v;
+  else if (k == "stage_lazy") c->stage_lazy = v != 0;
   else { c->err = "unknown option " + k; return IRF_EINVAL; }
   return IRF_OK;
 }
@@ -593,7 +601,7 @@ int irf_read_header(irf_ctx* c, const void* prefix, size_t n) {
     c->inflate_all(); c->check_dev_err("inflate"); c->parse_header_from_device(); c->staged = false;
   });
 }
-int irf_stage(irf_ctx* c, const void* bgzf, size_t own, size_t total, int has_header) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->stage(bgzf, own, total, has_header, true)); }
+int irf_stage(irf_ctx* c, const void* bgzf, size_t own, size_t total, int has_header) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->stage(bgzf, own, total, has_header, !c->stage_lazy)); }
 int irf_count(irf_ctx* c) { IRF_TRY(c, c->count()); }
 int irf_frame_info(irf_ctx* c, uint64_t* entry0, uint64_t* exit_rel) { if (!c || !c->counted) return IRF_ESTATE; if (entry0) *entry0 = c->frame_entry0; if (exit_rel) *exit_rel = c->frame_exit_rel; return IRF_OK; }
 int irf_finalize(irf_ctx* c) { IRF_TRY(c, c->finalize()); }

@@ -159,17 +159,22 @@ def run_plan(core, plan, device=None, group=None):
     import torch.distributed as dist
     dev = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
     rank, world = plan.rank, plan.world
-    hdr = np.ascontiguousarray(plan.header)
-    probe = min(hdr.size, 1 << 20)
-    while True:  # the header can span many blocks; grow the probe until it parses
-        try:
-            core.read_header(hdr.ctypes.data, probe)
-            break
-        except Exception:
-            if probe >= hdr.size:
-                raise
-            probe = min(hdr.size, probe * 4)
+    if getattr(core, "_plan_header_id", None) != id(plan):   # BAM2blocks::readBamHeader once per (context, plan)
+        hdr = np.ascontiguousarray(plan.header)
+        probe = min(hdr.size, 1 << 20)
+        while True:  # the header can span many blocks; grow the probe until it parses
+            try:
+                core.read_header(hdr.ctypes.data, probe)
+                break
+            except Exception:
+                if probe >= hdr.size:
+                    raise
+                probe = min(hdr.size, probe * 4)
+        core._plan_header_id = id(plan)
+        if hasattr(core, "set_option") and dev.type == "cuda":
+            core.set_option("stage_lazy", 1)   # stream the shard to the GPU beside the inflate kernel instead of copying first
     data = plan.data if plan.data.flags["C_CONTIGUOUS"] else np.ascontiguousarray(plan.data)
+    plan.data = data
     core.reset()
     core.stage(data.ctypes.data, plan.n_own, data.size, has_header=(rank == 0))
     core.count()

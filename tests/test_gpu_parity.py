@@ -248,3 +248,13 @@ def test_wrapper_script_bam_mode(built, tiny, tmp_path):
     assert again.returncode != 0      # refuses to overwrite
     other = subprocess.run([exe, "-m", "FastQ", "-r", tiny["ref_dir"], "-d", str(tmp_path / "x"), tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     assert other.returncode != 0
+
+
+def test_baseline_config0_chr22_1m_pairs(built, tmp_path):
+    """BASELINE.json configs[0]: 1M paired-end 2x100 over a 50 Mb chr22-like genome (~5k introns) — the reference-runnable
+    case — GPU on the coordinate-sorted BAM vs the oracle on the name-collated copy, every output file byte for byte."""
+    meta = _gen(tmp_path, "c1", genome="chr22", introns=5000, pairs=1_000_000, readlen=100, seed=1, chunks=64)
+    out = run_oracle(built, meta, str(tmp_path / "o"))
+    c = _gpu_run(meta, str(tmp_path / "g"))
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(out)
