@@ -194,7 +194,7 @@ def run_b200(a):
                       chunk_range=(clo, chi) if world > 1 else None, threads=threads)
     gen_s = time.perf_counter() - t0
     fsize = os.path.getsize(meta["sorted"])
-    host = torch.empty(fsize + 64, dtype=torch.uint8, pin_memory=True)   # pinned host copy of this rank's BGZF bytes
+    host = torch.empty(fsize + (1 << 18) + 64, dtype=torch.uint8, pin_memory=True)   # pinned host copy of this rank's BGZF bytes (+ room for the look-ahead)
     hv = host.numpy()
     with open(meta["sorted"], "rb") as f:
         f.readinto(memoryview(hv)[:fsize])

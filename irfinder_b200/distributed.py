@@ -146,8 +146,12 @@ class ShardPlan:
         dist.all_gather(heads, head.to(dev), group=group)
         dist.all_gather(ks, meta.to(dev), group=group)
         extra = heads[rank + 1][: int(ks[rank + 1].item())].cpu().numpy() if rank + 1 < world else np.zeros(0, np.uint8)
-        buf = torch.empty(part.size + extra.size + 64, dtype=torch.uint8, pin_memory=pin and torch.cuda.is_available()).numpy()
-        buf[: part.size] = part
+        base = part.base if isinstance(part.base, np.ndarray) else None
+        if base is not None and base.ndim == 1 and base.dtype == np.uint8 and part.ctypes.data == base.ctypes.data and base.size >= part.size + extra.size:
+            buf = base   # the caller left room behind its bytes: append the look-ahead in place (no second multi-GB pinned buffer)
+        else:
+            buf = torch.empty(part.size + extra.size + 64, dtype=torch.uint8, pin_memory=pin and torch.cuda.is_available()).numpy()
+            buf[: part.size] = part
         buf[part.size: part.size + extra.size] = extra
         hdr = part if rank == 0 else (np.frombuffer(header, dtype=np.uint8) if not isinstance(header, np.ndarray) else header)
         return ShardPlan(hdr[: 1 << 26], buf[: part.size + extra.size], part.size, rank, world)
