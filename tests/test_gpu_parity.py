@@ -258,3 +258,22 @@ def test_baseline_config0_chr22_1m_pairs(built, tmp_path):
     c = _gpu_run(meta, str(tmp_path / "g"))
     assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
     assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(out)
+
+
+def test_deep_introns_use_the_global_histogram_path(built, tmp_path):
+    """Depths beyond the 8192-bin shared-memory histogram (BASELINE.json configs[3]: dense intronic coverage) take the
+    per-CTA global scratch histogram in intron_stats_kernel; statistics must still match the oracle exactly."""
+    import micro_fixture
+    from bamutil import record, write_bam
+    p = micro_fixture.write(str(tmp_path / "m"))
+    recs = [record("d%05d" % i, 0, 1400 + (i % 300), "100M", 16 * (i & 1)) for i in range(12000)]          # ~4000x over intron 1
+    recs += [record("e%05d" % i, 0, 3100 + (i % 7), "120M", 0) for i in range(9500)]                       # ~9500x over intron 2
+    recs += [record("f%05d" % i, 0, 900, "100M1000N50M", 0) for i in range(40)]
+    bam = str(tmp_path / "deep.bam")
+    write_bam(bam, micro_fixture.REFS, recs, level=1)
+    meta = dict(cover=p["cover"], sj=p["sj"], rc=p["rc"], roi=p["roi"], collated=bam, sorted=bam)
+    run_oracle(built, meta, str(tmp_path / "o"))
+    c = _gpu_run(meta, str(tmp_path / "g"))
+    d = c.table("depth"); half = d.size // 2
+    assert int((d[:half] + d[half:]).max()) >= 8192, "workload too shallow to exercise the scratch path"
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
