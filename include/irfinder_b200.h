@@ -49,7 +49,7 @@ void irf_destroy(irf_ctx* ctx);
 const char* irf_last_error(irf_ctx* ctx);
 
 /* Options (strings): "trim_center" (default 40), "dump_fragments" (0/1), "inflate_variant" (0-6),
- * "junc_capacity_log2" (default 24), "require_eof" (default 1), "stage_lazy" (default 0; 1 = irf_stage only records the host
+ * "junc_capacity_log2" (default 24), "require_eof" (default 1), "verify_crc" (default 1: check every block's CRC-32 as gzip does), "stage_lazy" (default 0; 1 = irf_stage only records the host
  * buffer and irf_count streams it to the GPU beside the inflate kernel: the buffer must then stay valid until irf_count returns).
  * Must be set before irf_load_ref / the first run. */
 int irf_set_option(irf_ctx* ctx, const char* key, const char* value);

@@ -27,7 +27,7 @@ __host__ __device__ inline u64 jkey_make(u64 gleft, u64 gap) { return (gleft << 
 // ---- error bits set by kernels in DevTables::err
 enum DevErr : int {
   DERR_INFLATE = 1, DERR_TRUNCATED = 2, DERR_BAD_RECORD = 4, DERR_JUNC_FULL = 8, DERR_JKEY_RANGE = 16,
-  DERR_PAIR_FULL = 32, DERR_REFID = 64, DERR_DUMP_FULL = 128, DERR_STARVED = 256,
+  DERR_PAIR_FULL = 32, DERR_REFID = 64, DERR_DUMP_FULL = 128, DERR_STARVED = 256, DERR_CRC = 512,
 };
 
 // ---- counters (the reference prints these on stdout; SURVEY.md §5 "Metrics")

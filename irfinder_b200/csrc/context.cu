@@ -39,7 +39,7 @@ struct DevBuf {
 template <class T> static void upload(DevBuf& b, const vector<T>& v, cudaStream_t s) {
   b.ensure(v.size() * sizeof(T)); if (!v.empty()) IRF_CUDA(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
 }
-struct Blk { u64 c_off; u32 c_len; u32 isize; u64 file_off; };
+struct Blk { u64 c_off; u32 c_len; u32 isize; u64 file_off; u32 crc; };
 static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std::min<u64>(p, 1ull << 31); }
 
@@ -48,7 +48,7 @@ static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std:
 struct irf_ctx {
   int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr;
   // options
-  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0;
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1;
   // references (host)
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
@@ -60,7 +60,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
-  DevBuf d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
+  DevBuf d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -192,7 +192,7 @@ struct irf_ctx {
     if (bsize < 0) { if (why) *why = string("BGZF block without BC subfield at offset ") + std::to_string(off); return false; }
     total = (size_t)bsize + 1; if (total < 12 + xlen + 8) { if (why) *why = "bad BGZF BSIZE"; return false; }
     if (off + total > n_total) { if (why) *why = "truncated BGZF block (file cut short)"; return false; }
-    b.file_off = off; b.c_off = off + 12 + xlen; b.c_len = (u32)(total - 12 - xlen - 8); memcpy(&b.isize, p + off + total - 4, 4);
+    b.file_off = off; b.c_off = off + 12 + xlen; b.c_len = (u32)(total - 12 - xlen - 8); memcpy(&b.isize, p + off + total - 4, 4); memcpy(&b.crc, p + off + total - 8, 4);
     if (b.isize > 65536) { if (why) *why = "BGZF ISIZE > 64 KiB"; return false; }
     return true;
   }
@@ -242,8 +242,9 @@ struct irf_ctx {
     if (require_eof && has_header && n_own == n_total) { if (blks.empty() || blks.back().isize != 0) throw string("BGZF EOF marker missing (truncated file?)"); }
     timing[6] = now_ms() - t0;
     h_src = (const uint8_t*)src; src_total = blks.empty() ? 0 : (size_t)(blks.back().c_off + blks.back().c_len + 8);
-    vector<u64> c_off(blks.size()), u_off(blks.size()); vector<u32> c_len(blks.size()), u_len(blks.size()); u64 u = 0;
-    for (size_t i = 0; i < blks.size(); i++) { c_off[i] = blks[i].c_off; c_len[i] = blks[i].c_len; u_off[i] = u; u_len[i] = blks[i].isize; u += blks[i].isize; }
+    vector<u64> c_off(blks.size()), u_off(blks.size()); vector<u32> c_len(blks.size()), u_len(blks.size()), crcs(blks.size()); u64 u = 0;
+    for (size_t i = 0; i < blks.size(); i++) { c_off[i] = blks[i].c_off; c_len[i] = blks[i].c_len; u_off[i] = u; u_len[i] = blks[i].isize; crcs[i] = blks[i].crc; u += blks[i].isize; }
+    upload(d_crc, crcs, s_compute);
     Uend = u;
     upload(d_c_off, c_off, s_compute); upload(d_c_len, c_len, s_compute); upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute);
     d_comp.ensure(src_total + 64); d_U.ensure(Uend + 64);
@@ -310,7 +311,7 @@ struct irf_ctx {
     string m = string(stage_name) + ":";
     if (e & DERR_INFLATE) m += " corrupt DEFLATE data in a BGZF block;"; if (e & DERR_TRUNCATED) m += " truncated BAM record stream;"; if (e & DERR_BAD_RECORD) m += " malformed BAM record / unframeable stream;";
     if (e & DERR_JUNC_FULL) m += " junction table full (raise junc_capacity_log2);"; if (e & DERR_JKEY_RANGE) m += " junction outside the supported key range;";
-    if (e & DERR_PAIR_FULL) m += " pairing table full;"; if (e & DERR_REFID) m += " record refID beyond the header's reference list;"; if (e & DERR_DUMP_FULL) m += " fragment dump buffer full;"; if (e & DERR_STARVED) m += " inflate kernel starved of input (host copy stalled);";
+    if (e & DERR_PAIR_FULL) m += " pairing table full;"; if (e & DERR_REFID) m += " record refID beyond the header's reference list;"; if (e & DERR_DUMP_FULL) m += " fragment dump buffer full;"; if (e & DERR_STARVED) m += " inflate kernel starved of input (host copy stalled);"; if (e & DERR_CRC) m += " CRC-32 of an inflated BGZF block does not match its footer;";
     throw m;
   }
 
@@ -337,6 +338,7 @@ struct irf_ctx {
     IRF_CUDA(cudaEventRecord(e0, s_compute));
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
     inflate_all();
+    if (verify_crc && !inflated_input) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)blks.size(), d_status.as<int>(), T.err ? T.err : d_err.as<int>(), s_compute);
     check_dev_err("inflate");
     IRF_CUDA(cudaEventRecord(e1, s_compute));
     if (staged_has_header) parse_header_from_device();
@@ -519,7 +521,7 @@ void irf_destroy(irf_ctx* c) {
   if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
-                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
+                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
@@ -540,6 +542,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "require_eof") c->require_eof = v != 0;
   else if (k == "entry0") c->entry0_override = v;
   else if (k == "stage_lazy") c->stage_lazy = v != 0;
+  else if (k == "verify_crc") c->verify_crc = v != 0;
   else { c->err = "unknown option " + k; return IRF_EINVAL; }
   return IRF_OK;
 }

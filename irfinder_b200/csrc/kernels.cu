@@ -146,6 +146,62 @@ void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// S1b: CRC-32 (IEEE, reflected, as in RFC 1952) of each inflated block.  One warp per block: the block is cut from its END
+// into 2 KiB slices, lane i takes slice i (lanes before the start of a short block stay empty), each lane runs the
+// table-driven register update over its slice (slicing-by-4 tables in shared memory), and the 32 registers are merged in a
+// 5-level tree: combine(A, B) = A * x^(8|B|) mod P  xor  B, where |B| is always 2^k * 2 KiB so the five multipliers are constants.
+constexpr u32 CRC_POLY = 0xEDB88320u; constexpr u32 CRC_SLICE = 2048;
+__host__ __device__ inline u32 crc_mulmod(u32 a, u32 b) {   // product of two polynomials mod P, bit 31 = x^0 (zlib's multmodp)
+  u32 p = 0;
+  for (int i = 0; i < 32; i++) { if (a & (0x80000000u >> i)) p ^= b; b = (b & 1u) ? (b >> 1) ^ CRC_POLY : b >> 1; }
+  return p;
+}
+struct CrcMul { u32 x[5]; };
+__global__ void __launch_bounds__(256) crc_check_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, const u32* __restrict__ want,
+                                                         int nblk, CrcMul M, int* __restrict__ status, int* __restrict__ err) {
+  __shared__ u32 T[4][256];
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = (u32)i; for (int k = 0; k < 8; k++) c = (c & 1u) ? (c >> 1) ^ CRC_POLY : c >> 1; T[0][i] = c; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = T[0][i]; for (int t = 1; t < 4; t++) { c = T[0][c & 255u] ^ (c >> 8); T[t][i] = c; } }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  for (int b = blockIdx.x * wpb + (threadIdx.x >> 5); b < nblk; b += gridDim.x * wpb) {
+    u32 len = u_len[b]; if (!len) continue;
+    const uint8_t* base = U + u_off[b];
+    long long hi = (long long)len - (long long)(31 - lane) * CRC_SLICE, lo = hi - CRC_SLICE;   // this lane's slice [lo, hi) of the block
+    if (lo < 0) lo = 0;
+    u32 r = 0;
+    if (hi > 0) {
+      if (lo == 0) r = 0xFFFFFFFFu;   // the lane holding the first byte carries the initial register
+      const uint8_t* p = base + lo; const uint8_t* e = base + hi;
+      while (p < e && ((uintptr_t)p & 15)) { r = T[0][(r ^ *p++) & 255u] ^ (r >> 8); }
+      for (; p + 16 <= e; p += 16) {   // 128-bit loads: each lane streams its own slice, so wide loads keep the sector traffic down
+        uint4 q = *(const uint4*)p; u32 w;
+        w = q.x ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
+        w = q.y ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
+        w = q.z ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
+        w = q.w ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
+      }
+      while (p < e) { r = T[0][(r ^ *p++) & 255u] ^ (r >> 8); }
+    }
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+      u32 v = __shfl_xor_sync(0xffffffffu, r, 1 << k); bool upper = (lane >> k) & 1;
+      u32 a = upper ? v : r, bb = upper ? r : v;   // a = the earlier bytes, bb = the later 2^k slices
+      r = crc_mulmod(M.x[k], a) ^ bb;
+    }
+    if (lane == 0 && (~r) != want[b]) { status[b] = 100; atomicOr(err, DERR_CRC); }
+  }
+}
+void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s) {
+  static CrcMul M; static bool init = false;
+  if (!init) { u32 p = 0x40000000u;   // x^1; square up to x^(8 * 2048) = x^(2^14), then keep squaring
+    for (int i = 0; i < 14; i++) p = crc_mulmod(p, p);
+    for (int k = 0; k < 5; k++) { M.x[k] = p; p = crc_mulmod(p, p); } init = true; }
+  if (nblk > 0) { int grid = std::min((nblk + 7) / 8, 148 * 8); crc_check_kernel<<<grid, 256, 0, s>>>(U, u_off, u_len, crc_expected, nblk, M, status, err); IRF_LAUNCHED(); }
+}
+
+// ------------------------------------------------------------------------------------------------
 // S2: record framing.  Records straddle BGZF blocks and each starts with its own block_size, so record
 // starts form a serial chain.  We guess each block's entry (first record start at
 // or after the block's first inflated byte) from the record layout, walk all blocks in parallel, then check

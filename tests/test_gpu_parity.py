@@ -188,6 +188,15 @@ def test_bad_inputs_fail_loudly(tiny, tmp_path):
         c.run_bytes(bytes(corrupt))
     with pytest.raises(IRFError):
         c.run_bytes(b"this is not a BAM file at all, not even gzip")
+    bad_crc = bytearray(data)     # a block whose payload is intact but whose CRC-32 footer is wrong (what `gzip -cd` would reject)
+    bs = (data[16] | data[17] << 8) + 1
+    bad_crc[bs - 8] ^= 0x01
+    with pytest.raises(IRFError) as ei:
+        c.run_bytes(bytes(bad_crc))
+    assert "CRC" in str(ei.value)
+    c.set_option("verify_crc", 0)
+    c.run_bytes(bytes(bad_crc))     # the check can be switched off
+    c.set_option("verify_crc", 1)
     c.run_bytes(data)               # the context stays usable afterwards
     assert c.stats()["pairs"] > 0
 
