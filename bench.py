@@ -178,7 +178,15 @@ def run_b200(a):
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     total_pairs = a.pairs * world
-    wd = os.path.join(a.workdir, f"w{world}_r{rank}")
+    base = a.workdir
+    if world > 1 and os.path.isdir("/dev/shm"):   # N shards are generated at once: keep them off a possibly small disk
+        try:
+            st = os.statvfs("/dev/shm")
+            if st.f_bavail * st.f_frsize > 3 * world * a.pairs * 300:
+                base = "/dev/shm/irf_bench"
+        except OSError:
+            pass
+    wd = os.path.join(base, f"w{world}_r{rank}")
     t0 = time.perf_counter()
     if rank == 0:
         build.build_tools()
@@ -198,6 +206,11 @@ def run_b200(a):
     hv = host.numpy()
     with open(meta["sorted"], "rb") as f:
         f.readinto(memoryview(hv)[:fsize])
+    if world > 1:   # N shards of this size would otherwise sit on disk at once; the bytes now live in pinned memory
+        hdr_bytes = None if rank == 0 else np.fromfile(meta["sorted"] + ".header", dtype=np.uint8)
+        for fn in (meta["sorted"], os.path.join(wd, "key.json")):
+            if os.path.exists(fn):
+                os.remove(fn)
     counts = torch.tensor([meta["pairs"] + meta["singles"], meta["records"], meta["compressed_bytes"], meta["inflated_bytes"]], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(counts)
@@ -223,8 +236,7 @@ def run_b200(a):
             core.reset(); core.count(); core.finalize()
     else:
         from irfinder_b200.distributed import ShardPlan, run_plan
-        hdr = None if rank == 0 else np.fromfile(meta["sorted"] + ".header", dtype=np.uint8)
-        plan = ShardPlan.from_parts(hv[:fsize], hdr, rank, world, dist, torch.device("cuda", local))
+        plan = ShardPlan.from_parts(hv[:fsize], hdr_bytes, rank, world, dist, torch.device("cuda", local))
 
         def step():   # sharded steps re-stage their byte range: the host->device copy is part of the multi-GPU step
             run_plan(core, plan, device=torch.device("cuda", local))
