@@ -42,6 +42,7 @@ def parse_args():
     ap.add_argument("--workdir", default=os.environ.get("IRF_BENCH_DIR", "/tmp/irf_bench"))
     ap.add_argument("--cpu-sample-pairs", type=int, default=1_000_000)
     ap.add_argument("--inflate-variant", type=int, default=-1)
+    ap.add_argument("--de-percent", type=int, default=-1, help="share of BGZF blocks given to the hardware decompression engine (library default when < 0)")
     return ap.parse_args()
 
 
@@ -216,6 +217,8 @@ def run_b200(a):
         dist.all_reduce(counts)
     n_units, n_records, comp_bytes, infl_bytes = (int(x) for x in counts.tolist())   # fragments = pairs (a few orphans count as one unit each)
     opts = {} if a.inflate_variant < 0 else {"inflate_variant": a.inflate_variant}
+    if a.de_percent >= 0:
+        opts["de_percent"] = a.de_percent
     core = IRFinderCore(local, **opts)
     t1 = time.perf_counter()
     core.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])

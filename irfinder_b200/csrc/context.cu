@@ -5,6 +5,7 @@
 // (binding name-keyed reference tables to BAM refIDs), kernel orchestration and result download.
 // There is no CPU implementation of any counting step in this library: without a CUDA device every entry
 // point fails with IRF_ECUDA.
+#include <cuda.h>
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -41,14 +42,31 @@ template <class T> static void upload(DevBuf& b, const vector<T>& v, cudaStream_
 }
 struct Blk { u64 c_off; u32 c_len; u32 isize; u64 file_off; u32 crc; };
 static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+typedef CUresult (*pfn_decompress)(CUmemDecompressParams*, size_t, unsigned int, size_t*, CUstream);
+typedef CUresult (*pfn_devattr)(int*, CUdevice_attribute, CUdevice);
+typedef CUresult (*pfn_ctxdev)(CUdevice*);
+struct DriverApi {   // the few driver-API calls of the decompression-engine path, resolved through the runtime so that the
+  pfn_decompress decompress = nullptr; pfn_devattr devattr = nullptr; pfn_ctxdev ctxdev = nullptr; bool tried = false;   // library carries no link-time dependency on libcuda
+  void load() {
+    if (tried) return; tried = true; cudaDriverEntryPointQueryResult q;
+    void* f = nullptr;
+    if (cudaGetDriverEntryPoint("cuMemBatchDecompressAsync", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) decompress = (pfn_decompress)f;
+    f = nullptr; if (cudaGetDriverEntryPoint("cuDeviceGetAttribute", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) devattr = (pfn_devattr)f;
+    f = nullptr; if (cudaGetDriverEntryPoint("cuCtxGetDevice", &f, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) ctxdev = (pfn_ctxdev)f;
+    cudaGetLastError();
+  }
+  bool deflate_engine() { load(); if (!decompress || !devattr || !ctxdev) return false; CUdevice d; int mask = 0; if (ctxdev(&d) != CUDA_SUCCESS) return false;
+    if (devattr(&mask, CU_DEVICE_ATTRIBUTE_MEM_DECOMPRESS_ALGORITHM_MASK, d) != CUDA_SUCCESS) return false; return (mask & CU_MEM_DECOMPRESS_ALGORITHM_DEFLATE) != 0; }
+};
+static DriverApi g_drv;
 static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std::min<u64>(p, 1ull << 31); }
 
 }  // namespace
 
 struct irf_ctx {
-  int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr;
+  int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr, s_de = nullptr;
   // options
-  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1;
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1;
   // references (host)
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
@@ -60,7 +78,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
-  DevBuf d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
+  DevBuf d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -79,7 +97,7 @@ struct irf_ctx {
     int n = 0; cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) throw string("no CUDA device: this library has no CPU path (") + cudaGetErrorString(e) + ")";
     device = dev; IRF_CUDA(cudaSetDevice(dev));
-    IRF_CUDA(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_copy, cudaStreamNonBlocking));
+    IRF_CUDA(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_copy, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_de, cudaStreamNonBlocking));
     d_stats.ensure(ST_COUNT * 8); d_err.ensure(4); d_small.ensure(256);
   }
   void sync() { IRF_CUDA(cudaStreamSynchronize(s_compute)); }
@@ -250,7 +268,7 @@ struct irf_ctx {
     d_comp.ensure(src_total + 64); d_U.ensure(Uend + 64);
     size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
     sync();  // the host vectors above go out of scope
-    resident = false; staged = true; staged_has_header = has_header != 0;
+    resident = false; staged = true; staged_has_header = has_header != 0; engines_planned = false;
     if (copy_now) { if (src_total) IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); sync(); resident = true; h_src = nullptr; }
   }
   void stage_inflated(const void* src, size_t n) {  // reference stdin mode with an already-inflated stream
@@ -266,22 +284,62 @@ struct irf_ctx {
   // the copy stream, each followed by a tiny stream-ordered "watermark" copy that tells the kernel how many bytes have
   // landed; warps whose next blocks lie beyond the watermark wait for it.  (Batched launches were tried first: every launch
   // ends with tens of milliseconds of partly idle SMs because one lane needs ~40 ms per 64 KiB block.)
+  // Which blocks go to the hardware decompression engine (DE) and which to the SM kernel.  The file is cut into the same
+  // 256 MB chunks the streamed copy uses; inside every chunk the first de_percent % of the blocks are the DE's, the rest
+  // the kernel's, so both engines always have landed data to work on.
+  void plan_engines(int de_percent) {
+    const size_t nb = blks.size(), chunk = 256ull << 20;
+    sm_list.clear(); de_list.clear(); de_chunk_end.clear();
+    const bool de_ok = de_percent > 0 && inflate_variant != 8 && g_drv.deflate_engine();
+    size_t b0 = 0, nch = (src_total + chunk - 1) / chunk;
+    for (size_t c = 0; c < std::max<size_t>(nch, 1); c++) {
+      size_t hi = std::min(src_total, (c + 1) * chunk), b1 = b0;
+      while (b1 < nb && (blks[b1].c_off + blks[b1].c_len + 8 <= hi || c + 1 >= nch)) b1++;
+      size_t nde = de_ok ? (b1 - b0) * (size_t)de_percent / 100 : 0;
+      for (size_t b = b0; b < b1; b++) { if (blks[b].isize == 0) continue; if (b < b0 + nde) de_list.push_back((u32)b); else sm_list.push_back((u32)b); }
+      de_chunk_end.push_back(de_list.size()); b0 = b1;
+    }
+    de_params.resize(de_list.size()); d_de_act.ensure(nb * 4);
+    for (size_t i = 0; i < de_list.size(); i++) { const Blk& k = blks[de_list[i]]; CUmemDecompressParams& q = de_params[i]; memset(&q, 0, sizeof q);
+      q.srcNumBytes = k.c_len; q.dstNumBytes = k.isize; q.dstActBytes = d_de_act.as<cuuint32_t>() + de_list[i]; q.src = d_comp.as<uint8_t>() + k.c_off; q.algo = CU_MEM_DECOMPRESS_ALGORITHM_DEFLATE; }
+    { u64 u = 0; size_t j = 0; for (size_t bI = 0; bI < nb && j < de_list.size(); bI++) { if (de_list[j] == bI) { de_params[j].dst = d_U.as<uint8_t>() + u; j++; } u += blks[bI].isize; } }
+    upload(d_sm_list, sm_list, s_compute); upload(d_de_list, de_list, s_compute); sync();
+    engines_planned = true; planned_percent = de_percent;
+  }
+  vector<u32> sm_list, de_list; vector<size_t> de_chunk_end; vector<CUmemDecompressParams> de_params; bool engines_planned = false;
+
+  // S1: BGZF inflate on two engines at once.  The Blackwell decompression engine (cuMemBatchDecompressAsync, raw DEFLATE,
+  // no SM involved) takes its share of every chunk; one persistent launch of inflate_kernel takes the rest.  When the bytes
+  // are still on the host the copy runs beside both on the copy stream in 256 MB chunks: the DE batch of a chunk is
+  // stream-ordered behind that chunk's copy, and the kernel follows an 8-byte "watermark" copied after every chunk.
   void inflate_all() {
     if (inflated_input) return;
     size_t nb = blks.size(); if (!nb) return;
+    // resident bytes: the two engines share the work (70/30 measured best); bytes streamed from the host arrive at PCIe speed,
+    // which the decompression engine alone keeps up with, so the SMs stay out of the way (measured: 288 ms vs 333 ms mixed)
+    const int want_percent = resident ? de_percent : de_percent_stream;
+    if (!engines_planned || planned_percent != want_percent) plan_engines(want_percent);
     IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
     unsigned long long* wm = (unsigned long long*)(d_small.as<uint8_t>() + 224);
     const bool stream_in = !resident && inflate_variant != 8;
     if (!resident && !stream_in) { IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); }
     if (stream_in) IRF_CUDA(cudaMemsetAsync(wm, 0, 8, s_compute));
-    InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)nb, d_status.as<int>(), T.err ? T.err : d_err.as<int>(),
-                  (unsigned int*)(d_small.as<uint8_t>() + 160), stream_in ? wm : nullptr};
-    cudaEvent_t k0, k1, ready; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1)); IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+    const bool listed = !de_list.empty();
+    InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), listed ? (int)sm_list.size() : (int)nb, d_status.as<int>(),
+                  T.err ? T.err : d_err.as<int>(), (unsigned int*)(d_small.as<uint8_t>() + 160), stream_in ? wm : nullptr, listed ? d_sm_list.as<u32>() : nullptr};
+    cudaEvent_t k0, k1, ready, de_done; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1));
+    IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming)); IRF_CUDA(cudaEventCreateWithFlags(&de_done, cudaEventDisableTiming));
+    IRF_CUDA(cudaEventRecord(k0, s_compute));
+    IRF_CUDA(cudaEventRecord(ready, s_compute)); IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0)); IRF_CUDA(cudaStreamWaitEvent(s_de, ready, 0));   // tables + zeroed watermark first
+    auto submit_de = [&](size_t from, size_t to) {
+      if (to <= from) return; size_t bad = 0;
+      CUresult r = g_drv.decompress(de_params.data() + from, to - from, 0, &bad, (CUstream)s_de);
+      if (r != CUDA_SUCCESS) throw string("cuMemBatchDecompressAsync failed with CUresult ") + std::to_string((int)r) + " (cuda)";
+    };
+    vector<cudaEvent_t> chunk_ev;
     if (stream_in) {
-      IRF_CUDA(cudaEventRecord(ready, s_compute)); IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0));   // tables + zeroed watermark first
-      // The copies are queued BEFORE the kernel is launched.  If the driver happens to map both streams onto one hardware
-      // queue the kernel then simply runs after the copies (no overlap, but no wait-for-ever either); with separate queues
-      // the copy engine and the kernel run side by side.
+      // Copies (and the DE batches behind them) are queued BEFORE the kernel is launched: if the driver maps two of these
+      // streams onto one hardware queue the kernel then simply runs after them instead of waiting for ever.
       const size_t chunk = 256ull << 20; size_t nch = (src_total + chunk - 1) / chunk;
       if (wm_host_cap < nch) { if (wm_host) cudaFreeHost(wm_host); IRF_CUDA(cudaMallocHost((void**)&wm_host, (nch + 8) * 8)); wm_host_cap = nch + 8; }
       for (size_t i = 0; i < nch; i++) {
@@ -289,17 +347,20 @@ struct irf_ctx {
         IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
         wm_host[i] = (i + 1 == nch) ? hi + 4096 : hi;   // the last mark also covers the kernel's look-ahead margin
         IRF_CUDA(cudaMemcpyAsync(wm, &wm_host[i], 8, cudaMemcpyHostToDevice, s_copy));
+        if (listed) { cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_de, ev, 0)); chunk_ev.push_back(ev);
+          submit_de(i ? de_chunk_end[i - 1] : 0, de_chunk_end[i]); }
       }
-    }
-    IRF_CUDA(cudaEventRecord(k0, s_compute)); launch_inflate(a, inflate_variant, s_compute); IRF_CUDA(cudaEventRecord(k1, s_compute));
-    if (stream_in) {
-      double tc0 = now_ms(); IRF_CUDA(cudaStreamSynchronize(s_copy));
-      if (getenv("IRF_DEBUG_TIMING")) fprintf(stderr, "[inflate] %zu bytes streamed, copies drained %.1f ms after the launch\n", src_total, now_ms() - tc0);
-    }
+    } else if (listed) { const size_t cap = 32768;   // very large batches (> ~150k operations) were measured 2.5x slower per byte
+      for (size_t i = 0; i < de_list.size(); i += cap) submit_de(i, std::min(de_list.size(), i + cap)); }
+    launch_inflate(a, inflate_variant, s_compute);
+    if (listed) { launch_de_check(d_de_list.as<u32>(), (int)de_list.size(), d_de_act.as<u32>(), d_u_len.as<u32>(), d_status.as<int>(), a.err, s_de);
+      IRF_CUDA(cudaEventRecord(de_done, s_de)); IRF_CUDA(cudaStreamWaitEvent(s_compute, de_done, 0)); }
+    IRF_CUDA(cudaEventRecord(k1, s_compute));
+    if (stream_in) IRF_CUDA(cudaStreamSynchronize(s_copy));
     IRF_CUDA(cudaGetLastError()); sync();
     float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k0, k1)); timing[1] = ms; n_inflate_launches = 1;
-    if (getenv("IRF_DEBUG_TIMING")) fprintf(stderr, "[inflate] kernel %.1f ms\n", ms);
-    cudaEventDestroy(k0); cudaEventDestroy(k1); cudaEventDestroy(ready);
+    if (getenv("IRF_DEBUG_TIMING")) fprintf(stderr, "[inflate] %.1f ms: %zu blocks on the decompression engine, %zu on the SM kernel%s\n", ms, de_list.size(), listed ? sm_list.size() : nb, stream_in ? " (streamed from the host)" : "");
+    cudaEventDestroy(k0); cudaEventDestroy(k1); cudaEventDestroy(ready); cudaEventDestroy(de_done); for (auto e : chunk_ev) cudaEventDestroy(e);
     resident = true;
   }
   unsigned long long* wm_host = nullptr; size_t wm_host_cap = 0;
@@ -521,14 +582,14 @@ void irf_destroy(irf_ctx* c) {
   if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
-                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
+                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->wm_host) cudaFreeHost(c->wm_host);
-  if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy);
+  if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy); if (c->s_de) cudaStreamDestroy(c->s_de);
   delete c;
 }
 const char* irf_last_error(irf_ctx* c) { return c ? c->err.c_str() : "null context"; }
@@ -543,6 +604,8 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "entry0") c->entry0_override = v;
   else if (k == "stage_lazy") c->stage_lazy = v != 0;
   else if (k == "verify_crc") c->verify_crc = v != 0;
+  else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
+  else if (k == "de_percent_stream") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent_stream = (int)v; c->engines_planned = false; }
   else { c->err = "unknown option " + k; return IRF_EINVAL; }
   return IRF_OK;
 }

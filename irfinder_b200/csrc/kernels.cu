@@ -47,7 +47,8 @@ __device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
 template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM, int RB, int PZ>
 __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                              uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
-                                                             int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark) {
+                                                             int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark,
+                                                             const u32* __restrict__ list) {   // list: optional indices of the blocks this kernel owns (the rest go to the decompression engine)
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // per warp: [lit LUT][dist LUT][2 x 32 canonical-limit entries] (16-bit, lane-interleaved) [output ring: 2^RB bytes per lane]
@@ -63,7 +64,7 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
       base = __shfl_sync(0xffffffffu, base, 0);
       if (base >= (unsigned int)nblk) break;
       if (watermark) {   // streaming input: wait until the host->device copy has passed the last byte these 32 blocks need
-        int lastb = min((int)base + 31, nblk - 1); u64 need = c_off[lastb] + c_len[lastb] + 160; bool starved = false;   // + the bit reader's look-ahead, rounded up to whole sectors:
+        int lastb = min((int)base + 31, nblk - 1); if (list) lastb = (int)list[lastb]; u64 need = c_off[lastb] + c_len[lastb] + 160; bool starved = false;   // + the bit reader's look-ahead, rounded up to whole sectors:
                                                                                // no lane may pull a not-yet-written sector into L1
         if (lane == 0) {
           long long t0 = clock64();
@@ -76,9 +77,9 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
         starved = __shfl_sync(0xffffffffu, (int)starved, 0) != 0;
         if (starved) { if (lane == 0) atomicOr(err, DERR_STARVED); break; }
       }
-      int b = (int)base + lane;
+      int b = (int)base + lane; const bool in_range = b < nblk; if (list && in_range) b = (int)list[b];
       InflateLane<32, LB, DB, RB, PZ> L;
-      bool work = b < nblk && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
+      bool work = in_range && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
       if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, ring); else L.idle();
       while (__any_sync(0xffffffffu, !L.done())) L.step();   // the vote keeps the warp converged (see InflateLane)
       if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
@@ -127,7 +128,7 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-    inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark); IRF_LAUNCHED();
+    inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();
   }
 }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
@@ -192,6 +193,13 @@ __global__ void __launch_bounds__(256) crc_check_kernel(const uint8_t* __restric
     }
     if (lane == 0 && (~r) != want[b]) { status[b] = 100; atomicOr(err, DERR_CRC); }
   }
+}
+__global__ void de_check_kernel(const u32* __restrict__ list, int n, const u32* __restrict__ act, const u32* __restrict__ u_len, int* __restrict__ status, int* __restrict__ err) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+  u32 b = list[i]; if (act[b] != u_len[b]) { status[b] = INF_ERR_ISIZE; atomicOr(err, DERR_INFLATE); }
+}
+void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s) {
+  if (n > 0) { de_check_kernel<<<(n + 255) / 256, 256, 0, s>>>(list, n, act, u_len, status, err); IRF_LAUNCHED(); }
 }
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s) {
   static CrcMul M; static bool init = false;

@@ -9,6 +9,7 @@ struct InflateArgs {
   uint8_t* U; const u64* u_off; const u32* u_len;            // inflated bytes, per-block offset / ISIZE
   int nblk; int* status; int* err; unsigned int* next_block;   // next_block: device work counter, zeroed by the launcher
   const unsigned long long* watermark;   // optional: bytes of `comp` that have landed so far (streaming from the host); null = all resident
+  const u32* list;                       // optional: nblk indices into the block arrays (blocks not listed are inflated elsewhere)
 };
 struct FrameArgs {
   const uint8_t* U; const u64* u_off; const u32* u_len; int nblk; u64 Uend; u64 rec0; int rec0_valid;  // rec0: inflated offset of the first record when known exactly
@@ -18,6 +19,7 @@ struct FrameArgs {
 
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
 // CRC-32 of every inflated BGZF block against the value in its footer (what `gzip -cd` checks for the reference)
+void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s);
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s);
 void launch_frame_guess(const FrameArgs& a, cudaStream_t s);
 void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s);

@@ -175,7 +175,9 @@ def test_repeated_runs_are_idempotent(tiny, tmp_path):
 def test_bad_inputs_fail_loudly(tiny, tmp_path):
     from irfinder_b200 import IRFError
     data = open(tiny["sorted"], "rb").read()
-    c = _core()
+    # de_percent=0: malformed DEFLATE must go to the SM kernel, which reports it and carries on; the hardware decompression
+    # engine answers a malformed stream with a sticky CUDA error that would take this whole test process with it
+    c = _core(de_percent=0)
     c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
     with pytest.raises(IRFError):   # cut mid-block
         c.run_bytes(data[: len(data) // 2])
@@ -286,3 +288,12 @@ def test_deep_introns_use_the_global_histogram_path(built, tmp_path):
     d = c.table("depth"); half = d.size // 2
     assert int((d[:half] + d[half:]).max()) >= 8192, "workload too shallow to exercise the scratch path"
     assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+
+
+@pytest.mark.parametrize("de_percent", [0, 35, 100])
+def test_inflate_engines_agree(tiny, tmp_path, de_percent):
+    """BGZF blocks may be inflated by the SM kernel, by the Blackwell hardware decompression engine, or split between them:
+    the outputs must not depend on the split (and CRC-32 of every block is verified in all cases)."""
+    c = _gpu_run(tiny, str(tmp_path / "g"), de_percent=de_percent)
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
