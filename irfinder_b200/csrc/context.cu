@@ -186,6 +186,7 @@ struct irf_ctx {
   }
 
   void reset() {
+    join_crc();
     if (!bound) { counted = finalized = false; return; }
     cudaStream_t s = s_compute;
     IRF_CUDA(cudaMemsetAsync(d_sp_count.p, 0, sp.pos.size() * 8, s)); IRF_CUDA(cudaMemsetAsync(d_roi_count.p, 0, roi.rois.size() * 8, s));
@@ -255,6 +256,7 @@ struct irf_ctx {
 
   void stage(const void* src, size_t n_own, size_t n_total, int has_header, bool copy_now) {
     if (n_own > n_total) throw string("nbytes_own > nbytes_total");
+    join_crc();
     double t0 = now_ms();
     inflated_input = false; scan_bgzf((const uint8_t*)src, n_own, n_total);
     if (require_eof && has_header && n_own == n_total) { if (blks.empty() || blks.back().isize != 0) throw string("BGZF EOF marker missing (truncated file?)"); }
@@ -306,6 +308,8 @@ struct irf_ctx {
     upload(d_sm_list, sm_list, s_compute); upload(d_de_list, de_list, s_compute); sync();
     engines_planned = true; planned_percent = de_percent;
   }
+  bool crc_pending = false;
+  void join_crc() { if (crc_pending) { IRF_CUDA(cudaStreamSynchronize(s_de)); crc_pending = false; } }
   vector<u32> sm_list, de_list; vector<size_t> de_chunk_end; vector<CUmemDecompressParams> de_params; bool engines_planned = false;
 
   // S1: BGZF inflate on two engines at once.  The Blackwell decompression engine (cuMemBatchDecompressAsync, raw DEFLATE,
@@ -348,7 +352,8 @@ struct irf_ctx {
         wm_host[i] = (i + 1 == nch) ? hi + 4096 : hi;   // the last mark also covers the kernel's look-ahead margin
         IRF_CUDA(cudaMemcpyAsync(wm, &wm_host[i], 8, cudaMemcpyHostToDevice, s_copy));
         if (listed) { cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_de, ev, 0)); chunk_ev.push_back(ev);
-          submit_de(i ? de_chunk_end[i - 1] : 0, de_chunk_end[i]); }
+          size_t f0 = i ? de_chunk_end[i - 1] : 0, f1 = de_chunk_end[i]; submit_de(f0, f1);
+          if (verify_crc && f1 > f0) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(f1 - f0), d_status.as<int>(), a.err, s_de, d_de_list.as<u32>() + f0); }
       }
     } else if (listed) { const size_t cap = 32768;   // very large batches (> ~150k operations) were measured 2.5x slower per byte
       for (size_t i = 0; i < de_list.size(); i += cap) submit_de(i, std::min(de_list.size(), i + cap)); }
@@ -356,6 +361,13 @@ struct irf_ctx {
     if (listed) { launch_de_check(d_de_list.as<u32>(), (int)de_list.size(), d_de_act.as<u32>(), d_u_len.as<u32>(), d_status.as<int>(), a.err, s_de);
       IRF_CUDA(cudaEventRecord(de_done, s_de)); IRF_CUDA(cudaStreamWaitEvent(s_compute, de_done, 0)); }
     IRF_CUDA(cudaEventRecord(k1, s_compute));
+    if (verify_crc) {   // CRC-32 of what is not checked yet, on the side stream: it overlaps record framing and counting and is joined in count()
+      IRF_CUDA(cudaEventRecord(ready, s_compute)); IRF_CUDA(cudaStreamWaitEvent(s_de, ready, 0));
+      if (!listed) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)nb, d_status.as<int>(), a.err, s_de);
+      else { if (!stream_in) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)de_list.size(), d_status.as<int>(), a.err, s_de, d_de_list.as<u32>());
+             launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)sm_list.size(), d_status.as<int>(), a.err, s_de, d_sm_list.as<u32>()); }
+      crc_pending = true;
+    }
     if (stream_in) IRF_CUDA(cudaStreamSynchronize(s_copy));
     IRF_CUDA(cudaGetLastError()); sync();
     float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k0, k1)); timing[1] = ms; n_inflate_launches = 1;
@@ -399,7 +411,6 @@ struct irf_ctx {
     IRF_CUDA(cudaEventRecord(e0, s_compute));
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
     inflate_all();
-    if (verify_crc && !inflated_input) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)blks.size(), d_status.as<int>(), T.err ? T.err : d_err.as<int>(), s_compute);
     check_dev_err("inflate");
     IRF_CUDA(cudaEventRecord(e1, s_compute));
     if (staged_has_header) parse_header_from_device();
@@ -439,6 +450,7 @@ struct irf_ctx {
     launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), lc[0], s_compute);
     launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), lc[1], s_compute);
     IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaGetLastError());
+    join_crc();
     check_dev_err("fragment counting");
     float a, b, c; IRF_CUDA(cudaEventElapsedTime(&a, e0, e1)); IRF_CUDA(cudaEventElapsedTime(&b, e1, e2)); IRF_CUDA(cudaEventElapsedTime(&c, e2, e3));
     timing[0] = a; timing[2] = b; timing[3] = c; timing[5] = a + b + c;
@@ -664,7 +676,7 @@ int irf_read_header(irf_ctx* c, const void* prefix, size_t n) {
     bool req = c->require_eof; c->require_eof = false;
     try { c->stage(prefix, 0, n, 1, false); } catch (...) { c->require_eof = req; throw; } c->require_eof = req;
     if (!c->bound) IRF_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4, c->s_compute));
-    c->inflate_all(); c->check_dev_err("inflate"); c->parse_header_from_device(); c->staged = false;
+    c->inflate_all(); c->join_crc(); c->check_dev_err("inflate"); c->parse_header_from_device(); c->staged = false;
   });
 }
 int irf_stage(irf_ctx* c, const void* bgzf, size_t own, size_t total, int has_header) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->stage(bgzf, own, total, has_header, !c->stage_lazy)); }

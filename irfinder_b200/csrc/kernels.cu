@@ -159,14 +159,15 @@ __host__ __device__ inline u32 crc_mulmod(u32 a, u32 b) {   // product of two po
 }
 struct CrcMul { u32 x[5]; };
 __global__ void __launch_bounds__(256) crc_check_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, const u32* __restrict__ want,
-                                                         int nblk, CrcMul M, int* __restrict__ status, int* __restrict__ err) {
+                                                         int nblk, CrcMul M, int* __restrict__ status, int* __restrict__ err, const u32* __restrict__ list) {
   __shared__ u32 T[4][256];
   for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = (u32)i; for (int k = 0; k < 8; k++) c = (c & 1u) ? (c >> 1) ^ CRC_POLY : c >> 1; T[0][i] = c; }
   __syncthreads();
   for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = T[0][i]; for (int t = 1; t < 4; t++) { c = T[0][c & 255u] ^ (c >> 8); T[t][i] = c; } }
   __syncthreads();
   const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
-  for (int b = blockIdx.x * wpb + (threadIdx.x >> 5); b < nblk; b += gridDim.x * wpb) {
+  for (int bi = blockIdx.x * wpb + (threadIdx.x >> 5); bi < nblk; bi += gridDim.x * wpb) {
+    const int b = list ? (int)list[bi] : bi;   // optional list of block indices (the blocks one engine produced)
     u32 len = u_len[b]; if (!len) continue;
     const uint8_t* base = U + u_off[b];
     long long hi = (long long)len - (long long)(31 - lane) * CRC_SLICE, lo = hi - CRC_SLICE;   // this lane's slice [lo, hi) of the block
@@ -201,12 +202,12 @@ __global__ void de_check_kernel(const u32* __restrict__ list, int n, const u32* 
 void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s) {
   if (n > 0) { de_check_kernel<<<(n + 255) / 256, 256, 0, s>>>(list, n, act, u_len, status, err); IRF_LAUNCHED(); }
 }
-void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s) {
+void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list) {
   static CrcMul M; static bool init = false;
   if (!init) { u32 p = 0x40000000u;   // x^1; square up to x^(8 * 2048) = x^(2^14), then keep squaring
     for (int i = 0; i < 14; i++) p = crc_mulmod(p, p);
     for (int k = 0; k < 5; k++) { M.x[k] = p; p = crc_mulmod(p, p); } init = true; }
-  if (nblk > 0) { int grid = std::min((nblk + 7) / 8, 148 * 8); crc_check_kernel<<<grid, 256, 0, s>>>(U, u_off, u_len, crc_expected, nblk, M, status, err); IRF_LAUNCHED(); }
+  if (nblk > 0) { int grid = std::min((nblk + 7) / 8, 148 * 8); crc_check_kernel<<<grid, 256, 0, s>>>(U, u_off, u_len, crc_expected, nblk, M, status, err, list); IRF_LAUNCHED(); }
 }
 
 // ------------------------------------------------------------------------------------------------

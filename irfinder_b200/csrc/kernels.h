@@ -20,7 +20,7 @@ struct FrameArgs {
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
 // CRC-32 of every inflated BGZF block against the value in its footer (what `gzip -cd` checks for the reference)
 void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s);
-void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s);
+void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list = nullptr);
 void launch_frame_guess(const FrameArgs& a, cudaStream_t s);
 void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s);
 void launch_frame_mark(const FrameArgs& a, uint8_t* mask, u32* n_bad, cudaStream_t s);

@@ -162,12 +162,15 @@ int directional(const JunctionRef& ref, const std::vector<std::string>& chr_name
   unsigned long long same = 0, diff = 0, ev = 0, nev = 0, evk = 0, nevk = 0;
   std::vector<const std::vector<JRow>*> by_id(chr_names.size(), nullptr);
   for (size_t i = 0; i < chr_names.size(); i++) { auto it = ref.flat.find(chr_names[i]); if (it != ref.flat.end()) by_id[i] = &it->second; }
+  // `counted` is ordered by (refid, start, end) and so is every chromosome's annotation: one forward cursor per chromosome
+  int cur_id = -1; size_t cur = 0;
   for (auto& e : counted) {  // thresholds [C-11]
     u32 c0 = e.cnt[0], c1 = e.cnt[1]; if (c0 + c1 <= 8) continue;
     u32 bits = 0;
     if (e.refid >= 0 && e.refid < (int)by_id.size() && by_id[e.refid]) { auto& v = *by_id[e.refid];
-      auto it = std::lower_bound(v.begin(), v.end(), e, [](const JRow& r, const JuncEntry& k) { return r.start != k.start ? r.start < k.start : r.end < k.end; });
-      if (it != v.end() && it->start == e.start && it->end == e.end) bits = it->bits; }
+      if (e.refid != cur_id) { cur_id = e.refid; cur = 0; }
+      while (cur < v.size() && (v[cur].start < e.start || (v[cur].start == e.start && v[cur].end < e.end))) cur++;
+      if (cur < v.size() && v[cur].start == e.start && v[cur].end == e.end) bits = v[cur].bits; }
     if (c0 > c1 * 4) { ev++; if (bits) evk++; if (bits == 1) same++; else if (bits == 2) diff++; }
     else if (c1 > c0 * 4) { ev++; if (bits) evk++; if (bits == 2) same++; else if (bits == 1) diff++; }
     else { nev++; if (bits) nevk++; }
