@@ -290,8 +290,8 @@ struct irf_ctx {
   // 256 MB chunks the streamed copy uses; inside every chunk the first de_percent % of the blocks are the DE's, the rest
   // the kernel's, so both engines always have landed data to work on.
   void plan_engines(int de_percent) {
-    const size_t nb = blks.size(), chunk = 256ull << 20;
-    sm_list.clear(); de_list.clear(); de_chunk_end.clear();
+    const size_t nb = blks.size(), chunk = chunk_bytes;
+    sm_list.clear(); de_list.clear(); de_chunk_end.clear(); chunk_blk_end.clear();
     const bool de_ok = de_percent > 0 && inflate_variant != 8 && g_drv.deflate_engine();
     size_t b0 = 0, nch = (src_total + chunk - 1) / chunk;
     for (size_t c = 0; c < std::max<size_t>(nch, 1); c++) {
@@ -299,7 +299,7 @@ struct irf_ctx {
       while (b1 < nb && (blks[b1].c_off + blks[b1].c_len + 8 <= hi || c + 1 >= nch)) b1++;
       size_t nde = de_ok ? (b1 - b0) * (size_t)de_percent / 100 : 0;
       for (size_t b = b0; b < b1; b++) { if (blks[b].isize == 0) continue; if (b < b0 + nde) de_list.push_back((u32)b); else sm_list.push_back((u32)b); }
-      de_chunk_end.push_back(de_list.size()); b0 = b1;
+      de_chunk_end.push_back(de_list.size()); chunk_blk_end.push_back(b1); b0 = b1;
     }
     de_params.resize(de_list.size()); d_de_act.ensure(nb * 4);
     for (size_t i = 0; i < de_list.size(); i++) { const Blk& k = blks[de_list[i]]; CUmemDecompressParams& q = de_params[i]; memset(&q, 0, sizeof q);
@@ -310,6 +310,7 @@ struct irf_ctx {
   }
   bool crc_pending = false;
   void join_crc() { if (crc_pending) { IRF_CUDA(cudaStreamSynchronize(s_de)); crc_pending = false; } }
+  size_t chunk_bytes = 256ull << 20; vector<size_t> chunk_blk_end; int stream_pipeline = 1;
   vector<u32> sm_list, de_list; vector<size_t> de_chunk_end; vector<CUmemDecompressParams> de_params; bool engines_planned = false;
 
   // S1: BGZF inflate on two engines at once.  The Blackwell decompression engine (cuMemBatchDecompressAsync, raw DEFLATE,
@@ -344,7 +345,7 @@ struct irf_ctx {
     if (stream_in) {
       // Copies (and the DE batches behind them) are queued BEFORE the kernel is launched: if the driver maps two of these
       // streams onto one hardware queue the kernel then simply runs after them instead of waiting for ever.
-      const size_t chunk = 256ull << 20; size_t nch = (src_total + chunk - 1) / chunk;
+      const size_t chunk = chunk_bytes; size_t nch = (src_total + chunk - 1) / chunk;
       if (wm_host_cap < nch) { if (wm_host) cudaFreeHost(wm_host); IRF_CUDA(cudaMallocHost((void**)&wm_host, (nch + 8) * 8)); wm_host_cap = nch + 8; }
       for (size_t i = 0; i < nch; i++) {
         size_t lo = i * chunk, hi = std::min(src_total, lo + chunk);
@@ -404,9 +405,90 @@ struct irf_ctx {
     if (!have_header || names != chr_names || lens != chr_lens || !bound) { chr_names = names; chr_lens = lens; have_header = true; chr_map_update(); }
   }
 
+  // S1-S3 as one pipeline for bytes that are still on the host (the end-to-end path).  The file is cut into chunks; every
+  // chunk is copied, inflated by the decompression engine and CRC-checked on the side streams (all queued up front, chained
+  // by events), and the compute stream frames, pairs and counts chunk k as soon as chunk k+1 has been inflated (a record that
+  // starts in chunk k may end in chunk k+1).  Mate pairing is order-free, so counting chunk by chunk gives the same tables;
+  // the PCIe transfer (the bound of the end-to-end path) then hides framing and counting as well as the inflate.
+  bool can_pipeline() { return !resident && !inflated_input && stream_pipeline && staged_has_header && nblk_own == (int)blks.size() && !blks.empty() && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine(); }
+  void count_streaming() {
+    cudaEvent_t e0, e3; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e3)); IRF_CUDA(cudaEventRecord(e0, s_compute));
+    if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
+    if (!engines_planned || planned_percent != 100) plan_engines(100);
+    const size_t nb = blks.size(), nch = chunk_blk_end.size();
+    int* errp = T.err ? T.err : d_err.as<int>();
+    IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
+    cudaEvent_t ready; IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ready, s_compute));
+    IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0)); IRF_CUDA(cudaStreamWaitEvent(s_de, ready, 0));
+    vector<cudaEvent_t> ev_copy(nch), ev_inf(nch); vector<u64> inf_end(nch);   // inflated offset where each chunk ends
+    { u64 u = 0; size_t b = 0; for (size_t c = 0; c < nch; c++) { for (; b < chunk_blk_end[c]; b++) u += blks[b].isize; inf_end[c] = u; } }
+    for (size_t c = 0; c < nch; c++) {
+      size_t lo = c * chunk_bytes, hi = std::min(src_total, lo + chunk_bytes);
+      if (hi > lo) IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
+      IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev_copy[c], s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_de, ev_copy[c], 0));
+      size_t f0 = c ? de_chunk_end[c - 1] : 0, f1 = de_chunk_end[c];
+      for (size_t i = f0; i < f1; i += 32768) { size_t bad = 0; CUresult r = g_drv.decompress(de_params.data() + i, std::min(f1, i + 32768) - i, 0, &bad, (CUstream)s_de);
+        if (r != CUDA_SUCCESS) throw string("cuMemBatchDecompressAsync failed with CUresult ") + std::to_string((int)r) + " (cuda)"; }
+      if (f1 > f0) { launch_de_check(d_de_list.as<u32>() + f0, (int)(f1 - f0), d_de_act.as<u32>(), d_u_len.as<u32>(), d_status.as<int>(), errp, s_de);
+        if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(f1 - f0), d_status.as<int>(), errp, s_de, d_de_list.as<u32>() + f0); }
+      IRF_CUDA(cudaEventCreate(&ev_inf[c])); IRF_CUDA(cudaEventRecord(ev_inf[c], s_de));
+    }
+    auto cleanup = [&]() { for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); };
+    try {
+      // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
+      for (size_t c = 0;; c++) {
+        IRF_CUDA(cudaEventSynchronize(ev_inf[c])); check_dev_err("inflate");
+        u64 full = Uend; Uend = inf_end[c]; bool ok = true;
+        try { parse_header_from_device(); } catch (const string& e) { ok = false; if (e.find("truncated") == string::npos || c + 1 == nch) { Uend = full; throw; } }
+        Uend = full; if (ok) break;
+      }
+      if (!bound) chr_map_update();
+      pslots = next_pow2(std::max<u64>(1024, Uend / 80)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
+      u32* n_bad = d_small.as<u32>(); u64* totals = (u64*)(d_small.as<uint8_t>() + 16); u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192);
+      u64 entry_prev = rec0; n_rec = 0; n_cand = 0; frame_rounds = 0; size_t b0 = 0;
+      for (size_t c = 0; c < nch; c++) {
+        size_t b1 = chunk_blk_end[c]; int nbk = (int)(b1 - b0); if (!nbk) continue;
+        IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[std::min(c + 1, nch - 1)], 0));   // chunk c is counted once chunk c+1 is inflated
+        const u64 visible = inf_end[std::min(c + 1, nch - 1)];
+        FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, nbk, visible, entry_prev, 1, T.n_ref, T.ref_len,
+                     d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err};
+        launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
+        for (int rounds = 0;; rounds++) {
+          IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mask.as<uint8_t>() + b0, n_bad, s_compute);
+          u32 hb = 0; IRF_CUDA(cudaMemcpyAsync(&hb, n_bad, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
+          if (!hb) break; if (rounds > nbk + 2) throw string("record framing did not converge"); frame_rounds++;
+          launch_walk_count(fa, d_mask.as<uint8_t>() + b0, s_compute);
+        }
+        IRF_CUDA(cudaMemsetAsync(totals, 0, 16, s_compute)); launch_frame_totals(fa, totals, s_compute);
+        u64 ht[2] = {0, 0}, ex = 0; IRF_CUDA(cudaMemcpyAsync(ht, totals, 16, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(&ex, d_exit.as<u64>() + (b1 - 1), 8, cudaMemcpyDeviceToHost, s_compute));
+        sync(); check_dev_err("record framing");
+        entry_prev = ex; n_rec += ht[0]; n_cand += ht[1];
+        if (ht[0]) {
+          d_rec_base.ensure((size_t)nbk * 8); d_rec_off.ensure((ht[0] + ht[0] / 2) * 8); d_pair_list.ensure((ht[1] + ht[1] / 2 + 16) * 16); d_single_list.ensure((ht[0] + ht[0] / 2 + 16) * 8);
+          launch_scan_counts(d_nrec.as<u32>() + b0, d_rec_base.as<u64>(), nbk, s_compute); launch_walk_list(fa, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
+          IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
+          launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), ht[0], d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute);
+          u64 lc[2] = {0, 0}; IRF_CUDA(cudaMemcpyAsync(lc, list_counts, 16, cudaMemcpyDeviceToHost, s_compute)); sync();
+          launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), lc[0], s_compute); launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), lc[1], s_compute);
+          sync();   // the work lists are reused by the next chunk
+        }
+        b0 = b1;
+      }
+      if (entry_prev != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
+      IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaStreamSynchronize(s_copy)); IRF_CUDA(cudaStreamSynchronize(s_de)); sync();
+      check_dev_err("fragment counting");
+      float tot = 0, inf = 0; IRF_CUDA(cudaEventElapsedTime(&tot, e0, e3)); IRF_CUDA(cudaEventElapsedTime(&inf, e0, ev_inf[nch - 1]));
+      timing[0] = inf; timing[1] = inf; timing[2] = 0; timing[3] = tot - inf; timing[5] = tot; n_inflate_launches = 0;
+      frame_entry0 = rec0; frame_exit_rel = 0;
+    } catch (...) { cudaStreamSynchronize(s_copy); cudaStreamSynchronize(s_de); cudaStreamSynchronize(s_compute); cleanup(); throw; }
+    cleanup();
+    resident = true; counted = true; finalized = false;
+  }
+
   // S2 + S3
   void count() {
     if (!staged) throw string("nothing staged");
+    if (can_pipeline()) { count_streaming(); return; }
     cudaEvent_t e0, e1, e2, e3; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventCreate(&e2)); IRF_CUDA(cudaEventCreate(&e3));
     IRF_CUDA(cudaEventRecord(e0, s_compute));
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
@@ -617,6 +699,8 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "stage_lazy") c->stage_lazy = v != 0;
   else if (k == "verify_crc") c->verify_crc = v != 0;
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
+  else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
+  else if (k == "stream_pipeline") c->stream_pipeline = v != 0;
   else if (k == "de_percent_stream") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent_stream = (int)v; c->engines_planned = false; }
   else { c->err = "unknown option " + k; return IRF_EINVAL; }
   return IRF_OK;

@@ -297,3 +297,21 @@ def test_inflate_engines_agree(tiny, tmp_path, de_percent):
     c = _gpu_run(tiny, str(tmp_path / "g"), de_percent=de_percent)
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
     assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+
+
+@pytest.mark.parametrize("chunk_kb", [64, 300])
+def test_streaming_pipeline_counts_chunk_by_chunk(tiny, tmp_path, chunk_kb):
+    """Host-resident input is copied, inflated, framed and counted chunk by chunk (count_streaming).  Tiny chunks put a chunk
+    boundary after every few BGZF blocks, so records and mate pairs straddle chunks all the time; outputs must not change."""
+    c = _core(stream_chunk_kb=chunk_kb)
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    for bam in (tiny["sorted"], tiny["collated"]):
+        c.run_bam(bam)
+        out = str(tmp_path / ("g_" + os.path.basename(bam)))
+        c.write_outputs(out)
+        assert_same_outputs(tiny["oracle_out"], out)
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+    c.set_option("stream_pipeline", 0)     # the unpipelined path must agree
+    c.run_bam(tiny["sorted"])
+    c.write_outputs(str(tmp_path / "g_plain"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g_plain"))
