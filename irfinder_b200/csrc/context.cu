@@ -256,9 +256,20 @@ struct irf_ctx {
 
   void stage(const void* src, size_t n_own, size_t n_total, int has_header, bool copy_now) {
     if (n_own > n_total) throw string("nbytes_own > nbytes_total");
-    join_crc();
+    join_crc(); IRF_CUDA(cudaStreamSynchronize(s_copy)); drop_pre_copies();
     double t0 = now_ms();
-    inflated_input = false; scan_bgzf((const uint8_t*)src, n_own, n_total);
+    inflated_input = false;
+    if (!copy_now && stream_pipeline && has_header && n_own == n_total && n_total > 0 && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine()) {
+      // end-to-end path: the bytes can start crossing PCIe before the host has even walked the BGZF block chain
+      d_comp.ensure(n_total + 64);
+      // only the first two chunks: the small table uploads that follow the scan share the host->device copy engine with these
+      // transfers and would otherwise queue behind the whole file
+      for (size_t lo = 0; lo < n_total && pre_ev_copy.size() < 2; lo += chunk_bytes) { size_t hi = std::min(n_total, lo + chunk_bytes);
+        IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, (const uint8_t*)src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
+        cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); pre_ev_copy.push_back(ev); }
+      pre_copied_bytes = std::min(n_total, pre_ev_copy.size() * chunk_bytes);
+    }
+    scan_bgzf((const uint8_t*)src, n_own, n_total);
     if (require_eof && has_header && n_own == n_total) { if (blks.empty() || blks.back().isize != 0) throw string("BGZF EOF marker missing (truncated file?)"); }
     timing[6] = now_ms() - t0;
     h_src = (const uint8_t*)src; src_total = blks.empty() ? 0 : (size_t)(blks.back().c_off + blks.back().c_len + 8);
@@ -267,7 +278,8 @@ struct irf_ctx {
     upload(d_crc, crcs, s_compute);
     Uend = u;
     upload(d_c_off, c_off, s_compute); upload(d_c_len, c_len, s_compute); upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute);
-    d_comp.ensure(src_total + 64); d_U.ensure(Uend + 64);
+    if (pre_ev_copy.empty()) d_comp.ensure(src_total + 64);
+    d_U.ensure(Uend + 64);
     size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
     sync();  // the host vectors above go out of scope
     resident = false; staged = true; staged_has_header = has_header != 0; engines_planned = false;
@@ -308,6 +320,8 @@ struct irf_ctx {
     upload(d_sm_list, sm_list, s_compute); upload(d_de_list, de_list, s_compute); sync();
     engines_planned = true; planned_percent = de_percent;
   }
+  vector<cudaEvent_t> pre_ev_copy; size_t pre_copied_bytes = 0;
+  void drop_pre_copies() { for (auto e : pre_ev_copy) cudaEventDestroy(e); pre_ev_copy.clear(); pre_copied_bytes = 0; }
   bool crc_pending = false;
   void join_crc() { if (crc_pending) { IRF_CUDA(cudaStreamSynchronize(s_de)); crc_pending = false; } }
   size_t chunk_bytes = 256ull << 20; vector<size_t> chunk_blk_end; int stream_pipeline = 1;
@@ -422,10 +436,13 @@ struct irf_ctx {
     IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0)); IRF_CUDA(cudaStreamWaitEvent(s_de, ready, 0));
     vector<cudaEvent_t> ev_copy(nch), ev_inf(nch); vector<u64> inf_end(nch);   // inflated offset where each chunk ends
     { u64 u = 0; size_t b = 0; for (size_t c = 0; c < nch; c++) { for (; b < chunk_blk_end[c]; b++) u += blks[b].isize; inf_end[c] = u; } }
+    const size_t npre = std::min(pre_ev_copy.size(), nch);   // chunks whose copy stage() already queued (same chunking)
     for (size_t c = 0; c < nch; c++) {
       size_t lo = c * chunk_bytes, hi = std::min(src_total, lo + chunk_bytes);
-      if (hi > lo) IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
-      IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev_copy[c], s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_de, ev_copy[c], 0));
+      if (c < npre) { ev_copy[c] = pre_ev_copy[c]; }
+      else { if (hi > lo) IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
+        IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev_copy[c], s_copy)); }
+      IRF_CUDA(cudaStreamWaitEvent(s_de, ev_copy[c], 0));
       size_t f0 = c ? de_chunk_end[c - 1] : 0, f1 = de_chunk_end[c];
       for (size_t i = f0; i < f1; i += 32768) { size_t bad = 0; CUresult r = g_drv.decompress(de_params.data() + i, std::min(f1, i + 32768) - i, 0, &bad, (CUstream)s_de);
         if (r != CUDA_SUCCESS) throw string("cuMemBatchDecompressAsync failed with CUresult ") + std::to_string((int)r) + " (cuda)"; }
@@ -433,6 +450,8 @@ struct irf_ctx {
         if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(f1 - f0), d_status.as<int>(), errp, s_de, d_de_list.as<u32>() + f0); }
       IRF_CUDA(cudaEventCreate(&ev_inf[c])); IRF_CUDA(cudaEventRecord(ev_inf[c], s_de));
     }
+    for (size_t c = npre; c < pre_ev_copy.size(); c++) cudaEventDestroy(pre_ev_copy[c]);
+    pre_ev_copy.clear(); pre_copied_bytes = 0;   // ownership of the first npre events moved to ev_copy
     auto cleanup = [&]() { for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); };
     try {
       // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
@@ -489,6 +508,7 @@ struct irf_ctx {
   void count() {
     if (!staged) throw string("nothing staged");
     if (can_pipeline()) { count_streaming(); return; }
+    if (!pre_ev_copy.empty()) { IRF_CUDA(cudaStreamSynchronize(s_copy)); if (pre_copied_bytes >= src_total) resident = true; drop_pre_copies(); }
     cudaEvent_t e0, e1, e2, e3; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventCreate(&e2)); IRF_CUDA(cudaEventCreate(&e3));
     IRF_CUDA(cudaEventRecord(e0, s_compute));
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
@@ -639,9 +659,11 @@ struct irf_ctx {
   }
 
   void run_host_buffer(const void* p, size_t n) {
-    stage(p, n, n, 1, false);
-    if (bound) reset();
-    count(); finalize();
+    const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr; double t0 = now_ms(), t1, t2, t3;
+    stage(p, n, n, 1, false); t1 = now_ms();
+    if (bound) reset(); t2 = now_ms();
+    count(); t3 = now_ms(); finalize();
+    if (dbg) fprintf(stderr, "[run] stage %.1f ms, reset %.1f ms, count %.1f ms, finalize %.1f ms\n", t1 - t0, t2 - t1, t3 - t2, now_ms() - t3);
   }
   void* pinned_buf(size_t n) { if (n > pinned_cap) { if (pinned) cudaFreeHost(pinned); pinned = nullptr; IRF_CUDA(cudaMallocHost(&pinned, n + 64)); pinned_cap = n; } return pinned; }
   size_t read_fd_all(int fd, size_t hint) {
@@ -713,7 +735,15 @@ int irf_run_bam(irf_ctx* c, const char* path, const char* /*bai_path*/) {
   IRF_TRY(c, {
     int fd = open(path, O_RDONLY); if (fd < 0) throw string("cannot open ") + path;
     struct stat st; size_t hint = 0; if (fstat(fd, &st) == 0 && st.st_size > 0) hint = (size_t)st.st_size + 1;
-    size_t n = 0; try { n = c->read_fd_all(fd, hint); } catch (...) { close(fd); throw; } close(fd);
+    size_t n = 0;
+    try {
+      if (hint > (64u << 20)) {   // regular file of known size: several threads pread disjoint slices into the pinned buffer
+        size_t size = hint - 1; uint8_t* dst = (uint8_t*)c->pinned_buf(size); unsigned nt = std::min(8u, std::max(1u, std::thread::hardware_concurrency())); vector<std::thread> th; vector<int> bad(nt, 0);
+        for (unsigned t = 0; t < nt; t++) th.emplace_back([&, t]() { size_t lo = size * t / nt, hi = size * (t + 1) / nt; while (lo < hi) { ssize_t k = pread(fd, dst + lo, std::min<size_t>(hi - lo, 64u << 20), (off_t)lo); if (k <= 0) { bad[t] = 1; break; } lo += (size_t)k; } });
+        for (auto& x : th) x.join(); for (int b : bad) if (b) throw string("read error");
+        n = size;
+      } else n = c->read_fd_all(fd, hint);
+    } catch (...) { close(fd); throw; } close(fd);
     c->run_host_buffer(c->pinned, n);
   });
 }
