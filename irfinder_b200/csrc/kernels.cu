@@ -397,7 +397,7 @@ struct FragSink {
       if (a < b) { int32_t* d = T.diff + (u64)dir * T.P + T.seg_coff[lo]; atomicAdd(d + (a - ss), 1); atomicAdd(d + (b - ss), -1); }
     }
   }
-  __device__ void block(int s, int l) {
+  __device__ __noinline__ void block(int s, int l) {   // one body shared by every call site: the fully inlined version thrashed the instruction cache
     u32 a = read_start + (u32)s, e = a + (u32)l;
     nuc += (u32)l;
     if (have_prev && prev_len >= JUNC_MIN_FLANK && l >= JUNC_MIN_FLANK) junction(prev_end, a);
@@ -408,8 +408,9 @@ struct FragSink {
   }
   // FragmentsInChr / FragmentsInROI ::ProcessBlocks (row a13)
   __device__ void fragment_counts(u32 fs, u32 fe) {
-    { u32 key = (u32)dir * (u32)T.n_ref + (u32)chr; u32 act = __activemask(); u32 grp = __match_any_sync(act, key);   // neighbouring records share chromosome and strand
-      if ((int)(__ffs(grp) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&T.chr_count[key], (u32)__popc(grp)); }
+    { u32 key = (u32)dir * (u32)T.n_ref + (u32)chr; u32 act = __activemask(); int first = __ffs(act) - 1;   // neighbouring records share chromosome and strand:
+      u32 key0 = __shfl_sync(act, key, first); u32 same = __ballot_sync(act, key == key0);                  // one atomic for everybody who agrees with the first lane
+      if (key != key0) atomicAdd(&T.chr_count[key], 1u); else if ((int)(threadIdx.x & 31) == first) atomicAdd(&T.chr_count[key], (u32)__popc(same)); }
     Range r = T.roi_range[chr]; if (r.begin == r.end) return;
     u32 lo = T.roi_bidx[bucket_of(fs)];
     while (lo < r.end && T.roi_end[lo] <= fs) lo++;                          // first ROI with end > fs
