@@ -17,10 +17,21 @@ static std::vector<std::string> split_tabs(const std::string& line) {
   return f;
 }
 
+// Reference files are written by BuildRef (Perl); a malformed line is reported with its file and line number instead of
+// being skipped, because a silently dropped intron or junction changes every downstream table.
+static u32 parse_u32(const std::string& f, const char* file, size_t line, const char* what) {
+  if (f.empty() || f.size() > 10) throw std::string(file) + " line " + std::to_string(line) + ": bad " + what + " '" + f + "'";
+  unsigned long long v = 0; for (char ch : f) { if (ch < '0' || ch > '9') throw std::string(file) + " line " + std::to_string(line) + ": bad " + what + " '" + f + "'"; v = v * 10 + (unsigned)(ch - '0'); }
+  if (v > 0xffffffffull) throw std::string(file) + " line " + std::to_string(line) + ": " + what + " out of range";
+  return (u32)v;
+}
+static void bad_line(const char* file, size_t line, const std::string& why) { throw std::string(file) + " line " + std::to_string(line) + ": " + why; }
+
 // SpansPoint::loadRef — "chr pos strand"; the strand column is not used at lookup time [C-9]
 void SpansPointRef::loadRef(std::istream& in) {
-  std::map<std::string, std::vector<u32>> by_chr; std::string line;
-  while (std::getline(in, line)) { if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 2) continue; by_chr[f[0]].push_back((u32)std::stoul(f[1])); }
+  std::map<std::string, std::vector<u32>> by_chr; std::string line; size_t ln = 0;
+  while (std::getline(in, line)) { ln++; if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 2) bad_line("ref-read-continues.ref", ln, "expected 'chr<TAB>pos[<TAB>strand]'");
+    by_chr[f[0]].push_back(parse_u32(f[1], "ref-read-continues.ref", ln, "position")); }
   pos.clear(); chr_range.clear();
   for (auto& c : by_chr) { std::sort(c.second.begin(), c.second.end()); Range r; r.begin = (u32)pos.size(); pos.insert(pos.end(), c.second.begin(), c.second.end()); r.end = (u32)pos.size(); chr_range[c.first] = r; }
 }
@@ -32,10 +43,11 @@ int SpansPointRef::lookup_index(const std::string& chr, u32 p) const {
 
 // JunctionCount::loadRef — "chr start end strand"
 void JunctionRef::loadRef(std::istream& in) {
-  std::string line;
+  std::string line; size_t ln = 0;
   while (std::getline(in, line)) {
-    if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) continue;
-    u32& bits = chr_junc[f[0]][std::make_pair((u32)std::stoul(f[1]), (u32)std::stoul(f[2]))];
+    ln++; if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) bad_line("ref-sj.ref", ln, "expected 'chr<TAB>start<TAB>end<TAB>strand'");
+    u32 js = parse_u32(f[1], "ref-sj.ref", ln, "start"), je = parse_u32(f[2], "ref-sj.ref", ln, "end"); if (je < js) bad_line("ref-sj.ref", ln, "junction end before start");
+    u32& bits = chr_junc[f[0]][std::make_pair(js, je)];
     if (f[3] == "-") bits |= 1; else if (f[3] == "+") bits |= 2;
   }
   flat.clear();
@@ -44,8 +56,9 @@ void JunctionRef::loadRef(std::istream& in) {
 
 // FragmentsInROI::loadRef — "chr start end name", kept sorted by end
 void RoiRef::loadRef(std::istream& in) {
-  std::map<std::string, std::vector<Roi>> by_chr; std::string line;
-  while (std::getline(in, line)) { if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) continue; by_chr[f[0]].push_back(Roi{(u32)std::stoul(f[1]), (u32)std::stoul(f[2]), f[3]}); }
+  std::map<std::string, std::vector<Roi>> by_chr; std::string line; size_t ln = 0;
+  while (std::getline(in, line)) { ln++; if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 4) bad_line("ref-ROI.bed", ln, "expected 'chr<TAB>start<TAB>end<TAB>name'");
+    Roi r{parse_u32(f[1], "ref-ROI.bed", ln, "start"), parse_u32(f[2], "ref-ROI.bed", ln, "end"), f[3]}; if (r.end < r.start) bad_line("ref-ROI.bed", ln, "end before start"); by_chr[f[0]].push_back(r); }
   rois.clear(); chr_range.clear(); present = true;
   for (auto& c : by_chr) {
     std::stable_sort(c.second.begin(), c.second.end(), [](const Roi& a, const Roi& b) { return a.end < b.end; });
@@ -55,16 +68,21 @@ void RoiRef::loadRef(std::istream& in) {
 
 // CoverageBlocks::loadRef — BED12; measured segments are the union of every record's blocks
 void CoverageRef::loadRef(std::istream& in) {
-  std::map<std::string, std::vector<std::pair<u32, u32>>> raw; std::string line;
+  std::map<std::string, std::vector<std::pair<u32, u32>>> raw; std::string line; size_t ln = 0; const char* F = "ref-cover.bed";
   BEDrecords.clear();
   while (std::getline(in, line)) {
-    if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 12) continue;
-    BEDrecord r; r.chrName = f[0]; r.start = (u32)std::stoul(f[1]); r.end = (u32)std::stoul(f[2]); r.name = f[3]; r.direction = (f[5] == "+");
+    ln++; if (line.empty()) continue; auto f = split_tabs(line); if (f.size() < 12) bad_line(F, ln, "expected 12 BED columns, found " + std::to_string(f.size()));
+    BEDrecord r; r.chrName = f[0]; r.start = parse_u32(f[1], F, ln, "start"); r.end = parse_u32(f[2], F, ln, "end"); r.name = f[3]; r.direction = (f[5] == "+");
+    if (r.end < r.start) bad_line(F, ln, "end before start");
+    u32 nblocks = parse_u32(f[9], F, ln, "blockCount");
     std::istringstream ls(f[10]), os(f[11]); std::string a, b;
     while (std::getline(ls, a, ',') && std::getline(os, b, ',')) {
-      if (a.empty() || b.empty()) break; u32 len = (u32)std::stoul(a), off = (u32)std::stoul(b);
+      if (a.empty() || b.empty()) break; u32 len = parse_u32(a, F, ln, "block size"), off = parse_u32(b, F, ln, "block start");
+      if ((u64)r.start + off + len > r.end) bad_line(F, ln, "block reaches beyond the record's end");
+      if (!r.blocks.empty() && r.start + off < r.blocks.back().second) bad_line(F, ln, "blocks overlap or are not in ascending order");
       r.blocks.push_back({r.start + off, r.start + off + len}); raw[r.chrName].push_back(r.blocks.back());
     }
+    if (r.blocks.size() != nblocks) bad_line(F, ln, "blockCount says " + std::to_string(nblocks) + " but " + std::to_string(r.blocks.size()) + " blocks are listed");
     BEDrecords.push_back(std::move(r));
   }
   seg_start.clear(); seg_end.clear(); seg_coff.clear(); chr_range.clear(); P = 0;

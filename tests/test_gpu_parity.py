@@ -315,3 +315,21 @@ def test_streaming_pipeline_counts_chunk_by_chunk(tiny, tmp_path, chunk_kb):
     c.run_bam(tiny["sorted"])
     c.write_outputs(str(tmp_path / "g_plain"))
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g_plain"))
+
+
+def test_malformed_reference_files_are_reported_with_line_numbers(tiny, tmp_path):
+    from irfinder_b200 import IRFError
+    c = _core()
+    lines = open(tiny["cover"]).read().split("\n")
+    for mutate, needle in ((lambda f: f[:11], "12 BED columns"), (lambda f: f[:9] + ["7"] + f[10:], "blockCount"), (lambda f: f[:1] + ["12x"] + f[2:], "bad start")):
+        f = lines[2].split("\t")
+        bad = str(tmp_path / "bad-cover.bed")
+        open(bad, "w").write("\n".join(lines[:2] + ["\t".join(mutate(f))] + lines[3:]))
+        with pytest.raises(IRFError) as ei:
+            c.load_ref(bad, tiny["sj"], tiny["rc"], tiny["roi"])
+        assert "ref-cover.bed line 3" in str(ei.value) and needle in str(ei.value)
+    with pytest.raises(IRFError):
+        c.load_ref(tiny["cover"], str(tmp_path / "missing.ref"), tiny["rc"], tiny["roi"])
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])   # a good set still loads afterwards
+    c.run_bam(tiny["sorted"])
+    assert c.stats()["pairs"] > 0
