@@ -64,9 +64,9 @@ static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std:
 }  // namespace
 
 struct irf_ctx {
-  int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr, s_de = nullptr;
+  int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr, s_de = nullptr, s_chk = nullptr;
   // options
-  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1;
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1, de_percent_overlap = 79, resident_pipeline = 1;
   // references (host)
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
@@ -86,7 +86,7 @@ struct irf_ctx {
   // results
   vector<u64> h_stats; vector<u32> h_sp, h_roi, h_chr, h_dump; vector<JuncEntry> h_junc; vector<IntronRow> rows_nondir, rows_dir; vector<int32_t> h_depth;
   struct JuncOut { int32_t refid; u32 start, end, neg, pos; }; vector<JuncOut> h_junc_out;
-  int directionality = 0; string stdout_text, dir_log; double timing[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
+  int directionality = 0; string stdout_text, dir_log; double timing[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
   bool counted = false, finalized = false;
   string err;
 
@@ -97,7 +97,8 @@ struct irf_ctx {
     int n = 0; cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) throw string("no CUDA device: this library has no CPU path (") + cudaGetErrorString(e) + ")";
     device = dev; IRF_CUDA(cudaSetDevice(dev));
-    IRF_CUDA(cudaStreamCreateWithFlags(&s_compute, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_copy, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_de, cudaStreamNonBlocking));
+    { int lo_p = 0, hi_p = 0; IRF_CUDA(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));   // counting kernels take freed SM slots ahead of the long inflate launch on the side stream
+      IRF_CUDA(cudaStreamCreateWithPriority(&s_compute, cudaStreamNonBlocking, hi_p)); IRF_CUDA(cudaStreamCreateWithPriority(&s_copy, cudaStreamNonBlocking, lo_p)); } IRF_CUDA(cudaStreamCreateWithFlags(&s_de, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_chk, cudaStreamNonBlocking));
     d_stats.ensure(ST_COUNT * 8); d_err.ensure(4); d_small.ensure(256);
   }
   void sync() { IRF_CUDA(cudaStreamSynchronize(s_compute)); }
@@ -301,24 +302,41 @@ struct irf_ctx {
   // Which blocks go to the hardware decompression engine (DE) and which to the SM kernel.  The file is cut into the same
   // 256 MB chunks the streamed copy uses; inside every chunk the first de_percent % of the blocks are the DE's, the rest
   // the kernel's, so both engines always have landed data to work on.
-  void plan_engines(int de_percent) {
+  // mode 1 (resident overlap): the SM kernel takes the leading chunks whole, the DE the last de_percent % of the chunks (k_de of them).
+  size_t k_de = 0;
+  double sm_byte_share() const {   // fraction of the algorithmic bytes (compressed in + inflated out) that inflate_kernel handles under the current plan
+    double all = 0, sm = 0; for (auto& b : blks) all += (double)b.c_len + b.isize;
+    if (de_list.empty()) return all > 0 ? 1.0 : 0.0;
+    for (u32 i : sm_list) sm += (double)blks[i].c_len + blks[i].isize;
+    return all > 0 ? sm / all : 0.0;
+  }
+  static size_t overlap_lanes() { int l = inflate_resident_lanes(); return l > 0 ? (size_t)l : 94720; }   // 148 SMs x 5 CTAs x 128 lanes before the first launch
+  void plan_engines(int de_percent, int mode = 0) {
     const size_t nb = blks.size(), chunk = chunk_bytes;
     sm_list.clear(); de_list.clear(); de_chunk_end.clear(); chunk_blk_end.clear();
     const bool de_ok = de_percent > 0 && inflate_variant != 8 && g_drv.deflate_engine();
-    size_t b0 = 0, nch = (src_total + chunk - 1) / chunk;
-    for (size_t c = 0; c < std::max<size_t>(nch, 1); c++) {
-      size_t hi = std::min(src_total, (c + 1) * chunk), b1 = b0;
+    const size_t nch = std::max<size_t>((src_total + chunk - 1) / chunk, 1);
+    for (size_t c = 0, b1 = 0; c < nch; c++) { size_t hi = std::min(src_total, (c + 1) * chunk);
       while (b1 < nb && (blks[b1].c_off + blks[b1].c_len + 8 <= hi || c + 1 >= nch)) b1++;
-      size_t nde = de_ok ? (b1 - b0) * (size_t)de_percent / 100 : 0;
+      chunk_blk_end.push_back(b1); }
+    size_t k_sm = 0;
+    if (mode == 1 && de_ok) {   // leading chunks for the kernel: its share of the blocks, cut back to whole waves of its grid when it exceeds one
+      size_t target = nb * (size_t)(100 - de_percent) / 100, lanes = overlap_lanes(), waves = (target + lanes / 4) / lanes, budget = waves ? waves * lanes : target;
+      while (k_sm + 1 < nch && chunk_blk_end[k_sm] <= budget) k_sm++;
+    }
+    k_de = nch - k_sm;
+    for (size_t c = 0, b0 = 0; c < nch; c++) {
+      size_t b1 = chunk_blk_end[c];
+      size_t nde = !de_ok ? 0 : mode == 1 ? (c >= k_sm ? b1 - b0 : 0) : (b1 - b0) * (size_t)de_percent / 100;
       for (size_t b = b0; b < b1; b++) { if (blks[b].isize == 0) continue; if (b < b0 + nde) de_list.push_back((u32)b); else sm_list.push_back((u32)b); }
-      de_chunk_end.push_back(de_list.size()); chunk_blk_end.push_back(b1); b0 = b1;
+      de_chunk_end.push_back(de_list.size()); b0 = b1;
     }
     de_params.resize(de_list.size()); d_de_act.ensure(nb * 4);
     for (size_t i = 0; i < de_list.size(); i++) { const Blk& k = blks[de_list[i]]; CUmemDecompressParams& q = de_params[i]; memset(&q, 0, sizeof q);
       q.srcNumBytes = k.c_len; q.dstNumBytes = k.isize; q.dstActBytes = d_de_act.as<cuuint32_t>() + de_list[i]; q.src = d_comp.as<uint8_t>() + k.c_off; q.algo = CU_MEM_DECOMPRESS_ALGORITHM_DEFLATE; }
     { u64 u = 0; size_t j = 0; for (size_t bI = 0; bI < nb && j < de_list.size(); bI++) { if (de_list[j] == bI) { de_params[j].dst = d_U.as<uint8_t>() + u; j++; } u += blks[bI].isize; } }
     upload(d_sm_list, sm_list, s_compute); upload(d_de_list, de_list, s_compute); sync();
-    engines_planned = true; planned_percent = de_percent;
+    engines_planned = true; planned_percent = de_percent + 1000 * mode;
   }
   vector<cudaEvent_t> pre_ev_copy; size_t pre_copied_bytes = 0;
   void drop_pre_copies() { for (auto e : pre_ev_copy) cudaEventDestroy(e); pre_ev_copy.clear(); pre_copied_bytes = 0; }
@@ -385,7 +403,7 @@ struct irf_ctx {
     }
     if (stream_in) IRF_CUDA(cudaStreamSynchronize(s_copy));
     IRF_CUDA(cudaGetLastError()); sync();
-    float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k0, k1)); timing[1] = ms; n_inflate_launches = 1;
+    float ms = 0; IRF_CUDA(cudaEventElapsedTime(&ms, k0, k1)); timing[1] = ms; n_inflate_launches = 1; timing[10] = ms; timing[11] = sm_byte_share();
     if (getenv("IRF_DEBUG_TIMING")) fprintf(stderr, "[inflate] %.1f ms: %zu blocks on the decompression engine, %zu on the SM kernel%s\n", ms, de_list.size(), listed ? sm_list.size() : nb, stream_in ? " (streamed from the host)" : "");
     cudaEventDestroy(k0); cudaEventDestroy(k1); cudaEventDestroy(ready); cudaEventDestroy(de_done); for (auto e : chunk_ev) cudaEventDestroy(e);
     resident = true;
@@ -425,11 +443,20 @@ struct irf_ctx {
   // starts in chunk k may end in chunk k+1).  Mate pairing is order-free, so counting chunk by chunk gives the same tables;
   // the PCIe transfer (the bound of the end-to-end path) then hides framing and counting as well as the inflate.
   bool can_pipeline() { return !resident && !inflated_input && stream_pipeline && staged_has_header && nblk_own == (int)blks.size() && !blks.empty() && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine(); }
-  void count_streaming() {
+  // The same pipeline for bytes that are already resident (repeated irf_count on staged bytes, the device-only figure): no
+  // copies; ONE persistent inflate_kernel launch on the side stream takes the leading chunks of the file while the
+  // decompression engine inflates the last de_percent_overlap % of the chunks one by one; the compute stream counts the
+  // kernel's chunks when that launch is done and then the DE's chunks as they appear, so the DE never waits for the SMs.
+  bool can_overlap() { return resident && !inflated_input && resident_pipeline && staged_has_header && nblk_own == (int)blks.size() && !blks.empty() && de_percent > 0 && de_percent_overlap > 0
+                              && inflate_variant != 8 && g_drv.deflate_engine() && (src_total + chunk_bytes - 1) / chunk_bytes >= 8
+                              && (resident_pipeline == 2 || blks.size() * (size_t)(100 - de_percent_overlap) / 100 * 10 >= overlap_lanes() * 9); }   // pays once the kernel's share fills its grid
+  void count_streaming(bool from_host = true) {
     cudaEvent_t e0, e3; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e3)); IRF_CUDA(cudaEventRecord(e0, s_compute));
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
-    if (!engines_planned || planned_percent != 100) plan_engines(100);
-    const size_t nb = blks.size(), nch = chunk_blk_end.size();
+    if (from_host) { if (!engines_planned || planned_percent != 100) plan_engines(100); }
+    else if (!engines_planned || planned_percent != 1000 + de_percent_overlap) plan_engines(de_percent_overlap, 1);
+    const size_t nb = blks.size(), nch = chunk_blk_end.size(); const bool sm_used = !from_host && !sm_list.empty(); const size_t ksm = sm_used ? nch - k_de : 0;   // chunks [0, ksm) are the SM kernel's
+    cudaEvent_t k0 = nullptr, k1 = nullptr;
     int* errp = T.err ? T.err : d_err.as<int>();
     IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
     cudaEvent_t ready; IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ready, s_compute));
@@ -439,22 +466,33 @@ struct irf_ctx {
     const size_t npre = std::min(pre_ev_copy.size(), nch);   // chunks whose copy stage() already queued (same chunking)
     for (size_t c = 0; c < nch; c++) {
       size_t lo = c * chunk_bytes, hi = std::min(src_total, lo + chunk_bytes);
-      if (c < npre) { ev_copy[c] = pre_ev_copy[c]; }
+      if (!from_host) { IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); }
+      else if (c < npre) { ev_copy[c] = pre_ev_copy[c]; }
       else { if (hi > lo) IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
         IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev_copy[c], s_copy)); }
-      IRF_CUDA(cudaStreamWaitEvent(s_de, ev_copy[c], 0));
+      if (from_host) IRF_CUDA(cudaStreamWaitEvent(s_de, ev_copy[c], 0));
       size_t f0 = c ? de_chunk_end[c - 1] : 0, f1 = de_chunk_end[c];
       for (size_t i = f0; i < f1; i += 32768) { size_t bad = 0; CUresult r = g_drv.decompress(de_params.data() + i, std::min(f1, i + 32768) - i, 0, &bad, (CUstream)s_de);
         if (r != CUDA_SUCCESS) throw string("cuMemBatchDecompressAsync failed with CUresult ") + std::to_string((int)r) + " (cuda)"; }
-      if (f1 > f0) { launch_de_check(d_de_list.as<u32>() + f0, (int)(f1 - f0), d_de_act.as<u32>(), d_u_len.as<u32>(), d_status.as<int>(), errp, s_de);
-        if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(f1 - f0), d_status.as<int>(), errp, s_de, d_de_list.as<u32>() + f0); }
       IRF_CUDA(cudaEventCreate(&ev_inf[c])); IRF_CUDA(cudaEventRecord(ev_inf[c], s_de));
+      // the length and CRC-32 checks run on their own stream: on the DE's stream they would hold the next batch back whenever
+      // the SMs are busy; a mismatch raises the error flag, which is read after the last chunk
+      if (f1 > f0) { IRF_CUDA(cudaStreamWaitEvent(s_chk, ev_inf[c], 0)); launch_de_check(d_de_list.as<u32>() + f0, (int)(f1 - f0), d_de_act.as<u32>(), d_u_len.as<u32>(), d_status.as<int>(), errp, s_chk);
+        if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(f1 - f0), d_status.as<int>(), errp, s_chk, d_de_list.as<u32>() + f0); }
     }
     for (size_t c = npre; c < pre_ev_copy.size(); c++) cudaEventDestroy(pre_ev_copy[c]);
     pre_ev_copy.clear(); pre_copied_bytes = 0;   // ownership of the first npre events moved to ev_copy
-    auto cleanup = [&]() { for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); };
+    if (sm_used) {   // the SM kernel's share, one launch beside everything else
+      IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1)); IRF_CUDA(cudaEventRecord(k0, s_copy));
+      InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)sm_list.size(), d_status.as<int>(),
+                    errp, (unsigned int*)(d_small.as<uint8_t>() + 160), nullptr, d_sm_list.as<u32>()};
+      launch_inflate(a, inflate_variant, s_copy); IRF_CUDA(cudaEventRecord(k1, s_copy));
+      if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)sm_list.size(), d_status.as<int>(), errp, s_copy, d_sm_list.as<u32>());
+    }
+    auto cleanup = [&]() { for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); if (k1) cudaEventDestroy(k1); };
     try {
       // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
+      if (sm_used) IRF_CUDA(cudaEventSynchronize(k1));   // the header lies in the kernel's share
       for (size_t c = 0;; c++) {
         IRF_CUDA(cudaEventSynchronize(ev_inf[c])); check_dev_err("inflate");
         u64 full = Uend; Uend = inf_end[c]; bool ok = true;
@@ -468,6 +506,7 @@ struct irf_ctx {
       for (size_t c = 0; c < nch; c++) {
         size_t b1 = chunk_blk_end[c]; int nbk = (int)(b1 - b0); if (!nbk) continue;
         IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[std::min(c + 1, nch - 1)], 0));   // chunk c is counted once chunk c+1 is inflated
+        if (sm_used && c < ksm) IRF_CUDA(cudaStreamWaitEvent(s_compute, k1, 0));
         const u64 visible = inf_end[std::min(c + 1, nch - 1)];
         FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, nbk, visible, entry_prev, 1, T.n_ref, T.ref_len,
                      d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err};
@@ -494,12 +533,16 @@ struct irf_ctx {
         b0 = b1;
       }
       if (entry_prev != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
-      IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaStreamSynchronize(s_copy)); IRF_CUDA(cudaStreamSynchronize(s_de)); sync();
+      IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaStreamSynchronize(s_copy)); IRF_CUDA(cudaStreamSynchronize(s_de)); IRF_CUDA(cudaStreamSynchronize(s_chk)); sync();
       check_dev_err("fragment counting");
       float tot = 0, inf = 0; IRF_CUDA(cudaEventElapsedTime(&tot, e0, e3)); IRF_CUDA(cudaEventElapsedTime(&inf, e0, ev_inf[nch - 1]));
-      timing[0] = inf; timing[1] = inf; timing[2] = 0; timing[3] = tot - inf; timing[5] = tot; n_inflate_launches = 0;
+      timing[10] = 0; timing[11] = 0;
+      if (sm_used) { float t_sm = 0; IRF_CUDA(cudaEventElapsedTime(&t_sm, e0, k1)); inf = std::max(inf, t_sm); IRF_CUDA(cudaEventElapsedTime(&t_sm, k0, k1)); timing[10] = t_sm; timing[11] = sm_byte_share(); }
+      if (getenv("IRF_DEBUG_TIMING")) { float t_de = 0, t_sm = 0; IRF_CUDA(cudaEventElapsedTime(&t_de, e0, ev_inf[nch - 1])); if (sm_used) IRF_CUDA(cudaEventElapsedTime(&t_sm, k0, k1));
+        fprintf(stderr, "[pipeline] %s: %zu chunks (%zu DE), DE done at %.1f ms, SM inflate %.1f ms, all counted at %.1f ms\n", from_host ? "streamed" : "resident", nch, nch - ksm, t_de, t_sm, tot); }
+      timing[0] = inf; timing[1] = inf; timing[2] = 0; timing[3] = tot - inf; timing[5] = tot; n_inflate_launches = sm_used ? 1 : 0;
       frame_entry0 = rec0; frame_exit_rel = 0;
-    } catch (...) { cudaStreamSynchronize(s_copy); cudaStreamSynchronize(s_de); cudaStreamSynchronize(s_compute); cleanup(); throw; }
+    } catch (...) { cudaStreamSynchronize(s_copy); cudaStreamSynchronize(s_de); cudaStreamSynchronize(s_chk); cudaStreamSynchronize(s_compute); cleanup(); throw; }
     cleanup();
     resident = true; counted = true; finalized = false;
   }
@@ -507,7 +550,8 @@ struct irf_ctx {
   // S2 + S3
   void count() {
     if (!staged) throw string("nothing staged");
-    if (can_pipeline()) { count_streaming(); return; }
+    if (can_pipeline()) { count_streaming(true); return; }
+    if (can_overlap()) { count_streaming(false); return; }
     if (!pre_ev_copy.empty()) { IRF_CUDA(cudaStreamSynchronize(s_copy)); if (pre_copied_bytes >= src_total) resident = true; drop_pre_copies(); }
     cudaEvent_t e0, e1, e2, e3; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventCreate(&e2)); IRF_CUDA(cudaEventCreate(&e3));
     IRF_CUDA(cudaEventRecord(e0, s_compute));
@@ -705,7 +749,7 @@ void irf_destroy(irf_ctx* c) {
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->wm_host) cudaFreeHost(c->wm_host);
-  if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy); if (c->s_de) cudaStreamDestroy(c->s_de);
+  if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy); if (c->s_de) cudaStreamDestroy(c->s_de); if (c->s_chk) cudaStreamDestroy(c->s_chk);
   delete c;
 }
 const char* irf_last_error(irf_ctx* c) { return c ? c->err.c_str() : "null context"; }
@@ -723,6 +767,8 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "stream_pipeline") c->stream_pipeline = v != 0;
+  else if (k == "resident_pipeline") { if (v < 0 || v > 2) return IRF_EINVAL; c->resident_pipeline = (int)v; }
+  else if (k == "de_percent_overlap") { if (v < 1 || v > 100) return IRF_EINVAL; c->de_percent_overlap = (int)v; }
   else if (k == "de_percent_stream") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent_stream = (int)v; c->engines_planned = false; }
   else { c->err = "unknown option " + k; return IRF_EINVAL; }
   return IRF_OK;
@@ -761,7 +807,7 @@ int irf_directionality(irf_ctx* c) { return c ? c->directionality : 0; }
 int irf_get_table(irf_ctx* c, int which, const void** p, size_t* n) {
   if (!c || !p || !n) return IRF_EINVAL;
   IRF_TRY(c, {
-    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; *p = c->timing; *n = 10; }
+    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; *p = c->timing; *n = 12; }
     else {
       if (!c->finalized) throw string("no finished run to read tables from");
       switch (which) {

@@ -115,6 +115,8 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
   }
 }
 
+static int g_inflate_lanes = 0;
+int inflate_resident_lanes() { return g_inflate_lanes; }   // lanes (= BGZF blocks in flight) of the last inflate launch's full grid; 0 before the first launch
 template <int WARPS, int LB, int DB, int HB = 1, int LC = 0, int RB = 0, int PZ = 0>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   size_t smem = (size_t)WARPS * ((((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t) + (RB ? (size_t)(1 << RB) * 32 : 0));
@@ -125,6 +127,7 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
     int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
+  g_inflate_lanes = sms * ctas_per_sm * WARPS * 32;
   int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));

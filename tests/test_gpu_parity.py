@@ -333,3 +333,27 @@ def test_malformed_reference_files_are_reported_with_line_numbers(tiny, tmp_path
     c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])   # a good set still loads afterwards
     c.run_bam(tiny["sorted"])
     assert c.stats()["pairs"] > 0
+
+
+@pytest.mark.parametrize("share", [30, 65, 100])
+def test_resident_pipeline_overlaps_engines(tiny, tmp_path, share):
+    """Bytes already on the GPU are re-counted by the overlapped pipeline (count_streaming(false)): the SM kernel inflates the
+    leading chunks, the decompression engine the rest chunk by chunk, counting follows both.  Small chunks make the tiny input
+    span enough chunks to take that path; the share of the two engines and repeated counts must not change any output."""
+    import numpy as np
+    c = _core(stream_chunk_kb=64, de_percent_overlap=share, resident_pipeline=2)
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    data = np.fromfile(tiny["sorted"], dtype=np.uint8)
+    assert data.size >= 8 * 65536          # otherwise the path under test is not taken
+    c.stage(data.ctypes.data, data.size)
+    for rep in range(2):
+        c.reset(); c.count(); c.finalize()
+        out = str(tmp_path / ("g%d" % rep))
+        c.write_outputs(out)
+        assert_same_outputs(tiny["oracle_out"], out)
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+        assert c.timing()["inflate_launches"] == (0 if share == 100 else 1)
+    c.set_option("resident_pipeline", 0)
+    c.reset(); c.count(); c.finalize()
+    c.write_outputs(str(tmp_path / "plain"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "plain"))
