@@ -442,12 +442,12 @@ struct irf_ctx {
   // by events), and the compute stream frames, pairs and counts chunk k as soon as chunk k+1 has been inflated (a record that
   // starts in chunk k may end in chunk k+1).  Mate pairing is order-free, so counting chunk by chunk gives the same tables;
   // the PCIe transfer (the bound of the end-to-end path) then hides framing and counting as well as the inflate.
-  bool can_pipeline() { return !resident && !inflated_input && stream_pipeline && staged_has_header && nblk_own == (int)blks.size() && !blks.empty() && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine(); }
+  bool can_pipeline() { return !resident && !inflated_input && stream_pipeline && (staged_has_header || have_header) && nblk_own > 0 && !blks.empty() && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine(); }
   // The same pipeline for bytes that are already resident (repeated irf_count on staged bytes, the device-only figure): no
   // copies; ONE persistent inflate_kernel launch on the side stream takes the leading chunks of the file while the
   // decompression engine inflates the last de_percent_overlap % of the chunks one by one; the compute stream counts the
   // kernel's chunks when that launch is done and then the DE's chunks as they appear, so the DE never waits for the SMs.
-  bool can_overlap() { return resident && !inflated_input && resident_pipeline && staged_has_header && nblk_own == (int)blks.size() && !blks.empty() && de_percent > 0 && de_percent_overlap > 0
+  bool can_overlap() { return resident && !inflated_input && resident_pipeline && (staged_has_header || have_header) && nblk_own > 0 && !blks.empty() && de_percent > 0 && de_percent_overlap > 0
                               && inflate_variant != 8 && g_drv.deflate_engine() && (src_total + chunk_bytes - 1) / chunk_bytes >= 8
                               && (resident_pipeline == 2 || blks.size() * (size_t)(100 - de_percent_overlap) / 100 * 10 >= overlap_lanes() * 9); }   // pays once the kernel's share fills its grid
   void count_streaming(bool from_host = true) {
@@ -492,8 +492,8 @@ struct irf_ctx {
     auto cleanup = [&]() { for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); if (k1) cudaEventDestroy(k1); };
     try {
       // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
-      if (sm_used) IRF_CUDA(cudaEventSynchronize(k1));   // the header lies in the kernel's share
-      for (size_t c = 0;; c++) {
+      if (sm_used && staged_has_header) IRF_CUDA(cudaEventSynchronize(k1));   // the header lies in the kernel's share
+      for (size_t c = 0; staged_has_header; c++) {
         IRF_CUDA(cudaEventSynchronize(ev_inf[c])); check_dev_err("inflate");
         u64 full = Uend; Uend = inf_end[c]; bool ok = true;
         try { parse_header_from_device(); } catch (const string& e) { ok = false; if (e.find("truncated") == string::npos || c + 1 == nch) { Uend = full; throw; } }
@@ -502,13 +502,19 @@ struct irf_ctx {
       if (!bound) chr_map_update();
       pslots = next_pow2(std::max<u64>(1024, Uend / 80)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
       u32* n_bad = d_small.as<u32>(); u64* totals = (u64*)(d_small.as<uint8_t>() + 16); u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192);
-      u64 entry_prev = rec0; n_rec = 0; n_cand = 0; frame_rounds = 0; size_t b0 = 0;
+      // A shard of a larger file (multi-GPU) has no header and ends with look-ahead blocks that are inflated but not counted
+      // here: its first record start is a guess unless the caller passed one ("entry0"), exactly as in count().
+      u64 entry_prev = rec0; int entry_valid = 1; n_rec = 0; n_cand = 0; frame_rounds = 0; size_t b0 = 0; u64 fe0 = rec0; bool first = true;
+      if (!staged_has_header) { entry_valid = entry0_override >= 0; entry_prev = entry_valid ? (u64)entry0_override : 0; entry0_override = -1; }
       for (size_t c = 0; c < nch; c++) {
-        size_t b1 = chunk_blk_end[c]; int nbk = (int)(b1 - b0); if (!nbk) continue;
-        IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[std::min(c + 1, nch - 1)], 0));   // chunk c is counted once chunk c+1 is inflated
+        size_t b1 = std::min<size_t>(chunk_blk_end[c], (size_t)nblk_own); if (b1 <= b0) continue;
+        const int nbk = (int)(b1 - b0); const bool last_own = b1 == (size_t)nblk_own;
+        // chunk c is counted once chunk c+1 is inflated; the last counted chunk waits for everything (the look-ahead)
+        const size_t need = last_own ? nch - 1 : std::min(c + 1, nch - 1);
+        IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[need], 0));
         if (sm_used && c < ksm) IRF_CUDA(cudaStreamWaitEvent(s_compute, k1, 0));
-        const u64 visible = inf_end[std::min(c + 1, nch - 1)];
-        FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, nbk, visible, entry_prev, 1, T.n_ref, T.ref_len,
+        const u64 visible = inf_end[need];
+        FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, nbk, visible, entry_prev, entry_valid, T.n_ref, T.ref_len,
                      d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err};
         launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
         for (int rounds = 0;; rounds++) {
@@ -519,8 +525,9 @@ struct irf_ctx {
         }
         IRF_CUDA(cudaMemsetAsync(totals, 0, 16, s_compute)); launch_frame_totals(fa, totals, s_compute);
         u64 ht[2] = {0, 0}, ex = 0; IRF_CUDA(cudaMemcpyAsync(ht, totals, 16, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(&ex, d_exit.as<u64>() + (b1 - 1), 8, cudaMemcpyDeviceToHost, s_compute));
+        if (first) IRF_CUDA(cudaMemcpyAsync(&fe0, d_entry.as<u64>() + b0, 8, cudaMemcpyDeviceToHost, s_compute));
         sync(); check_dev_err("record framing");
-        entry_prev = ex; n_rec += ht[0]; n_cand += ht[1];
+        entry_prev = ex; entry_valid = 1; first = false; n_rec += ht[0]; n_cand += ht[1];
         if (ht[0]) {
           d_rec_base.ensure((size_t)nbk * 8); d_rec_off.ensure((ht[0] + ht[0] / 2) * 8); d_pair_list.ensure((ht[1] + ht[1] / 2 + 16) * 16); d_single_list.ensure((ht[0] + ht[0] / 2 + 16) * 8);
           launch_scan_counts(d_nrec.as<u32>() + b0, d_rec_base.as<u64>(), nbk, s_compute); launch_walk_list(fa, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
@@ -532,7 +539,7 @@ struct irf_ctx {
         }
         b0 = b1;
       }
-      if (entry_prev != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
+      if (nblk_own == (int)nb && entry_prev != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
       IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaStreamSynchronize(s_copy)); IRF_CUDA(cudaStreamSynchronize(s_de)); IRF_CUDA(cudaStreamSynchronize(s_chk)); sync();
       check_dev_err("fragment counting");
       float tot = 0, inf = 0; IRF_CUDA(cudaEventElapsedTime(&tot, e0, e3)); IRF_CUDA(cudaEventElapsedTime(&inf, e0, ev_inf[nch - 1]));
@@ -541,7 +548,7 @@ struct irf_ctx {
       if (getenv("IRF_DEBUG_TIMING")) { float t_de = 0, t_sm = 0; IRF_CUDA(cudaEventElapsedTime(&t_de, e0, ev_inf[nch - 1])); if (sm_used) IRF_CUDA(cudaEventElapsedTime(&t_sm, k0, k1));
         fprintf(stderr, "[pipeline] %s: %zu chunks (%zu DE), DE done at %.1f ms, SM inflate %.1f ms, all counted at %.1f ms\n", from_host ? "streamed" : "resident", nch, nch - ksm, t_de, t_sm, tot); }
       timing[0] = inf; timing[1] = inf; timing[2] = 0; timing[3] = tot - inf; timing[5] = tot; n_inflate_launches = sm_used ? 1 : 0;
-      frame_entry0 = rec0; frame_exit_rel = 0;
+      { u64 own_end = 0; for (int i = 0; i < nblk_own; i++) own_end += blks[i].isize; frame_entry0 = fe0; frame_exit_rel = entry_prev >= own_end ? entry_prev - own_end : 0; }
     } catch (...) { cudaStreamSynchronize(s_copy); cudaStreamSynchronize(s_de); cudaStreamSynchronize(s_chk); cudaStreamSynchronize(s_compute); cleanup(); throw; }
     cleanup();
     resident = true; counted = true; finalized = false;
