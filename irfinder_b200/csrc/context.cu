@@ -773,6 +773,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "verify_crc") c->verify_crc = v != 0;
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
+  else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements
   else if (k == "stream_pipeline") c->stream_pipeline = v != 0;
   else if (k == "resident_pipeline") { if (v < 0 || v > 2) return IRF_EINVAL; c->resident_pipeline = (int)v; }
   else if (k == "de_percent_overlap") { if (v < 1 || v > 100) return IRF_EINVAL; c->de_percent_overlap = (int)v; }

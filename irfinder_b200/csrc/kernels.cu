@@ -115,7 +115,8 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_kernel(const uint8_t* __re
   }
 }
 
-static int g_inflate_lanes = 0;
+static int g_inflate_lanes = 0, g_inflate_cta_cap = 0;
+void set_inflate_cta_cap(int ctas_per_sm) { g_inflate_cta_cap = ctas_per_sm; }   // 0 = as many CTAs per SM as fit
 int inflate_resident_lanes() { return g_inflate_lanes; }   // lanes (= BGZF blocks in flight) of the last inflate launch's full grid; 0 before the first launch
 template <int WARPS, int LB, int DB, int HB = 1, int LC = 0, int RB = 0, int PZ = 0>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
@@ -127,8 +128,9 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
     int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
-  g_inflate_lanes = sms * ctas_per_sm * WARPS * 32;
-  int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * ctas_per_sm);   // 148 SMs x resident CTAs
+  const int per_sm = g_inflate_cta_cap > 0 ? std::min(g_inflate_cta_cap, ctas_per_sm) : ctas_per_sm;
+  g_inflate_lanes = sms * per_sm * WARPS * 32;
+  int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
     inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();

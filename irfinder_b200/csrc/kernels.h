@@ -19,6 +19,7 @@ struct FrameArgs {
 
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
 int inflate_resident_lanes();
+void set_inflate_cta_cap(int ctas_per_sm);
 // CRC-32 of every inflated BGZF block against the value in its footer (what `gzip -cd` checks for the reference)
 void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s);
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list = nullptr);
