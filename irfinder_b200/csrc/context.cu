@@ -40,6 +40,13 @@ struct DevBuf {
 template <class T> static void upload(DevBuf& b, const vector<T>& v, cudaStream_t s) {
   b.ensure(v.size() * sizeof(T)); if (!v.empty()) IRF_CUDA(cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, s));
 }
+// page-locked, device-mapped host memory for tables the GPU fetches itself (launch_host_fetch)
+struct HostArena {
+  void* p = nullptr; void* dp = nullptr; size_t cap = 0;
+  void* get(size_t n) { n += 64; if (n > cap) { release(); IRF_CUDA(cudaHostAlloc(&p, n + n / 4, cudaHostAllocMapped)); cap = n + n / 4; IRF_CUDA(cudaHostGetDevicePointer(&dp, p, 0)); } return p; }
+  const void* dev(const void* host) const { return (const uint8_t*)dp + ((const uint8_t*)host - (const uint8_t*)p); }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; dp = nullptr; cap = 0; }
+};
 struct Blk { u64 c_off; u32 c_len; u32 isize; u64 file_off; u32 crc; };
 static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 typedef CUresult (*pfn_decompress)(CUmemDecompressParams*, size_t, unsigned int, size_t*, CUstream);
@@ -263,9 +270,11 @@ struct irf_ctx {
     if (!copy_now && stream_pipeline && has_header && n_own == n_total && n_total > 0 && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine()) {
       // end-to-end path: the bytes can start crossing PCIe before the host has even walked the BGZF block chain
       d_comp.ensure(n_total + 64);
-      // only the first two chunks: the small table uploads that follow the scan share the host->device copy engine with these
-      // transfers and would otherwise queue behind the whole file
-      for (size_t lo = 0; lo < n_total && pre_ev_copy.size() < 2; lo += chunk_bytes) { size_t hi = std::min(n_total, lo + chunk_bytes);
+      // Every chunk is queued now when the references are already bound to this header (any run after a context's first):
+      // nothing else needs the DMA engine then, the block tables are fetched by a kernel.  A first run still has the bound
+      // reference tables to upload once the header is known, and those would queue behind the whole file: two chunks only.
+      const size_t max_pre = bound ? (size_t)-1 : 2;
+      for (size_t lo = 0; lo < n_total && pre_ev_copy.size() < max_pre; lo += chunk_bytes) { size_t hi = std::min(n_total, lo + chunk_bytes);
         IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, (const uint8_t*)src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
         cudaEvent_t ev; IRF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev, s_copy)); pre_ev_copy.push_back(ev); }
       pre_copied_bytes = std::min(n_total, pre_ev_copy.size() * chunk_bytes);
@@ -274,15 +283,17 @@ struct irf_ctx {
     if (require_eof && has_header && n_own == n_total) { if (blks.empty() || blks.back().isize != 0) throw string("BGZF EOF marker missing (truncated file?)"); }
     timing[6] = now_ms() - t0;
     h_src = (const uint8_t*)src; src_total = blks.empty() ? 0 : (size_t)(blks.back().c_off + blks.back().c_len + 8);
-    vector<u64> c_off(blks.size()), u_off(blks.size()); vector<u32> c_len(blks.size()), u_len(blks.size()), crcs(blks.size()); u64 u = 0;
-    for (size_t i = 0; i < blks.size(); i++) { c_off[i] = blks[i].c_off; c_len[i] = blks[i].c_len; u_off[i] = u; u_len[i] = blks[i].isize; crcs[i] = blks[i].crc; u += blks[i].isize; }
-    upload(d_crc, crcs, s_compute);
-    Uend = u;
-    upload(d_c_off, c_off, s_compute); upload(d_c_len, c_len, s_compute); upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute);
+    // block tables: written into the page-locked arena and fetched by a kernel (see launch_host_fetch)
+    { const size_t nbk = blks.size(), a8 = (nbk * 8 + 15) & ~(size_t)15, a4 = (nbk * 4 + 15) & ~(size_t)15; uint8_t* base = (uint8_t*)h_tab.get(2 * a8 + 3 * a4);
+      u64* c_off = (u64*)base; u64* u_off = (u64*)(base + a8); u32* c_len = (u32*)(base + 2 * a8); u32* u_len = (u32*)(base + 2 * a8 + a4); u32* crcs = (u32*)(base + 2 * a8 + 2 * a4); u64 u = 0;
+      for (size_t i = 0; i < nbk; i++) { c_off[i] = blks[i].c_off; c_len[i] = blks[i].c_len; u_off[i] = u; u_len[i] = blks[i].isize; crcs[i] = blks[i].crc; u += blks[i].isize; }
+      Uend = u;
+      auto fetch = [&](DevBuf& b, const void* src, size_t bytes) { b.ensure(bytes + 16); launch_host_fetch(b.p, h_tab.dev(src), bytes, s_compute); };
+      fetch(d_c_off, c_off, nbk * 8); fetch(d_u_off, u_off, nbk * 8); fetch(d_c_len, c_len, nbk * 4); fetch(d_u_len, u_len, nbk * 4); fetch(d_crc, crcs, nbk * 4); }
     if (pre_ev_copy.empty()) d_comp.ensure(src_total + 64);
     d_U.ensure(Uend + 64);
     size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
-    sync();  // the host vectors above go out of scope
+    sync();  // allocation changes above settle before anything is queued against the buffers
     resident = false; staged = true; staged_has_header = has_header != 0; engines_planned = false;
     if (copy_now) { if (src_total) IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); sync(); resident = true; h_src = nullptr; }
   }
@@ -312,6 +323,7 @@ struct irf_ctx {
   }
   static size_t overlap_lanes() { int l = inflate_resident_lanes(); return l > 0 ? (size_t)l : 94720; }   // 148 SMs x 5 CTAs x 128 lanes before the first launch
   void plan_engines(int de_percent, int mode = 0) {
+    sync();   // a fetch of the previous plan's lists may still be queued against the arena rewritten below
     const size_t nb = blks.size(), chunk = chunk_bytes;
     sm_list.clear(); de_list.clear(); de_chunk_end.clear(); chunk_blk_end.clear();
     const bool de_ok = de_percent > 0 && inflate_variant != 8 && g_drv.deflate_engine();
@@ -335,9 +347,12 @@ struct irf_ctx {
     for (size_t i = 0; i < de_list.size(); i++) { const Blk& k = blks[de_list[i]]; CUmemDecompressParams& q = de_params[i]; memset(&q, 0, sizeof q);
       q.srcNumBytes = k.c_len; q.dstNumBytes = k.isize; q.dstActBytes = d_de_act.as<cuuint32_t>() + de_list[i]; q.src = d_comp.as<uint8_t>() + k.c_off; q.algo = CU_MEM_DECOMPRESS_ALGORITHM_DEFLATE; }
     { u64 u = 0; size_t j = 0; for (size_t bI = 0; bI < nb && j < de_list.size(); bI++) { if (de_list[j] == bI) { de_params[j].dst = d_U.as<uint8_t>() + u; j++; } u += blks[bI].isize; } }
-    upload(d_sm_list, sm_list, s_compute); upload(d_de_list, de_list, s_compute); sync();
+    { const size_t a1 = (sm_list.size() * 4 + 15) & ~(size_t)15, a2 = (de_list.size() * 4 + 15) & ~(size_t)15; uint8_t* base = (uint8_t*)h_lists.get(a1 + a2);
+      if (!sm_list.empty()) memcpy(base, sm_list.data(), sm_list.size() * 4); if (!de_list.empty()) memcpy(base + a1, de_list.data(), de_list.size() * 4);
+      d_sm_list.ensure(a1 + 16); d_de_list.ensure(a2 + 16); launch_host_fetch(d_sm_list.p, h_lists.dev(base), sm_list.size() * 4, s_compute); launch_host_fetch(d_de_list.p, h_lists.dev(base + a1), de_list.size() * 4, s_compute); }
     engines_planned = true; planned_percent = de_percent + 1000 * mode;
   }
+  HostArena h_tab, h_lists;
   vector<cudaEvent_t> pre_ev_copy; size_t pre_copied_bytes = 0;
   void drop_pre_copies() { for (auto e : pre_ev_copy) cudaEventDestroy(e); pre_ev_copy.clear(); pre_copied_bytes = 0; }
   bool crc_pending = false;
@@ -688,24 +703,29 @@ struct irf_ctx {
     finalized = true;
   }
 
+  TextTable t_ir, t_dir, t_junc, t_sp;
   void write_outputs(const char* outdir) {
     if (!finalized) throw string("no finished run to write");
     double t0 = now_ms(); string d = outdir;
     auto put = [&](const char* name, const string& s) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; size_t w = fwrite(s.data(), 1, s.size(), f); int rc = fclose(f); if (w != s.size() || rc) throw string("short write to ") + p; };
-    // the six tables are independent: format and write them side by side
-    vector<std::function<void()>> jobs;
-    auto putv = [&](const char* name, const vector<string>& parts) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; bool ok = true;
-      for (auto& s : parts) ok &= fwrite(s.data(), 1, s.size(), f) == s.size(); if (fclose(f) || !ok) throw string("short write to ") + p; };
-    jobs.push_back([&]() { putv("IRFinder-IR-nondir.txt", format_ir_table_parts(cov, rows_nondir)); });
-    if (directionality != 0) jobs.push_back([&]() { putv("IRFinder-IR-dir.txt", format_ir_table_parts(cov, rows_dir)); });
-    jobs.push_back([&]() { putv("IRFinder-JuncCount.txt", format_junctions_parts(jref, chr_names, h_junc)); });
-    jobs.push_back([&]() { putv("IRFinder-SpansPoint.txt", format_spans_parts(sp, h_sp)); });
-    jobs.push_back([&]() { put("IRFinder-ChrCoverage.txt", format_chr(chr_names, h_chr)); if (roi.present) put("IRFinder-ROI.txt", format_roi(roi, h_roi)); });
-    vector<string> errs(jobs.size()); vector<std::thread> th;
+    // every table is cut into independent parts; ONE pool of threads formats the parts of all tables, then the files are written side by side
     const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr;
-    for (size_t i = 0; i < jobs.size(); i++) th.emplace_back([&, i]() { double tj = now_ms(); try { jobs[i](); if (dbg) fprintf(stderr, "[output] job %zu %8.3f ms\n", i, now_ms() - tj); } catch (const string& e) { errs[i] = e; } catch (const std::exception& e) { errs[i] = e.what(); } });
-    for (auto& t : th) t.join();
-    for (auto& e : errs) if (!e.empty()) throw e;
+    vector<std::function<void()>> tasks;   // the tables themselves are members: their buffers are reused from run to run
+    prepare_ir_table(t_ir, cov, rows_nondir); if (directionality != 0) prepare_ir_table(t_dir, cov, rows_dir);
+    prepare_junctions(t_junc, jref, chr_names, h_junc); prepare_spans(t_sp, sp, h_sp);
+    for (TextTable* t : {&t_ir, &t_dir, &t_junc, &t_sp}) for (auto& f : t->tasks) tasks.push_back(f);
+    string s_chr, s_roi; tasks.push_back([&]() { s_chr = format_chr(chr_names, h_chr); if (roi.present) s_roi = format_roi(roi, h_roi); });
+    double t1 = now_ms(); run_tasks(tasks, format_threads()); double t2 = now_ms();
+    auto putv = [&](const char* name, const vector<string>& parts) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; bool ok = true;
+      for (auto& x : parts) ok &= fwrite(x.data(), 1, x.size(), f) == x.size(); if (fclose(f) || !ok) throw string("short write to ") + p; };
+    vector<std::function<void()>> writers;
+    writers.push_back([&]() { putv("IRFinder-IR-nondir.txt", t_ir.parts); });
+    if (directionality != 0) writers.push_back([&]() { putv("IRFinder-IR-dir.txt", t_dir.parts); });
+    writers.push_back([&]() { putv("IRFinder-JuncCount.txt", t_junc.parts); });
+    writers.push_back([&]() { putv("IRFinder-SpansPoint.txt", t_sp.parts); });
+    writers.push_back([&]() { put("IRFinder-ChrCoverage.txt", s_chr); if (roi.present) put("IRFinder-ROI.txt", s_roi); });
+    run_tasks(writers, (unsigned)writers.size());
+    if (dbg) fprintf(stderr, "[output] prepare %.2f ms, format %zu parts %.2f ms, write %.2f ms\n", t1 - t0, tasks.size(), t2 - t1, now_ms() - t2);
     timing[7] = now_ms() - t0;
   }
 
@@ -756,6 +776,7 @@ void irf_destroy(irf_ctx* c) {
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->wm_host) cudaFreeHost(c->wm_host);
+  c->h_tab.release(); c->h_lists.release();
   if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy); if (c->s_de) cudaStreamDestroy(c->s_de); if (c->s_chk) cudaStreamDestroy(c->s_chk);
   delete c;
 }

@@ -204,6 +204,17 @@ __global__ void de_check_kernel(const u32* __restrict__ list, int n, const u32* 
   int i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
   u32 b = list[i]; if (act[b] != u_len[b]) { status[b] = INF_ERR_ISIZE; atomicOr(err, DERR_INFLATE); }
 }
+// Small tables (block offsets, lengths, CRCs, work lists) are fetched by a kernel from page-locked host memory instead of
+// being copied by the DMA engine: the engine's queue is full of the BGZF bytes' 256 MB chunk copies at that time and a
+// table queued behind them would arrive after the whole file.
+__global__ void host_fetch_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src_host, size_t n16) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) dst[i] = src_host[i];
+}
+void launch_host_fetch(void* dst_dev, const void* src_host_mapped, size_t nbytes, cudaStream_t s) {
+  size_t n16 = (nbytes + 15) / 16; if (!n16) return;
+  int grid = (int)std::min<size_t>((n16 + 255) / 256, 148 * 2);
+  host_fetch_kernel<<<grid, 256, 0, s>>>((uint4*)dst_dev, (const uint4*)src_host_mapped, n16); IRF_LAUNCHED();
+}
 void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s) {
   if (n > 0) { de_check_kernel<<<(n + 255) / 256, 256, 0, s>>>(list, n, act, u_len, status, err); IRF_LAUNCHED(); }
 }

@@ -21,6 +21,7 @@ void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
 int inflate_resident_lanes();
 void set_inflate_cta_cap(int ctas_per_sm);
 // CRC-32 of every inflated BGZF block against the value in its footer (what `gzip -cd` checks for the reference)
+void launch_host_fetch(void* dst_dev, const void* src_host_mapped, size_t nbytes, cudaStream_t s);   // nbytes is rounded up to 16: both buffers must be padded
 void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, int* status, int* err, cudaStream_t s);
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list = nullptr);
 void launch_frame_guess(const FrameArgs& a, cudaStream_t s);

@@ -4,7 +4,9 @@
 #include <algorithm>
 #include <atomic>
 #include <charconv>
+#include <cmath>
 #include <cstring>
+#include <memory>
 #include <sstream>
 #include <thread>
 
@@ -103,78 +105,137 @@ void CoverageRef::pieces(const std::string& chr, u32 s, u32 e, std::vector<Intro
 }
 
 // ---------------------------------------------------------------------------------------------
-// formatting: std::ostream << (default precision 6) == printf("%g") == to_chars(general, 6)
-static inline void put_u(std::string& s, unsigned long long v) { char b[24]; auto r = std::to_chars(b, b + sizeof b, v); s.append(b, r.ptr); }
-static inline void put_i(std::string& s, long long v) { char b[24]; auto r = std::to_chars(b, b + sizeof b, v); s.append(b, r.ptr); }
-static inline void put_g(std::string& s, double v) {
-  // %g prints integral values below 1e6 as plain integers; that covers most cells (0, 1, integer percentiles) without the general path
-  if (v >= 0 && v < 1e6) { unsigned long long u = (unsigned long long)v; if ((double)u == v) { put_u(s, u); return; } }
-  char b[40]; auto r = std::to_chars(b, b + sizeof b, v, std::chars_format::general, 6); s.append(b, r.ptr);
+// formatting: std::ostream << (default precision 6) == printf("%g") == to_chars(general, 6).
+// All writers work on raw char pointers into buffers sized from a per-row bound; tables are cut into independent parts so
+// that one pool of threads can format every table of a run at once (TextTable in refs.h).
+static inline char* put_u(char* p, unsigned long long v) { return std::to_chars(p, p + 24, v).ptr; }
+static inline char* put_i(char* p, long long v) { return std::to_chars(p, p + 24, v).ptr; }
+static inline void put_u(std::string& s, unsigned long long v) { char b[24]; s.append(b, put_u(b, v)); }
+static inline char* put_s(char* p, const std::string& s) { memcpy(p, s.data(), s.size()); return p + s.size(); }
+
+// %g with 6 significant digits for finite v in [1e-5, 1e15), exactly as printf rounds (round-half-even on the exact binary
+// value): v = m * 2^e is scaled by a power of ten in 128-bit integer arithmetic, so quotient and remainder are exact.
+// Everything outside that range (and inf/nan) goes to std::to_chars, which is slower (~5x) but rare in these tables.
+static const unsigned long long P10[] = {1ull, 10ull, 100ull, 1000ull, 10000ull, 100000ull, 1000000ull, 10000000ull, 100000000ull, 1000000000ull, 10000000000ull, 100000000000ull};
+static const double D10[] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15};
+static const double DM10[] = {1e0, 1e-1, 1e-2, 1e-3, 1e-4, 1e-5};
+static bool six_digits(unsigned long long m, int e, int X, unsigned long long& D) {   // D = round(v / 10^(X-5)); false when out of the supported shifts
+  typedef unsigned __int128 u128; int k = 5 - X;
+  if (e >= 0) return false;
+  int sh = -e; u128 q, r, half_or_den;
+  if (k >= 0) { if (k > 11 || sh > 120) return false; u128 N = (u128)m * P10[k]; q = N >> sh; r = N & (((u128)1 << sh) - 1); half_or_den = (u128)1 << (sh - 1);
+    if (r > half_or_den || (r == half_or_den && (q & 1))) q++; }
+  else { int j = -k; if (j > 11 || sh > 60) return false; u128 den = (u128)P10[j] << sh; q = (u128)m / den; r = (u128)m % den;
+    if (2 * r > den || (2 * r == den && (q & 1))) q++; }
+  D = (unsigned long long)q; return true;
 }
+static char* put_g_general(char* p, double v) { return std::to_chars(p, p + 32, v, std::chars_format::general, 6).ptr; }
+static inline char* put_g(char* p, double v) {
+  // integral values below 1e6 print as plain integers; that covers most cells (0, 1, integer percentiles)
+  if (v >= 0 && v < 1e6) { unsigned long long u = (unsigned long long)v; if ((double)u == v && !(u == 0 && std::signbit(v))) return put_u(p, u); }
+  double a = v < 0 ? -v : v;
+  if (!(a >= 1e-5 && a < 1e15)) return put_g_general(p, v);
+  unsigned long long b; memcpy(&b, &a, 8); int be = (int)(b >> 52) & 0x7ff; if (be == 0 || be == 0x7ff) return put_g_general(p, v);
+  unsigned long long m = (b & ((1ull << 52) - 1)) | (1ull << 52); int e = be - 1075;
+  int X; if (a >= 1.0) { X = 0; while (X < 14 && a >= D10[X + 1]) X++; } else { X = -1; while (X > -5 && a < DM10[-X]) X--; }
+  unsigned long long D = 0;
+  for (int tries = 0;; tries++) {
+    if (tries > 2 || !six_digits(m, e, X, D)) return put_g_general(p, v);
+    if (D < 100000ull) { X--; continue; }
+    if (D > 1000000ull) { X++; continue; }
+    if (D == 1000000ull) { D = 100000ull; X++; }
+    break;
+  }
+  if (v < 0) *p++ = '-';
+  char d[6]; { unsigned long long t = D; for (int i = 5; i >= 0; i--) { d[i] = (char)('0' + t % 10); t /= 10; } }
+  int nd = 6; while (nd > 1 && d[nd - 1] == '0') nd--;
+  if (X < -4 || X >= 6) {   // d.ddddde+XX
+    *p++ = d[0]; if (nd > 1) { *p++ = '.'; for (int i = 1; i < nd; i++) *p++ = d[i]; }
+    *p++ = 'e'; int ax = X; if (ax < 0) { *p++ = '-'; ax = -ax; } else *p++ = '+';
+    if (ax < 10) *p++ = '0'; return put_u(p, (unsigned long long)ax);
+  }
+  if (X >= 0) { for (int i = 0; i <= X; i++) *p++ = d[i]; if (nd > X + 1) { *p++ = '.'; for (int i = X + 1; i < nd; i++) *p++ = d[i]; } return p; }
+  *p++ = '0'; *p++ = '.'; for (int i = 0; i < -X - 1; i++) *p++ = '0'; for (int i = 0; i < nd; i++) *p++ = d[i];
+  return p;
+}
+std::string format_g6(double v) { char b[48]; return std::string(b, put_g(b, v)); }   // for the unit test of the formatter
 
 static const char* HDR_IR = "Chr\tStart\tEnd\tName\tNull\tStrand\tExcludedBases\tCoverage\tIntronDepth\tIntronDepth25Percentile\tIntronDepth50Percentile\tIntronDepth75Percentile\tExonToIntronReadsLeft\tExonToIntronReadsRight\tIntronDepthFirst50bp\tIntronDepthLast50bp\tSpliceLeft\tSpliceRight\tSpliceExact\tIRratio\tWarnings\n";
 static const char* WARN[5] = {"-", "LowCover", "LowSplicing", "MinorIsoform", "NonUniformIntronCover"};
 
-static void format_ir_rows(const CoverageRef& cov, const std::vector<IntronRow>& rows, size_t a, size_t b, std::string& s) {
-  for (size_t i = a; i < b; i++) {
-    const auto& rec = cov.BEDrecords[i]; const IntronRow& r = rows[i];
-    s += rec.chrName; s += '\t'; put_u(s, rec.start); s += '\t'; put_u(s, rec.end); s += '\t'; s += rec.name; s += "\t0\t"; s += rec.direction ? '+' : '-'; s += '\t';
-    put_i(s, r.excluded); s += '\t'; put_g(s, r.coverage); s += '\t'; put_g(s, r.depth); s += '\t'; put_g(s, r.p25); s += '\t'; put_g(s, r.p50); s += '\t'; put_g(s, r.p75); s += '\t';
-    put_u(s, r.sp_left); s += '\t'; put_u(s, r.sp_right); s += '\t'; put_g(s, r.first50); s += '\t'; put_g(s, r.last50); s += '\t';
-    put_u(s, r.jc_left); s += '\t'; put_u(s, r.jc_right); s += '\t'; put_u(s, r.jc_exact); s += '\t';
-    if (r.depth == 0 && std::max(r.jc_left, r.jc_right) == 0) s += '0'; else put_g(s, r.irratio);
-    s += '\t'; s += WARN[r.warning]; s += '\n';
-  }
+// a part is formatted into the thread's scratch buffer (sized from an upper bound of its rows, reused from part to part) and
+// then copied into the part's string at its exact size; a TextTable that is reused keeps its strings' capacity, so a
+// long-lived caller does not fault fresh pages in on every run
+template <class F> static void fill_part(std::string& s, size_t bound, F f) {
+  thread_local std::vector<char> scratch; if (scratch.size() < bound) scratch.resize(bound + bound / 4);
+  char* b = scratch.data(); char* e = f(b); s.assign(b, (size_t)(e - b));
 }
-static unsigned fmt_threads(size_t n, unsigned cap = 6) { unsigned nt = std::max(1u, std::min(cap, std::thread::hardware_concurrency())); return n < 20000 ? 1 : nt; }
-template <class F> static void run_parts(unsigned nt, F f) {   // f(t) for t in [0, nt), on nt threads
-  if (nt == 1) { f(0); return; }
-  std::vector<std::thread> th; for (unsigned t = 0; t < nt; t++) th.emplace_back([&, t]() { f(t); }); for (auto& t : th) t.join();
-}
-static std::string join_parts(const std::vector<std::string>& parts) { size_t tot = 0; for (auto& p : parts) tot += p.size(); std::string out; out.reserve(tot); for (auto& p : parts) out += p; return out; }
 
-std::vector<std::string> format_ir_table_parts(const CoverageRef& cov, const std::vector<IntronRow>& rows) {
-  size_t n = cov.BEDrecords.size(); unsigned nt = fmt_threads(n, 16);
-  std::vector<std::string> parts(nt + 1); parts[0] = HDR_IR;
-  run_parts(nt, [&](unsigned t) { size_t a = n * t / nt, b = n * (t + 1) / nt; parts[t + 1].reserve((b - a) * 160); format_ir_rows(cov, rows, a, b, parts[t + 1]); });
-  return parts;
+static void format_ir_rows(const CoverageRef& cov, const std::vector<IntronRow>& rows, size_t a, size_t b, std::string& s) {
+  size_t bound = 0; for (size_t i = a; i < b; i++) bound += cov.BEDrecords[i].chrName.size() + cov.BEDrecords[i].name.size() + 360;   // 3 x 20 + 8 x 24 + 5 x 10 + tabs + warning
+  fill_part(s, bound, [&](char* p) {
+    for (size_t i = a; i < b; i++) {
+      const auto& rec = cov.BEDrecords[i]; const IntronRow& r = rows[i];
+      p = put_s(p, rec.chrName); *p++ = '\t'; p = put_u(p, rec.start); *p++ = '\t'; p = put_u(p, rec.end); *p++ = '\t'; p = put_s(p, rec.name); *p++ = '\t'; *p++ = '0'; *p++ = '\t'; *p++ = rec.direction ? '+' : '-'; *p++ = '\t';
+      p = put_i(p, r.excluded); *p++ = '\t'; p = put_g(p, r.coverage); *p++ = '\t'; p = put_g(p, r.depth); *p++ = '\t'; p = put_g(p, r.p25); *p++ = '\t'; p = put_g(p, r.p50); *p++ = '\t'; p = put_g(p, r.p75); *p++ = '\t';
+      p = put_u(p, r.sp_left); *p++ = '\t'; p = put_u(p, r.sp_right); *p++ = '\t'; p = put_g(p, r.first50); *p++ = '\t'; p = put_g(p, r.last50); *p++ = '\t';
+      p = put_u(p, r.jc_left); *p++ = '\t'; p = put_u(p, r.jc_right); *p++ = '\t'; p = put_u(p, r.jc_exact); *p++ = '\t';
+      if (r.depth == 0 && std::max(r.jc_left, r.jc_right) == 0) *p++ = '0'; else p = put_g(p, r.irratio);
+      *p++ = '\t'; const char* w = WARN[r.warning]; size_t wl = strlen(w); memcpy(p, w, wl); p += wl; *p++ = '\n';
+    }
+    return p; });
 }
-std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>& rows) { return join_parts(format_ir_table_parts(cov, rows)); }
+
+void run_tasks(std::vector<std::function<void()>>& tasks, unsigned threads) {
+  if (tasks.empty()) return;
+  threads = std::max(1u, std::min<unsigned>(threads, (unsigned)tasks.size()));
+  if (threads == 1) { for (auto& t : tasks) t(); return; }
+  std::atomic<size_t> next(0); std::vector<std::string> errs(threads); std::vector<std::thread> th;
+  for (unsigned k = 0; k < threads; k++) th.emplace_back([&, k]() { try { for (;;) { size_t i = next.fetch_add(1); if (i >= tasks.size()) break; tasks[i](); } } catch (const std::string& e) { errs[k] = e; } catch (const std::exception& e) { errs[k] = e.what(); } });
+  for (auto& t : th) t.join();
+  for (auto& e : errs) if (!e.empty()) throw e;
+}
+unsigned format_threads() { return std::max(1u, std::min(16u, std::thread::hardware_concurrency())); }
+static std::string join_parts(const std::vector<std::string>& parts) { size_t tot = 0; for (auto& p : parts) tot += p.size(); std::string out; out.reserve(tot); for (auto& p : parts) out += p; return out; }
+static unsigned parts_for(size_t rows, size_t rows_per_part) { return (unsigned)std::max<size_t>(1, std::min<size_t>(64, rows / rows_per_part)); }
+
+void prepare_ir_table(TextTable& t, const CoverageRef& cov, const std::vector<IntronRow>& rows) {
+  size_t n = cov.BEDrecords.size(); unsigned np = parts_for(n, 4000);
+  t.tasks.clear(); t.parts.resize(np + 1); t.parts[0] = HDR_IR;
+  for (unsigned k = 0; k < np; k++) t.tasks.push_back([&t, &cov, &rows, n, np, k]() { format_ir_rows(cov, rows, n * k / np, n * (k + 1) / np, t.parts[k + 1]); });
+}
 
 // per-chromosome rows in (start,end) order: annotated junctions (possibly uncounted) merged with counted ones
-static std::map<std::string, std::vector<JRow>> merged_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
-  std::map<std::string, std::vector<JRow>> out = ref.flat;
-  std::map<std::string, std::vector<JRow>> extra;
-  for (auto& e : counted) { if (e.refid < 0 || e.refid >= (int)chr_names.size()) continue; extra[chr_names[e.refid]].push_back(JRow{e.start, e.end, 0, e.cnt[0], e.cnt[1]}); }
-  for (auto& x : extra) {
-    auto& v = x.second; std::sort(v.begin(), v.end(), [](const JRow& a, const JRow& b) { return a.start != b.start ? a.start < b.start : a.end < b.end; });
-    auto& base = out[x.first]; std::vector<JRow> m; m.reserve(base.size() + v.size()); size_t i = 0, j = 0;
-    while (i < base.size() || j < v.size()) {
-      bool takeA = j >= v.size() || (i < base.size() && (base[i].start < v[j].start || (base[i].start == v[j].start && base[i].end <= v[j].end)));
-      if (takeA) { JRow r = base[i++]; if (j < v.size() && v[j].start == r.start && v[j].end == r.end) { r.c0 += v[j].c0; r.c1 += v[j].c1; j++; } m.push_back(r); }
-      else { if (!m.empty() && m.back().start == v[j].start && m.back().end == v[j].end) { m.back().c0 += v[j].c0; m.back().c1 += v[j].c1; } else m.push_back(v[j]); j++; }
+static void merge_and_format_junctions(const std::string& chr, const std::vector<JRow>* base, std::vector<JRow>& v, std::string& s) {
+  auto less = [](const JRow& a, const JRow& b) { return a.start != b.start ? a.start < b.start : a.end < b.end; };
+  if (!std::is_sorted(v.begin(), v.end(), less)) std::sort(v.begin(), v.end(), less);
+  static const std::vector<JRow> none; const std::vector<JRow>& B = base ? *base : none;
+  fill_part(s, (B.size() + v.size()) * (chr.size() + 90), [&](char* p) {
+    auto emit = [&](const JRow& r) { p = put_s(p, chr); *p++ = '\t'; p = put_u(p, r.start); *p++ = '\t'; p = put_u(p, r.end); *p++ = '\t'; *p++ = r.bits == 1 ? '-' : r.bits == 2 ? '+' : '.'; *p++ = '\t';
+      p = put_u(p, (unsigned long long)r.c0 + r.c1); *p++ = '\t'; p = put_u(p, r.c1); *p++ = '\t'; p = put_u(p, r.c0); *p++ = '\n'; };
+    size_t i = 0, j = 0; JRow cur{}; bool have = false;   // same-key rows (annotation + counts, or repeated counted keys) collapse into one
+    auto push = [&](const JRow& r) { if (have && cur.start == r.start && cur.end == r.end) { cur.c0 += r.c0; cur.c1 += r.c1; cur.bits |= r.bits; } else { if (have) emit(cur); cur = r; have = true; } };
+    while (i < B.size() || j < v.size()) {
+      bool takeA = j >= v.size() || (i < B.size() && (B[i].start < v[j].start || (B[i].start == v[j].start && B[i].end <= v[j].end)));
+      if (takeA) push(B[i++]); else push(v[j++]);
     }
-    base.swap(m);
-  }
-  return out;
+    if (have) emit(cur);
+    return p; });
 }
-static void format_junction_rows(const std::string& chr, const std::vector<JRow>& rows, std::string& s) {
-  s.reserve(rows.size() * 40);
-  for (auto& r : rows) {
-    s += chr; s += '\t'; put_u(s, r.start); s += '\t'; put_u(s, r.end); s += '\t'; s += r.bits == 1 ? '-' : r.bits == 2 ? '+' : '.'; s += '\t';
-    put_u(s, (unsigned long long)r.c0 + r.c1); s += '\t'; put_u(s, r.c1); s += '\t'; put_u(s, r.c0); s += '\n';
-  }
+void prepare_junctions(TextTable& t, const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
+  auto extra = std::make_shared<std::map<std::string, std::vector<JRow>>>();
+  { const std::string* last_name = nullptr; std::vector<JRow>* last = nullptr; int last_id = -1;   // counted entries arrive grouped by refid
+    for (auto& e : counted) { if (e.refid < 0 || e.refid >= (int)chr_names.size()) continue;
+      if (e.refid != last_id) { last_id = e.refid; last_name = &chr_names[e.refid]; last = &(*extra)[*last_name]; }
+      last->push_back(JRow{e.start, e.end, 0, e.cnt[0], e.cnt[1]}); } }
+  std::map<std::string, std::pair<const std::vector<JRow>*, std::vector<JRow>*>> chrs;
+  for (auto& c : ref.flat) chrs[c.first].first = &c.second;
+  for (auto& c : *extra) chrs[c.first].second = &c.second;
+  t.tasks.clear(); t.parts.resize(chrs.size() + 1); t.parts[0] = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";
+  auto none = std::make_shared<std::vector<JRow>>();
+  size_t k = 1; for (auto& c : chrs) { const std::string name = c.first; auto base = c.second.first; auto v = c.second.second; size_t idx = k++;
+    t.tasks.push_back([&t, name, base, v, idx, extra, none]() { std::vector<JRow> empty; merge_and_format_junctions(name, base, v ? *v : empty, t.parts[idx]); }); }
 }
-std::vector<std::string> format_junctions_parts(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) {
-  auto m = merged_junctions(ref, chr_names, counted);
-  std::vector<std::pair<const std::string*, const std::vector<JRow>*>> chrs; for (auto& c : m) chrs.push_back({&c.first, &c.second});
-  std::vector<std::string> parts(chrs.size() + 1); parts[0] = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";
-  size_t total = 0; for (auto& c : chrs) total += c.second->size();
-  unsigned nt = fmt_threads(total); std::atomic<size_t> next(0);
-  run_parts(nt, [&](unsigned) { for (;;) { size_t i = next.fetch_add(1); if (i >= chrs.size()) break; format_junction_rows(*chrs[i].first, *chrs[i].second, parts[i + 1]); } });
-  return parts;
-}
-std::string format_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) { return join_parts(format_junctions_parts(ref, chr_names, counted)); }
 int directional(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted, std::string& log) {
   // only counted junctions can pass the evidence threshold, so walk those and look the annotation up (no merged map needed)
   unsigned long long same = 0, diff = 0, ev = 0, nev = 0, evk = 0, nevk = 0;
@@ -202,14 +263,23 @@ int directional(const JunctionRef& ref, const std::vector<std::string>& chr_name
   if (diff > same * 100 && evk > nevk * 100) return -1;
   return 0;
 }
-std::vector<std::string> format_spans_parts(const SpansPointRef& ref, const std::vector<u32>& count) {
-  size_t n = ref.pos.size(); unsigned nt = fmt_threads(n);
-  std::vector<const std::string*> name_of(n); for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) name_of[i] = &c.first;
-  std::vector<std::string> parts(nt + 1); parts[0] = "SP_seqname\tcoord\ttotal\tpos\tneg\n";
-  run_parts(nt, [&](unsigned t) { size_t a = n * t / nt, b = n * (t + 1) / nt; std::string& s = parts[t + 1]; s.reserve((b - a) * 32);
-    for (size_t i = a; i < b; i++) { u32 neg = count[i], pos = count[n + i]; s += *name_of[i]; s += '\t'; put_u(s, ref.pos[i]); s += '\t'; put_u(s, (unsigned long long)neg + pos); s += '\t'; put_u(s, pos); s += '\t'; put_u(s, neg); s += '\n'; } });
-  return parts;
+void prepare_spans(TextTable& t, const SpansPointRef& ref, const std::vector<u32>& count) {
+  size_t n = ref.pos.size(); unsigned np = parts_for(n, 20000);
+  auto name_of = std::make_shared<std::vector<const std::string*>>(n); for (auto& c : ref.chr_range) for (u32 i = c.second.begin; i < c.second.end; i++) (*name_of)[i] = &c.first;
+  size_t longest = 0; for (auto& c : ref.chr_range) longest = std::max(longest, c.first.size());
+  t.tasks.clear(); t.parts.resize(np + 1); t.parts[0] = "SP_seqname\tcoord\ttotal\tpos\tneg\n";
+  for (unsigned k = 0; k < np; k++) t.tasks.push_back([&t, &ref, &count, name_of, n, np, k, longest]() {
+    size_t a = n * k / np, b = n * (k + 1) / np;
+    fill_part(t.parts[k + 1], (b - a) * (longest + 60), [&](char* p) {
+      for (size_t i = a; i < b; i++) { u32 neg = count[i], pos = count[n + i]; p = put_s(p, *(*name_of)[i]); *p++ = '\t'; p = put_u(p, ref.pos[i]); *p++ = '\t'; p = put_u(p, (unsigned long long)neg + pos); *p++ = '\t'; p = put_u(p, pos); *p++ = '\t'; p = put_u(p, neg); *p++ = '\n'; }
+      return p; }); });
 }
+static std::vector<std::string> finish(TextTable& t) { run_tasks(t.tasks, format_threads()); return std::move(t.parts); }
+std::vector<std::string> format_ir_table_parts(const CoverageRef& cov, const std::vector<IntronRow>& rows) { TextTable t; prepare_ir_table(t, cov, rows); return finish(t); }
+std::vector<std::string> format_junctions_parts(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) { TextTable t; prepare_junctions(t, ref, chr_names, counted); return finish(t); }
+std::vector<std::string> format_spans_parts(const SpansPointRef& ref, const std::vector<u32>& count) { TextTable t; prepare_spans(t, ref, count); return finish(t); }
+std::string format_ir_table(const CoverageRef& cov, const std::vector<IntronRow>& rows) { return join_parts(format_ir_table_parts(cov, rows)); }
+std::string format_junctions(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted) { return join_parts(format_junctions_parts(ref, chr_names, counted)); }
 std::string format_spans(const SpansPointRef& ref, const std::vector<u32>& count) { return join_parts(format_spans_parts(ref, count)); }
 std::string format_roi(const RoiRef& ref, const std::vector<u32>& count) {
   std::string s = "ROI_Name\ttotal\tpos\tneg\n"; size_t n = ref.rois.size();

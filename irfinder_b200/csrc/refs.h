@@ -5,6 +5,7 @@
 #pragma once
 #include <cstdint>
 #include <istream>
+#include <functional>
 #include <map>
 #include <ostream>
 #include <string>
@@ -50,6 +51,16 @@ struct JuncEntry { int refid; u32 start, end; u32 cnt[2]; };
 
 // text writers (byte layout per SURVEY.md B.7 / B.8).  Large tables come back as consecutive pieces (formatted by several
 // threads) so the caller can write them without another copy.
+// A table is prepared as parts (part 0 = header line) plus one task per remaining part; the tasks are independent of each
+// other and of other tables' tasks, so a caller can pool the tasks of all its tables (run_tasks) and then write the parts.
+// The TextTable must stay where it is until its tasks have run (they point into it), as must the inputs.
+struct TextTable { std::vector<std::string> parts; std::vector<std::function<void()>> tasks; };
+void prepare_ir_table(TextTable& t, const CoverageRef& cov, const std::vector<IntronRow>& rows);
+void prepare_junctions(TextTable& t, const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted);
+void prepare_spans(TextTable& t, const SpansPointRef& ref, const std::vector<u32>& count);
+void run_tasks(std::vector<std::function<void()>>& tasks, unsigned threads);   // rethrows the first failure as std::string
+unsigned format_threads();
+std::string format_g6(double v);   // one cell as the tables print it (printf("%g")); exposed for tests
 std::vector<std::string> format_ir_table_parts(const CoverageRef& cov, const std::vector<IntronRow>& rows);
 std::vector<std::string> format_junctions_parts(const JunctionRef& ref, const std::vector<std::string>& chr_names, const std::vector<JuncEntry>& counted);
 std::vector<std::string> format_spans_parts(const SpansPointRef& ref, const std::vector<u32>& count);

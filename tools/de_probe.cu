@@ -27,12 +27,17 @@ int main(int argc, char** argv) {
   for (size_t i = 0; i < bl.size(); i++) { memset(&P[i], 0, sizeof P[i]); P[i].srcNumBytes = bl[i].clen; P[i].dstNumBytes = bl[i].ulen; P[i].dstActBytes = dact + i; P[i].src = dc + bl[i].coff; P[i].dst = du + bl[i].uoff; P[i].algo = CU_MEM_DECOMPRESS_ALGORITHM_DEFLATE; }
   CUmemDecompressParams* Pd = nullptr; if (params_on_device) { cudaMalloc(&Pd, P.size() * sizeof P[0]); cudaMemcpy(Pd, P.data(), P.size() * sizeof P[0], cudaMemcpyHostToDevice); }
   cudaStream_t s; cudaStreamCreate(&s); cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+  // DE_STREAMS=k: batches go round-robin to k streams (does the engine overlap batches of different streams?)
+  int ns = getenv("DE_STREAMS") ? atoi(getenv("DE_STREAMS")) : 1; if (ns < 1) ns = 1; std::vector<cudaStream_t> ss(ns); std::vector<cudaEvent_t> done(ns);
+  for (int k = 0; k < ns; k++) { cudaStreamCreateWithFlags(&ss[k], cudaStreamNonBlocking); cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming); }
   for (int rep = 0; rep < 3; rep++) {
-    cudaEventRecord(e0, s);
-    for (size_t i = 0; i < bl.size(); i += batch) { size_t c = std::min(batch, bl.size() - i), ei = 0; CUresult r = cuMemBatchDecompressAsync((params_on_device ? Pd : P.data()) + i, c, 0, &ei, (CUstream)s);
+    cudaEventRecord(e0, s); for (int k = 0; k < ns; k++) cudaStreamWaitEvent(ss[k], e0, 0);
+    int k = 0;
+    for (size_t i = 0; i < bl.size(); i += batch, k = (k + 1) % ns) { size_t c = std::min(batch, bl.size() - i), ei = 0; CUresult r = cuMemBatchDecompressAsync((params_on_device ? Pd : P.data()) + i, c, 0, &ei, (CUstream)ss[k]);
       if (r != CUDA_SUCCESS) { const char* es; cuGetErrorString(r, &es); printf("cuMemBatchDecompressAsync -> %d %s (index %zu)\n", (int)r, es ? es : "?", ei); return 1; } }
+    for (int j = 0; j < ns; j++) { cudaEventRecord(done[j], ss[j]); cudaStreamWaitEvent(s, done[j], 0); }
     cudaEventRecord(e1, s); cudaError_t ce = cudaStreamSynchronize(s); if (ce != cudaSuccess) { printf("sync -> %s\n", cudaGetErrorString(ce)); return 1; }
-    float ms; cudaEventElapsedTime(&ms, e0, e1); printf("rep %d: %.2f ms, %.1f GB/s (compressed + inflated)\n", rep, ms, (n + u) / ms / 1e6);
+    float ms; cudaEventElapsedTime(&ms, e0, e1); printf("streams %d batch %zu rep %d: %.2f ms, %.1f GB/s (compressed + inflated), %.1f GB/s inflated\n", ns, batch, rep, ms, (n + u) / ms / 1e6, u / ms / 1e6);
   }
   std::vector<unsigned char> out(u); cudaMemcpy(out.data(), du, u, cudaMemcpyDeviceToHost); std::vector<unsigned> act(bl.size()); cudaMemcpy(act.data(), dact, bl.size() * 4, cudaMemcpyDeviceToHost);
   if (getenv("DE_CORRUPT")) { printf("block 3: expected %zu bytes, engine reported %u; block 4: expected %zu, reported %u\n", bl[3].ulen, act[3], bl[4].ulen, act[4]); return 0; }
