@@ -655,9 +655,21 @@ struct irf_ctx {
     if (!counted) throw string("irf_count has not run");
     if (finalized) return;
     cudaEvent_t e0, e1; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventRecord(e0, s_compute));
-    const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr; double tdbg = now_ms(); auto mark = [&](const char* what) { if (dbg) { sync(); double t = now_ms(); fprintf(stderr, "[finalize] %-22s %8.3f ms\n", what, t - tdbg); tdbg = t; } };
-    u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0); mark("leftovers");
-    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute); mark("depth scan");
+    const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr; double tdbg = now_ms(); auto mark = [&](const char* what) { if (dbg) { sync(); cudaStreamSynchronize(s_copy); double t = now_ms(); fprintf(stderr, "[finalize] %-22s %8.3f ms\n", what, t - tdbg); tdbg = t; } };
+    // Two streams: the compute stream exports and sorts the junction tables while the host turns them into rows and runs
+    // Directional(); the side stream takes the per-intron statistics (maximum depth, histogram kernel, row read-back), which
+    // need the scanned depth and the junction hash tables but not the exported rows.
+    cudaEvent_t ev_scan, ev_side; IRF_CUDA(cudaEventCreateWithFlags(&ev_scan, cudaEventDisableTiming)); IRF_CUDA(cudaEventCreateWithFlags(&ev_side, cudaEventDisableTiming));
+    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute); IRF_CUDA(cudaEventRecord(ev_scan, s_compute));
+    u32* dmax = d_small.as<u32>() + 2; u32 hmax = 0;
+    IRF_CUDA(cudaStreamWaitEvent(s_copy, ev_scan, 0)); IRF_CUDA(cudaMemsetAsync(dmax, 0, 4, s_copy)); launch_max_depth(T.diff, cov.P, dmax, s_copy);
+    IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_copy));
+    u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0); mark("scan + leftovers");
+    IRF_CUDA(cudaStreamSynchronize(s_copy));
+    u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
+    u32 bins = hmax >= 8192 ? hmax + 1 : 1; d_scratch.ensure((u64)grid * bins * 4);
+    launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy);
+    pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy));
     // junctions -> host (JunctionCount map contents)
     u64 nj = export_table(0); vector<u64> k(nj); vector<u32> c(nj * 2);
     if (nj) {   // sort by key on the device: key order == (refID, start, end) order
@@ -670,19 +682,13 @@ struct irf_ctx {
         h_junc[i] = JuncEntry{rid, (u32)(gl - chr_goff[rid]), (u32)(gl - chr_goff[rid] + gap), {c[2 * i], c[2 * i + 1]}}; } }
     h_junc_out.resize(nj); for (u64 i = 0; i < nj; i++) h_junc_out[i] = JuncOut{h_junc[i].refid, h_junc[i].start, h_junc[i].end, h_junc[i].cnt[0], h_junc[i].cnt[1]};
     mark("junction export+sort"); dir_log.clear(); directionality = directional(jref, chr_names, h_junc, dir_log); mark("directional");
-    // per-intron statistics
-    u32* dmax = d_small.as<u32>() + 2; IRF_CUDA(cudaMemsetAsync(dmax, 0, 4, s_compute)); launch_max_depth(T.diff, cov.P, dmax, s_compute);
-    u32 hmax = 0; IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
-    mark("max depth"); u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
-    u32 bins = hmax >= 8192 ? hmax + 1 : 1; d_scratch.ensure((u64)grid * bins * 4);
-    launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
-    pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
-    mark("intron stats nondir");
+    IRF_CUDA(cudaStreamSynchronize(s_copy)); mark("intron stats nondir (side stream)");
     if (directionality == 0 && !rows_dir.empty()) { cudaHostUnregister(rows_dir.data()); vector<IntronRow>().swap(rows_dir); }
     if (directionality != 0) {
-      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, directionality, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_compute);
-      pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); sync();
+      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, directionality, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy);
+      pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); IRF_CUDA(cudaStreamSynchronize(s_copy));
     }
+    IRF_CUDA(cudaEventRecord(ev_side, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_side, 0)); cudaEventDestroy(ev_scan); cudaEventDestroy(ev_side);
     mark("intron stats dir"); h_stats.assign(ST_COUNT, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
     IRF_CUDA(cudaMemcpyAsync(h_stats.data(), d_stats.p, ST_COUNT * 8, cudaMemcpyDeviceToHost, s_compute));
     if (!h_sp.empty()) IRF_CUDA(cudaMemcpyAsync(h_sp.data(), d_sp_count.p, h_sp.size() * 4, cudaMemcpyDeviceToHost, s_compute));
@@ -707,15 +713,18 @@ struct irf_ctx {
   void write_outputs(const char* outdir) {
     if (!finalized) throw string("no finished run to write");
     double t0 = now_ms(); string d = outdir;
-    auto put = [&](const char* name, const string& s) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; size_t w = fwrite(s.data(), 1, s.size(), f); int rc = fclose(f); if (w != s.size() || rc) throw string("short write to ") + p; };
     // every table is cut into independent parts; ONE pool of threads formats the parts of all tables, then the files are written side by side
     const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr;
     vector<std::function<void()>> tasks;   // the tables themselves are members: their buffers are reused from run to run
-    prepare_ir_table(t_ir, cov, rows_nondir); if (directionality != 0) prepare_ir_table(t_dir, cov, rows_dir);
-    prepare_junctions(t_junc, jref, chr_names, h_junc); prepare_spans(t_sp, sp, h_sp);
+    { vector<std::function<void()>> prep;   // cutting the tables into parts is itself worth a thread each (junction bucketing, span names)
+      prep.push_back([&]() { prepare_ir_table(t_ir, cov, rows_nondir); if (directionality != 0) prepare_ir_table(t_dir, cov, rows_dir); });
+      prep.push_back([&]() { prepare_junctions(t_junc, jref, chr_names, h_junc); }); prep.push_back([&]() { prepare_spans(t_sp, sp, h_sp); });
+      run_tasks(prep, 3); }
+    if (directionality == 0) { t_dir.parts.clear(); t_dir.tasks.clear(); }
     for (TextTable* t : {&t_ir, &t_dir, &t_junc, &t_sp}) for (auto& f : t->tasks) tasks.push_back(f);
     string s_chr, s_roi; tasks.push_back([&]() { s_chr = format_chr(chr_names, h_chr); if (roi.present) s_roi = format_roi(roi, h_roi); });
     double t1 = now_ms(); run_tasks(tasks, format_threads()); double t2 = now_ms();
+    // one writer per file (parallel pwrite of one file's parts was measured no faster: page-cache allocation is the cost)
     auto putv = [&](const char* name, const vector<string>& parts) { string p = d + "/" + name; FILE* f = fopen(p.c_str(), "wb"); if (!f) throw string("cannot write ") + p; bool ok = true;
       for (auto& x : parts) ok &= fwrite(x.data(), 1, x.size(), f) == x.size(); if (fclose(f) || !ok) throw string("short write to ") + p; };
     vector<std::function<void()>> writers;
@@ -723,7 +732,7 @@ struct irf_ctx {
     if (directionality != 0) writers.push_back([&]() { putv("IRFinder-IR-dir.txt", t_dir.parts); });
     writers.push_back([&]() { putv("IRFinder-JuncCount.txt", t_junc.parts); });
     writers.push_back([&]() { putv("IRFinder-SpansPoint.txt", t_sp.parts); });
-    writers.push_back([&]() { put("IRFinder-ChrCoverage.txt", s_chr); if (roi.present) put("IRFinder-ROI.txt", s_roi); });
+    writers.push_back([&]() { putv("IRFinder-ChrCoverage.txt", vector<string>{s_chr}); if (roi.present) putv("IRFinder-ROI.txt", vector<string>{s_roi}); });
     run_tasks(writers, (unsigned)writers.size());
     if (dbg) fprintf(stderr, "[output] prepare %.2f ms, format %zu parts %.2f ms, write %.2f ms\n", t1 - t0, tasks.size(), t2 - t1, now_ms() - t2);
     timing[7] = now_ms() - t0;
