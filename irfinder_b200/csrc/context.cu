@@ -525,7 +525,10 @@ struct irf_ctx {
         size_t b1 = std::min<size_t>(chunk_blk_end[c], (size_t)nblk_own); if (b1 <= b0) continue;
         const int nbk = (int)(b1 - b0); const bool last_own = b1 == (size_t)nblk_own;
         // chunk c is counted once chunk c+1 is inflated; the last counted chunk waits for everything (the look-ahead)
-        const size_t need = last_own ? nch - 1 : std::min(c + 1, nch - 1);
+        // (with the default 256 MB chunks that is the next chunk; tiny test chunks wait for 8 MB of look-ahead so that any
+        // realistic record, however many small chunks it spans, is complete)
+        size_t need = std::min(c + 1, nch - 1); while (need + 1 < nch && inf_end[need] - inf_end[c] < (8u << 20)) need++;
+        if (last_own) need = nch - 1;
         IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[need], 0));
         if (sm_used && c < ksm) IRF_CUDA(cudaStreamWaitEvent(s_compute, k1, 0));
         const u64 visible = inf_end[need];

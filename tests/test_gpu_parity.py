@@ -379,3 +379,91 @@ def test_sharded_run_through_the_chunk_pipeline(tiny, tmp_path, mode):
         c.write_outputs(out)
         assert_same_outputs(tiny["oracle_out"], out)
         assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+
+
+def _adversarial_records(sj_path, seed):
+    """Hand-made alignments that a read simulator never produces, around the annotated junctions of the tiny genome."""
+    import random
+    from bamutil import record
+    rnd = random.Random(seed)
+    junc = [l.split("\t") for l in open(sj_path).read().split("\n") if l]
+    junc = [(0 if j[0] == "chrA" else 1, int(j[1]), int(j[2])) for j in junc if j[0] in ("chrA", "chrB")]
+    P, PROPER, UNMAP, MUNMAP, REV, MREV, R1, R2, SEC, QCF, DUP, SUP = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40, 0x80, 0x100, 0x200, 0x400, 0x800
+    frags = []          # one entry per fragment: mates stay next to each other in the order the oracle reads (SURVEY.md B.2)
+
+    class _Sink:
+        def append(self, r):
+            frags.append([r])
+    recs = _Sink()
+
+    def pair(name, refid, p1, c1, p2, c2, f1=0, f2=0, mref=None):
+        a = record(name, refid, p1, c1, P | PROPER | R1 | f1, refid if mref is None else mref, p2, 300)
+        b = record(name, refid if mref is None else mref, p2, c2, P | PROPER | R2 | f2, refid, p1, -300)
+        frags.append([a, b] if rnd.randrange(2) else [b, a])
+
+    for i in range(1500):
+        ref, s, e = junc[rnd.randrange(len(junc))]
+        gap = e - s
+        kind = rnd.randrange(14)
+        a, b = rnd.randrange(1, 60), rnd.randrange(1, 60)            # flanks below and above the 5-base threshold
+        name = "q%05d" % i
+        if kind == 0:    # spliced read exactly on an annotated junction, short and long flanks, both strands
+            recs.append(record(name, ref, s - a, f"{a}M{gap}N{b}M", REV * rnd.randrange(2)))
+        elif kind == 1:  # every CIGAR operation: clips, insertion, deletion, padding, = and X, two gaps
+            recs.append(record(name, ref, s - 30, f"3H4S10=2X1I8M2D10M{gap}N12M1P5M40N9M6S", REV * rnd.randrange(2)))
+        elif kind == 2:  # pair whose reads overlap, read 2 first
+            pair(name, ref, s - 80, "100M", s - 40, "100M", MREV, REV)
+        elif kind == 3:  # read 2 contained in read 1, both spliced over the same junction
+            pair(name, ref, s - 50, f"50M{gap}N50M", s - 20, f"20M{gap}N10M", MREV, REV)
+        elif kind == 4:  # far apart mates (no overlap), reverse read first in the file
+            pair(name, ref, max(0, s - 900), "75M", s - 10, f"10M{gap}N65M", REV, MREV)
+        elif kind == 5:  # mates on different chromosomes
+            pair(name, ref, s - 10, "60M", 1000 + i, "60M", mref=2)
+        elif kind == 6:  # mate flagged unmapped (placed at its mate's position, as aligners do)
+            recs.append(record(name, ref, s - 20, "70M", P | MUNMAP | R1))
+            recs.append(record(name, ref, s - 20, "", P | UNMAP | R2, lseq=70))
+        elif kind == 7:  # secondary / supplementary / QC-fail / duplicate flags on otherwise ordinary reads
+            recs.append(record(name, ref, s - 30, f"30M{gap}N40M", rnd.choice([SEC, SUP, QCF, DUP, SEC | REV])))
+        elif kind == 8:  # the same read name used by two different pairs
+            pair("shared", ref, s - 60, "50M", e + 5, "50M", MREV, REV)
+        elif kind == 9:  # a paired flag with the mate never present in the file
+            recs.append(record(name, ref, e - 10, "90M", P | PROPER | R1 | MREV, ref, e + 200, 300))
+        elif kind == 10:  # read ending exactly at / starting exactly at the splice sites
+            recs.append(record(name, ref, s - 50, "50M", 0)); recs.append(record(name + "b", ref, e, "50M", REV))
+        elif kind == 11:  # novel junction sharing one annotated end
+            recs.append(record(name, ref, s - 25, f"25M{gap + 7}N25M", 0))
+        elif kind == 12:  # intron-body reads at both edges of the measured region
+            recs.append(record(name, ref, s + rnd.randrange(0, 8), "50M", 0)); recs.append(record(name + "b", ref, max(s, e - 50 - rnd.randrange(0, 8)), "50M", REV))
+        else:             # deletion instead of a gap across the whole intron (counts as coverage, not as a junction)
+            recs.append(record(name, ref, s - 10, f"10M{min(gap, 2000)}D10M", 0))
+    recs.append(record("first_base", 0, 0, "80M", 0))
+    recs.append(record("last_base", 1, 300000 - 80, "80M", REV))
+    recs.append(record("empty_chr", 2, 100, "80M", 0))
+    recs.append(record("long_read", 0, 50000, "60000M5000N90000M", 0))             # one 225 KB record across four BGZF blocks
+    recs.append(record("unmapped_tail", -1, -1, "", UNMAP, lseq=100))
+    rnd.shuffle(frags)
+    collated = [r for f in frags for r in f]
+    scattered = list(collated)
+    rnd.shuffle(scattered)          # mates far apart, in any order: only the GPU path (hash pairing) reads this one
+    return collated, scattered
+
+
+@pytest.mark.parametrize("block", [65280, 3000])
+def test_adversarial_alignments_match_oracle(built, tiny, tmp_path, block):
+    """Flag combinations, CIGAR operations, name collisions, cross-chromosome and orphan mates, reads at chromosome ends and a
+    read longer than three BGZF blocks, shuffled, in normal and in very small BGZF blocks: GPU tables must equal the oracle's."""
+    from bamutil import write_bam
+    refs = [("chrA", 400000), ("chrB", 300000), ("chrEmpty", 50000)]
+    collated, scattered = _adversarial_records(tiny["sj"], 5)
+    bam, bam2 = str(tmp_path / "adv.bam"), str(tmp_path / "adv_scattered.bam")
+    write_bam(bam, refs, collated, block=block, level=1)
+    write_bam(bam2, refs, scattered, block=block, level=1)
+    meta = dict(tiny, sorted=bam, collated=bam)
+    ostd = run_oracle(built, meta, str(tmp_path / "o"))
+    want = _stats_from_stdout(ostd)
+    assert int(want["Total pairs processed"]) > 300 and int(want["Total singles processed"]) > 500 and int(want["Skipped reads"]) > 50 and int(want["Error reads"]) > 50
+    for i, (path, opts) in enumerate([(bam, {}), (bam2, {}), (bam2, dict(stream_chunk_kb=64, de_percent=0, de_percent_stream=0)),
+                                      (bam2, dict(stream_chunk_kb=64))]):      # chunk pipeline: the long read spans several 64 KB chunks
+        c = _gpu_run(meta, str(tmp_path / f"g{i}"), bam=path, **opts)
+        assert_same_outputs(str(tmp_path / "o"), str(tmp_path / f"g{i}"))
+        assert _stats_from_stdout(c.stdout_text) == want
