@@ -467,3 +467,36 @@ def test_adversarial_alignments_match_oracle(built, tiny, tmp_path, block):
         c = _gpu_run(meta, str(tmp_path / f"g{i}"), bam=path, **opts)
         assert_same_outputs(str(tmp_path / "o"), str(tmp_path / f"g{i}"))
         assert _stats_from_stdout(c.stdout_text) == want
+
+
+def test_header_only_and_many_contig_inputs(built, tiny, tmp_path):
+    """Ragged inputs: a BAM with a header and no alignments at all, and one whose header (4000 contigs, > 64 KB) spans several
+    BGZF blocks with alignments only on the annotated chromosomes and on the last contig."""
+    from bamutil import record, write_bam
+    refs = [("chrA", 400000), ("chrB", 300000), ("chrEmpty", 50000)]
+    empty = str(tmp_path / "empty.bam")
+    write_bam(empty, refs, [], level=1)
+    meta = dict(tiny, sorted=empty, collated=empty)
+    ostd = run_oracle(built, meta, str(tmp_path / "o0"))
+    c = _gpu_run(meta, str(tmp_path / "g0"))
+    assert_same_outputs(str(tmp_path / "o0"), str(tmp_path / "g0"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
+    assert c.stats()["records"] == 0
+
+    many = refs + [("scaffold_%04d_random_with_a_long_name" % i, 1000 + i) for i in range(4000)]
+    junc = [l.split("\t") for l in open(tiny["sj"]).read().split("\n") if l][:200]
+    recs = []
+    for i, j in enumerate(junc):
+        ref, s, e = (0 if j[0] == "chrA" else 1), int(j[1]), int(j[2])
+        recs.append(record("m%04d" % i, ref, s - 40, f"40M{e - s}N40M", 16 * (i & 1)))
+        recs.append(record("s%04d" % i, 3 + (i * 19) % 4000, 10, "50M", 0))
+    recs.append(record("last", len(many) - 1, 100, "30M", 16))
+    big = str(tmp_path / "many.bam")
+    raw = write_bam(big, many, recs, level=1)
+    assert raw.index(b"m0000\0") > 2 * 65280, "the header must span more than two BGZF blocks for this test to mean anything"
+    meta = dict(tiny, sorted=big, collated=big)
+    ostd = run_oracle(built, meta, str(tmp_path / "o1"))
+    for i, opts in enumerate([{}, dict(stream_chunk_kb=64), dict(de_percent=0, de_percent_stream=0)]):
+        c = _gpu_run(meta, str(tmp_path / f"g1_{i}"), **opts)
+        assert_same_outputs(str(tmp_path / "o1"), str(tmp_path / f"g1_{i}"))
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
