@@ -162,7 +162,7 @@ def run_reference(a):
             "config": {"workload": workload_name(a, a.pairs * a.gpus), "sampled": sample, "generation_s": round(gen_s, 1)},
             "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
@@ -185,7 +185,7 @@ def run_b200(a):
     if world > 1 and os.path.isdir("/dev/shm"):   # N shards are generated at once: keep them off a possibly small disk
         try:
             st = os.statvfs("/dev/shm")
-            if st.f_bavail * st.f_frsize > 3 * world * a.pairs * 300:
+            if st.f_bavail * st.f_frsize > 1.5 * world * a.pairs * 300:   # all ranks' parts exist at once (~290 B per pair) until each has been read into pinned memory
                 base = "/dev/shm/irf_bench"
         except OSError:
             pass
@@ -347,12 +347,28 @@ def run_b200(a):
                          "algorithmic_bytes_per_launch": int(sm_bytes), "launches_per_step": inflate_launches / max(a.steps, 1), "avg_launch_ms": round(sm_ms, 3),
                          "both_engines": {"achieved": round(stage_achieved, 2), "frac": round(stage_achieved / peak, 5), "algorithmic_bytes_per_step": int(alg_bytes), "ms_until_all_inflated": round(avg_inflate_ms, 3)}},
             "cpu_baseline": cpu, "clocks": clocks}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
 
 
+_RESULT_FD = None
+
+
+def emit(line):
+    """The ONE line of stdout.  Everything else this process and its libraries print (NCCL's version banner, build logs)
+    goes to stderr: file descriptor 1 is pointed at stderr for the whole run and the original stdout is kept for this call."""
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
