@@ -1,9 +1,11 @@
 """Region-sharded multi-GPU run: one process and one irf_ctx per GPU, torch.distributed for the exchange.
 
 SURVEY.md §8e.  A coordinate-sorted BAM is cut at BGZF block boundaries into `world` byte ranges of equal
-compressed size; BGZF offsets order records by coordinate, so each range is a genomic region.  No BAI is
-needed: record framing inside a shard is speculative + verified (kernels.cu, S2) and the first record of
-shard r is cross-checked against the last record of shard r-1 (`frame handshake`).
+compressed size; BGZF offsets order records by coordinate, so each range is a genomic region.  The cut points
+come from the file's BAI index when one is given (`bai=`: block offsets of its linear index and bins) and from
+a scan for BGZF block headers otherwise; either way record framing inside a shard is speculative + verified
+(kernels.cu, S2) and the first record of shard r is cross-checked against the last record of shard r-1
+(`frame handshake`), so the index only chooses where to cut, it is never trusted for record boundaries.
 
 Exchange steps (all integer, so outputs are identical for every GPU count):
   1. halo:      records whose mate lies in another shard are trimmed to fixed part + name + CIGAR and
@@ -72,6 +74,56 @@ def shard_cuts(buf, world):
     return cuts
 
 
+def read_bai_block_offsets(bai_path):
+    """Compressed file offsets of BGZF blocks in which some alignment starts, from a BAI index (SAM v1 §5.2): the upper 48 bits
+    of every linear-index entry and of every bin chunk begin.  Sorted, unique.  These are the cut candidates of §8e's
+    "host reads the BAI": each is a block start by construction, so no scan of the BGZF bytes is needed."""
+    import struct
+    raw = open(bai_path, "rb").read()
+    if raw[:4] != b"BAI\1":
+        raise ValueError(f"{bai_path}: not a BAI index (bad magic)")
+    p = 4
+    n_ref, = struct.unpack_from("<i", raw, p)
+    p += 4
+    offs = set()
+    for _ in range(n_ref):
+        n_bin, = struct.unpack_from("<i", raw, p)
+        p += 4
+        for _ in range(n_bin):
+            bin_id, n_chunk = struct.unpack_from("<Ii", raw, p)
+            p += 8
+            if bin_id != 37450:                       # the pseudo-bin holds counts, not offsets
+                ch = np.frombuffer(raw, dtype="<u8", count=2 * n_chunk, offset=p)
+                offs.update(int(x) >> 16 for x in ch[0::2])
+            p += 16 * n_chunk
+        n_intv, = struct.unpack_from("<i", raw, p)
+        p += 4
+        io = np.frombuffer(raw, dtype="<u8", count=n_intv, offset=p)
+        offs.update(int(x) >> 16 for x in np.unique(io) if x)
+        p += 8 * n_intv
+    return sorted(offs)
+
+
+def shard_cuts_from_bai(bai_path, buf, world):
+    """Like shard_cuts, with the candidates taken from the BAI instead of a scan for block headers; a candidate that is not a
+    BGZF block start in `buf` (index of another file, truncated file) raises."""
+    n = len(buf)
+    cand = [c for c in read_bai_block_offsets(bai_path) if 0 < c < n]
+    cuts = [0]
+    for r in range(1, world):
+        want = n * r // world
+        i = int(np.searchsorted(np.asarray(cand, dtype=np.int64), want)) if cand else 0
+        near = [c for c in cand[max(0, i - 1): i + 1] if c > cuts[-1]]        # the candidates either side of the ideal cut
+        if not near:
+            near = [c for c in cand[i:] if c > cuts[-1]][:1]                      # sparse index: the next candidate, if any is left
+        c = min(near, key=lambda x: abs(x - want)) if near else n
+        if c < n and not _is_block_start(buf, c)[0]:
+            raise ValueError(f"{bai_path}: offset {c} is not a BGZF block start in this BAM (index of another file?)")
+        cuts.append(max(c, cuts[-1]))
+    cuts.append(n)
+    return cuts
+
+
 class _DevArray:
     def __init__(self, ptr, n, typestr):
         self.__cuda_array_interface__ = dict(shape=(int(n),), typestr=typestr, data=(int(ptr), False), version=3)
@@ -121,11 +173,12 @@ class ShardPlan:
         self.header, self.data, self.n_own, self.rank, self.world, self.cuts = header, data, int(n_own), rank, world, cuts
 
     @staticmethod
-    def from_buffer(buf, rank, world, lookahead=1 << 18, header_probe=1 << 22):
-        """Every rank sees the whole BAM (host memory or np.memmap); cuts balance compressed bytes."""
+    def from_buffer(buf, rank, world, lookahead=1 << 18, header_probe=1 << 22, bai=None):
+        """Every rank sees the whole BAM (host memory or np.memmap); cuts balance compressed bytes.  With `bai` (path of the
+        file's BAI index) the cut points come from the index, otherwise from a scan for BGZF block headers."""
         arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
         n = arr.size
-        cuts = shard_cuts(arr, world)
+        cuts = shard_cuts_from_bai(bai, arr, world) if bai else shard_cuts(arr, world)
         lo, hi = cuts[rank], cuts[rank + 1]
         hi_look = hi if rank == world - 1 else min(n, hi + lookahead)
         return ShardPlan(arr[: min(n, header_probe)], arr[lo:hi_look], hi - lo, rank, world, cuts)
@@ -233,12 +286,12 @@ def run_plan(core, plan, device=None, group=None, restage=True):
 
 
 
-def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 18):
+def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 18, bai=None):
     """Counts `buf` (the whole BGZF BAM in host memory, same bytes on every rank) across `world` ranks."""
-    return run_plan(core, ShardPlan.from_buffer(buf, rank, world, lookahead), device, group)
+    return run_plan(core, ShardPlan.from_buffer(buf, rank, world, lookahead, bai=bai), device, group)
 
 
-def run_sharded_local(cores, buf, lookahead=1 << 18, header_probe=1 << 20):
+def run_sharded_local(cores, buf, lookahead=1 << 18, header_probe=1 << 20, bai=None):
     """The same protocol with every "rank" a context in THIS process on the current GPU (no torch.distributed).
 
     Used by the single-GPU tests to check that a sharded run is byte-identical to an unsharded one, and usable to walk a
@@ -249,7 +302,7 @@ def run_sharded_local(cores, buf, lookahead=1 << 18, header_probe=1 << 20):
     dev = torch.device("cuda", torch.cuda.current_device())
     arr = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
     base, n = arr.ctypes.data, arr.size
-    cuts = shard_cuts(arr, world)
+    cuts = shard_cuts_from_bai(bai, arr, world) if bai else shard_cuts(arr, world)
     info = dict(cuts=cuts, recount=0, halo_records=0)
     frames = []
     for r, core in enumerate(cores):

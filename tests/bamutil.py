@@ -93,3 +93,76 @@ def read_records(raw):
         recs.append((refid, pos, flag, name, cg, mpos, raw[p:p + 4 + bs]))
         p += 4 + bs
     return refs, recs
+
+
+def reg2bin(beg, end):
+    """SAM v1 §5.3."""
+    end -= 1
+    for shift, base in ((14, 4681), (17, 585), (20, 73), (23, 9), (26, 1)):
+        if beg >> shift == end >> shift:
+            return base + (beg >> shift)
+    return 0
+
+
+def write_bai(bam_path, bai_path=None):
+    """Indexes a coordinate-sorted BAM the way `samtools index` does (bins with merged chunks + 16 kb linear index).
+    Test infrastructure: walks the BGZF blocks with zlib on the host."""
+    data = open(bam_path, "rb").read()
+    blocks, raw, off = [], bytearray(), 0           # (compressed offset, inflated offset)
+    while off + 18 <= len(data):
+        bs = (data[off + 16] | data[off + 17] << 8) + 1
+        blocks.append((off, len(raw)))
+        raw += zlib.decompress(data[off + 18:off + bs - 8], -15)
+        off += bs
+    starts = [b[1] for b in blocks]
+
+    def voff(u):
+        import bisect
+        i = bisect.bisect_right(starts, u) - 1
+        while i + 1 < len(blocks) and blocks[i + 1][1] == u:   # a record starting exactly at a block end belongs to the next block
+            i += 1
+        return blocks[i][0] << 16 | (u - blocks[i][1])
+
+    l_text, = struct.unpack_from("<i", raw, 4)
+    p = 8 + l_text
+    n_ref, = struct.unpack_from("<i", raw, p)
+    p += 4
+    for _ in range(n_ref):
+        ln, = struct.unpack_from("<i", raw, p)
+        p += 4 + ln + 4
+    bins = [dict() for _ in range(n_ref)]
+    lin = [dict() for _ in range(n_ref)]
+    while p + 4 <= len(raw):
+        bsz, = struct.unpack_from("<i", raw, p)
+        refid, pos, l_name, _mq, _bin, n_cig, flag, l_seq = struct.unpack_from("<iiBBHHHi", raw, p + 4)
+        end = pos
+        for k in range(n_cig):
+            v, = struct.unpack_from("<I", raw, p + 36 + l_name + 4 * k)
+            if "MIDNSHP=X"[v & 15] in "MDN=X":
+                end += v >> 4
+        end = max(end, pos + 1)
+        if refid >= 0:
+            b, e = voff(p), voff(p + 4 + bsz)
+            ch = bins[refid].setdefault(reg2bin(pos, end), [])
+            if ch and ch[-1][1] >> 16 == b >> 16:
+                ch[-1][1] = e
+            else:
+                ch.append([b, e])
+            for w in range(pos >> 14, ((end - 1) >> 14) + 1):
+                lin[refid].setdefault(w, b)
+        p += 4 + bsz
+    out = b"BAI\1" + struct.pack("<i", n_ref)
+    for r in range(n_ref):
+        out += struct.pack("<i", len(bins[r]))
+        for b in sorted(bins[r]):
+            out += struct.pack("<Ii", b, len(bins[r][b])) + b"".join(struct.pack("<QQ", x, y) for x, y in bins[r][b])
+        n_intv = max(lin[r]) + 1 if lin[r] else 0
+        out += struct.pack("<i", n_intv)
+        last = 0
+        for w in range(n_intv):
+            last = lin[r].get(w, last)
+            out += struct.pack("<Q", last)
+    bai_path = bai_path or bam_path + ".bai"
+    with open(bai_path, "wb") as f:
+        f.write(out)
+    return bai_path

@@ -109,3 +109,29 @@ def test_two_rank_merge_protocol_gloo(built, tmp_path):
     assert ("stage", cuts0[1], c0[[isinstance(x, tuple) and x[0] == "stage" for x in c0].index(True)][2], True) in c0
     assert [x for x in c1 if isinstance(x, tuple) and x[0] == "stage"][0][3] is False
     assert c0[-1] == "finalize" and c1[-1] == "finalize" and "opt" not in [x[0] for x in c0 + c1 if isinstance(x, tuple)]
+
+
+def test_shard_cuts_from_a_bai_index(built, tmp_path):
+    """§8e: with a BAI the cut points come from the index (block offsets of its bins and linear index); they must be BGZF
+    block starts, ordered, balanced about as well as the scanned cuts, and an index of another file must be refused."""
+    import numpy as np
+    from bamutil import write_bai
+    from irfinder_b200 import synth
+    from irfinder_b200.distributed import ShardPlan, _is_block_start, read_bai_block_offsets, shard_cuts, shard_cuts_from_bai
+    meta = synth.generate(str(tmp_path / "w"), genome="tiny", introns=200, pairs=20000, readlen=100, seed=5, chunks=5, collated=False)
+    bai = write_bai(meta["sorted"])
+    buf = np.fromfile(meta["sorted"], dtype=np.uint8)
+    offs = read_bai_block_offsets(bai)
+    assert len(offs) > 20 and offs == sorted(set(offs)) and all(_is_block_start(buf, o)[0] for o in offs)
+    for world in (2, 3, 8):
+        cuts = shard_cuts_from_bai(bai, buf, world)
+        scanned = shard_cuts(buf, world)
+        assert cuts[0] == 0 and cuts[-1] == buf.size and cuts == sorted(cuts) and len(cuts) == world + 1
+        assert all(c == buf.size or _is_block_start(buf, c)[0] for c in cuts[1:-1])
+        gap = max(b - a for a, b in zip([0] + offs, offs + [buf.size]))           # the index is coarser than the block chain: one cut
+        assert all(abs(a - b) <= gap for a, b in zip(cuts, scanned)), (cuts, scanned)   # candidate per 16 kb window that has reads
+        plans = [ShardPlan.from_buffer(buf, r, world, bai=bai) for r in range(world)]
+        assert sum(p.n_own for p in plans) == buf.size
+    other = synth.generate(str(tmp_path / "w2"), genome="tiny", introns=200, pairs=9000, readlen=100, seed=6, chunks=3, collated=False)
+    with pytest.raises(ValueError):
+        shard_cuts_from_bai(write_bai(other["sorted"]), buf, 4)
