@@ -85,7 +85,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
-  DevBuf d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
+  DevBuf d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -292,7 +292,7 @@ struct irf_ctx {
       fetch(d_c_off, c_off, nbk * 8); fetch(d_u_off, u_off, nbk * 8); fetch(d_c_len, c_len, nbk * 4); fetch(d_u_len, u_len, nbk * 4); fetch(d_crc, crcs, nbk * 4); }
     if (pre_ev_copy.empty()) d_comp.ensure(src_total + 64);
     d_U.ensure(Uend + 64);
-    size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
+    size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb); d_mism.ensure(nb);
     sync();  // allocation changes above settle before anything is queued against the buffers
     resident = false; staged = true; staged_has_header = has_header != 0; engines_planned = false;
     if (copy_now) { if (src_total) IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); sync(); resident = true; h_src = nullptr; }
@@ -302,7 +302,7 @@ struct irf_ctx {
     for (size_t i = 0; i < nb; i++) { u_off[i] = (u64)i * CH; u_len[i] = (u32)std::min<size_t>(CH, n - i * CH); blks.push_back(Blk{0, 0, u_len[i], 0}); }
     nblk_own = (int)nb; Uend = n; upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute); d_U.ensure(n + 64);
     IRF_CUDA(cudaMemcpyAsync(d_U.p, src, n, cudaMemcpyHostToDevice, s_compute));
-    d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb);
+    d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb); d_mism.ensure(nb);
     sync(); staged = true; staged_has_header = true; resident = true;
   }
 
@@ -536,9 +536,16 @@ struct irf_ctx {
                      d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err};
         launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
         for (int rounds = 0;; rounds++) {
-          IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mask.as<uint8_t>() + b0, n_bad, s_compute);
+          IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mism.as<uint8_t>() + b0, d_mask.as<uint8_t>() + b0, n_bad, s_compute);
           u32 hb = 0; IRF_CUDA(cudaMemcpyAsync(&hb, n_bad, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
           if (!hb) break; if (rounds > nbk + 2) throw string("record framing did not converge"); frame_rounds++;
+          if (getenv("IRF_DEBUG_FRAMING") && (rounds < 3 || rounds % 100 == 0)) {
+            vector<uint8_t> hm(nbk); vector<u64> he(nbk), hx(nbk); IRF_CUDA(cudaMemcpy(hm.data(), d_mask.as<uint8_t>() + b0, nbk, cudaMemcpyDeviceToHost));
+            IRF_CUDA(cudaMemcpy(he.data(), d_entry.as<u64>() + b0, nbk * 8, cudaMemcpyDeviceToHost)); IRF_CUDA(cudaMemcpy(hx.data(), d_exit.as<u64>() + b0, nbk * 8, cudaMemcpyDeviceToHost));
+            size_t none = 0; for (int i = 0; i < nbk; i++) none += hx[i] == ~0ull;
+            fprintf(stderr, "[framing] chunk %zu (%d blocks from %zu): round %d repairs %u entries, %zu blocks without an exit;", c, nbk, b0, rounds, hb, none);
+            int shown = 0; for (int i = 0; i < nbk && shown < 4; i++) if (hm[i]) { fprintf(stderr, " block %d: entry now %llu (block starts at %llu), old exit of it %llu;", i, (unsigned long long)he[i], (unsigned long long)blks[b0 + i].isize, (unsigned long long)hx[i]); shown++; }
+            fprintf(stderr, "\n"); }
           launch_walk_count(fa, d_mask.as<uint8_t>() + b0, s_compute);
         }
         IRF_CUDA(cudaMemsetAsync(totals, 0, 16, s_compute)); launch_frame_totals(fa, totals, s_compute);
@@ -594,7 +601,7 @@ struct irf_ctx {
     launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
     u32* n_bad = d_small.as<u32>(); int rounds = 0;
     for (;;) {
-      IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mask.as<uint8_t>(), n_bad, s_compute);
+      IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mism.as<uint8_t>(), d_mask.as<uint8_t>(), n_bad, s_compute);
       u32 hb = 0; IRF_CUDA(cudaMemcpyAsync(&hb, n_bad, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
       if (!hb) break; if (++rounds > nb + 2) throw string("record framing did not converge");
       launch_walk_count(fa, d_mask.as<uint8_t>(), s_compute);
@@ -782,7 +789,7 @@ void irf_destroy(irf_ctx* c) {
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
-                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
+                   &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());

@@ -291,11 +291,25 @@ __global__ void walk_count_kernel(const uint8_t* __restrict__ U, const u64* __re
   u64 x; u32 nr, nc; int fe; walk_count_block(U, e, u_off[b] + u_len[b], Uend, x, nr, nc, fe);
   exit_off[b] = x; n_rec[b] = nr; n_cand[b] = nc; ferr[b] = (uint8_t)fe;
 }
-__global__ void frame_mark_kernel(int nblk, u64* __restrict__ entry, const u64* __restrict__ exit_off, uint8_t* __restrict__ mask, u32* __restrict__ n_bad) {
+// Repair step, in two kernels so that no thread reads an entry another thread is rewriting.  mism[b] = block b's entry
+// disagrees with its predecessor's exit.  A block is repaired (entry := predecessor's exit, re-walked) only when the
+// predecessor itself agrees with ITS predecessor: an exit computed from an entry that is about to change is garbage, and
+// copying it forward would overwrite the next block's (usually correct) guess -- one wrong guess then chases a wave of
+// garbage through every later block, one block per round (seen: 5500 rounds in a 50M-pair file).  With the rule, the first
+// disagreeing block is always repaired (everything before it is a proven chain), so the loop ends, and isolated wrong
+// guesses anywhere in the file are all repaired in the same round.
+__global__ void frame_mismatch_kernel(int nblk, const u64* __restrict__ entry, const u64* __restrict__ exit_off, uint8_t* __restrict__ mism) {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= nblk) return;
   uint8_t m = 0;
-  if (b >= 1) { u64 want = exit_off[b - 1]; if (want != ~0ull && entry[b] != want) { entry[b] = want; m = 1; atomicAdd(n_bad, 1u); } }
+  if (b >= 1) { u64 want = exit_off[b - 1]; m = want != ~0ull && entry[b] != want; }
+  mism[b] = m;
+}
+__global__ void frame_mark_kernel(int nblk, u64* __restrict__ entry, const u64* __restrict__ exit_off, const uint8_t* __restrict__ mism, uint8_t* __restrict__ mask, u32* __restrict__ n_bad) {
+  int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= nblk) return;
+  uint8_t m = 0;
+  if (b >= 1 && mism[b]) { atomicAdd(n_bad, 1u); if (!mism[b - 1]) { entry[b] = exit_off[b - 1]; m = 1; } }
   mask[b] = m;
 }
 __global__ void frame_totals_kernel(int nblk, const u32* __restrict__ n_rec, const u32* __restrict__ n_cand, const uint8_t* __restrict__ ferr, const u64* __restrict__ exit_off, int* __restrict__ err, u64* __restrict__ totals) {
@@ -315,9 +329,10 @@ void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s) 
   int grid = (a.nblk + 127) / 128;
   if (grid) { walk_count_kernel<<<grid, 128, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.entry, a.exit_off, a.n_rec, a.n_cand, mask, a.ferr); IRF_LAUNCHED(); }
 }
-void launch_frame_mark(const FrameArgs& a, uint8_t* mask, u32* n_bad, cudaStream_t s) {
+void launch_frame_mark(const FrameArgs& a, uint8_t* mism, uint8_t* mask, u32* n_bad, cudaStream_t s) {
   int grid = (a.nblk + 255) / 256;
-  if (grid) { frame_mark_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, mask, n_bad); IRF_LAUNCHED(); }
+  if (grid) { frame_mismatch_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, mism); IRF_LAUNCHED();
+    frame_mark_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, mism, mask, n_bad); IRF_LAUNCHED(); }
 }
 void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s) {
   int grid = (a.nblk + 255) / 256;

@@ -26,7 +26,7 @@ void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, i
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list = nullptr);
 void launch_frame_guess(const FrameArgs& a, cudaStream_t s);
 void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s);
-void launch_frame_mark(const FrameArgs& a, uint8_t* mask, u32* n_bad, cudaStream_t s);
+void launch_frame_mark(const FrameArgs& a, uint8_t* mism_scratch, uint8_t* mask, u32* n_bad, cudaStream_t s);   // both byte arrays hold a.nblk entries
 void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s);
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s);
 void launch_scan_counts(const u32* in, u64* out, int n, cudaStream_t s);
