@@ -533,7 +533,7 @@ struct irf_ctx {
         if (sm_used && c < ksm) IRF_CUDA(cudaStreamWaitEvent(s_compute, k1, 0));
         const u64 visible = inf_end[need];
         FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, nbk, visible, entry_prev, entry_valid, T.n_ref, T.ref_len,
-                     d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err};
+                     d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err, (int*)(d_small.as<uint8_t>() + 48)};
         launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
         for (int rounds = 0;; rounds++) {
           IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mism.as<uint8_t>() + b0, d_mask.as<uint8_t>() + b0, n_bad, s_compute);
@@ -596,7 +596,7 @@ struct irf_ctx {
     if (!bound) chr_map_update();
     int nb = (int)blks.size();
     FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), nb, Uend, rec0, staged_has_header ? 1 : 0, T.n_ref, T.ref_len,
-                 d_entry.as<u64>(), d_exit.as<u64>(), d_nrec.as<u32>(), d_ncand.as<u32>(), d_ferr.as<uint8_t>(), T.err};
+                 d_entry.as<u64>(), d_exit.as<u64>(), d_nrec.as<u32>(), d_ncand.as<u32>(), d_ferr.as<uint8_t>(), T.err, (int*)(d_small.as<uint8_t>() + 48)};
     if (!staged_has_header && entry0_override >= 0) { fa.rec0 = (u64)entry0_override; fa.rec0_valid = 1; entry0_override = -1; }
     launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
     u32* n_bad = d_small.as<u32>(); int rounds = 0;

@@ -252,11 +252,11 @@ __device__ bool plausible_record(const uint8_t* U, u64 off, u64 Uend, int n_ref,
 }
 
 __global__ void frame_guess_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk, u64 Uend, u64 rec0, int rec0_valid,
-                                   int n_ref, const int32_t* __restrict__ ref_len, u64* __restrict__ entry) {
+                                   int n_ref, const int32_t* __restrict__ ref_len, u64* __restrict__ entry, int* __restrict__ first) {
   int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (b >= nblk) return;
   u64 o = u_off[b], e = o + u_len[b];
-  if (rec0_valid && o <= rec0) { if (lane == 0) entry[b] = rec0; return; }
+  if (rec0_valid && o <= rec0) { if (lane == 0) { entry[b] = rec0; atomicMin(first, b); } return; }
   u64 found = ~0ull;
   for (u64 base = o; base < e; base += 32) {
     u64 c = base + lane, nx = 0, nx2 = 0;
@@ -265,7 +265,7 @@ __global__ void frame_guess_kernel(const uint8_t* __restrict__ U, const u64* __r
     u32 m = __ballot_sync(0xffffffffu, ok);
     if (m) { found = base + (u64)(__ffs(m) - 1); break; }
   }
-  if (lane == 0) entry[b] = found;
+  if (lane == 0) { entry[b] = found; if (found != ~0ull) atomicMin(first, b); }
 }
 
 // Walks the records that start inside block b; exit = first record start at or beyond the block end.
@@ -291,18 +291,18 @@ __global__ void walk_count_kernel(const uint8_t* __restrict__ U, const u64* __re
   u64 x; u32 nr, nc; int fe; walk_count_block(U, e, u_off[b] + u_len[b], Uend, x, nr, nc, fe);
   exit_off[b] = x; n_rec[b] = nr; n_cand[b] = nc; ferr[b] = (uint8_t)fe;
 }
-// Repair step, in two kernels so that no thread reads an entry another thread is rewriting.  mism[b] = block b's entry
-// disagrees with its predecessor's exit.  A block is repaired (entry := predecessor's exit, re-walked) only when the
-// predecessor itself agrees with ITS predecessor: an exit computed from an entry that is about to change is garbage, and
-// copying it forward would overwrite the next block's (usually correct) guess -- one wrong guess then chases a wave of
-// garbage through every later block, one block per round (seen: 5500 rounds in a 50M-pair file).  With the rule, the first
-// disagreeing block is always repaired (everything before it is a proven chain), so the loop ends, and isolated wrong
-// guesses anywhere in the file are all repaired in the same round.
-__global__ void frame_mismatch_kernel(int nblk, const u64* __restrict__ entry, const u64* __restrict__ exit_off, uint8_t* __restrict__ mism) {
+// Repair step, in two kernels so that no thread reads an entry another thread is rewriting.  Block b is "consistent" when
+// its entry equals its predecessor's exit (blocks up to the first one that has an entry at all start the chain and count
+// as consistent).  An inconsistent block is repaired (entry := predecessor's exit, re-walked) only when the predecessor is
+// consistent: an exit computed from an entry that is itself unconfirmed is garbage, and copying it forward overwrites the
+// next block's (usually correct) guess -- one wrong guess then chases a wave of garbage through every later block, one
+// block per round (seen: 5500 rounds in a 50M-pair file).  The first inconsistent block always has a consistent
+// predecessor, so every round makes progress, and isolated wrong guesses anywhere in the file are repaired in the same round.
+__global__ void frame_mismatch_kernel(int nblk, const u64* __restrict__ entry, const u64* __restrict__ exit_off, const int* __restrict__ first, uint8_t* __restrict__ mism) {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= nblk) return;
   uint8_t m = 0;
-  if (b >= 1) { u64 want = exit_off[b - 1]; m = want != ~0ull && entry[b] != want; }
+  if (b > *first) { u64 want = exit_off[b - 1]; m = want == ~0ull || entry[b] != want; }
   mism[b] = m;
 }
 __global__ void frame_mark_kernel(int nblk, u64* __restrict__ entry, const u64* __restrict__ exit_off, const uint8_t* __restrict__ mism, uint8_t* __restrict__ mask, u32* __restrict__ n_bad) {
@@ -323,7 +323,7 @@ __global__ void frame_totals_kernel(int nblk, const u32* __restrict__ n_rec, con
 
 void launch_frame_guess(const FrameArgs& a, cudaStream_t s) {
   long threads = (long)a.nblk * 32; int grid = (int)((threads + 255) / 256);
-  if (grid) { frame_guess_kernel<<<grid, 256, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.rec0, a.rec0_valid, a.n_ref, a.ref_len, a.entry); IRF_LAUNCHED(); }
+  if (grid) { IRF_CUDA(cudaMemsetAsync(a.first, 0x7f, sizeof(int), s)); frame_guess_kernel<<<grid, 256, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.rec0, a.rec0_valid, a.n_ref, a.ref_len, a.entry, a.first); IRF_LAUNCHED(); }
 }
 void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s) {
   int grid = (a.nblk + 127) / 128;
@@ -331,7 +331,7 @@ void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s) 
 }
 void launch_frame_mark(const FrameArgs& a, uint8_t* mism, uint8_t* mask, u32* n_bad, cudaStream_t s) {
   int grid = (a.nblk + 255) / 256;
-  if (grid) { frame_mismatch_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, mism); IRF_LAUNCHED();
+  if (grid) { frame_mismatch_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, a.first, mism); IRF_LAUNCHED();
     frame_mark_kernel<<<grid, 256, 0, s>>>(a.nblk, a.entry, a.exit_off, mism, mask, n_bad); IRF_LAUNCHED(); }
 }
 void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s) {

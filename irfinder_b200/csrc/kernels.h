@@ -15,6 +15,7 @@ struct FrameArgs {
   const uint8_t* U; const u64* u_off; const u32* u_len; int nblk; u64 Uend; u64 rec0; int rec0_valid;  // rec0: inflated offset of the first record when known exactly
   int n_ref; const int32_t* ref_len;
   u64* entry; u64* exit_off; u32* n_rec; u32* n_cand; uint8_t* ferr; int* err;  // ferr: per-block framing error of the latest walk
+  int* first = nullptr;   // device scalar: index of the first block that has an entry (set by launch_frame_guess, read by launch_frame_mark)
 };
 
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);

@@ -506,3 +506,39 @@ def test_header_only_and_many_contig_inputs(built, tiny, tmp_path):
         c = _gpu_run(meta, str(tmp_path / f"g1_{i}"), **opts)
         assert_same_outputs(str(tmp_path / "o1"), str(tmp_path / f"g1_{i}"))
         assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
+
+
+def test_decoy_record_at_a_block_start_is_repaired_in_one_round(built, tiny, tmp_path):
+    """Record framing guesses each BGZF block's first record from the byte layout.  Here the quality string of a long read
+    carries, exactly at a block start, bytes that look like two well-formed records whose chain leaves the block at a wrong
+    offset.  The guess for that block is therefore wrong; the repair must fix it from the predecessor's exit without
+    overwriting the (correct) guesses of the 300+ blocks that follow, i.e. in a couple of rounds, not one round per block."""
+    import struct
+    from bamutil import BGZF_EOF, bgzf, header, record
+    refs = [("chrA", 400000), ("chrB", 300000), ("chrEmpty", 50000)]
+    B = 2048
+    head = header(refs, True) + b"".join(record("p%04d" % i, 0, 1000 + i, "100M", 0) for i in range(40))
+    long_read = bytearray(record("decoy_carrier", 0, 5000, "6000M", 0))
+    qual0 = len(long_read) - 4 - 6000            # quality string = the 6000 bytes before the 4-byte tag
+    k = (len(head) + qual0 + B - 1) // B + 1     # a block start well inside the quality string
+    at = k * B - len(head)
+    assert qual0 < at and at + 200 < qual0 + 6000
+
+    def fake(block_size, name=b"abc\0"):
+        return struct.pack("<iiiBBHHHiiii", block_size, 0, 100, len(name), 30, 4680, 1, 0, 10, -1, -1, 0) + name + struct.pack("<I", 10 << 4)
+    f1, f2 = fake(60), fake(B + 777)
+    long_read[at:at + len(f1)] = f1
+    long_read[at + 64:at + 64 + len(f2)] = f2     # f1's chain: next record at +4+60
+    tail = b"".join(record("t%05d" % i, 0, 20000 + 3 * i, "60M500N60M" if i % 5 == 0 else "120M", 16 * (i & 1)) for i in range(3500))
+    raw = head + bytes(long_read) + tail
+    assert len(raw) // B - k > 300
+    bam = str(tmp_path / "decoy.bam")
+    with open(bam, "wb") as f:
+        f.write(bgzf(raw, B, 1) + BGZF_EOF)
+    meta = dict(tiny, sorted=bam, collated=bam)
+    ostd = run_oracle(built, meta, str(tmp_path / "o"))
+    for i, opts in enumerate([{}, dict(stream_pipeline=0), dict(stream_pipeline=0, de_percent=0, de_percent_stream=0)]):
+        c = _gpu_run(meta, str(tmp_path / f"g{i}"), **opts)
+        assert_same_outputs(str(tmp_path / "o"), str(tmp_path / f"g{i}"))
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
+        assert c.timing()["launches"] < 120, "framing repair ran one round per block"
