@@ -676,8 +676,11 @@ struct irf_ctx {
     IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_copy));
     u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0); mark("scan + leftovers");
     IRF_CUDA(cudaStreamSynchronize(s_copy));
-    u32 n_in = (u32)cov.BEDrecords.size(); int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), 148 * 4);
-    u32 bins = hmax >= 8192 ? hmax + 1 : 1; d_scratch.ensure((u64)grid * bins * 4);
+    // shared-memory histograms (the usual case): one short-lived CTA per intron, so the export kernels of the other stream
+    // get SM slots as CTAs retire; deep data needs a global scratch histogram per CTA, hence a fixed number of looping CTAs
+    u32 n_in = (u32)cov.BEDrecords.size(); u32 bins = hmax >= 8192 ? hmax + 1 : 1;
+    int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), bins == 1 ? (1u << 20) : 148 * 4);
+    d_scratch.ensure((u64)grid * bins * 4);
     launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy);
     pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy));
     // junctions -> host (JunctionCount map contents)
