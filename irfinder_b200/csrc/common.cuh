@@ -32,6 +32,7 @@ enum DevErr : int {
 
 // ---- counters (the reference prints these on stdout; SURVEY.md §5 "Metrics")
 enum Stat : int { ST_SINGLE = 0, ST_PAIRED, ST_SHORT, ST_INTERSECT, ST_LONG, ST_SKIPPED, ST_ERROR, ST_NUCLEOTIDES, ST_RECORDS, ST_COUNT };
+constexpr int ST_CAND = ST_COUNT, ST_SLOTS = ST_COUNT + 1;   // internal: pair-candidate records seen (orphans = candidates - 2 x pairs); not part of the public table
 
 struct Range { u32 begin, end; };
 
@@ -57,7 +58,7 @@ struct DevTables {
   u64* jc_keys; u32* jc_cnt; u32 jc_mask;
   u64* jl_keys; u32* jl_cnt; u32 jl_mask;   // left ends (key = concatenated coordinate)
   u64* jr_keys; u32* jr_cnt; u32 jr_mask;   // right ends
-  u64* stats;               // [ST_COUNT]
+  u64* stats;               // [ST_SLOTS]
   int* err;
   // optional fragment dump (tests): words appended at dump[atomicAdd(dump_cursor, n)]
   u32* dump; u64* dump_cursor; u64 dump_cap;

@@ -106,7 +106,7 @@ struct irf_ctx {
     device = dev; IRF_CUDA(cudaSetDevice(dev));
     { int lo_p = 0, hi_p = 0; IRF_CUDA(cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p));   // counting kernels take freed SM slots ahead of the long inflate launch on the side stream
       IRF_CUDA(cudaStreamCreateWithPriority(&s_compute, cudaStreamNonBlocking, hi_p)); IRF_CUDA(cudaStreamCreateWithPriority(&s_copy, cudaStreamNonBlocking, lo_p)); } IRF_CUDA(cudaStreamCreateWithFlags(&s_de, cudaStreamNonBlocking)); IRF_CUDA(cudaStreamCreateWithFlags(&s_chk, cudaStreamNonBlocking));
-    d_stats.ensure(ST_COUNT * 8); d_err.ensure(4); d_small.ensure(256);
+    d_stats.ensure(ST_SLOTS * 8); d_err.ensure(4); d_small.ensure(256);
   }
   void sync() { IRF_CUDA(cudaStreamSynchronize(s_compute)); }
 
@@ -202,7 +202,7 @@ struct irf_ctx {
     IRF_CUDA(cudaMemsetAsync(d_jc_keys.p, 0xff, (u64)jc_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jc_cnt.p, 0, (u64)jc_slots * 8, s));
     IRF_CUDA(cudaMemsetAsync(d_jl_keys.p, 0xff, (u64)jside_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jl_cnt.p, 0, (u64)jside_slots * 8, s));
     IRF_CUDA(cudaMemsetAsync(d_jr_keys.p, 0xff, (u64)jside_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jr_cnt.p, 0, (u64)jside_slots * 8, s));
-    IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_COUNT * 8, s)); IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
+    IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_SLOTS * 8, s)); IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
     if (dump_fragments) IRF_CUDA(cudaMemsetAsync(d_dump_cursor.p, 0, 8, s));
     launch_ht_insert_keys(T.jc_keys, T.jc_mask, d_annot_keys.as<u64>(), n_annot, T.err, s);
     counted = finalized = false; sharded = false; halo_leftover = 0; launches0 = launch_counter();
@@ -674,7 +674,7 @@ struct irf_ctx {
     u32* dmax = d_small.as<u32>() + 2; u32 hmax = 0;
     IRF_CUDA(cudaStreamWaitEvent(s_copy, ev_scan, 0)); IRF_CUDA(cudaMemsetAsync(dmax, 0, 4, s_copy)); launch_max_depth(T.diff, cov.P, dmax, s_copy);
     IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_copy));
-    u64 errors = sharded ? halo_leftover : count_leftovers(nullptr, 0); mark("scan + leftovers");
+    mark("scan");
     IRF_CUDA(cudaStreamSynchronize(s_copy));
     // shared-memory histograms (the usual case): one short-lived CTA per intron, so the export kernels of the other stream
     // get SM slots as CTAs retire; deep data needs a global scratch histogram per CTA, hence a fixed number of looping CTAs
@@ -702,14 +702,16 @@ struct irf_ctx {
       pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); IRF_CUDA(cudaStreamSynchronize(s_copy));
     }
     IRF_CUDA(cudaEventRecord(ev_side, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_side, 0)); cudaEventDestroy(ev_scan); cudaEventDestroy(ev_side);
-    mark("intron stats dir"); h_stats.assign(ST_COUNT, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
-    IRF_CUDA(cudaMemcpyAsync(h_stats.data(), d_stats.p, ST_COUNT * 8, cudaMemcpyDeviceToHost, s_compute));
+    mark("intron stats dir"); h_stats.assign(ST_SLOTS, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
+    IRF_CUDA(cudaMemcpyAsync(h_stats.data(), d_stats.p, ST_SLOTS * 8, cudaMemcpyDeviceToHost, s_compute));
     if (!h_sp.empty()) IRF_CUDA(cudaMemcpyAsync(h_sp.data(), d_sp_count.p, h_sp.size() * 4, cudaMemcpyDeviceToHost, s_compute));
     if (!h_roi.empty()) IRF_CUDA(cudaMemcpyAsync(h_roi.data(), d_roi_count.p, h_roi.size() * 4, cudaMemcpyDeviceToHost, s_compute));
     if (!h_chr.empty()) IRF_CUDA(cudaMemcpyAsync(h_chr.data(), d_chr_count.p, h_chr.size() * 4, cudaMemcpyDeviceToHost, s_compute));
     IRF_CUDA(cudaEventRecord(e1, s_compute)); sync();
     check_dev_err("finalize"); mark("tables d2h");
-    h_stats[ST_ERROR] += errors;
+    // orphans (pair candidates whose mate never came) = candidates - 2 x pairs; a sharded run counted them during the halo exchange
+    h_stats[ST_ERROR] += sharded ? halo_leftover : h_stats[ST_CAND] - 2 * h_stats[ST_PAIRED];
+    h_stats.resize(ST_COUNT);
     float ms; IRF_CUDA(cudaEventElapsedTime(&ms, e0, e1)); timing[4] = ms; cudaEventDestroy(e0); cudaEventDestroy(e1);
     h_dump.clear(); h_depth.clear();
     if (dump_fragments) { u64 n = 0; IRF_CUDA(cudaMemcpy(&n, d_dump_cursor.p, 8, cudaMemcpyDeviceToHost)); n = std::min(n, dump_cap); h_dump.resize(n); if (n) IRF_CUDA(cudaMemcpy(h_dump.data(), d_dump.p, n * 4, cudaMemcpyDeviceToHost)); }

@@ -572,14 +572,14 @@ __device__ __forceinline__ void warp_add_stat(u64* slot, u64 v) {
 __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask,
                                                             u64* __restrict__ pair_list, u64* __restrict__ single_list, u64* __restrict__ list_counts) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0;
+  bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0, cand = 0;
   if (i < nrec) {
     e = rec_off[i]; Core c; load_core(U, e, c);
     if ((c.flag & 0x4) || c.refID < 0) skipped = 1;                          // [C-6] only unmapped records are skipped
     else if (c.refID >= T.n_ref) atomicOr(T.err, DERR_REFID);
     else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) is_single = true;   // [C-7]
     else {
-      u64 mo; Core m;
+      u64 mo; Core m; cand = 1;
       if (pair_lookup_or_wait(T, ptab, pmask, U, e, c, mo, m)) {
         is_pair = true;
         bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);       // read 1 = left mate; level starts: the earlier record
@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const ui
   }
   u64 at = warp_append(&list_counts[0], is_pair); if (is_pair) { pair_list[2 * at] = o1; pair_list[2 * at + 1] = o2; }
   at = warp_append(&list_counts[1], is_single); if (is_single) single_list[at] = e;
-  warp_add_stat(&T.stats[ST_SKIPPED], skipped);
+  warp_add_stat(&T.stats[ST_SKIPPED], skipped); warp_add_stat(&T.stats[ST_CAND], cand);
   if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
 }
 __global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs) {
