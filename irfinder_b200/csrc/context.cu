@@ -7,11 +7,14 @@
 // point fails with IRF_ECUDA.
 #include <cuda.h>
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -267,7 +270,9 @@ struct irf_ctx {
     join_crc(); IRF_CUDA(cudaStreamSynchronize(s_copy)); drop_pre_copies();
     double t0 = now_ms();
     inflated_input = false;
-    if (!copy_now && stream_pipeline && has_header && n_own == n_total && n_total > 0 && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine()) {
+    feed_stop();
+    if (feed_fd >= 0 && !copy_now && has_header && n_own == n_total && n_total > 0 && feed_capable()) { d_comp.ensure(n_total + 64); feed_start(n_total); }
+    else if (!copy_now && stream_pipeline && has_header && n_own == n_total && n_total > 0 && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine()) {
       // end-to-end path: the bytes can start crossing PCIe before the host has even walked the BGZF block chain
       d_comp.ensure(n_total + 64);
       // Every chunk is queued now when the references are already bound to this header (any run after a context's first):
@@ -290,7 +295,7 @@ struct irf_ctx {
       Uend = u;
       auto fetch = [&](DevBuf& b, const void* src, size_t bytes) { b.ensure(bytes + 16); launch_host_fetch(b.p, h_tab.dev(src), bytes, s_compute); };
       fetch(d_c_off, c_off, nbk * 8); fetch(d_u_off, u_off, nbk * 8); fetch(d_c_len, c_len, nbk * 4); fetch(d_u_len, u_len, nbk * 4); fetch(d_crc, crcs, nbk * 4); }
-    if (pre_ev_copy.empty()) d_comp.ensure(src_total + 64);
+    if (pre_ev_copy.empty() && !feed_active) d_comp.ensure(src_total + 64);
     d_U.ensure(Uend + 64);
     size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb); d_mism.ensure(nb);
     sync();  // allocation changes above settle before anything is queued against the buffers
@@ -452,6 +457,59 @@ struct irf_ctx {
     if (!have_header || names != chr_names || lens != chr_lens || !bound) { chr_names = names; chr_lens = lens; have_header = true; chr_map_update(); }
   }
 
+  // ---- file input: a ring of page-locked buffers instead of a page-locked copy of the whole file ----------------------
+  // irf_run_bam maps the file (for the BGZF block scan, which touches two pages per block) and hands its descriptor to
+  // the feeder: a few threads pread() 16 MB pieces straight into free ring slots and queue each slot's host->device copy
+  // in file order; a chunk's event is recorded behind its last piece.  Page-locking 14 GB for one run cost ~4 s (and as
+  // long again to release); the ring is 128 MB, allocated once per context.
+  struct Piece { size_t lo, hi; int chunk; bool last; };
+  static constexpr int FEED_SLOTS = 8; static constexpr size_t FEED_SLOT_BYTES = 16u << 20;
+  int feed_fd = -1; int file_ring = 1;   // option "file_ring": 0 never, 1 files above 64 MB, 2 always
+  vector<Piece> feed_pieces; vector<cudaEvent_t> feed_ev_chunk; vector<char> feed_chunk_queued; cudaEvent_t feed_slot_ev[FEED_SLOTS] = {};
+  uint8_t* feed_ring = nullptr; std::mutex feed_mu; std::condition_variable feed_cv; size_t feed_next = 0, feed_queued_upto = 0; bool feed_abort = false, feed_active = false; string feed_error; vector<std::thread> feed_threads;
+  bool feed_capable() { return file_ring && stream_pipeline && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine(); }
+  void feed_worker() {
+    cudaSetDevice(device);
+    for (;;) {
+      size_t i; { std::lock_guard<std::mutex> g(feed_mu); if (feed_abort) return; i = feed_next++; }
+      if (i >= feed_pieces.size()) return;
+      const Piece pc = feed_pieces[i]; const int slot = (int)(i % FEED_SLOTS); uint8_t* buf = feed_ring + (size_t)slot * FEED_SLOT_BYTES;
+      { std::unique_lock<std::mutex> lk(feed_mu); feed_cv.wait(lk, [&] { return feed_abort || feed_queued_upto + FEED_SLOTS > i; }); if (feed_abort) return; }   // piece i - FEED_SLOTS has been queued
+      bool ok = true;
+      if (i >= (size_t)FEED_SLOTS) ok = cudaEventSynchronize(feed_slot_ev[slot]) == cudaSuccess;                                                                  // ... and its copy has left the slot
+      for (size_t off = pc.lo; ok && off < pc.hi;) { ssize_t k = pread(feed_fd, buf + (off - pc.lo), pc.hi - off, (off_t)off); if (k <= 0) ok = false; else off += (size_t)k; }
+      std::unique_lock<std::mutex> lk(feed_mu); feed_cv.wait(lk, [&] { return feed_abort || feed_queued_upto == i; }); if (feed_abort) return;
+      if (ok) ok = cudaMemcpyAsync(d_comp.as<uint8_t>() + pc.lo, buf, pc.hi - pc.lo, cudaMemcpyHostToDevice, s_copy) == cudaSuccess && cudaEventRecord(feed_slot_ev[slot], s_copy) == cudaSuccess;
+      if (ok && pc.last) ok = cudaEventRecord(feed_ev_chunk[pc.chunk], s_copy) == cudaSuccess;
+      if (!ok) { feed_error = "read error (file input ring)"; feed_abort = true; std::fill(feed_chunk_queued.begin(), feed_chunk_queued.end(), 1); lk.unlock(); feed_cv.notify_all(); return; }
+      if (pc.last) feed_chunk_queued[pc.chunk] = 1;
+      feed_queued_upto = i + 1; lk.unlock(); feed_cv.notify_all();
+    }
+  }
+  void feed_start(size_t total) {
+    feed_stop();
+    if (!feed_ring) { IRF_CUDA(cudaMallocHost((void**)&feed_ring, FEED_SLOTS * FEED_SLOT_BYTES)); for (int k = 0; k < FEED_SLOTS; k++) IRF_CUDA(cudaEventCreateWithFlags(&feed_slot_ev[k], cudaEventDisableTiming)); }
+    const size_t nch = std::max<size_t>((total + chunk_bytes - 1) / chunk_bytes, 1), sub = std::min(FEED_SLOT_BYTES, chunk_bytes);
+    feed_pieces.clear();
+    for (size_t c = 0; c < nch; c++) { size_t lo = c * chunk_bytes, hi = std::min(total, lo + chunk_bytes); if (hi <= lo) { feed_pieces.push_back(Piece{lo, lo, (int)c, true}); continue; }
+      for (size_t o = lo; o < hi; o += sub) feed_pieces.push_back(Piece{o, std::min(hi, o + sub), (int)c, o + sub >= hi}); }
+    feed_ev_chunk.resize(nch); for (auto& e : feed_ev_chunk) IRF_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    feed_chunk_queued.assign(nch, 0); feed_next = 0; feed_queued_upto = 0; feed_abort = false; feed_error.clear(); feed_active = true;
+    unsigned nt = std::min<unsigned>(4, std::max(1u, std::thread::hardware_concurrency()));
+    for (unsigned t = 0; t < nt; t++) feed_threads.emplace_back([this]() { feed_worker(); });
+  }
+  cudaEvent_t feed_wait_chunk(size_t c) {   // returns once every copy of chunk c has been queued on the copy stream
+    std::unique_lock<std::mutex> lk(feed_mu); feed_cv.wait(lk, [&] { return feed_abort || feed_chunk_queued[c]; });
+    if (!feed_error.empty()) throw feed_error;
+    return feed_ev_chunk[c];
+  }
+  void feed_stop() {
+    if (!feed_active) return;
+    { std::lock_guard<std::mutex> g(feed_mu); if (feed_queued_upto < feed_pieces.size()) feed_abort = true; } feed_cv.notify_all();
+    for (auto& t : feed_threads) t.join(); feed_threads.clear();
+    cudaStreamSynchronize(s_copy); for (auto e : feed_ev_chunk) cudaEventDestroy(e); feed_ev_chunk.clear(); feed_active = false;
+  }
+
   // S1-S3 as one pipeline for bytes that are still on the host (the end-to-end path).  The file is cut into chunks; every
   // chunk is copied, inflated by the decompression engine and CRC-checked on the side streams (all queued up front, chained
   // by events), and the compute stream frames, pairs and counts chunk k as soon as chunk k+1 has been inflated (a record that
@@ -479,9 +537,12 @@ struct irf_ctx {
     vector<cudaEvent_t> ev_copy(nch), ev_inf(nch); vector<u64> inf_end(nch);   // inflated offset where each chunk ends
     { u64 u = 0; size_t b = 0; for (size_t c = 0; c < nch; c++) { for (; b < chunk_blk_end[c]; b++) u += blks[b].isize; inf_end[c] = u; } }
     const size_t npre = std::min(pre_ev_copy.size(), nch);   // chunks whose copy stage() already queued (same chunking)
+    const bool fed = from_host && feed_active;                 // file input: the feeder threads queue the copies (same chunking)
+    if (fed && feed_ev_chunk.size() < nch) throw string("internal: file ring and pipeline disagree on the chunk count");
     for (size_t c = 0; c < nch; c++) {
       size_t lo = c * chunk_bytes, hi = std::min(src_total, lo + chunk_bytes);
       if (!from_host) { IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); }
+      else if (fed) { ev_copy[c] = feed_wait_chunk(c); }
       else if (c < npre) { ev_copy[c] = pre_ev_copy[c]; }
       else { if (hi > lo) IRF_CUDA(cudaMemcpyAsync(d_comp.as<uint8_t>() + lo, h_src + lo, hi - lo, cudaMemcpyHostToDevice, s_copy));
         IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ev_copy[c], s_copy)); }
@@ -504,7 +565,7 @@ struct irf_ctx {
       launch_inflate(a, inflate_variant, s_copy); IRF_CUDA(cudaEventRecord(k1, s_copy));
       if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)sm_list.size(), d_status.as<int>(), errp, s_copy, d_sm_list.as<u32>());
     }
-    auto cleanup = [&]() { for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); if (k1) cudaEventDestroy(k1); };
+    auto cleanup = [&]() { if (fed) feed_stop(); else for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); if (k1) cudaEventDestroy(k1); };
     try {
       // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
       if (sm_used && staged_has_header) IRF_CUDA(cudaEventSynchronize(k1));   // the header lies in the kernel's share
@@ -582,6 +643,7 @@ struct irf_ctx {
   // S2 + S3
   void count() {
     if (!staged) throw string("nothing staged");
+    if (feed_active && !can_pipeline()) { for (size_t c2 = 0; c2 < feed_chunk_queued.size(); c2++) feed_wait_chunk(c2); feed_stop(); resident = true; }   // everything is on the GPU: count stage by stage
     if (can_pipeline()) { count_streaming(true); return; }
     if (can_overlap()) { count_streaming(false); return; }
     if (!pre_ev_copy.empty()) { IRF_CUDA(cudaStreamSynchronize(s_copy)); if (pre_copied_bytes >= src_total) resident = true; drop_pre_copies(); }
@@ -801,6 +863,7 @@ void irf_destroy(irf_ctx* c) {
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->wm_host) cudaFreeHost(c->wm_host);
   c->h_tab.release(); c->h_lists.release();
+  c->feed_stop(); if (c->feed_ring) { cudaFreeHost(c->feed_ring); for (int k = 0; k < irf_ctx::FEED_SLOTS; k++) cudaEventDestroy(c->feed_slot_ev[k]); }
   if (c->s_compute) cudaStreamDestroy(c->s_compute); if (c->s_copy) cudaStreamDestroy(c->s_copy); if (c->s_de) cudaStreamDestroy(c->s_de); if (c->s_chk) cudaStreamDestroy(c->s_chk);
   delete c;
 }
@@ -819,6 +882,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements
+  else if (k == "file_ring") { if (v < 0 || v > 2) return IRF_EINVAL; c->file_ring = (int)v; }
   else if (k == "stream_pipeline") c->stream_pipeline = v != 0;
   else if (k == "resident_pipeline") { if (v < 0 || v > 2) return IRF_EINVAL; c->resident_pipeline = (int)v; }
   else if (k == "de_percent_overlap") { if (v < 1 || v > 100) return IRF_EINVAL; c->de_percent_overlap = (int)v; }
@@ -834,10 +898,21 @@ int irf_run_bam(irf_ctx* c, const char* path, const char* /*bai_path*/) {
   IRF_TRY(c, {
     int fd = open(path, O_RDONLY); if (fd < 0) throw string("cannot open ") + path;
     struct stat st; size_t hint = 0; if (fstat(fd, &st) == 0 && st.st_size > 0) hint = (size_t)st.st_size + 1;
+    const size_t size = hint ? hint - 1 : 0;
+    if (size && S_ISREG(st.st_mode) && c->feed_capable() && (c->file_ring == 2 || size > (64u << 20))) {
+      // regular file: mapped for the BGZF block scan, its bytes go to the GPU through the ring of page-locked buffers
+      void* map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (map == MAP_FAILED) { close(fd); throw string("cannot open ") + path + " (mmap failed)"; }
+      madvise(map, size, MADV_RANDOM);   // the scan reads two small pieces of every block; the bulk goes through pread
+      c->feed_fd = fd;
+      try { c->run_host_buffer(map, size); } catch (...) { c->feed_stop(); c->feed_fd = -1; c->h_src = nullptr; munmap(map, size); close(fd); throw; }
+      c->feed_stop(); c->feed_fd = -1; c->h_src = nullptr; munmap(map, size); close(fd);
+      return IRF_OK;
+    }
     size_t n = 0;
     try {
       if (hint > (64u << 20)) {   // regular file of known size: several threads pread disjoint slices into the pinned buffer
-        size_t size = hint - 1; uint8_t* dst = (uint8_t*)c->pinned_buf(size); unsigned nt = std::min(8u, std::max(1u, std::thread::hardware_concurrency())); vector<std::thread> th; vector<int> bad(nt, 0);
+        uint8_t* dst = (uint8_t*)c->pinned_buf(size); unsigned nt = std::min(8u, std::max(1u, std::thread::hardware_concurrency())); vector<std::thread> th; vector<int> bad(nt, 0);
         for (unsigned t = 0; t < nt; t++) th.emplace_back([&, t]() { size_t lo = size * t / nt, hi = size * (t + 1) / nt; while (lo < hi) { ssize_t k = pread(fd, dst + lo, std::min<size_t>(hi - lo, 64u << 20), (off_t)lo); if (k <= 0) { bad[t] = 1; break; } lo += (size_t)k; } });
         for (auto& x : th) x.join(); for (int b : bad) if (b) throw string("read error");
         n = size;

@@ -542,3 +542,33 @@ def test_decoy_record_at_a_block_start_is_repaired_in_one_round(built, tiny, tmp
         assert_same_outputs(str(tmp_path / "o"), str(tmp_path / f"g{i}"))
         assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
         assert c.timing()["launches"] < 120, "framing repair ran one round per block"
+
+
+@pytest.mark.parametrize("chunk_kb", [0, 64])
+def test_file_input_through_the_page_locked_ring(tiny, tmp_path, chunk_kb):
+    """irf_run_bam on a regular file: the file is mapped for the block scan and its bytes reach the GPU through a small ring of
+    page-locked buffers filled by pread threads (forced here for a small file with file_ring=2).  Same outputs; the ring
+    is reused from run to run; a file that fails validation while the feeder threads are running leaves the context usable."""
+    from irfinder_b200 import IRFError
+    opts = dict(file_ring=2)
+    if chunk_kb:
+        opts["stream_chunk_kb"] = chunk_kb
+    c = _core(**opts)
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    for i, bam in enumerate([tiny["sorted"], tiny["collated"], tiny["sorted"]]):
+        c.run_bam(bam)
+        out = str(tmp_path / f"g{i}")
+        c.write_outputs(out)
+        assert_same_outputs(tiny["oracle_out"], out)
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+    cut = str(tmp_path / "cut.bam")
+    data = open(tiny["sorted"], "rb").read()
+    open(cut, "wb").write(data[: len(data) // 2])
+    with pytest.raises(IRFError):
+        c.run_bam(cut)
+    c.run_bam(tiny["sorted"])
+    c.write_outputs(str(tmp_path / "again"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "again"))
+    c.reset(); c.count(); c.finalize()          # the bytes stay resident after a file run as after any other
+    c.write_outputs(str(tmp_path / "recount"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "recount"))
