@@ -343,7 +343,7 @@ def run_b200(a):
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes), "stage_ms": {k: round(v, 3) for k, v in e2e_stage.items()}},
             "gpu_launches": launches,
             "roofline": {"bound": "hbm", "kernel": "inflate_kernel: one persistent launch, %.0f %% of the inflate bytes; the hardware decompression engine inflates the other %.0f %% concurrently" % (sm_share * 100, 100 - sm_share * 100),
-                         "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic, "peak_source": peak_src,
+                         "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic, "traffic_source": "profiles/inflate_traffic.json: DRAM bytes per algorithmic byte of this kernel from one ncu --set full capture (12M-pair input) x this launch's algorithmic bytes", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(sm_bytes), "launches_per_step": inflate_launches / max(a.steps, 1), "avg_launch_ms": round(sm_ms, 3),
                          "both_engines": {"achieved": round(stage_achieved, 2), "frac": round(stage_achieved / peak, 5), "algorithmic_bytes_per_step": int(alg_bytes), "ms_until_all_inflated": round(avg_inflate_ms, 3)}},
             "cpu_baseline": cpu, "clocks": clocks}
