@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--inflate-variant", type=int, default=-1)
     ap.add_argument("--de-percent-overlap", type=int, default=0, help="share of the file's chunks given to the decompression engine by the overlapped resident pipeline (library default when 0)")
     ap.add_argument("--resident-pipeline", type=int, default=-1, help="0 = count resident bytes stage by stage, 1 = overlapped pipeline when the input is large enough (library default), 2 = always")
+    ap.add_argument("--numa-bind", type=int, default=0, help="1 = run this rank on the CPUs of its GPU's NUMA node (so its page-locked buffer is node-local); off by default, not yet measured")
     ap.add_argument("--de-percent", type=int, default=-1, help="share of BGZF blocks given to the hardware decompression engine (library default when < 0)")
     return ap.parse_args()
 
@@ -180,6 +181,8 @@ def run_b200(a):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if a.numa_bind:
+        numa_bind(local)
     total_pairs = a.pairs * world
     base = a.workdir
     if world > 1 and os.path.isdir("/dev/shm"):   # N shards are generated at once: keep them off a possibly small disk
@@ -350,6 +353,27 @@ def run_b200(a):
     emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
+
+
+def numa_bind(local):
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off (first-touch then places the page-locked buffer there)."""
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local)
+        bus = "%04x:%02x:%02x.0" % (getattr(p, "pci_domain_id", 0), p.pci_bus_id, p.pci_device_id)
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node < 0:
+            return
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            print(f"[bench] rank on GPU {local} ({bus}) bound to NUMA node {node}: {len(cpus)} CPUs", file=sys.stderr)
+    except Exception as e:   # topology files missing in a container, attribute names differ between torch versions: run unbound
+        print(f"[bench] --numa-bind ignored: {e}", file=sys.stderr)
 
 
 _RESULT_FD = None
