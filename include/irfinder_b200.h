@@ -48,7 +48,7 @@ int irf_create(irf_ctx** out, const int* device_ids, int n_devices);
 void irf_destroy(irf_ctx* ctx);
 const char* irf_last_error(irf_ctx* ctx);
 
-/* Options (strings): "trim_center" (default 40), "dump_fragments" (0/1), "inflate_variant" (0-6),
+/* Options (strings): "trim_center" (default 40), "dump_fragments" (0/1), "inflate_variant" (0-11: A/B variants of the SM inflate kernel, 0 = default),
  * "de_percent" (default 70) / "de_percent_stream" (default 100): share of the BGZF blocks inflated by the Blackwell hardware
  * decompression engine when the bytes are resident / streamed from the host; the rest go to the SM kernel; 0 = SM kernel only.
  * "resident_pipeline" (default 1): large resident inputs are counted by the overlapped chunk pipeline, in which the engine takes the

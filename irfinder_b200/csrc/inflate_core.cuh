@@ -19,6 +19,7 @@
 // zlib; the shipped library only ever instantiates it inside kernels.
 #pragma once
 #include <stdint.h>
+#include <type_traits>
 
 #ifdef __CUDACC__
 #define IRF_HD __host__ __device__ __forceinline__
@@ -43,12 +44,12 @@ enum InflateStatus : int {
 // Lane-interleaved table of 16-bit entries living in shared memory (LANES = 32) or a plain array (LANES = 1):
 // entry idx of lane l sits at base[idx * LANES + l].  Two neighbouring lanes share a 4-byte bank, so a warp's 32 random
 // look-ups cost at most two wavefronts, and the address is one multiply-add.
-template <int LANES>
+template <int LANES, class E = uint16_t>
 struct LaneTable {
-  uint16_t* base;  // start of the warp's table region, already offset by the lane
-  IRF_HD void bind(uint16_t* region, int lane) { base = region + lane; }
-  IRF_HD uint16_t get(uint32_t idx) const { return base[idx * LANES]; }
-  IRF_HD void set(uint32_t idx, uint16_t v) const { base[idx * LANES] = v; }
+  E* base;  // start of the warp's table region, already offset by the lane
+  IRF_HD void bind(E* region, int lane) { base = region + lane; }
+  IRF_HD E get(uint32_t idx) const { return base[idx * LANES]; }
+  IRF_HD void set(uint32_t idx, E v) const { base[idx * LANES] = v; }
 };
 
 struct BitReader {
@@ -143,9 +144,17 @@ struct OutCursor {
 // aux[l] (l = 1..15) = upper bound of the length-l codes, left-justified to 15 bits; aux[16 + l] = index of the
 // first length-l symbol in `symbol` minus the first length-l code.  `symbol` (ordered by length, value) stays in
 // per-lane local memory: it is touched once per long code.
-template <int LANES, int BITS, int MAXSYM>
+// E = uint16_t: LUT entry = sym << 4 | len, 0 => long code or invalid.  E = uint8_t (alphabets of at most 31 symbols and
+// BITS <= 8: the distance and code-length codes): entry = sym << 3 | (len - 1), 0xFF => long code or invalid; halves the
+// table's shared memory.
+template <int LANES, int BITS, int MAXSYM, class E = uint16_t>
 struct Huff {
-  LaneTable<LANES> lut;          // entry = sym << 4 | len (len 1..BITS); 0 => long code or invalid
+  static_assert(sizeof(E) == 2 || (MAXSYM <= 32 && BITS <= 7), "byte entries hold 5 symbol bits and 3 length bits; 0xFF is reserved");
+  static IRF_HD E enc(int sym, int len) { return sizeof(E) == 2 ? (E)(sym << 4 | len) : (E)(sym << 3 | (len - 1)); }
+  static IRF_HD E none() { return sizeof(E) == 2 ? (E)0 : (E)0xFF; }
+  static IRF_HD int len_of(E e) { return sizeof(E) == 2 ? (int)(e & 15) : (e == (E)0xFF ? 0 : (int)(e & 7) + 1); }
+  static IRF_HD int sym_of(E e) { return sizeof(E) == 2 ? (int)(e >> 4) : (int)(e >> 3); }
+  LaneTable<LANES, E> lut;       // 2^BITS entries per lane
   LaneTable<LANES> aux;          // 32 entries per lane
   uint16_t* symbol;              // MAXSYM entries in the lane's local memory (kept outside this struct so its scalars stay in registers)
 
@@ -155,7 +164,7 @@ struct Huff {
     uint16_t count[16];
     for (int i = 0; i < 16; i++) count[i] = 0;
     for (int i = 0; i < n; i++) count[lens[i]]++;
-    for (uint32_t i = 0; i < (1u << BITS); i++) lut.set(i, 0);
+    for (uint32_t i = 0; i < (1u << BITS); i++) lut.set(i, none());
     for (int i = 0; i < 32; i++) aux.set(i, 0);
     if (count[0] == n) return true;  // no codes: any use is an error later
     int left = 1;
@@ -175,7 +184,7 @@ struct Huff {
 #else
         uint32_t rev = 0; for (int b = 0; b < l; b++) rev |= ((code >> b) & 1u) << (l - 1 - b);
 #endif
-        uint16_t e = (uint16_t)(s << 4 | l);
+        E e = enc(s, l);
         for (uint32_t i = rev; i < (1u << BITS); i += (1u << l)) lut.set(i, e);
       }
     }
@@ -206,9 +215,9 @@ struct Huff {
 #endif
   }
   IRF_HD int decode(BitReader& br) const {
-    uint16_t e = lut.get(br.peek(BITS));
-    int l = e & 15;
-    if (l) { br.drop(l); return e >> 4; }
+    E e = lut.get(br.peek(BITS));
+    int l = len_of(e);
+    if (l) { br.drop(l); return sym_of(e); }
     return slow15(br, head15(br));
   }
 };
@@ -220,11 +229,14 @@ struct Huff {
 // (Huffman table builds) are a third, rarer state.
 enum LaneState : int { LS_HEADER = 0, LS_SYMBOL = 1, LS_COPY = 2, LS_FINISH = 3, LS_DONE = 4, LS_SLOWLIT = 5, LS_SLOWDIST = 6 };
 
-template <int LANES, int LIT_BITS, int DIST_BITS, int RING_BITS = 0, int PREZERO = 0>
+// DIST8: the distance LUT (and the code-length LUT that borrows its storage) uses byte entries (see Huff).
+template <int LANES, int LIT_BITS, int DIST_BITS, int RING_BITS = 0, int PREZERO = 0, int DIST8 = 0>
 struct InflateLane {
+  using DistEntry = typename std::conditional<DIST8 != 0, uint8_t, uint16_t>::type;
+  static constexpr size_t DIST_LUT_U16 = DIST8 ? (size_t)(1u << DIST_BITS) * LANES / 2 + ((size_t)(1u << DIST_BITS) * LANES & 1) : (size_t)(1u << DIST_BITS) * LANES;   // the distance LUT's size in 16-bit units
   static constexpr uint32_t NEAR = RING_BITS ? (1u << RING_BITS) - 8u : 0u;   // matches up to this distance are copied inside the ring
   BitReader br; OutCursor<LANES, RING_BITS> oc; uint32_t tick;
-  Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32> hd;
+  Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32, DistEntry> hd;
   int state, status, bfinal; uint32_t copy_len, copy_dist, isize;
   uint32_t pend_n; uint32_t pend[8];  // bytes of a match chunk loaded in the previous step, one register each so nothing has to
                                       // wait for a load just to pack it (untouched until stored in this step)
@@ -234,9 +246,9 @@ struct InflateLane {
   IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize_, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store, uint8_t* ring_region = nullptr) {
     hl.symbol = sym_store; hd.symbol = sym_store + 288; tick = 0;
     br.init(cdata, clen); oc.init(out, isize_, ring_region, lane); isize = isize_; if (PREZERO) oc.prezero(256);
-    hl.lut.bind(lit_lut_base, lane); hd.lut.bind(dist_lut_base, lane);
+    hl.lut.bind(lit_lut_base, lane); hd.lut.bind((DistEntry*)dist_lut_base, lane);
     // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][lit aux (32)][dist aux (32)], all lane-interleaved
-    hd.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES, lane); hl.aux.bind(dist_lut_base + (size_t)((1u << DIST_BITS) + 32) * LANES, lane);
+    hd.aux.bind(dist_lut_base + DIST_LUT_U16, lane); hl.aux.bind(dist_lut_base + DIST_LUT_U16 + (size_t)32 * LANES, lane);
     state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = copy_dist = 0; pend_n = 0; slow_sym = 0;
   }
   IRF_HD void idle() { state = LS_DONE; status = INF_OK; pend_n = 0; }
@@ -271,7 +283,7 @@ struct InflateLane {
       for (int i = 0; i < 19; i++) lens[i] = 0;
       for (int i = 0; i < hclen; i++) { br.refill(); lens[order[i]] = (uint8_t)br.take(3); }
       // the code-length code (<= 7 bits) borrows the distance LUT region
-      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.aux.base = hd.aux.base;
+      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19, DistEntry> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.aux.base = hd.aux.base;
       if (!hc.build(lens, 19)) return fail(INF_ERR_CODELEN);
       int idx = 0;
       while (idx < hlit + hdist) {
@@ -311,8 +323,8 @@ struct InflateLane {
     else { int xb = (sym - 261) >> 2; len = ((4u + ((uint32_t)(sym - 261) & 3u)) << xb) + 3u + br.take(xb); }
     copy_len = len;
     br.refill();
-    uint16_t e = hd.lut.get(br.peek(DIST_BITS)); int l = e & 15;
-    if (l) { br.drop(l); return handle_dist(e >> 4); }
+    DistEntry e = hd.lut.get(br.peek(DIST_BITS)); int l = hd.len_of(e);
+    if (l) { br.drop(l); return handle_dist(hd.sym_of(e)); }
     int idx = hd.slow_index(br, hd.head15(br));
     if (idx < 0) return fail(INF_ERR_SYMBOL);
     slow_sym = hd.symbol[idx]; state = LS_SLOWDIST;   // local-memory load: consumed in the next step
@@ -397,10 +409,10 @@ struct InflateLane {
 
 // Decodes one raw DEFLATE stream of `clen` bytes at `cdata` into exactly `isize` bytes at `out` (scalar driver,
 // used by the host emulation in tests/emu).  Both buffers need 8 readable bytes of slack after their ends.
-template <int LANES, int LIT_BITS, int DIST_BITS, int RING_BITS = 0, int PREZERO = 0>
+template <int LANES, int LIT_BITS, int DIST_BITS, int RING_BITS = 0, int PREZERO = 0, int DIST8 = 0>
 IRF_HD int inflate_block(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize,
                          uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint8_t* ring_region = nullptr) {
-  InflateLane<LANES, LIT_BITS, DIST_BITS, RING_BITS, PREZERO> L; uint16_t sym_store[320];
+  InflateLane<LANES, LIT_BITS, DIST_BITS, RING_BITS, PREZERO, DIST8> L; uint16_t sym_store[320];
   L.start(cdata, clen, out, isize, lit_lut_base, dist_lut_base, lane, sym_store, ring_region);
   while (!L.done()) L.step();
   return L.status;

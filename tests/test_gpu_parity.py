@@ -572,3 +572,13 @@ def test_file_input_through_the_page_locked_ring(tiny, tmp_path, chunk_kb):
     c.reset(); c.count(); c.finalize()          # the bytes stay resident after a file run as after any other
     c.write_outputs(str(tmp_path / "recount"))
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "recount"))
+
+
+@pytest.mark.parametrize("variant", [10, 11, 7, 2])
+def test_inflate_kernel_variants_agree(tiny, tmp_path, variant):
+    """The A/B variants of the SM inflate kernel (pre-written sectors, wider LUTs, byte-entry distance LUT with five or six
+    CTAs per SM; the shared-memory output-ring variants are disabled, see launch_inflate) must produce the same bytes as the default: outputs equal the oracle's with the
+    decompression engine switched off, so every block goes through the variant under test, and every CRC-32 is checked."""
+    c = _gpu_run(tiny, str(tmp_path / "g"), inflate_variant=variant, de_percent=0, de_percent_stream=0)
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
+    assert c.timing()["inflate_launches"] >= 1 and c.timing()["sm_inflate_share"] == 1.0
