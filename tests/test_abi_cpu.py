@@ -58,3 +58,18 @@ def test_library_links_no_zlib(built):
     """Inflate is a device kernel; the shipped library must not pull in zlib."""
     out = subprocess.run(["ldd", built["lib"]], stdout=subprocess.PIPE, text=True).stdout
     assert "libz." not in out
+
+
+def test_cli_reports_usage_and_missing_gpu(built):
+    """The `irfinder` drop-in prints the reference's usage line for a wrong argument count and, on a box without a CUDA
+    device, fails with a clear message instead of falling back to anything."""
+    import subprocess
+    exe = os.path.join(ROOT, "bin", "irfinder")
+    if not os.path.exists(exe):
+        pytest.skip("CLI not built")
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    assert r.returncode == 1 and "Usage: irfinder <outputDirectory>" in r.stderr
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe, "/tmp", "a", "b", "c", "NULL", "x.bam"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        assert r.returncode == 2 and "cannot initialise CUDA device" in r.stderr and r.stdout == ""

@@ -96,3 +96,48 @@ def test_oracle_rejects_truncated_stream(built, tmp_path):
     os.makedirs(str(tmp_path / "o"))
     r = subprocess.run([built["oracle"], str(tmp_path / "o"), p["cover"], p["sj"], p["rc"], p["roi"], rp], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     assert r.returncode != 0
+
+
+def _int_columns(path, key_cols, val_cols):
+    rows = {}
+    with open(path) as f:
+        next(f)
+        for line in f:
+            c = line.rstrip("\n").split("\t")
+            rows[tuple(c[i] for i in key_cols)] = [int(c[i]) for i in val_cols]
+    return rows
+
+
+def test_integer_tables_are_additive_over_fragments(built, tmp_path):
+    """Linearity: every integer table is a sum over fragments, so splitting the templates of a BAM into two files must give
+    tables that add up to the whole file's (junction, span-point, chromosome and ROI counts, and the read counters)."""
+    from irfinder_b200 import synth
+    meta = synth.generate(str(tmp_path / "w"), genome="tiny", introns=150, pairs=5000, readlen=100, seed=24, chunks=2)
+    refs, recs = read_records(inflate_file(meta["collated"]))
+    groups, i = [], 0
+    while i < len(recs):
+        if i + 1 < len(recs) and recs[i][3] == recs[i + 1][3]:
+            groups.append(recs[i:i + 2]); i += 2
+        else:
+            groups.append(recs[i:i + 1]); i += 1
+    rnd = random.Random(9)
+    parts = ([], [])
+    for g in groups:
+        parts[rnd.randrange(2)].extend(r[6] for r in g)
+    outs, stats = [], []
+    for k, rs in enumerate(parts):
+        bam = str(tmp_path / f"part{k}.bam")
+        write_bam(bam, refs, rs, level=1)
+        stats.append(_stats(run_oracle(built, meta, str(tmp_path / f"o{k}"), bam=bam)))
+        outs.append(str(tmp_path / f"o{k}"))
+    whole = _stats(run_oracle(built, meta, str(tmp_path / "all")))
+    for key in ("Total reads processed", "Total nucleotides", "Total singles processed", "Total pairs processed", "Short pairs", "Intersect pairs", "Long pairs", "Skipped reads", "Error reads"):
+        assert int(whole[key]) == int(stats[0][key]) + int(stats[1][key]), key
+    for name, keys, vals in (("IRFinder-JuncCount.txt", (0, 1, 2), (4, 5, 6)), ("IRFinder-SpansPoint.txt", (0, 1), (2, 3, 4)),
+                             ("IRFinder-ChrCoverage.txt", (0,), (1, 2, 3)), ("IRFinder-ROI.txt", (0,), (1, 2, 3))):
+        a, b, w = (_int_columns(os.path.join(d, name), keys, vals) for d in (outs[0], outs[1], str(tmp_path / "all")))
+        assert set(w) == set(a) | set(b), name          # a novel junction appears in the whole iff it appears in a part
+        for k, v in w.items():
+            va, vb = a.get(k, [0] * len(v)), b.get(k, [0] * len(v))
+            assert v == [x + y for x, y in zip(va, vb)], (name, k)
+    assert int(whole["Total pairs processed"]) > 1000
