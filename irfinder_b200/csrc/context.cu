@@ -902,12 +902,13 @@ int irf_run_bam(irf_ctx* c, const char* path, const char* /*bai_path*/) {
     if (size && S_ISREG(st.st_mode) && c->feed_capable() && (c->file_ring == 2 || size > (64u << 20))) {
       // regular file: mapped for the BGZF block scan, its bytes go to the GPU through the ring of page-locked buffers
       void* map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
-      if (map == MAP_FAILED) { close(fd); throw string("cannot open ") + path + " (mmap failed)"; }
-      madvise(map, size, MADV_RANDOM);   // the scan reads two small pieces of every block; the bulk goes through pread
-      c->feed_fd = fd;
-      try { c->run_host_buffer(map, size); } catch (...) { c->feed_stop(); c->feed_fd = -1; c->h_src = nullptr; munmap(map, size); close(fd); throw; }
-      c->feed_stop(); c->feed_fd = -1; c->h_src = nullptr; munmap(map, size); close(fd);
-      return IRF_OK;
+      if (map != MAP_FAILED) {   // (a file system that cannot map files takes the page-locked copy below)
+        madvise(map, size, MADV_RANDOM);   // the scan reads two small pieces of every block; the bulk goes through pread
+        c->feed_fd = fd;
+        try { c->run_host_buffer(map, size); } catch (...) { c->feed_stop(); c->feed_fd = -1; c->h_src = nullptr; munmap(map, size); close(fd); throw; }
+        c->feed_stop(); c->feed_fd = -1; c->h_src = nullptr; munmap(map, size); close(fd);
+        return IRF_OK;
+      }
     }
     size_t n = 0;
     try {
