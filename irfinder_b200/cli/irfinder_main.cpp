@@ -2,7 +2,7 @@
 //   irfinder <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|/dev/stdin|->
 // Same six positional arguments, same output files, counters and directionality on stdout, non-zero exit on error.
 // Extras go in the environment so the reference invocation works unchanged:
-//   IRF_DEVICE (GPU ordinal, default 0), IRF_TRIM_CENTER, IRF_STDIN_INFLATED=1 (stdin carries inflated BAM
+//   IRF_DEVICE (GPU ordinal, default 0), IRF_TRIM_CENTER, IRF_SAFE_INFLATE=1 (no hardware decompression engine), IRF_STDIN_INFLATED=1 (stdin carries inflated BAM
 //   bytes, as the reference's `gzip -cd |` pipe does; default: auto-detect from the gzip magic).
 #include <cstdio>
 #include <cstdlib>
@@ -17,6 +17,7 @@ int main(int argc, char** argv) {
   irf_ctx* ctx = nullptr;
   if (irf_create(&ctx, &dev, 1) != IRF_OK) { fprintf(stderr, "irfinder: cannot initialise CUDA device %d\n", dev); return 2; }
   if (const char* t = getenv("IRF_TRIM_CENTER")) irf_set_option(ctx, "trim_center", t);
+  if (const char* t = getenv("IRF_SAFE_INFLATE")) irf_set_option(ctx, "safe_inflate", t);   // untrusted input: SM inflate kernel only (recoverable errors that name the problem)
   int rc = irf_load_ref(ctx, argv[2], argv[3], argv[4], argv[5]);
   if (rc == IRF_OK) {
     bool is_stdin = !strcmp(argv[6], "-") || !strcmp(argv[6], "/dev/stdin");

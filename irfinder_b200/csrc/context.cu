@@ -193,11 +193,15 @@ struct irf_ctx {
     T.stats = d_stats.as<u64>(); T.err = d_err.as<int>();
     T.dump = dump_fragments ? d_dump.as<u32>() : nullptr; T.dump_cursor = dump_fragments ? d_dump_cursor.as<u64>() : nullptr; T.dump_cap = dump_cap;
     bound = true; sync();
-    reset();
+    reset(true);   // in the middle of a count: the inflate / CRC checks of this very run may already have raised the error flag
   }
 
-  void reset() {
-    join_crc();
+  // keep_err: zero the tables but leave the device error flag alone.  chr_map_update() runs inside count() after the first
+  // bytes have been inflated, while the CRC-32 and length checks of this run are queued or running on the side streams; clearing
+  // the flag there would lose a mismatch they report (the flag is zeroed by the API-level irf_reset / at the start of a count on
+  // an unbound context instead).
+  void reset(bool keep_err = false) {
+    if (!keep_err) join_crc();
     if (!bound) { counted = finalized = false; return; }
     cudaStream_t s = s_compute;
     IRF_CUDA(cudaMemsetAsync(d_sp_count.p, 0, sp.pos.size() * 8, s)); IRF_CUDA(cudaMemsetAsync(d_roi_count.p, 0, roi.rois.size() * 8, s));
@@ -205,7 +209,7 @@ struct irf_ctx {
     IRF_CUDA(cudaMemsetAsync(d_jc_keys.p, 0xff, (u64)jc_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jc_cnt.p, 0, (u64)jc_slots * 8, s));
     IRF_CUDA(cudaMemsetAsync(d_jl_keys.p, 0xff, (u64)jside_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jl_cnt.p, 0, (u64)jside_slots * 8, s));
     IRF_CUDA(cudaMemsetAsync(d_jr_keys.p, 0xff, (u64)jside_slots * 8, s)); IRF_CUDA(cudaMemsetAsync(d_jr_cnt.p, 0, (u64)jside_slots * 8, s));
-    IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_SLOTS * 8, s)); IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
+    IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_SLOTS * 8, s)); if (!keep_err) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
     if (dump_fragments) IRF_CUDA(cudaMemsetAsync(d_dump_cursor.p, 0, 8, s));
     launch_ht_insert_keys(T.jc_keys, T.jc_mask, d_annot_keys.as<u64>(), n_annot, T.err, s);
     counted = finalized = false; sharded = false; halo_leftover = 0; launches0 = launch_counter();
@@ -218,7 +222,9 @@ struct irf_ctx {
     const uint8_t* h = p + off;
     if (h[0] != 31 || h[1] != 139 || h[2] != 8 || !(h[3] & 4)) { if (why) *why = string("not a BGZF block at offset ") + std::to_string(off); return false; }
     u32 xlen = h[10] | (u32)h[11] << 8; if (off + 12 + xlen > n_total) { if (why) *why = "truncated BGZF extra field"; return false; }
-    int bsize = -1; for (u32 x = 0; x + 4 <= xlen;) { const uint8_t* sf = h + 12 + x; u32 slen = sf[2] | (u32)sf[3] << 8; if (sf[0] == 'B' && sf[1] == 'C' && slen == 2) { bsize = sf[4] | (int)sf[5] << 8; break; } x += 4 + slen; }
+    int bsize = -1; for (u32 x = 0; x + 4 <= xlen;) { const uint8_t* sf = h + 12 + x; u32 slen = sf[2] | (u32)sf[3] << 8;
+      if (x + 4 + slen > xlen) { if (why) *why = string("BGZF extra field with an inconsistent subfield at offset ") + std::to_string(off); return false; }   // the payload must lie inside the extra field
+      if (sf[0] == 'B' && sf[1] == 'C' && slen == 2) { bsize = sf[4] | (int)sf[5] << 8; break; } x += 4 + slen; }
     if (bsize < 0) { if (why) *why = string("BGZF block without BC subfield at offset ") + std::to_string(off); return false; }
     total = (size_t)bsize + 1; if (total < 12 + xlen + 8) { if (why) *why = "bad BGZF BSIZE"; return false; }
     if (off + total > n_total) { if (why) *why = "truncated BGZF block (file cut short)"; return false; }
@@ -822,6 +828,13 @@ struct irf_ctx {
     count(); t3 = now_ms(); finalize();
     if (dbg) fprintf(stderr, "[run] stage %.1f ms, reset %.1f ms, count %.1f ms, finalize %.1f ms\n", t1 - t0, t2 - t1, t3 - t2, now_ms() - t3);
   }
+  // A CUDA failure while blocks were with the hardware decompression engine is, in practice, malformed DEFLATE data: the engine
+  // reports it as a device-side fault that leaves this process's CUDA context unusable (every later call fails too).
+  string cuda_hint() const {
+    if (de_list.empty()) return "";
+    return " [blocks were being inflated by the hardware decompression engine, which reports malformed DEFLATE data as a CUDA fault: the input is probably corrupt;"
+           " this process's CUDA context is lost; rerun with option safe_inflate=1 (IRF_SAFE_INFLATE=1 for the irfinder binary) to have the SM kernel name the damaged block]";
+  }
   void* pinned_buf(size_t n) { if (n > pinned_cap) { if (pinned) cudaFreeHost(pinned); pinned = nullptr; IRF_CUDA(cudaMallocHost(&pinned, n + 64)); pinned_cap = n; } return pinned; }
   size_t read_fd_all(int fd, size_t hint) {
     size_t cap = std::max<size_t>(hint, 1 << 20), n = 0; vector<uint8_t> tmp; uint8_t* dst = (uint8_t*)pinned_buf(cap);
@@ -834,7 +847,7 @@ struct irf_ctx {
 };
 
 // ------------------------------------------------------------------------------------------------ C ABI
-#define IRF_TRY(ctx, ...) do { if (!(ctx)) return IRF_EINVAL; try { cudaSetDevice((ctx)->device); __VA_ARGS__; return IRF_OK; } catch (const string& e_) { (ctx)->err = e_; return classify(e_); } catch (const std::exception& e_) { (ctx)->err = e_.what(); return IRF_EINVAL; } } while (0)
+#define IRF_TRY(ctx, ...) do { if (!(ctx)) return IRF_EINVAL; try { cudaSetDevice((ctx)->device); __VA_ARGS__; return IRF_OK; } catch (const string& e_) { (ctx)->err = e_; int rc_ = classify(e_); if (rc_ == IRF_ECUDA) (ctx)->err += (ctx)->cuda_hint(); return rc_; } catch (const std::exception& e_) { (ctx)->err = e_.what(); return IRF_EINVAL; } } while (0)
 static int classify(const string& e) {
   if (e.find("cuda") != string::npos || e.find("CUDA") != string::npos) return IRF_ECUDA;
   if (e.find("cannot open") != string::npos || e.find("cannot write") != string::npos || e.find("read error") != string::npos || e.find("short write") != string::npos) return IRF_EIO;
@@ -880,6 +893,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "stage_lazy") c->stage_lazy = v != 0;
   else if (k == "verify_crc") c->verify_crc = v != 0;
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
+  else if (k == "safe_inflate") { if (v) { c->de_percent = 0; c->de_percent_stream = 0; } else { c->de_percent = 70; c->de_percent_stream = 100; } c->engines_planned = false; }   // untrusted input: every block through the SM kernel, which answers malformed DEFLATE with IRF_EFORMAT and stays usable
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements
   else if (k == "file_ring") { if (v < 0 || v > 2) return IRF_EINVAL; c->file_ring = (int)v; }
@@ -964,7 +978,7 @@ int irf_read_header(irf_ctx* c, const void* prefix, size_t n) {
     // inflate just the leading blocks that hold the header, through the same device path as a run
     bool req = c->require_eof; c->require_eof = false;
     try { c->stage(prefix, 0, n, 1, false); } catch (...) { c->require_eof = req; throw; } c->require_eof = req;
-    if (!c->bound) IRF_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4, c->s_compute));
+    IRF_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4, c->s_compute));   // a failed earlier run must not fail this one
     c->inflate_all(); c->join_crc(); c->check_dev_err("inflate"); c->parse_header_from_device(); c->staged = false;
   });
 }

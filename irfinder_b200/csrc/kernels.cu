@@ -123,11 +123,14 @@ int inflate_resident_lanes() { return g_inflate_lanes; }   // lanes (= BGZF bloc
 template <int WARPS, int LB, int DB, int HB = 1, int LC = 0, int RB = 0, int PZ = 0, int D8 = 0, int MINB = 0>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   size_t smem = (size_t)WARPS * (((size_t)((1 << LB) + 64) * 32 + (D8 ? (1 << DB) * 16 : (1 << DB) * 32)) * sizeof(uint16_t) + (RB ? (size_t)(1 << RB) * 32 : 0));
-  static int ctas_per_sm = 0, sms = 0;
+  // the shared-memory opt-in and the occupancy are per device: one cache slot per device ordinal
+  static int ctas_cache[64] = {0}, sms_cache[64] = {0};
+  int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");
+  int& ctas_per_sm = ctas_cache[dev]; int& sms = sms_cache[dev];
   if (!ctas_per_sm) {
     IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB>, WARPS * 32, smem));
-    int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
   const int per_sm = g_inflate_cta_cap > 0 ? std::min(g_inflate_cta_cap, ctas_per_sm) : ctas_per_sm;

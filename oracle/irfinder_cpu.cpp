@@ -18,6 +18,11 @@
 // callbacks), so it can be diffed function by function against upstream.
 //
 // usage: irfinder_cpu <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|-> [--dump-fragments FILE]
+//                     [--dump-depth FILE] [--depth-digest FILE]
+//   --dump-depth writes the per-base depth of every measured segment (CoverageBlock counters after finalise) as raw int32:
+//   [direction 0][direction 1], inside each chromosomes in name order, segments in coordinate order, len+1 values per segment
+//   (the last one is the closing counter, always 0) — the layout of the library's IRF_T_DEPTH table.  --depth-digest writes
+//   "n sum w1 w2 max" of the same sequence (w1 = sum v[i]*(i+1), w2 = sum v[i]*(i+1)^2, all mod 2^64) for full-size runs.
 //   <bam> may be BGZF/gzip (inflated through zlib, which is what the reference's `gzip -cd |` pipe does)
 //   or an already-inflated BAM byte stream.  Records must be mate-adjacent.
 //   env IRF_TRIM_CENTER overrides the trimmed-mean centre percentage [C-2].
@@ -304,6 +309,17 @@ class CoverageBlocks : public ReadBlockProcessor {
       }
   }
   void finalise() { for (auto& c : chrName_CoverageBlocks) for (auto& cb : c.second) cb.finalise(); }
+  // test hook: the finalised counters in the order documented in the header of this file
+  void dumpDepth(FILE* raw, FILE* digest) const {
+    unsigned long long n = 0, sum = 0, w1 = 0, w2 = 0; long long mx = 0;
+    for (int d = 0; d < 2; d++)
+      for (auto& c : chrName_CoverageBlocks)
+        for (auto& cb : c.second) {
+          if (raw) fwrite(cb.diff[d].data(), sizeof(int), cb.diff[d].size(), raw);
+          for (int v : cb.diff[d]) { n++; unsigned long long x = (unsigned long long)(long long)v; sum += x; w1 += x * n; w2 += x * (n * n); if (v > mx) mx = v; }
+        }
+    if (digest) fprintf(digest, "%llu %llu %llu %llu %lld\n", n, sum, w1, w2, mx);
+  }
   void fillHist(std::map<unsigned, unsigned>& hist, const string& chr, const vector<std::pair<unsigned, unsigned>>& blocks, int dir) const {
     auto c = chrName_CoverageBlocks.find(chr); if (c == chrName_CoverageBlocks.end()) return; const vector<CoverageBlock>& v = c->second;
     for (auto& bd : blocks) {
@@ -516,7 +532,7 @@ class BAM2blocks {
 
 // ---------------------------------------------------------------------------------------------
 int main(int argc, char** argv) {
-  if (argc < 7) { std::cerr << "Usage: irfinder_cpu <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|-> [--dump-fragments FILE]\n"; return 1; }
+  if (argc < 7) { std::cerr << "Usage: irfinder_cpu <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|-> [--dump-fragments FILE] [--dump-depth FILE] [--depth-digest FILE]\n"; return 1; }
   if (const char* t = getenv("IRF_TRIM_CENTER")) TRIM_CENTER_PERCENT = (unsigned)atoi(t);
   string outdir = argv[1];
   CoverageBlocksIRFinder oCov; JunctionCount oJC; SpansPoint oSP; FragmentsInChr oChr; FragmentsInROI oROI; bool haveROI = strcmp(argv[5], "NULL") != 0;
@@ -525,7 +541,8 @@ int main(int argc, char** argv) {
   { std::ifstream f(argv[4]); if (!f) { std::cerr << "cannot open " << argv[4] << "\n"; return 1; } oSP.setSpanLength(SPAN_OVERHANG_LEFT, SPAN_OVERHANG_RIGHT); oSP.loadRef(f); }
   if (haveROI) { std::ifstream f(argv[5]); if (!f) { std::cerr << "cannot open " << argv[5] << "\n"; return 1; } oROI.loadRef(f); }
   BAM2blocks BB;
-  for (int i = 7; i + 1 < argc; i += 2) if (!strcmp(argv[i], "--dump-fragments")) BB.dump = fopen(argv[i + 1], "w");
+  const char* depth_raw = nullptr; const char* depth_digest = nullptr;
+  for (int i = 7; i + 1 < argc; i += 2) { if (!strcmp(argv[i], "--dump-fragments")) BB.dump = fopen(argv[i + 1], "w"); else if (!strcmp(argv[i], "--dump-depth")) depth_raw = argv[i + 1]; else if (!strcmp(argv[i], "--depth-digest")) depth_digest = argv[i + 1]; }
   using namespace std::placeholders;
   BB.registerCallbackChrMappingChange(std::bind(&JunctionCount::ChrMapUpdate, &oJC, _1)); BB.registerCallbackProcessBlocks(std::bind(&JunctionCount::ProcessBlocks, &oJC, _1));
   BB.registerCallbackChrMappingChange(std::bind(&SpansPoint::ChrMapUpdate, &oSP, _1)); BB.registerCallbackProcessBlocks(std::bind(&SpansPoint::ProcessBlocks, &oSP, _1));
@@ -538,6 +555,7 @@ int main(int argc, char** argv) {
   if (BB.dump) fclose(BB.dump);
   if (rc) return rc;
   oCov.finalise();
+  if (depth_raw || depth_digest) { FILE* r = depth_raw ? fopen(depth_raw, "wb") : nullptr; FILE* g = depth_digest ? fopen(depth_digest, "w") : nullptr; oCov.dumpDepth(r, g); if (r) fclose(r); if (g) fclose(g); }
   int directionality = oJC.Directional(&std::cout);
   std::cout << "Directionality:\t" << directionality << "\n";
   { std::ofstream o(outdir + "/IRFinder-IR-nondir.txt"); oCov.WriteOutput(&o, oJC, oSP, 0); }

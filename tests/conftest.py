@@ -27,12 +27,16 @@ def built():
     return paths
 
 
-def run_oracle(built, meta, outdir, bam=None, dump=None, env=None, roi=True):
+def run_oracle(built, meta, outdir, bam=None, dump=None, env=None, roi=True, depth=None, depth_digest=None):
     """Runs the CPU restatement (tests are the only place allowed to)."""
     os.makedirs(outdir, exist_ok=True)
     cmd = [built["oracle"], outdir, meta["cover"], meta["sj"], meta["rc"], meta["roi"] if roi else "NULL", bam or meta["collated"]]
     if dump:
         cmd += ["--dump-fragments", dump]
+    if depth:
+        cmd += ["--dump-depth", depth]
+    if depth_digest:
+        cmd += ["--depth-digest", depth_digest]
     e = dict(os.environ)
     e.update(env or {})
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=e)
@@ -53,3 +57,19 @@ def assert_same_outputs(dir_a, dir_b):
                     if x != y:
                         raise AssertionError(f"{name} differs at line {i + 1}:\n  oracle: {x[:300]!r}\n  gpu:    {y[:300]!r}")
                 raise AssertionError(f"{name} differs in length: {len(la)} vs {len(lb)} lines")
+
+
+def depth_digest(v):
+    """The oracle's --depth-digest of an int32 sequence: (n, sum, sum v[i]*(i+1), sum v[i]*(i+1)^2, max), sums mod 2^64."""
+    import numpy as np
+    n, s, w1, w2, mx = len(v), 0, 0, 0, 0
+    M = (1 << 64) - 1
+    for lo in range(0, n, 1 << 24):
+        x = np.asarray(v[lo:lo + (1 << 24)]).astype(np.int64).view(np.uint64)
+        i = np.arange(lo + 1, lo + 1 + len(x), dtype=np.uint64)
+        with np.errstate(over="ignore"):
+            s = (s + int(x.sum(dtype=np.uint64))) & M
+            w1 = (w1 + int((x * i).sum(dtype=np.uint64))) & M
+            w2 = (w2 + int((x * (i * i)).sum(dtype=np.uint64))) & M
+        mx = max(mx, int(np.asarray(v[lo:lo + (1 << 24)]).max(initial=0)))
+    return n, s, w1, w2, mx

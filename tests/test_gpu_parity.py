@@ -41,7 +41,9 @@ def tiny(built, tmp_path_factory):
     tmp = tmp_path_factory.mktemp("tiny")
     meta = _gen(tmp, "w", genome="tiny", introns=300, pairs=30000, readlen=100, seed=11, chunks=7)
     meta["oracle_out"] = os.path.join(str(tmp), "oracle")
-    meta["oracle_stdout"] = run_oracle(built, meta, meta["oracle_out"], dump=os.path.join(str(tmp), "frags.txt"))
+    meta["oracle_depth"] = os.path.join(str(tmp), "depth.i32")
+    meta["oracle_depth_digest"] = os.path.join(str(tmp), "depth.digest")
+    meta["oracle_stdout"] = run_oracle(built, meta, meta["oracle_out"], dump=os.path.join(str(tmp), "frags.txt"), depth=meta["oracle_depth"], depth_digest=meta["oracle_depth_digest"])
     meta["oracle_frags"] = os.path.join(str(tmp), "frags.txt")
     return meta
 
@@ -96,9 +98,14 @@ def test_integer_tables_bit_exact(tiny, built, tmp_path):
     names = ["chrA", "chrB", "chrEmpty"]
     got = {(names[r["refid"]], int(r["start"]), int(r["end"])): (int(r["neg"]), int(r["pos"])) for r in j}
     assert got == want
-    # depth: sentinel slot of every measured segment is zero and depth is never negative
+    # per-base depth (CoverageBlocks counters after the scan), element for element against the oracle's dump, and through the
+    # digest the full-size parity runs use (tools/full_parity.py)
     d = c.table("depth")
-    assert d.min() >= 0
+    want_d = np.fromfile(tiny["oracle_depth"], dtype="<i4")
+    assert d.shape == want_d.shape and d.max() > 0
+    assert np.array_equal(d, want_d)
+    from conftest import depth_digest
+    assert list(depth_digest(d)) == [int(x) for x in open(tiny["oracle_depth_digest"]).read().split()]
 
 
 def test_stranded_library_writes_dir_table(built, tmp_path):
@@ -201,6 +208,74 @@ def test_bad_inputs_fail_loudly(tiny, tmp_path):
     c.set_option("verify_crc", 1)
     c.run_bytes(data)               # the context stays usable afterwards
     assert c.stats()["pairs"] > 0
+
+
+def _bgzf_block_offsets(data):
+    offs, off = [], 0
+    while off + 18 <= len(data):
+        offs.append(off)
+        off += (data[off + 16] | data[off + 17] << 8) + 1
+    return offs
+
+
+@pytest.mark.parametrize("path", ["staged", "pipelined", "pipelined_sm"])
+def test_bad_crc_in_a_late_block_on_a_fresh_context(built, tmp_path, path):
+    """The integrity flag must survive the table reset that ChrMapUpdate does in the middle of a context's FIRST count (the CLI
+    case): a wrong CRC-32 footer in a late block of a multi-MB file is reported on every path.  The damaged block's DEFLATE
+    payload is intact, so the hardware decompression engine can take it."""
+    from irfinder_b200 import IRFError
+    meta = _gen(tmp_path, "w", genome="tiny", introns=300, pairs=120000, readlen=100, seed=5, chunks=7)
+    data = bytearray(open(meta["sorted"], "rb").read())
+    offs = _bgzf_block_offsets(data)
+    assert len(offs) > 100 and len(data) > (6 << 20)
+    victim = offs[len(offs) * 9 // 10]
+    nxt = offs[len(offs) * 9 // 10 + 1]
+    data[nxt - 8] ^= 0x40                      # CRC-32 footer of a block near the end of the file
+    opts = dict(staged=dict(stream_pipeline=0), pipelined=dict(stream_chunk_kb=512), pipelined_sm=dict(stream_chunk_kb=512, de_percent=0))[path]
+    c = _core(**opts)                          # fresh context: the header is parsed and the references bound inside this very count
+    c.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])
+    with pytest.raises(IRFError) as ei:
+        c.run_bytes(bytes(data))
+    assert "CRC" in str(ei.value), (path, victim, str(ei.value))
+    data[nxt - 8] ^= 0x40
+    c.run_bytes(bytes(data))                   # and the context recovers
+    assert c.stats()["pairs"] > 0
+
+
+def test_cli_default_options_on_damaged_bams(built, tiny, tmp_path):
+    """"Truncated BGZF / bad CRC must be a hard error with non-zero exit" — through bin/irfinder with DEFAULT options
+    (every block goes to the hardware decompression engine).  Each damaged file runs in its own process: non-zero exit, a message
+    on stderr, no hang; a fresh process afterwards works, and IRF_SAFE_INFLATE=1 names the problem without a CUDA fault."""
+    exe = os.path.join(ROOT, "bin", "irfinder")
+    data = open(tiny["sorted"], "rb").read()
+    offs = _bgzf_block_offsets(data)
+    mid = offs[len(offs) // 2]
+    cases = {}
+    cases["truncated_mid_block"] = data[: mid + 1000]
+    flipped = bytearray(data)
+    for k in range(mid + 400, mid + 464):
+        flipped[k] ^= 0xA5                      # DEFLATE payload of a block in the middle of the file
+    cases["bit_flipped_payload"] = bytes(flipped)
+    one_bit = bytearray(data)
+    one_bit[mid + 700] ^= 0x10
+    cases["single_bit_flip"] = bytes(one_bit)
+    args = [tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"]]
+    for name, blob in cases.items():
+        bam = str(tmp_path / (name + ".bam"))
+        open(bam, "wb").write(blob)
+        for env_extra in ({}, {"IRF_SAFE_INFLATE": "1"}):
+            out = str(tmp_path / (name + ("_safe" if env_extra else "")))
+            os.makedirs(out, exist_ok=True)
+            r = subprocess.run([exe, out] + args + [bam], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60, env=dict(os.environ, **env_extra))
+            assert r.returncode != 0, (name, env_extra, r.stdout[-300:])
+            assert r.stderr.strip(), (name, env_extra)
+            if env_extra:
+                assert "CUDA" not in r.stderr and "cuda" not in r.stderr, (name, r.stderr)    # the SM kernel reports a format error, not a device fault
+    out = str(tmp_path / "good")
+    os.makedirs(out)
+    r = subprocess.run([exe, out] + args + [tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    assert_same_outputs(tiny["oracle_out"], out)
 
 
 def test_micro_fixture_by_hand_on_gpu(tmp_path):
