@@ -48,7 +48,9 @@ int irf_create(irf_ctx** out, const int* device_ids, int n_devices);
 void irf_destroy(irf_ctx* ctx);
 const char* irf_last_error(irf_ctx* ctx);
 
-/* Options (strings): "trim_center" (default 40), "dump_fragments" (0/1), "inflate_variant" (0-11: A/B variants of the SM inflate kernel, 0 = default),
+/* Options (strings): "trim_center" (default 40), "dump_fragments" (0/1), "inflate_variant" (A/B variants of the SM inflate kernel: 12 = two-phase
+ * token decode + warp-wide match resolve, 0-11 = the one-phase lane-per-block kernel and its table/occupancy variants),
+ * "safe_inflate" (1 = untrusted input: every block through the SM kernel, which answers malformed DEFLATE with IRF_EFORMAT and leaves the context usable),
  * "de_percent" (default 70) / "de_percent_stream" (default 100): share of the BGZF blocks inflated by the Blackwell hardware
  * decompression engine when the bytes are resident / streamed from the host; the rest go to the SM kernel; 0 = SM kernel only.
  * "resident_pipeline" (default 1): large resident inputs are counted by the overlapped chunk pipeline, in which the engine takes the
@@ -102,7 +104,8 @@ int irf_count(irf_ctx* ctx);
 int irf_frame_info(irf_ctx* ctx, uint64_t* entry0, uint64_t* exit_rel);
 /* Depth scan, junction merge, directionality and per-intron statistics on the (possibly all-reduced) tables. */
 int irf_finalize(irf_ctx* ctx);
-/* Device pointers of the additive tables, for an NCCL all-reduce by the caller (IRF_T_SPANS, _ROI, _CHR, _STATS, _DIFF). */
+/* Device pointers of the additive tables, for an NCCL all-reduce by the caller (IRF_T_SPANS, _ROI, _CHR, _STATS, _DIFF; in owner mode
+ * also IRF_T_ROWS_NONDIR / IRF_T_ROWS_DIR as 64-bit words). */
 int irf_get_device_table(irf_ctx* ctx, int which, void** dev_ptr, size_t* n_elems, int* elem_bytes);
 /* Junction tables as dense device arrays (keys uint64, counts uint32[n][2]); which = 0 exact, 1 left ends, 2 right ends. */
 int irf_export_junctions(irf_ctx* ctx, int which, void** dev_keys, void** dev_counts, size_t* n);
@@ -111,6 +114,24 @@ int irf_import_junctions(irf_ctx* ctx, int which, const void* dev_keys, const vo
 int irf_export_halo(irf_ctx* ctx, void** dev_bytes, size_t* nbytes, void** dev_offsets, size_t* nrec);
 /* Pairs the gathered halo records of all shards; this context counts the pairs whose key hash % n_owners == owner. */
 int irf_import_halo(irf_ctx* ctx, const void* dev_bytes, size_t nbytes, const void* dev_offsets, size_t nrec, int owner, int n_owners);
+
+/* ---- region-owned depth for sharded runs ("Depth needs no reduction (region-owned) ... per-intron stats computed by
+ * the owner; rows gathered to rank 0").  The reference has one process and one CoverageBlocks object; these calls split that object's
+ * counters (CoverageBlocks::ProcessBlocks / CoverageBlocksIRFinder::WriteOutput, ReadBlockProcessor_CoverageBlocks.cpp) by genomic region. ---- */
+/* refID / pos of the first record this context counted (refid = -2 when its shard held no record). */
+int irf_first_record(irf_ctx* ctx, int32_t* refid, int32_t* pos);
+/* Gives every measured segment an owning rank from the first-record coordinates of all ranks (same arrays on every rank); segments
+ * that share a ref-cover record stay together.  Switches the context to owner mode until the next irf_reset. */
+int irf_owner_plan(irf_ctx* ctx, const int32_t* first_refid, const int64_t* first_pos, int n_ranks, int my_rank);
+/* This rank's non-zero difference counters in segments it does not own: device arrays of uint64 table indices and int32 values. */
+int irf_export_foreign_depth(irf_ctx* ctx, void** dev_index, void** dev_value, size_t* n);
+/* Adds the listed counters that fall into segments this rank owns (entries for other owners are skipped, so every rank can be handed
+ * the concatenation of all ranks' lists). */
+int irf_import_depth(irf_ctx* ctx, const void* dev_index, const void* dev_value, size_t n);
+/* In owner mode irf_finalize computes the rows of the owned introns only and leaves both row tables on the device with all other rows
+ * zero: the caller adds the tables of all ranks as 64-bit integers (irf_get_device_table IRF_T_ROWS_NONDIR / IRF_T_ROWS_DIR; exactly one
+ * rank contributes a non-zero row, so the sum is exact) and then calls irf_finalize_rows, which brings them to the host. */
+int irf_finalize_rows(irf_ctx* ctx);
 
 /* No counterpart in the reference (it has no GPU path and therefore no allocation question).
  * Depth scan for callers that must not allocate GPU memory: out[i] = in[0] + ... + in[i] over `n` int32 difference

@@ -53,6 +53,11 @@ SYMBOLS = {
     "irf_import_junctions": (_i, [_vp, _i, _vp, _vp, _sz]),
     "irf_export_halo": (_i, [_vp, C.POINTER(_vp), C.POINTER(_sz), C.POINTER(_vp), C.POINTER(_sz)]),
     "irf_import_halo": (_i, [_vp, _vp, _sz, _vp, _sz, _i, _i]),
+    "irf_first_record": (_i, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "irf_owner_plan": (_i, [_vp, C.POINTER(C.c_int32), C.POINTER(C.c_int64), _i, _i]),
+    "irf_export_foreign_depth": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_sz)]),
+    "irf_import_depth": (_i, [_vp, _vp, _vp, _sz]),
+    "irf_finalize_rows": (_i, [_vp]),
     "irf_depth_scan_static": (_i, [_vp, _vp, _sz, _vp, C.c_char_p, _sz]),
 }
 _lib = None
@@ -197,6 +202,29 @@ class IRFinderCore:
         b, nb, o, nr = _vp(), _sz(), _vp(), _sz()
         self._ck(self.lib.irf_export_halo(self.h, C.byref(b), C.byref(nb), C.byref(o), C.byref(nr)))
         return b.value or 0, nb.value, o.value or 0, nr.value
+
+    # ---- region-owned depth (sharded runs)
+    def first_record(self):
+        a, b = C.c_int32(), C.c_int32()
+        self._ck(self.lib.irf_first_record(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def owner_plan(self, refids, positions, rank):
+        n = len(refids)
+        ra = (C.c_int32 * n)(*[int(x) for x in refids])
+        pa = (C.c_int64 * n)(*[int(x) for x in positions])
+        self._ck(self.lib.irf_owner_plan(self.h, ra, pa, n, rank))
+
+    def export_foreign_depth(self):
+        i, v, n = _vp(), _vp(), _sz()
+        self._ck(self.lib.irf_export_foreign_depth(self.h, C.byref(i), C.byref(v), C.byref(n)))
+        return i.value or 0, v.value or 0, n.value
+
+    def import_depth(self, idx_ptr, val_ptr, n):
+        self._ck(self.lib.irf_import_depth(self.h, _vp(idx_ptr), _vp(val_ptr), n))
+
+    def finalize_rows(self):
+        self._ck(self.lib.irf_finalize_rows(self.h))
 
     def import_halo(self, bytes_ptr, nbytes, offsets_ptr, nrec, owner, n_owners):
         self._ck(self.lib.irf_import_halo(self.h, _vp(bytes_ptr), nbytes, _vp(offsets_ptr), nrec, owner, n_owners))

@@ -19,6 +19,7 @@
 #include <cstring>
 #include <fstream>
 #include <functional>
+#include <map>
 #include <string>
 #include <thread>
 #include <vector>
@@ -88,7 +89,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
-  DevBuf d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
+  DevBuf d_tok, d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -212,7 +213,7 @@ struct irf_ctx {
     IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_SLOTS * 8, s)); if (!keep_err) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
     if (dump_fragments) IRF_CUDA(cudaMemsetAsync(d_dump_cursor.p, 0, 8, s));
     launch_ht_insert_keys(T.jc_keys, T.jc_mask, d_annot_keys.as<u64>(), n_annot, T.err, s);
-    counted = finalized = false; sharded = false; halo_leftover = 0; launches0 = launch_counter();
+    counted = finalized = false; sharded = false; halo_leftover = 0; owner_mode = false; rows_pending = false; launches0 = launch_counter();
   }
 
   // ---------------------------------------------------------------- BGZF scan (SAM v1 §4.1)
@@ -382,6 +383,7 @@ struct irf_ctx {
     // which the decompression engine alone keeps up with, so the SMs stay out of the way (measured: 288 ms vs 333 ms mixed)
     const int want_percent = resident ? de_percent : de_percent_stream;
     if (!engines_planned || planned_percent != want_percent) plan_engines(want_percent);
+    tok_scratch(de_list.empty() ? (int)nb : (int)sm_list.size());   // allocated (if it has to grow) before anything is queued
     IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
     unsigned long long* wm = (unsigned long long*)(d_small.as<uint8_t>() + 224);
     const bool stream_in = !resident && inflate_variant != 8;
@@ -390,6 +392,7 @@ struct irf_ctx {
     const bool listed = !de_list.empty();
     InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), listed ? (int)sm_list.size() : (int)nb, d_status.as<int>(),
                   T.err ? T.err : d_err.as<int>(), (unsigned int*)(d_small.as<uint8_t>() + 160), stream_in ? wm : nullptr, listed ? d_sm_list.as<u32>() : nullptr};
+    a.tok_scratch = tok_scratch(a.nblk); a.tok_scratch_bytes = d_tok.cap;
     cudaEvent_t k0, k1, ready, de_done; IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1));
     IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming)); IRF_CUDA(cudaEventCreateWithFlags(&de_done, cudaEventDisableTiming));
     IRF_CUDA(cudaEventRecord(k0, s_compute));
@@ -434,6 +437,8 @@ struct irf_ctx {
     cudaEventDestroy(k0); cudaEventDestroy(k1); cudaEventDestroy(ready); cudaEventDestroy(de_done); for (auto e : chunk_ev) cudaEventDestroy(e);
     resident = true;
   }
+  // match-token scratch of the two-phase inflate kernel (inflate_variant 12): TOK_CAP words per block in flight
+  uint32_t* tok_scratch(int nblk_kernel) { size_t need = inflate_scratch_bytes(inflate_variant, nblk_kernel); if (!need) return nullptr; if (need + 256 > d_tok.cap) { sync(); cudaStreamSynchronize(s_copy); d_tok.ensure(need); } return d_tok.as<uint32_t>(); }
   unsigned long long* wm_host = nullptr; size_t wm_host_cap = 0;
   int n_inflate_launches = 0;
 
@@ -534,6 +539,7 @@ struct irf_ctx {
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
     if (from_host) { if (!engines_planned || planned_percent != 100) plan_engines(100); }
     else if (!engines_planned || planned_percent != 1000 + de_percent_overlap) plan_engines(de_percent_overlap, 1);
+    if (!from_host && !sm_list.empty()) tok_scratch((int)sm_list.size());
     const size_t nb = blks.size(), nch = chunk_blk_end.size(); const bool sm_used = !from_host && !sm_list.empty(); const size_t ksm = sm_used ? nch - k_de : 0;   // chunks [0, ksm) are the SM kernel's
     cudaEvent_t k0 = nullptr, k1 = nullptr;
     int* errp = T.err ? T.err : d_err.as<int>();
@@ -568,6 +574,7 @@ struct irf_ctx {
       IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1)); IRF_CUDA(cudaEventRecord(k0, s_copy));
       InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)sm_list.size(), d_status.as<int>(),
                     errp, (unsigned int*)(d_small.as<uint8_t>() + 160), nullptr, d_sm_list.as<u32>()};
+      a.tok_scratch = tok_scratch(a.nblk); a.tok_scratch_bytes = d_tok.cap;
       launch_inflate(a, inflate_variant, s_copy); IRF_CUDA(cudaEventRecord(k1, s_copy));
       if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)sm_list.size(), d_status.as<int>(), errp, s_copy, d_sm_list.as<u32>());
     }
@@ -705,6 +712,69 @@ struct irf_ctx {
   }
   int frame_rounds = 0;
 
+  // ---------------------------------------------------------------- region-owned depth (multi-GPU)
+  // Every measured segment gets one owning rank from the genomic position of each rank's first record (a coordinate-sorted
+  // shard is a genomic region); segments that share a ref-cover record are kept together, so all blocks of an intron have one
+  // owner.  Each rank lists its non-zero counters in foreign segments (export_foreign_depth), the owners add them
+  // (import_depth), and irf_finalize computes the statistics of the owned introns only; the rows of the other introns stay
+  // zero on the device, so the caller merges the row tables with an integer SUM and then calls finalize_rows().
+  bool owner_mode = false, rows_pending = false; int owner_me = 0, owner_world = 1; u32 n_own_introns = 0;
+  DevBuf d_seg_owner, d_own_introns, d_fidx, d_fval, d_rows_dir; u64 foreign_cap = 1ull << 20;
+  void first_record(int32_t& refid, int32_t& pos) {
+    refid = -2; pos = 0; if (!counted) throw string("irf_count has not run");
+    if (n_rec == 0 || frame_entry0 + 12 > Uend) return;
+    int32_t w[2]; IRF_CUDA(cudaMemcpyAsync(w, d_U.as<uint8_t>() + frame_entry0 + 4, 8, cudaMemcpyDeviceToHost, s_compute)); sync();
+    refid = w[0]; pos = w[1];
+  }
+  void owner_plan(const int32_t* cut_refid, const int64_t* cut_pos, int world, int me) {
+    if (!bound) throw string("irf_count has not run");
+    if (world < 1 || world > 255 || me < 0 || me >= world) throw string("bad owner plan");
+    const u32 nseg = (u32)cov.seg_start.size(); const int n = (int)chr_names.size();
+    std::map<string, int> id; for (int i = n - 1; i >= 0; i--) id[chr_names[i]] = i;
+    // cut keys (refID, pos); a rank without records (refID < 0) owns nothing: its cut is the next rank's
+    vector<std::pair<int64_t, int64_t>> cut(world); const std::pair<int64_t, int64_t> INF{1ll << 40, 0};
+    for (int r = world - 1; r >= 0; r--) cut[r] = cut_refid[r] >= 0 ? std::make_pair((int64_t)cut_refid[r], cut_pos[r]) : (r + 1 < world ? cut[r + 1] : INF);
+    cut[0] = {-1, 0}; for (int r = 1; r < world; r++) cut[r] = std::max(cut[r], cut[r - 1]);
+    vector<std::pair<int64_t, int64_t>> key(nseg); vector<uint8_t> want(nseg, 0);
+    for (auto& c : cov.chr_range) { auto it = id.find(c.first); const int64_t rid = it == id.end() ? -1 : it->second;
+      for (u32 sgi = c.second.begin; sgi < c.second.end; sgi++) { key[sgi] = {rid, cov.seg_start[sgi]}; int r = 0; if (rid >= 0) { r = (int)(std::upper_bound(cut.begin(), cut.end(), key[sgi]) - cut.begin()) - 1; if (r < 0) r = 0; } want[sgi] = (uint8_t)r; } }
+    // segments joined by a ref-cover record stay together (union-find); the group goes to the smallest wanted owner
+    vector<u32> parent(nseg); for (u32 i = 0; i < nseg; i++) parent[i] = i;
+    std::function<u32(u32)> find = [&](u32 x) { while (parent[x] != x) { parent[x] = parent[parent[x]]; x = parent[x]; } return x; };
+    vector<u32> first_seg(cov.BEDrecords.size(), 0xffffffffu);
+    for (size_t k = 0; k < cov.BEDrecords.size(); k++) { auto& rec = cov.BEDrecords[k]; auto c = cov.chr_range.find(rec.chrName); if (c == cov.chr_range.end()) continue;
+      for (auto& b : rec.blocks) { if (b.first >= b.second) continue;
+        u32 sgi = (u32)(std::upper_bound(cov.seg_end.begin() + c->second.begin, cov.seg_end.begin() + c->second.end, b.first) - cov.seg_end.begin()); if (sgi >= c->second.end) continue;
+        if (first_seg[k] == 0xffffffffu) first_seg[k] = sgi; else { u32 a = find(first_seg[k]), bb = find(sgi); if (a != bb) parent[bb] = a; } } }
+    vector<uint8_t> group(nseg, 255); for (u32 i = 0; i < nseg; i++) { u32 r = find(i); group[r] = std::min(group[r], want[i]); }
+    vector<uint8_t> owner(nseg); for (u32 i = 0; i < nseg; i++) owner[i] = group[find(i)];
+    vector<u32> mine; for (size_t k = 0; k < cov.BEDrecords.size(); k++) { int o = first_seg[k] == 0xffffffffu ? 0 : owner[first_seg[k]]; if (o == me) mine.push_back((u32)k); }
+    upload(d_seg_owner, owner, s_compute); upload(d_own_introns, mine, s_compute); sync();
+    n_own_introns = (u32)mine.size(); owner_mode = true; owner_me = me; owner_world = world;
+  }
+  u64 export_foreign_depth() {
+    if (!owner_mode) throw string("irf_owner_plan must be called before the depth exchange");
+    u64* cur = (u64*)(d_small.as<uint8_t>() + 104);
+    for (;;) {
+      d_fidx.ensure(foreign_cap * 8); d_fval.ensure(foreign_cap * 4); IRF_CUDA(cudaMemsetAsync(cur, 0, 8, s_compute));
+      launch_foreign_depth(T, (u32)cov.seg_start.size(), d_seg_owner.as<uint8_t>(), (u32)owner_me, d_fidx.as<u64>(), d_fval.as<int32_t>(), cur, foreign_cap, s_compute);
+      u64 n = 0; IRF_CUDA(cudaMemcpyAsync(&n, cur, 8, cudaMemcpyDeviceToHost, s_compute)); sync();
+      if (n <= foreign_cap) return n;
+      foreign_cap = n + n / 4;   // rare: grow and list again
+    }
+  }
+  void import_depth(const u64* idx, const int32_t* val, u64 n) {
+    if (!owner_mode) throw string("irf_owner_plan must be called before the depth exchange");
+    launch_import_depth(T, (u32)cov.seg_start.size(), d_seg_owner.as<uint8_t>(), (u32)owner_me, idx, val, n, s_compute); sync();
+  }
+  void finalize_rows() {
+    if (!rows_pending) throw string("no owner-mode finalize to complete");
+    const u32 n_in = (u32)cov.BEDrecords.size();
+    pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute));
+    if (directionality != 0) { pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows_dir.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); }
+    sync(); rows_pending = false; finalized = true;
+  }
+
   u64 count_leftovers(u64* fill, u64 cap) {
     u64* n_left = (u64*)(d_small.as<uint8_t>() + 64); IRF_CUDA(cudaMemsetAsync(n_left, 0, 8, s_compute));
     launch_pair_leftover(d_ptab.as<u64>(), pslots, n_left, fill, cap, s_compute);
@@ -731,7 +801,7 @@ struct irf_ctx {
   // S4 + output-side statistics
   void finalize() {
     if (!counted) throw string("irf_count has not run");
-    if (finalized) return;
+    if (finalized || rows_pending) return;
     cudaEvent_t e0, e1; IRF_CUDA(cudaEventCreate(&e0)); IRF_CUDA(cudaEventCreate(&e1)); IRF_CUDA(cudaEventRecord(e0, s_compute));
     const bool dbg = getenv("IRF_DEBUG_TIMING") != nullptr; double tdbg = now_ms(); auto mark = [&](const char* what) { if (dbg) { sync(); cudaStreamSynchronize(s_copy); double t = now_ms(); fprintf(stderr, "[finalize] %-22s %8.3f ms\n", what, t - tdbg); tdbg = t; } };
     // Two streams: the compute stream exports and sorts the junction tables while the host turns them into rows and runs
@@ -747,10 +817,13 @@ struct irf_ctx {
     // shared-memory histograms (the usual case): one short-lived CTA per intron, so the export kernels of the other stream
     // get SM slots as CTAs retire; deep data needs a global scratch histogram per CTA, hence a fixed number of looping CTAs
     u32 n_in = (u32)cov.BEDrecords.size(); u32 bins = hmax >= 8192 ? hmax + 1 : 1;
-    int grid = (int)std::min<u32>(std::max<u32>(n_in, 1), bins == 1 ? (1u << 20) : 148 * 4);
+    // region-owned run: this rank computes the rows of its own introns only (the others stay zero and are merged by the caller)
+    const u32 n_do = owner_mode ? n_own_introns : n_in; const u32* do_list = owner_mode ? d_own_introns.as<u32>() : nullptr;
+    int grid = (int)std::min<u32>(std::max<u32>(n_do, 1), bins == 1 ? (1u << 20) : 148 * 4);
     d_scratch.ensure((u64)grid * bins * 4);
-    launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy);
-    pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy));
+    if (owner_mode) { d_rows_dir.ensure(n_in * sizeof(IntronRow)); IRF_CUDA(cudaMemsetAsync(d_rows.p, 0, n_in * sizeof(IntronRow), s_copy)); IRF_CUDA(cudaMemsetAsync(d_rows_dir.p, 0, n_in * sizeof(IntronRow), s_copy)); }
+    launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy, do_list);
+    if (!owner_mode) { pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); }
     // junctions -> host (JunctionCount map contents)
     u64 nj = export_table(0); vector<u64> k(nj); vector<u32> c(nj * 2);
     if (nj) {   // sort by key on the device: key order == (refID, start, end) order
@@ -766,8 +839,8 @@ struct irf_ctx {
     IRF_CUDA(cudaStreamSynchronize(s_copy)); mark("intron stats nondir (side stream)");
     if (directionality == 0 && !rows_dir.empty()) { cudaHostUnregister(rows_dir.data()); vector<IntronRow>().swap(rows_dir); }
     if (directionality != 0) {
-      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_in, directionality, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy);
-      pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); IRF_CUDA(cudaStreamSynchronize(s_copy));
+      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, directionality, trim_center, d_scratch.as<u32>(), bins, grid, owner_mode ? d_rows_dir.as<IntronRow>() : d_rows.as<IntronRow>(), s_copy, do_list);
+      if (!owner_mode) { pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); } IRF_CUDA(cudaStreamSynchronize(s_copy));
     }
     IRF_CUDA(cudaEventRecord(ev_side, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_side, 0)); cudaEventDestroy(ev_scan); cudaEventDestroy(ev_side);
     mark("intron stats dir"); h_stats.assign(ST_SLOTS, 0); h_sp.assign(sp.pos.size() * 2, 0); h_roi.assign(roi.rois.size() * 2, 0); h_chr.assign(chr_names.size() * 2, 0);
@@ -789,7 +862,7 @@ struct irf_ctx {
     line("Total reads processed", h_stats[ST_SINGLE] + h_stats[ST_PAIRED]); line("Total nucleotides", h_stats[ST_NUCLEOTIDES]); line("Total singles processed", h_stats[ST_SINGLE]);
     line("Total pairs processed", h_stats[ST_PAIRED]); line("Short pairs", h_stats[ST_SHORT]); line("Intersect pairs", h_stats[ST_INTERSECT]); line("Long pairs", h_stats[ST_LONG]);
     line("Skipped reads", h_stats[ST_SKIPPED]); line("Error reads", h_stats[ST_ERROR]);
-    finalized = true;
+    if (owner_mode) rows_pending = true; else finalized = true;   // region-owned run: the caller merges the row tables, then finalize_rows()
   }
 
   TextTable t_ir, t_dir, t_junc, t_sp;
@@ -868,9 +941,9 @@ void irf_destroy(irf_ctx* c) {
   if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
-                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
+                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
-                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
@@ -995,6 +1068,8 @@ int irf_get_device_table(irf_ctx* c, int which, void** dp, size_t* n, int* eb) {
     case IRF_T_ROI: *dp = c->d_roi_count.p; *n = c->roi.rois.size() * 2; *eb = 4; break;
     case IRF_T_CHR: *dp = c->d_chr_count.p; *n = c->chr_names.size() * 2; *eb = 4; break;
     case IRF_T_DIFF: *dp = c->d_diff.p; *n = c->cov.P * 2; *eb = 4; break;
+    case IRF_T_ROWS_NONDIR: *dp = c->d_rows.p; *n = c->cov.BEDrecords.size() * sizeof(IntronRow) / 8; *eb = 8; break;   // as 64-bit words, for the integer SUM merge of a region-owned run
+    case IRF_T_ROWS_DIR: if (!c->rows_pending) return IRF_ESTATE; *dp = c->d_rows_dir.p; *n = c->cov.BEDrecords.size() * sizeof(IntronRow) / 8; *eb = 8; break;
     default: return IRF_EINVAL;
   }
   return IRF_OK;
@@ -1011,6 +1086,14 @@ int irf_import_junctions(irf_ctx* c, int which, const void* keys, const void* co
     launch_ht_add(tk, tc, mask, (const u64*)keys, (const u32*)counts, n, c->T.err, c->s_compute); c->sync(); c->check_dev_err("junction merge");
   });
 }
+int irf_first_record(irf_ctx* c, int32_t* refid, int32_t* pos) { if (!refid || !pos) return IRF_EINVAL; IRF_TRY(c, c->first_record(*refid, *pos)); }
+int irf_owner_plan(irf_ctx* c, const int32_t* cut_refid, const int64_t* cut_pos, int n_ranks, int my_rank) { if (!cut_refid || !cut_pos) return IRF_EINVAL; IRF_TRY(c, c->owner_plan(cut_refid, cut_pos, n_ranks, my_rank)); }
+int irf_export_foreign_depth(irf_ctx* c, void** dev_index, void** dev_value, size_t* n) {
+  if (!dev_index || !dev_value || !n) return IRF_EINVAL;
+  IRF_TRY(c, { u64 k = c->export_foreign_depth(); *dev_index = c->d_fidx.p; *dev_value = c->d_fval.p; *n = (size_t)k; });
+}
+int irf_import_depth(irf_ctx* c, const void* dev_index, const void* dev_value, size_t n) { IRF_TRY(c, c->import_depth((const u64*)dev_index, (const int32_t*)dev_value, n)); }
+int irf_finalize_rows(irf_ctx* c) { IRF_TRY(c, c->finalize_rows()); }
 int irf_export_halo(irf_ctx* c, void** bytes, size_t* nbytes, void** offsets, size_t* nrec) {
   if (!bytes || !nbytes || !offsets || !nrec) return IRF_EINVAL;
   IRF_TRY(c, {

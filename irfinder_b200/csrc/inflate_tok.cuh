@@ -1,0 +1,206 @@
+// inflate_tok.cuh — two-phase DEFLATE for BGZF blocks: a lane decodes the Huffman stream of one block into literal bytes
+// (stored at their final place) and a list of LZ77 match tokens; afterwards the whole warp fills in the matches of each of
+// its 32 blocks (kernels.cu, inflate_tok_kernel).  Replaces `gzip -cd` of the reference's pipeline;
+// format authority RFC 1951.
+//
+// Why two phases (measured on the one-phase kernel of round 1, profiles/README.md): with the LZ77 copies inside the decode
+// loop a warp's lanes sat in different states (table build / symbol / copy) and only ~11 of 32 were active per instruction; each
+// copy was a dependent load from a 64 KiB-per-lane working set that missed L2 (13.6 DRAM bytes per algorithmic byte); every
+// output byte was one store instruction.  Here the decode loop does ONE thing per iteration in every lane — one literal/length
+// symbol (plus its distance symbol) — so lanes stay converged and, because zlib closes a DEFLATE block after a fixed number of
+// symbols, reach their next table build in nearly the same iteration; literals leave as aligned 32-bit words; matches become
+// 4-byte tokens that the warp resolves later with all 32 lanes working on ONE block (64 KiB working set per warp, not per lane).
+//
+// Token (32 bits):  lit_len << 24 | match_len << 15 | (dist - 1)
+//   lit_len   0..255  literal bytes since the end of the previous match (they are already in the output)
+//   match_len 0, 3..258; 0 = no match: the token only carries 255 literals of a long literal run
+//   dist      1..32768
+// Literals after the last match need no token.  At most isize/3 + isize/255 + 2 tokens per block (TOK_CAP).
+//
+// __host__ __device__ like inflate_core.cuh: tests/emu runs this very routine on the CPU against zlib.
+#pragma once
+#include "inflate_core.cuh"
+
+namespace irf {
+
+constexpr uint32_t TOK_CAP = 65536 / 3 + 65536 / 255 + 8;   // tokens one BGZF block can need (worst case): size of a lane's scratch region
+IRF_HD uint32_t tok_make(uint32_t lit, uint32_t mlen, uint32_t dist) { return lit << 24 | mlen << 15 | (dist - 1u); }
+IRF_HD uint32_t tok_lit(uint32_t t) { return t >> 24; }
+IRF_HD uint32_t tok_mlen(uint32_t t) { return (t >> 15) & 511u; }
+IRF_HD uint32_t tok_dist(uint32_t t) { return (t & 32767u) + 1u; }
+
+// Decode states of a lane (LS_* of inflate_core.cuh are reused): HEADER, SYMBOL, SLOWLIT / SLOWDIST (a code longer than the
+// LUT was found in the previous iteration; its symbol was fetched from the lane's local-memory table meanwhile), DONE.
+template <int LANES, int LIT_BITS, int DIST_BITS>
+struct TokLane {
+  BitReader br;
+  Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32> hd;
+  uint8_t* out;                // start of this block's output
+  uint32_t op, cap;            // bytes produced so far (literals written + match bytes left open), ISIZE
+  uint32_t acc, sh;            // literal bytes of the current aligned 32-bit output word; bit position of output offset `op` inside it
+  uint32_t dirty;              // the current word holds literal bytes that have not been stored yet (acc alone cannot tell: a literal may be 0)
+  int32_t lo_full, hi_full;    // words whose first byte lies at output offset [lo_full, hi_full) belong to this block alone
+  uint32_t mis;                // (address of out) & 3
+  uint32_t* tok; uint32_t ntok, lit_run;
+  int state, status, bfinal; uint32_t copy_len; uint16_t slow_sym;
+
+  // sym_store: 320 uint16 of lane-private scratch (288 literal/length symbols + 32 distance symbols); tok_region: TOK_CAP words
+  IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* o, uint32_t isize, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store, uint32_t* tok_region) {
+    hl.symbol = sym_store; hd.symbol = sym_store + 288;
+    br.init(cdata, clen); out = o; op = 0; cap = isize; acc = 0; dirty = 0; mis = (uint32_t)((uintptr_t)o & 3); sh = mis * 8;
+    lo_full = mis ? (int32_t)(4 - mis) : 0; hi_full = (int32_t)isize - (int32_t)(((uintptr_t)o + isize) & 3) - 3;   // first + 4 <= aligned end
+    tok = tok_region; ntok = 0; lit_run = 0;
+    hl.lut.bind(lit_lut_base, lane); hd.lut.bind(dist_lut_base, lane);
+    // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][dist aux (32)][lit aux (32)], all lane-interleaved
+    hd.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES, lane); hl.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES + (size_t)32 * LANES, lane);
+    state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = 0; slow_sym = 0;
+  }
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; ntok = 0; op = 0; cap = 0; }
+  IRF_HD bool done() const { return state == LS_DONE; }
+  IRF_HD void fail(int code) { status = code; state = LS_DONE; }
+
+  // Stores the word that holds output offset `o` (its literal bytes are in acc; bytes of open matches are zero and are filled in
+  // by the resolve phase): one aligned store when the word lies wholly inside this block, byte by byte otherwise (the first and
+  // the last word can be shared with the neighbouring blocks, which other warps write).
+  IRF_HD void flush_word_at(uint32_t o) {
+    const int32_t first = (int32_t)((o + mis) & ~3u) - (int32_t)mis;   // output offset of the word's first byte (negative: it starts before the block)
+    uint8_t* wp = out + first;
+    if (first >= lo_full && first < hi_full) *(uint32_t*)wp = acc;
+    else { for (int j = 0; j < 4; j++) { int32_t q = first + j; if (q >= 0 && q < (int32_t)cap) wp[j] = (uint8_t)(acc >> (8 * j)); } }
+    acc = 0; dirty = 0;
+  }
+  IRF_HD void put_literal(uint32_t byte) {   // caller has checked op < cap
+    acc |= byte << sh; sh += 8; dirty = 1;
+    if (sh == 32) { flush_word_at(op); sh = 0; }
+    op++;
+    if (++lit_run == 255) { tok[ntok++] = tok_make(255, 0, 1); lit_run = 0; }
+  }
+  IRF_HD void put_match(uint32_t len, uint32_t dist) {   // caller has checked the ranges
+    tok[ntok++] = tok_make(lit_run, len, dist); lit_run = 0;
+    if (sh + 8 * len < 32) { sh += 8 * len; op += len; return; }      // the match ends inside the current word: its bytes stay zero in acc
+    if (dirty) flush_word_at(op);                                      // literal bytes before the match in this word
+    op += len; sh = ((op + mis) & 3u) * 8; acc = 0;
+  }
+  IRF_HD void finish() {
+    if (dirty) flush_word_at(op);   // dirty implies 0 < sh < 32: offset `op` (even when it equals cap) still lies in the started word
+    status = op == cap ? INF_OK : INF_ERR_ISIZE; state = LS_DONE;
+  }
+
+  IRF_HD void header() {
+    uint8_t lens[320];
+    br.refill();
+    bfinal = (int)br.take(1); int btype = (int)br.take(2);
+    if (btype == 0) {  // stored block: rare in BAM; its bytes are literals
+      br.drop(br.bc & 7); br.refill();
+      uint32_t len = br.take(16); br.refill(); uint32_t nlen = br.take(16);
+      if ((len ^ nlen) != 0xffffu) return fail(INF_ERR_STORED);
+      if (op + len > cap) return fail(INF_ERR_OVERRUN_OUT);
+      for (uint32_t i = 0; i < len; i++) { br.refill(); put_literal(br.take(8)); if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); }
+      state = bfinal ? LS_FINISH : LS_HEADER; return;
+    }
+    if (btype == 3) return fail(INF_ERR_BTYPE);
+    if (btype == 1) {
+      int i = 0;
+      for (; i < 144; i++) lens[i] = 8; for (; i < 256; i++) lens[i] = 9; for (; i < 280; i++) lens[i] = 7; for (; i < 288; i++) lens[i] = 8;
+      if (!hl.build(lens, 288)) return fail(INF_ERR_CODELEN);
+      for (i = 0; i < 32; i++) lens[i] = 5;  // 30 and 31 complete the code but never occur
+      if (!hd.build(lens, 32)) return fail(INF_ERR_CODELEN);
+    } else {
+      br.refill();
+      int hlit = (int)br.take(5) + 257, hdist = (int)br.take(5) + 1, hclen = (int)br.take(4) + 4;
+      if (hlit > 286 || hdist > 30) return fail(INF_ERR_CODELEN);
+      const uint8_t order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+      for (int i = 0; i < 19; i++) lens[i] = 0;
+      for (int i = 0; i < hclen; i++) { br.refill(); lens[order[i]] = (uint8_t)br.take(3); }
+      // the code-length code (<= 7 bits) borrows the distance LUT region
+      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.aux.base = hd.aux.base;
+      if (!hc.build(lens, 19)) return fail(INF_ERR_CODELEN);
+      int idx = 0;
+      while (idx < hlit + hdist) {
+        br.refill();
+        int sym = hc.decode(br);
+        if (sym < 0) return fail(INF_ERR_CODELEN);
+        if (sym < 16) lens[idx++] = (uint8_t)sym;
+        else {
+          int rep, val = 0;
+          if (sym == 16) { if (idx == 0) return fail(INF_ERR_CODELEN); val = lens[idx - 1]; rep = 3 + (int)br.take(2); }
+          else if (sym == 17) rep = 3 + (int)br.take(3);
+          else rep = 11 + (int)br.take(7);
+          if (idx + rep > hlit + hdist) return fail(INF_ERR_CODELEN);
+          while (rep--) lens[idx++] = (uint8_t)val;
+        }
+        if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
+      }
+      if (lens[256] == 0) return fail(INF_ERR_CODELEN);
+      if (!hl.build(lens, hlit)) return fail(INF_ERR_CODELEN);
+      if (!hd.build(lens + hlit, hdist)) return fail(INF_ERR_CODELEN);
+    }
+    state = LS_SYMBOL;
+  }
+
+  IRF_HD void handle_dist(int ds) {
+    if (ds > 29) return fail(INF_ERR_SYMBOL);
+    uint32_t dist;
+    if (ds < 4) dist = (uint32_t)ds + 1u;
+    else { int xb = (ds >> 1) - 1; dist = ((2u + ((uint32_t)ds & 1u)) << xb) + 1u + br.take(xb); }
+    if (dist > op) return fail(INF_ERR_DIST);
+    if (op + copy_len > cap) return fail(INF_ERR_OVERRUN_OUT);
+    if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
+    put_match(copy_len, dist); state = LS_SYMBOL;
+  }
+  IRF_HD void handle_litlen(int sym) {
+    if (sym < 256) { if (op >= cap) return fail(INF_ERR_OVERRUN_OUT); put_literal((uint32_t)sym); return; }
+    if (sym == 256) { if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); state = bfinal ? LS_FINISH : LS_HEADER; return; }
+    if (sym > 285) return fail(INF_ERR_SYMBOL);
+    uint32_t len;
+    if (sym < 265) len = (uint32_t)sym - 254u;
+    else if (sym == 285) len = 258;
+    else { int xb = (sym - 261) >> 2; len = ((4u + ((uint32_t)(sym - 261) & 3u)) << xb) + 3u + br.take(xb); }
+    copy_len = len;
+    br.refill();
+    uint16_t e = hd.lut.get(br.peek(DIST_BITS)); int l = e & 15;
+    if (l) { br.drop(l); return handle_dist(e >> 4); }
+    int idx = hd.slow_index(br, hd.head15(br));
+    if (idx < 0) return fail(INF_ERR_SYMBOL);
+    slow_sym = hd.symbol[idx]; state = LS_SLOWDIST;   // local-memory load: consumed in the next iteration
+  }
+  // One literal/length symbol (with its distance) per call, in every lane that is decoding.
+  IRF_HD void symbol() {
+    br.refill();  // >= 33 bits: a 15-bit length code + 5 extra bits, then (after the refill in handle_litlen) 15 + 13 for the distance
+    uint16_t e = hl.lut.get(br.peek(LIT_BITS)); int l = e & 15;
+    if (l) { br.drop(l); return handle_litlen(e >> 4); }
+    int idx = hl.slow_index(br, hl.head15(br));
+    if (idx < 0) return fail(INF_ERR_SYMBOL);
+    slow_sym = hl.symbol[idx]; state = LS_SLOWLIT;      // local-memory load: consumed in the next iteration
+  }
+  IRF_HD void step(bool allow_header = true) {
+    if (state == LS_SLOWLIT) { state = LS_SYMBOL; handle_litlen(slow_sym); }
+    else if (state == LS_SLOWDIST) handle_dist(slow_sym);
+    else if (state == LS_SYMBOL) symbol();
+    else if (state == LS_HEADER && allow_header) header();
+    if (state == LS_FINISH) finish();
+  }
+};
+
+// Scalar resolve of one block's tokens (the reference semantics of the warp-wide resolve in kernels.cu; used by tests/emu).
+IRF_HD bool tok_resolve_scalar(uint8_t* out, uint32_t isize, const uint32_t* tok, uint32_t ntok) {
+  uint32_t pos = 0;
+  for (uint32_t i = 0; i < ntok; i++) {
+    uint32_t t = tok[i], lit = tok_lit(t), ml = tok_mlen(t), d = tok_dist(t);
+    pos += lit; if (pos + ml > isize || (ml && d > pos)) return false;
+    for (uint32_t k = 0; k < ml; k++) out[pos + k] = out[pos + k - d];
+    pos += ml;
+  }
+  return pos <= isize;
+}
+template <int LANES, int LIT_BITS, int DIST_BITS>
+IRF_HD int inflate_block_tok(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint32_t* tok_region, uint32_t* ntok_out = nullptr) {
+  TokLane<LANES, LIT_BITS, DIST_BITS> L; uint16_t sym_store[320];
+  L.start(cdata, clen, out, isize, lit_lut_base, dist_lut_base, lane, sym_store, tok_region);
+  while (!L.done()) L.step();
+  if (ntok_out) *ntok_out = L.ntok;
+  if (L.status) return L.status;
+  return tok_resolve_scalar(out, isize, tok_region, L.ntok) ? INF_OK : INF_ERR_DIST;
+}
+
+}  // namespace irf

@@ -16,6 +16,7 @@ namespace irf {
 static unsigned long long g_launches = 0;  // kernels launched by this library (bench.py reports it as gpu_launches)
 unsigned long long launch_counter() { return g_launches; }
 #define IRF_LAUNCHED() (++g_launches)
+void note_launch() { IRF_LAUNCHED(); }
 
 // ------------------------------------------------------------------------------------------------
 // small device helpers
@@ -141,10 +142,12 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
     inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();
   }
 }
+size_t inflate_scratch_bytes(int variant, int nblk) { return variant == 12 && nblk > 0 ? inflate_tok_scratch_bytes(nblk) : 0; }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
   // The shared-memory output-ring variants (1, 6, 9: RB > 0) are not offered any more: their sector flush raised a misaligned-address
   // fault for some output alignments (seen once the test suite ran them after other tests), and they measured slower anyway.
   if (variant == 1 || variant == 6 || variant == 9) throw std::string("inflate_variant ") + std::to_string(variant) + " (shared-memory output ring) is disabled: its sector flush faults on some output alignments";
+  if (variant == 12) { launch_inflate_tok(a, s); g_inflate_lanes = inflate_tok_lanes(); return; }   // two-phase kernel: token decode per lane, then warp-wide match resolve (inflate_tok.cu)
   switch (variant) {   // <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, output ring bits>
     case 2: launch_inflate_t<4, 6, 5, 1, 0, 0, 1>(a, s); break;   // pre-written output sectors
     case 3: launch_inflate_t<4, 6, 6, 1, 0, 0, 1>(a, s); break;
@@ -778,11 +781,13 @@ constexpr int IS_THREADS = 256, IS_SMEM_BINS = 8192;
 __device__ __forceinline__ u32 depth_at(const int32_t* depth, u64 P, u64 c, int sel) { return sel < 0 ? (u32)(depth[c] + depth[P + c]) : (u32)depth[(u64)sel * P + c]; }
 
 __global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, const int32_t* __restrict__ depth, const IntronDesc* __restrict__ introns, const IntronBlock* __restrict__ blocks,
-                                                                   u32 n_introns, int directionality, u32 trim_center, u32* __restrict__ scratch, u32 scratch_bins, IntronRow* __restrict__ rows) {
+                                                                   u32 n_introns, int directionality, u32 trim_center, u32* __restrict__ scratch, u32 scratch_bins, IntronRow* __restrict__ rows,
+                                                                   const u32* __restrict__ list) {   // list: optional indices of the introns to compute (region-owned multi-GPU runs); n_introns entries
   __shared__ u32 sh_hist[IS_SMEM_BINS]; __shared__ u32 sh_red[IS_THREADS / 32]; __shared__ u32 sh_max; __shared__ u64 sh_edge[4];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   u32* ghist = scratch + (u64)blockIdx.x * scratch_bins;
-  for (u32 it = blockIdx.x; it < n_introns; it += gridDim.x) {
+  for (u32 li = blockIdx.x; li < n_introns; li += gridDim.x) {
+    const u32 it = list ? list[li] : li;
     const IntronDesc in = introns[it];
     int sel = -1;
     if (directionality != 0) { bool measureDir = in.plus != 0; if (directionality < 0) measureDir = !measureDir; sel = measureDir ? 1 : 0; }
@@ -848,8 +853,45 @@ __global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, c
   }
 }
 void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
-                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s) {
-  if (n_introns) { intron_stats_kernel<<<grid, IS_THREADS, 0, s>>>(T, depth, introns, blocks, n_introns, directionality, trim_center, scratch, scratch_bins, rows); IRF_LAUNCHED(); }
+                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list) {
+  if (n_introns) { intron_stats_kernel<<<grid, IS_THREADS, 0, s>>>(T, depth, introns, blocks, n_introns, directionality, trim_center, scratch, scratch_bins, rows, list); IRF_LAUNCHED(); }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Region-owned depth (multi-GPU, SURVEY.md §8e "Depth needs no reduction (region-owned)").  Every measured segment has one
+// owning rank; a rank's difference counters outside its own segments are almost all zero (a coordinate-sorted shard covers
+// its own region plus the reads that reach over the cut), so instead of all-reducing the whole table each rank lists its
+// non-zero foreign counters as (index, value) and the owners add them.
+__global__ void __launch_bounds__(256) foreign_depth_kernel(const int32_t* __restrict__ diff, u64 P, const u32* __restrict__ seg_start, const u32* __restrict__ seg_end, const u64* __restrict__ seg_coff,
+                                                             const uint8_t* __restrict__ seg_owner, u32 nseg, u32 me, u64* __restrict__ out_idx, int32_t* __restrict__ out_val, u64* __restrict__ cursor, u64 cap) {
+  const u32 lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  for (u32 s = blockIdx.x * wpb + (threadIdx.x >> 5); s < nseg; s += gridDim.x * wpb) {
+    if (seg_owner[s] == me) continue;
+    const u64 c0 = seg_coff[s]; const u32 n = seg_end[s] - seg_start[s] + 1;
+    for (int dir = 0; dir < 2; dir++) {
+      const u64 base = (u64)dir * P + c0;
+      for (u32 o = 0; o < n; o += 32) {
+        const u32 i = o + lane; const int32_t v = i < n ? diff[base + i] : 0;
+        const u32 m = __ballot_sync(0xffffffffu, v != 0); if (!m) continue;
+        u64 at = 0; if (lane == 0) at = atomicAdd(cursor, (u64)__popc(m)); at = __shfl_sync(0xffffffffu, at, 0) + __popc(m & ((1u << lane) - 1u));
+        if (v != 0 && at < cap) { out_idx[at] = base + i; out_val[at] = v; }
+      }
+    }
+  }
+}
+__global__ void import_depth_kernel(int32_t* __restrict__ diff, u64 P, const u64* __restrict__ seg_coff, const uint8_t* __restrict__ seg_owner, u32 nseg, u32 me,
+                                    const u64* __restrict__ idx, const int32_t* __restrict__ val, u64 n) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+  const u64 g = idx[i], c = g >= P ? g - P : g;
+  u32 lo = 0, hi = nseg;                                  // last segment whose first slot is <= c
+  while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (seg_coff[mid] <= c) lo = mid; else hi = mid; }
+  if (seg_owner[lo] == me) atomicAdd(&diff[g], val[i]);
+}
+void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s) {
+  if (nseg) { foreign_depth_kernel<<<148 * 8, 256, 0, s>>>(T.diff, T.P, T.seg_start, T.seg_end, T.seg_coff, seg_owner, nseg, me, out_idx, out_val, cursor, cap); IRF_LAUNCHED(); }
+}
+void launch_import_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const u64* idx, const int32_t* val, u64 n, cudaStream_t s) {
+  u64 g = (n + 255) / 256; if (g && nseg) { import_depth_kernel<<<(unsigned)g, 256, 0, s>>>(T.diff, T.P, T.seg_coff, seg_owner, nseg, me, idx, val, n); IRF_LAUNCHED(); }
 }
 
 }  // namespace irf

@@ -10,6 +10,7 @@ struct InflateArgs {
   int nblk; int* status; int* err; unsigned int* next_block;   // next_block: device work counter, zeroed by the launcher
   const unsigned long long* watermark;   // optional: bytes of `comp` that have landed so far (streaming from the host); null = all resident
   const u32* list;                       // optional: nblk indices into the block arrays (blocks not listed are inflated elsewhere)
+  uint32_t* tok_scratch = nullptr; size_t tok_scratch_bytes = 0;   // two-phase kernel (variant 12): match-token scratch, inflate_scratch_bytes() bytes
 };
 struct FrameArgs {
   const uint8_t* U; const u64* u_off; const u32* u_len; int nblk; u64 Uend; u64 rec0; int rec0_valid;  // rec0: inflated offset of the first record when known exactly
@@ -19,6 +20,11 @@ struct FrameArgs {
 };
 
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
+size_t inflate_scratch_bytes(int variant, int nblk);   // device scratch the chosen kernel needs for a launch over nblk blocks (0 for the one-phase variants)
+void launch_inflate_tok(const InflateArgs& a, cudaStream_t s);   // inflate_tok.cu
+size_t inflate_tok_scratch_bytes(int nblk);
+int inflate_tok_lanes();
+void note_launch();                                     // bumps the library's kernel-launch counter (launchers outside kernels.cu)
 int inflate_resident_lanes();
 void set_inflate_cta_cap(int ctas_per_sm);
 // CRC-32 of every inflated BGZF block against the value in its footer (what `gzip -cd` checks for the reference)
@@ -47,6 +53,8 @@ void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s);
 u64 depth_scan_tiles(u64 n);
 void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s);
 void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
-                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s);
+                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list = nullptr);
+void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s);
+void launch_import_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const u64* idx, const int32_t* val, u64 n, cudaStream_t s);
 
 }  // namespace irf

@@ -12,13 +12,21 @@ Exchange steps (all integer, so outputs are identical for every GPU count):
                 all-gathered; every rank pairs the gathered set and counts the pairs whose key it owns.
   2. junctions: the three JunctionCount hash tables are exported as dense (key, counts) lists, all-gathered
                 and re-inserted (slot positions differ between ranks, so they cannot be reduced in place).
-  3. additive:  depth difference counters, span-point, ROI, chromosome and read counters are all-reduced
-                (SUM) in place on the library's device buffers (NCCL over NVLink).
-Afterwards every rank holds the complete tables and runs irf_finalize; rank 0 writes the files.
+  3. additive:  span-point, ROI, chromosome and read counters are all-reduced (SUM) in place on the library's
+                device buffers (NCCL over NVLink).
+  4. depth:     region-owned (§8e).  Every measured segment has one owning rank, chosen from the genomic position
+                of each rank's first record; a rank lists its non-zero difference counters in foreign segments
+                (reads reaching over a cut, cross-shard pairs: KBs to MBs) and the owners add them.  Nothing
+                table-sized crosses NVLink.  (A shard that is not a genomic region - unsorted input - would list
+                most of its counters; above FOREIGN_DENSE_LIMIT entries the table is all-reduced instead.)
+  5. rows:      irf_finalize computes the per-intron statistics of the OWNED introns only; the row tables (all
+                other rows zero) are summed as 64-bit integers and irf_finalize_rows brings them to the host.
+Afterwards every rank holds the complete tables; rank 0 writes the files.
 """
 import numpy as np
 
 _BGZF_MAGIC = bytes([31, 139, 8, 4])
+FOREIGN_DENSE_LIMIT = 1 << 27   # foreign depth entries (all ranks together) above which the depth table is all-reduced instead
 
 
 def _is_block_start(buf, off):
@@ -242,16 +250,23 @@ def run_plan(core, plan, device=None, group=None, restage=True):
     core.count()
     info = dict(cuts=plan.cuts, recount=0)
     if world > 1:
-        # ---- frame handshake: my first record must be where my left neighbour's last record ends
-        e0, ex = core.frame_info()
-        mine = torch.tensor([e0, ex], dtype=torch.int64, device=dev)
-        allv = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(allv, mine, group=group)
-        if rank > 0 and int(allv[rank][0]) != int(allv[rank - 1][1]):
-            core.set_option("entry0", int(allv[rank - 1][1]))
-            core.reset()
-            core.count()
-            info["recount"] = 1
+        # ---- frame handshake: my first record must be where my left neighbour's last record ends.  A recount changes the
+        # exit a rank reports, so the values are exchanged again until nobody has to move (one round in practice).
+        for _ in range(world + 1):
+            e0, ex = core.frame_info()
+            mine = torch.tensor([e0, ex], dtype=torch.int64, device=dev)
+            allv = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(allv, mine, group=group)
+            bad = [r for r in range(1, world) if int(allv[r][0]) != int(allv[r - 1][1])]
+            if not bad:
+                break
+            if rank in bad:
+                core.set_option("entry0", int(allv[rank - 1][1]))
+                core.reset()
+                core.count()
+                info["recount"] += 1
+        else:
+            raise RuntimeError("record framing of neighbouring shards does not agree")
         # ---- 1. halo
         hb, hnb, ho, hnr = core.export_halo()
         _sync(dev)
@@ -263,27 +278,62 @@ def run_plan(core, plan, device=None, group=None, restage=True):
         _sync(dev)
         core.import_halo(all_bytes.data_ptr(), int(sum(blens)), all_offs.data_ptr() if all_offs.numel() else 0, int(all_offs.numel()), rank, world)
         info["halo_records"] = int(all_offs.numel())
-        # ---- 2. junction tables
+        # ---- 2. junction tables: the three exports travel in ONE gather ([n0, n1, n2 | keys | counts as 64-bit words])
+        exp = [core.export_junctions(which) for which in range(3)]
+        _sync(dev)
+        packed = torch.cat([torch.tensor([e[2] for e in exp], dtype=torch.int64, device=dev)]
+                           + [_wrap(e[0], e[2], "<i8", dev) for e in exp] + [_wrap(e[1], e[2], "<i8", dev) for e in exp])
+        got, _ = _all_gather_var(packed, group, dist)
+        _sync(dev)
         for which in range(3):
-            kp, cp, nk = core.export_junctions(which)
-            _sync(dev)
-            keys, klens = _all_gather_var(_wrap(kp, nk, "<i8", dev), group, dist)
-            cnts, _ = _all_gather_var(_wrap(cp, nk * 2, "<i4", dev), group, dist)
-            _sync(dev)
+            ks, cs = [], []
             for r in range(world):
-                if r != rank and klens[r]:
-                    k, c = keys[r].contiguous(), cnts[r].contiguous()
-                    core.import_junctions(which, k.data_ptr(), c.data_ptr(), klens[r])
-        # ---- 3. additive tables, in place on the library's buffers
-        for name, typestr in (("diff", "<i4"), ("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
+                if r == rank:
+                    continue
+                n = [int(x) for x in got[r][:3].tolist()]
+                k0 = 3 + sum(n[:which])
+                c0 = 3 + sum(n) + sum(n[:which])
+                ks.append(got[r][k0:k0 + n[which]])
+                cs.append(got[r][c0:c0 + n[which]])
+            k, c = torch.cat(ks).contiguous(), torch.cat(cs).contiguous()
+            if k.numel():
+                core.import_junctions(which, k.data_ptr(), c.data_ptr(), int(k.numel()))
+        # ---- 3. small additive tables, in place on the library's buffers
+        for name, typestr in (("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
             p, cnt, _ = core.device_table(name)
             if cnt:
                 dist.all_reduce(_wrap(p, cnt, typestr, dev), op=dist.ReduceOp.SUM, group=group)
+        # ---- 4. depth: region-owned
+        rid, pos = core.first_record()
+        mine = torch.tensor([rid, pos], dtype=torch.int64, device=dev)
+        firsts = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(firsts, mine, group=group)
+        core.owner_plan([int(f[0]) for f in firsts], [int(f[1]) for f in firsts], rank)
+        ip, vp, nf = core.export_foreign_depth()
+        nfs = torch.tensor([nf], dtype=torch.int64, device=dev)
+        dist.all_reduce(nfs, op=dist.ReduceOp.SUM, group=group)
+        info["foreign_depth_entries"] = int(nfs.item())
+        if info["foreign_depth_entries"] > FOREIGN_DENSE_LIMIT:     # not region-shaped shards: the dense merge is cheaper
+            p, cnt, _ = core.device_table("diff")
+            dist.all_reduce(_wrap(p, cnt, "<i4", dev), op=dist.ReduceOp.SUM, group=group)
+        else:
+            idx, _ = _all_gather_var(_wrap(ip, nf, "<i8", dev), group, dist)
+            val, _ = _all_gather_var(_wrap(vp, nf, "<i4", dev), group, dist)
+            ai, av = torch.cat(idx).contiguous(), torch.cat(val).contiguous()
+            _sync(dev)
+            if ai.numel():
+                core.import_depth(ai.data_ptr(), av.data_ptr(), int(ai.numel()))
         _sync(dev)
     core.finalize()
+    if world > 1:
+        # ---- 5. rows of the owned introns -> every rank (integer SUM: exactly one rank holds a non-zero row)
+        for name in ("rows_nondir",) + (("rows_dir",) if core.directionality != 0 else ()):
+            p, cnt, _ = core.device_table(name)
+            if cnt:
+                dist.all_reduce(_wrap(p, cnt, "<i8", dev), op=dist.ReduceOp.SUM, group=group)
+        _sync(dev)
+        core.finalize_rows()
     return info
-
-
 
 
 def run_sharded(core, buf, rank, world, device=None, group=None, lookahead=1 << 18, bai=None):
@@ -353,13 +403,38 @@ def run_sharded_local(cores, buf, lookahead=1 << 18, header_probe=1 << 20, bai=N
                 for q, (k, c, nk) in enumerate(exp):
                     if q != r and nk:
                         core.import_junctions(which, k.data_ptr(), c.data_ptr(), nk)
-        for name, typestr in (("diff", "<i4"), ("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
+        for name, typestr in (("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
             views = [_wrap(*c.device_table(name)[:2], typestr, dev) for c in cores]
             if views[0].numel():
                 total = torch.stack(views).sum(0)
                 for v in views:
                     v.copy_(total)
+        # depth: region-owned, as in run_plan
+        firsts = [c.first_record() for c in cores]
+        for r, core in enumerate(cores):
+            core.owner_plan([f[0] for f in firsts], [f[1] for f in firsts], r)
+        lists = []
+        for c in cores:
+            ip, vp, nf = c.export_foreign_depth()
+            torch.cuda.synchronize()
+            lists.append((_wrap(ip, nf, "<i8", dev).clone(), _wrap(vp, nf, "<i4", dev).clone()))
+        ai, av = torch.cat([l[0] for l in lists]).contiguous(), torch.cat([l[1] for l in lists]).contiguous()
+        info["foreign_depth_entries"] = int(ai.numel())
+        torch.cuda.synchronize()
+        if ai.numel():
+            for core in cores:
+                core.import_depth(ai.data_ptr(), av.data_ptr(), int(ai.numel()))
         torch.cuda.synchronize()
     for core in cores:
         core.finalize()
+    if world > 1:
+        for name in ("rows_nondir",) + (("rows_dir",) if cores[0].directionality != 0 else ()):
+            views = [_wrap(*c.device_table(name)[:2], "<i8", dev) for c in cores]
+            if views[0].numel():
+                total = torch.stack(views).sum(0)
+                for v in views:
+                    v.copy_(total)
+        torch.cuda.synchronize()
+        for core in cores:
+            core.finalize_rows()
     return info

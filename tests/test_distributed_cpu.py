@@ -41,13 +41,38 @@ class FakeCore:
         self.halo = (np.arange(8 * (rank + 1), dtype=np.uint8), np.array([0, 8][: rank + 1] if rank == 0 else [0, 8], np.int64))
         self.imported_halo = None
         self.keep = []
+        self.directionality = 0
+        self.rows = np.zeros(8, np.int64)
+        self.t["rows_nondir"] = self.rows
+        self.owner = None
     def read_header(self, p, n): self.calls.append("header")
     def reset(self): self.calls.append("reset")
     def stage(self, p, own, total, has_header=True): self.calls.append(("stage", own, total, has_header))
     def count(self): self.calls.append("count")
     def set_option(self, k, v): self.calls.append(("opt", k, v))
     def frame_info(self): return (7 if self.rank else 0), 7   # consistent hand-shake: my entry == left neighbour's exit
-    def finalize(self): self.calls.append("finalize")
+    def finalize(self):
+        self.calls.append("finalize")
+        for j in range(8):            # owner mode: only the rows of the introns this rank owns
+            if j * self.world // 8 == self.rank:
+                self.rows[j] = (j + 1) * 100
+    def finalize_rows(self): self.calls.append("finalize_rows")
+    # region-owned depth: slot i of the 40 belongs to rank i * world // 40
+    def first_record(self): return self.rank, 1000 * self.rank
+    def owner_plan(self, refids, positions, rank): self.owner = (list(refids), list(positions), rank)
+    def _owner_of(self, i): return (i % 40) * self.world // 40
+    def export_foreign_depth(self):
+        d = self.t["diff"]
+        idx = np.array([i for i in range(d.size) if d[i] != 0 and self._owner_of(i) != self.rank], np.int64)
+        val = d[idx].astype(np.int32)
+        self.keep += [idx, val]
+        return (idx.ctypes.data if idx.size else 0), (val.ctypes.data if val.size else 0), idx.size
+    def import_depth(self, ip, vp, n):
+        import ctypes
+        idx = np.frombuffer((ctypes.c_int64 * n).from_address(ip), np.int64); val = np.frombuffer((ctypes.c_int32 * n).from_address(vp), np.int32)
+        for i, v in zip(idx, val):
+            if self._owner_of(int(i)) == self.rank:
+                self.t["diff"][int(i)] += int(v)
     def device_table(self, name):
         a = self.t[name]
         return (a.ctypes.data if a.size else 0), a.size, a.itemsize
@@ -77,6 +102,7 @@ def _worker(rank, world, port, path, q):
     buf = np.fromfile(path, dtype=np.uint8)
     core = FakeCore(rank, world)
     info = run_sharded(core, buf, rank, world, device="cpu")
+    assert core.owner == ([0, 1], [0, 1000], rank)
     q.put((rank, {k: v.tolist() for k, v in core.t.items()}, core.j, core.imported_halo, core.calls, info["cuts"]))
     dist.barrier()
     dist.destroy_process_group()
@@ -96,9 +122,17 @@ def test_two_rank_merge_protocol_gloo(built, tmp_path):
     assert all(p.exitcode == 0 for p in ps)
     (r0, t0, j0, h0, c0, cuts0), (r1, t1, j1, h1, c1, cuts1) = res
     assert cuts0 == cuts1 and len(cuts0) == 3
-    # additive tables: both ranks end with the element-wise sum
-    assert t0 == t1
-    assert t0["diff"] == (np.arange(40) * 3).tolist() and t0["spans"] == [3] * 6 and t0["chr"] == [1, 2] and t0["stats"] == (2 * np.arange(9) + 1).tolist()
+    # small additive tables: both ranks end with the element-wise sum
+    for name in ("spans", "chr", "stats", "rows_nondir"):
+        assert t0[name] == t1[name], name
+    assert t0["spans"] == [3] * 6 and t0["chr"] == [1, 2] and t0["stats"] == (2 * np.arange(9) + 1).tolist()
+    # depth is region-owned: each rank holds the complete sum in the slots it owns (rank 0: 0..19, rank 1: 20..39) and only its own
+    # contribution elsewhere; nothing table-sized was exchanged
+    want = (np.arange(40) * 3).tolist()
+    assert t0["diff"][:20] == want[:20] and t1["diff"][20:] == want[20:]
+    assert t0["diff"][20:] == np.arange(20, 40).tolist() and t1["diff"][:20] == (np.arange(20) * 2).tolist()
+    # rows: each rank computed its own introns, the integer sum gives both the whole table
+    assert t0["rows_nondir"] == [(j + 1) * 100 for j in range(8)]
     # junction tables: union of keys, shared key summed, identical on both ranks
     assert j0 == j1
     assert j0[0][1000] == [2, 0] and j0[0][5000] == [1, 2] and j0[0][5010] == [2, 2]
@@ -108,7 +142,7 @@ def test_two_rank_merge_protocol_gloo(built, tmp_path):
     # only rank 0 stages with the header; both finalize last
     assert ("stage", cuts0[1], c0[[isinstance(x, tuple) and x[0] == "stage" for x in c0].index(True)][2], True) in c0
     assert [x for x in c1 if isinstance(x, tuple) and x[0] == "stage"][0][3] is False
-    assert c0[-1] == "finalize" and c1[-1] == "finalize" and "opt" not in [x[0] for x in c0 + c1 if isinstance(x, tuple)]
+    assert c0[-2:] == ["finalize", "finalize_rows"] and c1[-2:] == ["finalize", "finalize_rows"] and "opt" not in [x[0] for x in c0 + c1 if isinstance(x, tuple)]
 
 
 def test_shard_cuts_from_a_bai_index(built, tmp_path):
