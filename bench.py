@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--de-percent-overlap", type=int, default=0, help="share of the file's chunks given to the decompression engine by the overlapped resident pipeline (library default when 0)")
     ap.add_argument("--resident-pipeline", type=int, default=-1, help="0 = count resident bytes stage by stage, 1 = overlapped pipeline when the input is large enough (library default), 2 = always")
     ap.add_argument("--numa-bind", type=int, default=0, help="1 = run this rank on the CPUs of its GPU's NUMA node (so its page-locked buffer is node-local); off by default, not yet measured")
+    ap.add_argument("--skip-parity", type=int, default=0, help="1 = skip the configs[0] parity check through the NCCL path that a multi-GPU run does before its timed loops")
     ap.add_argument("--de-percent", type=int, default=-1, help="share of BGZF blocks given to the hardware decompression engine (library default when < 0)")
     return ap.parse_args()
 
@@ -167,6 +168,58 @@ def run_reference(a):
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
+OUT_FILES = ["IRFinder-IR-nondir.txt", "IRFinder-IR-dir.txt", "IRFinder-JuncCount.txt", "IRFinder-SpansPoint.txt", "IRFinder-ChrCoverage.txt", "IRFinder-ROI.txt"]
+
+
+def sha_dir(d):
+    import hashlib
+    out = {}
+    for name in OUT_FILES:
+        p = os.path.join(d, name)
+        if os.path.exists(p):
+            out[name] = hashlib.sha256(open(p, "rb").read()).hexdigest()
+    return out
+
+
+def nccl_parity_check(rank, world, local, dist):
+    """Before the timed loops of a multi-GPU run: BASELINE configs[0] (1M pairs 2x100 over a 50 Mb chr22-like genome) goes through the
+    real NCCL path (run_sharded over this process group) and rank 0 compares the six output files with the CPU restatement's
+    (the oracle as the checker, on the name-collated copy of the same reads).  Returns ("identical" | first differing file, sha256s)."""
+    import numpy as np
+    import torch
+    from irfinder_b200 import IRFinderCore, build, synth
+    from irfinder_b200.distributed import run_sharded
+    wd = os.path.join("/dev/shm" if os.path.isdir("/dev/shm") else "/tmp", "irf_bench_parity")
+    if rank == 0:
+        meta = gen_cached(wd, **synth.CONFIGS["C1"])
+    dist.barrier()
+    meta = synth.describe(wd)
+    buf = np.fromfile(meta["sorted"], dtype=np.uint8)
+    core = IRFinderCore(local)
+    core.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])
+    info = run_sharded(core, buf, rank, world, device=torch.device("cuda", local))
+    verdict, shas = None, {}
+    if rank == 0:
+        got = os.path.join(wd, "gpu_out")
+        shutil.rmtree(got, ignore_errors=True)
+        core.write_outputs(got)
+        want = os.path.join(wd, "oracle_out")
+        if not os.path.exists(os.path.join(want, "done")):
+            shutil.rmtree(want, ignore_errors=True)
+            oracle_run(build.build_oracle(), meta, meta["collated"], want)
+            open(os.path.join(want, "done"), "w").close()
+        verdict = "identical"
+        for name in OUT_FILES:
+            pa, pb = os.path.join(want, name), os.path.join(got, name)
+            if os.path.exists(pa) != os.path.exists(pb) or (os.path.exists(pa) and open(pa, "rb").read() != open(pb, "rb").read()):
+                verdict = name
+                break
+        shas = sha_dir(got)
+    core.close()
+    dist.barrier()
+    return verdict, shas, info.get("foreign_depth_entries")
+
+
 def run_b200(a):
     import numpy as np
     import torch
@@ -183,6 +236,11 @@ def run_b200(a):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     if a.numa_bind:
         numa_bind(local)
+    parity_nccl, parity_sha, parity_foreign = None, {}, None
+    if world > 1 and not a.skip_parity:
+        if rank == 0:
+            build.build_tools()
+        parity_nccl, parity_sha, parity_foreign = nccl_parity_check(rank, world, local, dist)
     total_pairs = a.pairs * world
     base = a.workdir
     if world > 1 and os.path.isdir("/dev/shm"):   # N shards are generated at once: keep them off a possibly small disk
@@ -342,6 +400,8 @@ def run_b200(a):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8 bytes -> int32/u32 counts, f64 ratios", "data": "synthetic",
             "config": {"workload": workload_name(a, total_pairs), "fragments": n_units, "records": n_records, "compressed_bytes": comp_bytes,
                        "inflated_bytes": infl_bytes, "l2": "inputs larger than L2 (no flush needed)", "sharding": "one BGZF byte range (genomic region) of the BAM per rank, resident in that rank's HBM; halo exchange + NCCL table merge inside every step" if world > 1 else "single GPU",
+                       "parity_nccl": parity_nccl, "parity_nccl_what": "configs[0] (1M pairs, chr22-like) through run_sharded over this NCCL group vs the CPU restatement, six files byte for byte" if world > 1 else None,
+                       "parity_nccl_sha256": parity_sha or None, "parity_nccl_foreign_depth_entries": parity_foreign, "output_sha256": sha_dir(outdir),
                        "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "checks": "ok" if all(checks.values()) else {k: v for k, v in checks.items() if not v}, "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes), "stage_ms": {k: round(v, 3) for k, v in e2e_stage.items()}},
             "gpu_launches": launches,

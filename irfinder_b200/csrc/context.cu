@@ -77,7 +77,7 @@ static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std:
 struct irf_ctx {
   int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr, s_de = nullptr, s_chk = nullptr;
   // options
-  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 0, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1, de_percent_overlap = 79, resident_pipeline = 1;
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 12, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1, de_percent_overlap = 79, resident_pipeline = 1;
   // references (host)
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header

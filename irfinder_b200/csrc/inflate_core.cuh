@@ -251,7 +251,7 @@ struct InflateLane {
     hd.aux.bind(dist_lut_base + DIST_LUT_U16, lane); hl.aux.bind(dist_lut_base + DIST_LUT_U16 + (size_t)32 * LANES, lane);
     state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = copy_dist = 0; pend_n = 0; slow_sym = 0;
   }
-  IRF_HD void idle() { state = LS_DONE; status = INF_OK; pend_n = 0; }
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; pend_n = 0; tick = 0; oc.init(nullptr, 0, nullptr, 0); }   // the driver loop keeps stepping idle lanes: their cursor must be inert
   IRF_HD bool done() const { return state == LS_DONE; }
   IRF_HD void fail(int code) { status = code; state = LS_DONE; }
 

@@ -8,6 +8,8 @@
 //            otherwise (a match may read what an earlier match of the same batch writes);
 // then claims the next 32.  Replaces `gzip -cd` of the reference pipeline; RFC 1951.
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include "common.cuh"
 #include "inflate_tok.cuh"
 #include "kernels.h"
@@ -20,48 +22,68 @@ __device__ __forceinline__ const void* shfl_ptr(const void* p, int src) {
   return (const void*)((unsigned long long)hi << 32 | lo);
 }
 
-// Phase B for one batch of up to 32 tokens of one block: lane i holds token i (mlen = 0: nothing to copy) and the output offset
-// `mstart` where its match begins.  Everything below the first unfinished match is final, which gives the readiness test.
-constexpr uint32_t TOK_LONG = 24;   // matches longer than this are copied by the whole warp
-__device__ __forceinline__ void resolve_batch(uint8_t* ob, uint32_t mstart, uint32_t ml, uint32_t d, int lane) {
+// developer counters (IRF_TOK_PROF=1 prints them after a launch): cycles in phase A / phase B summed over warps, decode votes,
+// table-build events, resolve batches and rounds
+__device__ unsigned long long g_tok_prof[8];
+
+// Phase B for one batch of up to 32 tokens of one block: lane i holds token i (ml = 0: nothing to copy), the output offsets
+// [mstart, mend) of its match and the distance d.  Literals are final already, so a match may be copied as soon as no unfinished
+// match of the batch overlaps its source bytes.  Holes are ordered like the tokens, so the matches that can overlap lane i's
+// source [src, need) form a range of lanes [lo, hi) found by two binary searches over the warp (shuffles); a round then costs one
+// ballot and one AND per lane, and the number of rounds is the depth of the dependency chains, not the number of dependent matches.
+constexpr uint32_t TOK_LONG = 16;   // matches longer than this are copied by the whole warp
+__device__ __forceinline__ void resolve_batch(uint8_t* ob, uint32_t mstart, uint32_t ml, uint32_t d, int lane, uint32_t& rounds) {
+  const uint32_t mend = mstart + ml, src = mstart - d, need = src + min(ml, d);   // source bytes [src, need) must be final before this match may be copied
+  uint32_t lo = 0, hi = 0;   // lo = lanes whose hole ends at or before src; hi = lanes whose hole starts before need
+#pragma unroll
+  for (int step = 16; step; step >>= 1) {
+    const uint32_t a = __shfl_sync(0xffffffffu, mend, (int)(lo + step - 1)), b = __shfl_sync(0xffffffffu, mstart, (int)(hi + step - 1));
+    if (a <= src) lo += step;
+    if (b < need) hi += step;
+  }
+  hi = min(hi, (uint32_t)lane);
+  const uint32_t dep = hi > lo ? ((1u << hi) - 1u) & ~((1u << lo) - 1u) : 0u;   // earlier lanes of the batch whose output this match reads
   bool pending = ml != 0;
-  const uint32_t need = mstart - d + min(ml, d);   // source bytes [mstart - d, need) must be final before this match may be copied
   for (;;) {
     const unsigned pm = __ballot_sync(0xffffffffu, pending);
     if (!pm) break;
-    const int f = __ffs(pm) - 1;                     // first unfinished match: all output below its start is final
-    const uint32_t fstart = __shfl_sync(0xffffffffu, mstart, f), fml = __shfl_sync(0xffffffffu, ml, f);
-    if (fml > TOK_LONG) {                            // warp-uniform: all 32 lanes copy match f
-      const uint32_t fd = __shfl_sync(0xffffffffu, d, f);
+    rounds++;
+    const bool ready = pending && !(pm & dep);           // the first pending lane has no pending lane below it: every round makes progress
+    unsigned rl = __ballot_sync(0xffffffffu, ready && ml > TOK_LONG);
+    while (rl) {                                         // long matches: all 32 lanes copy one match (warp-uniform loop)
+      const int f = __ffs(rl) - 1; rl &= rl - 1;
+      const uint32_t fstart = __shfl_sync(0xffffffffu, mstart, f), fml = __shfl_sync(0xffffffffu, ml, f), fd = __shfl_sync(0xffffffffu, d, f);
       uint8_t* dp = ob + fstart; const uint8_t* sp = dp - fd;
-      if (fd >= 32) {                                // a 32-byte slab never reads what the same slab writes; earlier slabs are ordered by the barrier
+      if (fd >= 32) {                                    // a 32-byte slab never reads what the same slab writes; earlier slabs are ordered by the barrier
         for (uint32_t k0 = 0; k0 < fml; k0 += 32) { if (k0 + lane < fml) dp[k0 + lane] = sp[k0 + lane]; __syncwarp(); }
-      } else {                                       // period shorter than a slab: every byte is a copy of one of the fd final bytes before the match
+      } else {                                           // period shorter than a slab: every byte is a copy of one of the fd final bytes before the match
         for (uint32_t k = lane; k < fml; k += 32) dp[k] = sp[k % fd];
       }
-      if (lane == f) pending = false;
-      __syncwarp();
-      continue;
     }
-    const bool ready = pending && ml <= TOK_LONG && (lane == f || need <= fstart);
-    if (ready) {
-      uint8_t* dp = ob + mstart; const uint8_t* sp = dp - d; uint32_t w = 0, rem = ml;
-      while (rem) {                                  // 8 bytes per round: loads first, then stores; the source index wraps inside the period,
-        const uint32_t k = rem < 8 ? rem : 8; uint32_t v[8];   // so overlapping (run-length) matches only ever read the d final bytes
-#pragma unroll
-        for (int j = 0; j < 8; j++) { if ((uint32_t)j < k) v[j] = sp[w]; w++; if (w == d) w = 0; }
-#pragma unroll
-        for (int j = 0; j < 8; j++) if ((uint32_t)j < k) dp[j] = (uint8_t)v[j];
-        dp += k; rem -= k;
+    if (ready && ml <= TOK_LONG) {
+      uint8_t* dp = ob + mstart; const uint8_t* sp = dp - d;
+      if (d >= 4) {
+        // four source bytes per trip from two aligned word loads and a funnel shift (the words may reach a few bytes beyond the
+        // source: those bytes are dropped).  d >= 4: a trip never reads what the same trip writes; what an earlier trip of this
+        // lane wrote is read back in program order.
+        uint32_t rem = ml;
+        do {
+          const uint32_t* wa = (const uint32_t*)((uintptr_t)sp & ~(uintptr_t)3); const uint32_t v = __funnelshift_r(wa[0], wa[1], ((uint32_t)(uintptr_t)sp & 3u) * 8u);
+          dp[0] = (uint8_t)v; if (rem > 1) dp[1] = (uint8_t)(v >> 8); if (rem > 2) dp[2] = (uint8_t)(v >> 16); if (rem > 3) dp[3] = (uint8_t)(v >> 24);
+          sp += 4; dp += 4; rem = rem > 4 ? rem - 4 : 0;
+        } while (rem);
+      } else {                                           // run-length match (period 1..3): byte by byte, the source index wraps inside the period
+        uint32_t w = 0;
+        for (uint32_t k = 0; k < ml; k++) { dp[k] = sp[w]; w++; if (w == d) w = 0; }
       }
-      pending = false;
     }
+    if (ready) pending = false;
     __syncwarp();   // orders this round's stores before the next round's loads (and before the next batch)
   }
 }
 
-template <int WARPS, int LB, int DB, int PATIENCE>
-__global__ void __launch_bounds__(WARPS * 32) inflate_tok_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
+template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
+__global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                                   uint8_t* U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                                   int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark,
                                                                   const u32* __restrict__ list, uint32_t* tok_scratch) {
@@ -92,22 +114,27 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_tok_kernel(const uint8_t* 
     TokLane<32, LB, DB> L;
     const bool work = in_range && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
     if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, my_tok); else L.idle();
-    // ---- phase A.  Votes once per four symbols; a table build (thousands of instructions that every lane of the warp pays for)
-    // starts only when no lane is left decoding, half the warp is waiting for one, or the waiting lanes have waited PATIENCE votes.
-    int waited = 0;
+    // ---- phase A.  One vote per four decode iterations.  A table build (thousands of instructions that every lane of the warp
+    // pays for) starts only when no lane is left decoding, half the warp is waiting for one, or the waiting lanes have waited
+    // PATIENCE votes; zlib closes a DEFLATE block after a fixed number of symbols, so lanes mostly arrive together anyway.
+    int waited = 0; const long long tA = clock64(); uint32_t votes = 0, builds = 0, batches = 0, rounds = 0;
     for (;;) {
       const unsigned active = __ballot_sync(0xffffffffu, !L.done());
       if (!active) break;
       const bool at_header = L.state == LS_HEADER;
       const unsigned mh = __ballot_sync(0xffffffffu, at_header);
-      bool allow = false;
-      if (mh) { allow = (active & ~mh) == 0 || __popc(mh) >= 16 || waited >= PATIENCE; waited = allow ? 0 : waited + 1; }
-      L.step(allow && at_header); __syncwarp();
+      if (mh) {
+        const bool allow = (active & ~mh) == 0 || __popc(mh) >= 16 || waited >= PATIENCE; waited = allow ? 0 : waited + 1; builds += allow;
+        if (allow && at_header) L.header();
+        __syncwarp();
+      }
+      votes++;
 #pragma unroll 1
-      for (int k = 0; k < 3; k++) { L.step(false); __syncwarp(); }
+      for (int k = 0; k < 4; k++) { if (L.state == LS_SYMBOL) L.iter(); __syncwarp(); }
+      L.check();
     }
     if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
-    __syncwarp();
+    __syncwarp(); const long long tB = clock64();
     // ---- phase B: the warp resolves the matches of its 32 blocks, one block at a time
     for (int j = 0; j < 32; j++) {
       const uint32_t n = __shfl_sync(0xffffffffu, L.ntok, j); const int st = __shfl_sync(0xffffffffu, L.status, j);
@@ -123,44 +150,66 @@ __global__ void __launch_bounds__(WARPS * 32) inflate_tok_kernel(const uint8_t* 
         for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
         const uint32_t mstart = pos + incl - ml;
         pos += __shfl_sync(0xffffffffu, incl, 31);
-        resolve_batch(ob, mstart, ml, tok_dist(t), lane);
+        resolve_batch(ob, mstart, ml, tok_dist(t), lane, rounds); batches++;
       }
     }
     __syncwarp();
+    if (lane == 0) { const long long tC = clock64(); atomicAdd(&g_tok_prof[0], (unsigned long long)(tB - tA)); atomicAdd(&g_tok_prof[1], (unsigned long long)(tC - tB)); atomicAdd(&g_tok_prof[2], votes);
+      atomicAdd(&g_tok_prof[3], builds); atomicAdd(&g_tok_prof[4], batches); atomicAdd(&g_tok_prof[5], rounds); atomicAdd(&g_tok_prof[6], 1ull); }
   }
 }
 
-static int g_tok_ctas[64] = {0}, g_tok_sms[64] = {0};
-template <int WARPS, int LB, int DB, int PATIENCE>
-static void tok_geometry(int& ctas_per_sm, int& sms, size_t& smem) {
-  smem = (size_t)WARPS * ((size_t)((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
+// One geometry record per kernel instantiation and device (the shared-memory opt-in and the occupancy are per device).
+struct TokGeom { int ctas_per_sm, sms; size_t smem; int warps; };
+template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
+static TokGeom tok_geometry() {
+  static int ctas[64] = {0}, sms[64] = {0};
+  const size_t smem = (size_t)WARPS * ((size_t)((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
   int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");
-  if (!g_tok_ctas[dev]) {   // per device: the shared-memory opt-in and the occupancy
-    auto kern = inflate_tok_kernel<WARPS, LB, DB, PATIENCE>;
+  if (!ctas[dev]) {
+    auto kern = inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB>;
     IRF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_tok_ctas[dev], kern, WARPS * 32, smem));
-    IRF_CUDA(cudaDeviceGetAttribute(&g_tok_sms[dev], cudaDevAttrMultiProcessorCount, dev));
-    if (g_tok_ctas[dev] < 1) g_tok_ctas[dev] = 1;
+    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas[dev], kern, WARPS * 32, smem));
+    IRF_CUDA(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
+    if (ctas[dev] < 1) ctas[dev] = 1;
   }
-  ctas_per_sm = g_tok_ctas[dev]; sms = g_tok_sms[dev];
+  return TokGeom{ctas[dev], sms[dev], smem, WARPS};
 }
-constexpr int TOK_WARPS = 4, TOK_LB = 6, TOK_DB = 5, TOK_PATIENCE = 24;
-
-// lanes (= BGZF blocks in flight) of a full grid, and the scratch a launch over nblk blocks needs
-int inflate_tok_lanes() { int c, s; size_t m; tok_geometry<TOK_WARPS, TOK_LB, TOK_DB, TOK_PATIENCE>(c, s, m); return c * s * TOK_WARPS * 32; }
-size_t inflate_tok_scratch_bytes(int nblk) {
-  int c, s; size_t m; tok_geometry<TOK_WARPS, TOK_LB, TOK_DB, TOK_PATIENCE>(c, s, m);
-  const int need = (nblk + TOK_WARPS * 32 - 1) / (TOK_WARPS * 32), grid = std::max(1, std::min(need, c * s));
-  return (size_t)grid * TOK_WARPS * 32 * TOK_CAP * sizeof(uint32_t);
-}
-void launch_inflate_tok(const InflateArgs& a, cudaStream_t s) {
-  int c, sms; size_t smem; tok_geometry<TOK_WARPS, TOK_LB, TOK_DB, TOK_PATIENCE>(c, sms, smem);
-  const int need = (a.nblk + TOK_WARPS * 32 - 1) / (TOK_WARPS * 32), grid = std::min(need, c * sms);
+template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
+static void tok_launch(const InflateArgs& a, cudaStream_t s) {
+  const TokGeom g = tok_geometry<WARPS, LB, DB, PATIENCE, MINB>();
+  const int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, g.ctas_per_sm * g.sms);
   if (grid <= 0) return;
-  if (!a.tok_scratch || a.tok_scratch_bytes < (size_t)grid * TOK_WARPS * 32 * TOK_CAP * sizeof(uint32_t)) throw std::string("inflate: token scratch missing or too small");
+  if (!a.tok_scratch || a.tok_scratch_bytes < (size_t)grid * WARPS * 32 * TOK_CAP * sizeof(uint32_t)) throw std::string("inflate: token scratch missing or too small");
+  const bool prof = getenv("IRF_TOK_PROF") != nullptr;
+  if (prof) { unsigned long long z[8] = {0}; IRF_CUDA(cudaMemcpyToSymbol(g_tok_prof, z, sizeof z)); }
   IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-  inflate_tok_kernel<TOK_WARPS, TOK_LB, TOK_DB, TOK_PATIENCE><<<grid, TOK_WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch);
+  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch);
   note_launch();
+  if (prof) { IRF_CUDA(cudaStreamSynchronize(s)); unsigned long long z[8]; IRF_CUDA(cudaMemcpyFromSymbol(z, g_tok_prof, sizeof z));
+    fprintf(stderr, "[tok] <%d warps, %d/%d-bit LUTs> grid %d x %d CTAs/SM: phase A %.1f Mcycles/claim, phase B %.1f Mcycles/claim, %llu claims; per claim: %.0f votes, %.1f table builds, %.0f batches, %.2f rounds/batch\n", WARPS, LB, DB, grid, g.ctas_per_sm,
+            z[0] / 1e6 / std::max(1ull, z[6]), z[1] / 1e6 / std::max(1ull, z[6]), z[6], (double)z[2] / std::max(1ull, z[6]), (double)z[3] / std::max(1ull, z[6]), (double)z[4] / std::max(1ull, z[6]), (double)z[5] / std::max(1ull, z[4])); }
+}
+// variants: literal/length and distance LUT width against warps per SM (shared memory per warp = (2^LB + 2^DB + 64) * 64 bytes)
+//   12: 6/5 bits, 20 warps per SM     13: 7/6 bits, 12 warps     14: 8/6 bits, 9 warps     15: 9/6 bits, 5 warps
+#define IRF_TOK_DISPATCH(variant, CALL) \
+  switch (variant) { case 13: CALL(4, 7, 6, 24, 3); break; case 14: CALL(3, 8, 6, 24, 3); break; case 15: CALL(1, 9, 6, 24, 5); break; default: CALL(4, 6, 5, 24, 5); break; }
+static TokGeom tok_geom_of(int variant) {
+  TokGeom g{};
+#define IRF_TOK_GEOM(W, LB, DB, P, M) g = tok_geometry<W, LB, DB, P, M>()
+  IRF_TOK_DISPATCH(variant, IRF_TOK_GEOM)
+  return g;
+}
+// lanes (= BGZF blocks in flight) of a full grid, and the scratch a launch over nblk blocks needs
+int inflate_tok_lanes(int variant) { const TokGeom g = tok_geom_of(variant); return g.ctas_per_sm * g.sms * g.warps * 32; }
+size_t inflate_tok_scratch_bytes(int variant, int nblk) {
+  const TokGeom g = tok_geom_of(variant);
+  const int per = g.warps * 32, need = (nblk + per - 1) / per, grid = std::max(1, std::min(need, g.ctas_per_sm * g.sms));
+  return (size_t)grid * per * TOK_CAP * sizeof(uint32_t);
+}
+void launch_inflate_tok(const InflateArgs& a, int variant, cudaStream_t s) {
+#define IRF_TOK_LAUNCH(W, LB, DB, P, M) tok_launch<W, LB, DB, P, M>(a, s)
+  IRF_TOK_DISPATCH(variant, IRF_TOK_LAUNCH)
 }
 
 }  // namespace irf

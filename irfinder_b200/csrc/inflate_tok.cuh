@@ -29,8 +29,14 @@ IRF_HD uint32_t tok_lit(uint32_t t) { return t >> 24; }
 IRF_HD uint32_t tok_mlen(uint32_t t) { return (t >> 15) & 511u; }
 IRF_HD uint32_t tok_dist(uint32_t t) { return (t & 32767u) + 1u; }
 
-// Decode states of a lane (LS_* of inflate_core.cuh are reused): HEADER, SYMBOL, SLOWLIT / SLOWDIST (a code longer than the
-// LUT was found in the previous iteration; its symbol was fetched from the lane's local-memory table meanwhile), DONE.
+// Decode states of a lane (LS_* of inflate_core.cuh are reused): HEADER (a table build is due), SYMBOL (decoding), FINISH, DONE.
+//
+// Written for SIMT execution: iter() is ONE straight body that every decoding lane of a warp runs together — refill, one
+// literal/length look-up, then either up to two literals or one match (length + distance + token).  The first version of this
+// routine kept the round-1 layout (separate states for codes longer than the LUT, a second inlined copy of the symbol handler,
+// an error branch per check) and measured 9 of 32 lanes active per instruction: every one of those branches splits the warp and
+// the split paths run one after the other.  Here a long code is resolved on the spot, errors are collected in one flag that is
+// looked at once per vote, and the literal counter of a token is a subtraction at match time instead of an increment per literal.
 template <int LANES, int LIT_BITS, int DIST_BITS>
 struct TokLane {
   BitReader br;
@@ -41,21 +47,21 @@ struct TokLane {
   uint32_t dirty;              // the current word holds literal bytes that have not been stored yet (acc alone cannot tell: a literal may be 0)
   int32_t lo_full, hi_full;    // words whose first byte lies at output offset [lo_full, hi_full) belong to this block alone
   uint32_t mis;                // (address of out) & 3
-  uint32_t* tok; uint32_t ntok, lit_run;
-  int state, status, bfinal; uint32_t copy_len; uint16_t slow_sym;
+  uint32_t* tok; uint32_t ntok, last_end;   // last_end: output offset where the previous match ended
+  int state, status, bfinal; uint32_t bad;   // bad: an InflateStatus noticed inside iter(); turned into a failure by check()
 
   // sym_store: 320 uint16 of lane-private scratch (288 literal/length symbols + 32 distance symbols); tok_region: TOK_CAP words
   IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* o, uint32_t isize, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store, uint32_t* tok_region) {
     hl.symbol = sym_store; hd.symbol = sym_store + 288;
     br.init(cdata, clen); out = o; op = 0; cap = isize; acc = 0; dirty = 0; mis = (uint32_t)((uintptr_t)o & 3); sh = mis * 8;
     lo_full = mis ? (int32_t)(4 - mis) : 0; hi_full = (int32_t)isize - (int32_t)(((uintptr_t)o + isize) & 3) - 3;   // first + 4 <= aligned end
-    tok = tok_region; ntok = 0; lit_run = 0;
+    tok = tok_region; ntok = 0; last_end = 0;
     hl.lut.bind(lit_lut_base, lane); hd.lut.bind(dist_lut_base, lane);
     // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][dist aux (32)][lit aux (32)], all lane-interleaved
     hd.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES, lane); hl.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES + (size_t)32 * LANES, lane);
-    state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = 0; slow_sym = 0;
+    state = LS_HEADER; status = INF_OK; bfinal = 0; bad = 0;
   }
-  IRF_HD void idle() { state = LS_DONE; status = INF_OK; ntok = 0; op = 0; cap = 0; }
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; ntok = 0; op = 0; cap = 0; bad = 0; }
   IRF_HD bool done() const { return state == LS_DONE; }
   IRF_HD void fail(int code) { status = code; state = LS_DONE; }
 
@@ -73,13 +79,14 @@ struct TokLane {
     acc |= byte << sh; sh += 8; dirty = 1;
     if (sh == 32) { flush_word_at(op); sh = 0; }
     op++;
-    if (++lit_run == 255) { tok[ntok++] = tok_make(255, 0, 1); lit_run = 0; }
   }
   IRF_HD void put_match(uint32_t len, uint32_t dist) {   // caller has checked the ranges
-    tok[ntok++] = tok_make(lit_run, len, dist); lit_run = 0;
-    if (sh + 8 * len < 32) { sh += 8 * len; op += len; return; }      // the match ends inside the current word: its bytes stay zero in acc
+    uint32_t lit = op - last_end;
+    while (lit > 255) { tok[ntok++] = tok_make(255, 0, 1); lit -= 255; }   // a literal run longer than a token can say (rare)
+    tok[ntok++] = tok_make(lit, len, dist);
+    if (sh + 8 * len < 32) { sh += 8 * len; op += len; last_end = op; return; }   // the match ends inside the current word: its bytes stay zero in acc
     if (dirty) flush_word_at(op);                                      // literal bytes before the match in this word
-    op += len; sh = ((op + mis) & 3u) * 8; acc = 0;
+    op += len; last_end = op; sh = ((op + mis) & 3u) * 8; acc = 0;
   }
   IRF_HD void finish() {
     if (dirty) flush_word_at(op);   // dirty implies 0 < sh < 32: offset `op` (even when it equals cap) still lies in the started word
@@ -138,47 +145,47 @@ struct TokLane {
     state = LS_SYMBOL;
   }
 
-  IRF_HD void handle_dist(int ds) {
-    if (ds > 29) return fail(INF_ERR_SYMBOL);
-    uint32_t dist;
-    if (ds < 4) dist = (uint32_t)ds + 1u;
-    else { int xb = (ds >> 1) - 1; dist = ((2u + ((uint32_t)ds & 1u)) << xb) + 1u + br.take(xb); }
-    if (dist > op) return fail(INF_ERR_DIST);
-    if (op + copy_len > cap) return fail(INF_ERR_OVERRUN_OUT);
-    if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
-    put_match(copy_len, dist); state = LS_SYMBOL;
-  }
-  IRF_HD void handle_litlen(int sym) {
-    if (sym < 256) { if (op >= cap) return fail(INF_ERR_OVERRUN_OUT); put_literal((uint32_t)sym); return; }
-    if (sym == 256) { if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); state = bfinal ? LS_FINISH : LS_HEADER; return; }
-    if (sym > 285) return fail(INF_ERR_SYMBOL);
-    uint32_t len;
-    if (sym < 265) len = (uint32_t)sym - 254u;
-    else if (sym == 285) len = 258;
-    else { int xb = (sym - 261) >> 2; len = ((4u + ((uint32_t)(sym - 261) & 3u)) << xb) + 3u + br.take(xb); }
-    copy_len = len;
+  // One decode iteration of a lane in LS_SYMBOL: a literal (and a second one when the next code is a LUT-resolved literal too),
+  // or a match, or the end of the DEFLATE block.  Errors only set `bad`; nothing is stored outside the block whatever the input.
+  IRF_HD void iter() {
+    br.refill();  // >= 33 bits: two codes, or a 15-bit length code + 5 extra bits
+    uint32_t e = hl.lut.get(br.peek(LIT_BITS)); uint32_t l = e & 15u, sym = e >> 4;
+    if (l) br.drop((int)l);
+    else { int idx = hl.slow_index(br, hl.head15(br)); if (idx < 0) { bad = INF_ERR_SYMBOL; return; } sym = hl.symbol[idx]; }   // code longer than the LUT: canonical limits + the lane's symbol table
+    if (sym < 256) {
+      if (op >= cap) { bad = INF_ERR_OVERRUN_OUT; return; }
+      put_literal(sym);
+      e = hl.lut.get(br.peek(LIT_BITS)); l = e & 15u;
+      if (l && e < (256u << 4) && op < cap) { br.drop((int)l); put_literal(e >> 4); }
+      return;
+    }
+    if (sym == 256) { state = bfinal ? LS_FINISH : LS_HEADER; return; }
+    // ---- match: length, then the distance code
+    const uint32_t s = sym - 257u;                       // 0..28 for valid symbols
+    const uint32_t xb = (s < 8u || s >= 28u) ? 0u : (s - 4u) >> 2;
+    uint32_t len = s < 8u ? s + 3u : (s >= 28u ? 258u : ((4u + (s & 3u)) << xb) + 3u + br.take((int)xb));
     br.refill();
-    uint16_t e = hd.lut.get(br.peek(DIST_BITS)); int l = e & 15;
-    if (l) { br.drop(l); return handle_dist(e >> 4); }
-    int idx = hd.slow_index(br, hd.head15(br));
-    if (idx < 0) return fail(INF_ERR_SYMBOL);
-    slow_sym = hd.symbol[idx]; state = LS_SLOWDIST;   // local-memory load: consumed in the next iteration
+    uint32_t ed = hd.lut.get(br.peek(DIST_BITS)); uint32_t ld = ed & 15u, ds = ed >> 4;
+    if (ld) br.drop((int)ld);
+    else { int idx = hd.slow_index(br, hd.head15(br)); if (idx < 0) { bad = INF_ERR_SYMBOL; return; } ds = hd.symbol[idx]; }
+    const uint32_t xd = ds < 4u ? 0u : (ds >> 1) - 1u;
+    const uint32_t dist = ds < 4u ? ds + 1u : ((2u + (ds & 1u)) << xd) + 1u + br.take((int)(xd & 15u));
+    if ((s > 28u) | (ds > 29u)) { bad = INF_ERR_SYMBOL; return; }
+    if (dist > op) { bad = INF_ERR_DIST; return; }
+    if (op + len > cap) { bad = INF_ERR_OVERRUN_OUT; return; }
+    put_match(len, dist);
   }
-  // One literal/length symbol (with its distance) per call, in every lane that is decoding.
-  IRF_HD void symbol() {
-    br.refill();  // >= 33 bits: a 15-bit length code + 5 extra bits, then (after the refill in handle_litlen) 15 + 13 for the distance
-    uint16_t e = hl.lut.get(br.peek(LIT_BITS)); int l = e & 15;
-    if (l) { br.drop(l); return handle_litlen(e >> 4); }
-    int idx = hl.slow_index(br, hl.head15(br));
-    if (idx < 0) return fail(INF_ERR_SYMBOL);
-    slow_sym = hl.symbol[idx]; state = LS_SLOWLIT;      // local-memory load: consumed in the next iteration
-  }
-  IRF_HD void step(bool allow_header = true) {
-    if (state == LS_SLOWLIT) { state = LS_SYMBOL; handle_litlen(slow_sym); }
-    else if (state == LS_SLOWDIST) handle_dist(slow_sym);
-    else if (state == LS_SYMBOL) symbol();
-    else if (state == LS_HEADER && allow_header) header();
+  // once per vote of the driver loop: turn a noticed error into a failure, catch a bit reader that ran past its input
+  IRF_HD void check() {
+    if (state == LS_DONE) return;
+    if (bad) return fail((int)bad);
+    if (br.overrun()) return fail(INF_ERR_OVERRUN_IN);
     if (state == LS_FINISH) finish();
+  }
+  // scalar driver step (host emulation): one table build or one decode iteration
+  IRF_HD void step() {
+    if (state == LS_HEADER) header(); else if (state == LS_SYMBOL) iter();
+    check();
   }
 };
 

@@ -142,12 +142,12 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
     inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();
   }
 }
-size_t inflate_scratch_bytes(int variant, int nblk) { return variant == 12 && nblk > 0 ? inflate_tok_scratch_bytes(nblk) : 0; }
+size_t inflate_scratch_bytes(int variant, int nblk) { return variant >= 12 && variant <= 15 && nblk > 0 ? inflate_tok_scratch_bytes(variant, nblk) : 0; }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
   // The shared-memory output-ring variants (1, 6, 9: RB > 0) are not offered any more: their sector flush raised a misaligned-address
   // fault for some output alignments (seen once the test suite ran them after other tests), and they measured slower anyway.
   if (variant == 1 || variant == 6 || variant == 9) throw std::string("inflate_variant ") + std::to_string(variant) + " (shared-memory output ring) is disabled: its sector flush faults on some output alignments";
-  if (variant == 12) { launch_inflate_tok(a, s); g_inflate_lanes = inflate_tok_lanes(); return; }   // two-phase kernel: token decode per lane, then warp-wide match resolve (inflate_tok.cu)
+  if (variant >= 12 && variant <= 15) { launch_inflate_tok(a, variant, s); g_inflate_lanes = inflate_tok_lanes(variant); return; }   // two-phase kernel: token decode per lane, then warp-wide match resolve (inflate_tok.cu)
   switch (variant) {   // <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, output ring bits>
     case 2: launch_inflate_t<4, 6, 5, 1, 0, 0, 1>(a, s); break;   // pre-written output sectors
     case 3: launch_inflate_t<4, 6, 6, 1, 0, 0, 1>(a, s); break;

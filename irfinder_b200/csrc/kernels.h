@@ -21,9 +21,9 @@ struct FrameArgs {
 
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
 size_t inflate_scratch_bytes(int variant, int nblk);   // device scratch the chosen kernel needs for a launch over nblk blocks (0 for the one-phase variants)
-void launch_inflate_tok(const InflateArgs& a, cudaStream_t s);   // inflate_tok.cu
-size_t inflate_tok_scratch_bytes(int nblk);
-int inflate_tok_lanes();
+void launch_inflate_tok(const InflateArgs& a, int variant, cudaStream_t s);   // inflate_tok.cu; variants 12-15 differ in LUT width / warps per SM
+size_t inflate_tok_scratch_bytes(int variant, int nblk);
+int inflate_tok_lanes(int variant);
 void note_launch();                                     // bumps the library's kernel-launch counter (launchers outside kernels.cu)
 int inflate_resident_lanes();
 void set_inflate_cta_cap(int ctas_per_sm);

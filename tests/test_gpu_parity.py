@@ -649,7 +649,7 @@ def test_file_input_through_the_page_locked_ring(tiny, tmp_path, chunk_kb):
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "recount"))
 
 
-@pytest.mark.parametrize("variant", [10, 11, 7, 2])
+@pytest.mark.parametrize("variant", [0, 12, 13, 14, 15, 10, 11, 7, 2])
 def test_inflate_kernel_variants_agree(tiny, tmp_path, variant):
     """The A/B variants of the SM inflate kernel (pre-written sectors, wider LUTs, byte-entry distance LUT with five or six
     CTAs per SM; the shared-memory output-ring variants are disabled, see launch_inflate) must produce the same bytes as the default: outputs equal the oracle's with the
@@ -657,3 +657,18 @@ def test_inflate_kernel_variants_agree(tiny, tmp_path, variant):
     c = _gpu_run(tiny, str(tmp_path / "g"), inflate_variant=variant, de_percent=0, de_percent_stream=0)
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
     assert c.timing()["inflate_launches"] >= 1 and c.timing()["sm_inflate_share"] == 1.0
+
+
+@pytest.mark.parametrize("level,block", [(0, 65280), (6, 65280), (9, 65280), (6, 1500), (1, 20000)])
+def test_two_phase_inflate_on_other_encoders(built, tiny, tmp_path, level, block):
+    """The two-phase SM kernel (token decode per lane, warp-wide match resolve) on BGZF written by other encoder settings than the
+    generator's zlib level 1: stored blocks (level 0: literals only), levels 6 and 9 (long matches, lazy matching, run-length matches of
+    distance 1 in the header text and the quality strings), and small blocks (many blocks per warp, output words shared by neighbouring blocks)."""
+    from bamutil import BGZF_EOF, bgzf, inflate_file
+    raw = inflate_file(tiny["sorted"])
+    assert len(raw) > 1 << 20
+    bam = str(tmp_path / "re.bam")
+    open(bam, "wb").write(bgzf(raw, block=block, level=level) + BGZF_EOF)
+    c = _gpu_run(tiny, str(tmp_path / "g"), bam=bam, inflate_variant=12, de_percent=0, de_percent_stream=0)
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
+    assert c.timing()["sm_inflate_share"] == 1.0
