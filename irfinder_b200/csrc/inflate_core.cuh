@@ -147,8 +147,13 @@ struct OutCursor {
 // E = uint16_t: LUT entry = sym << 4 | len, 0 => long code or invalid.  E = uint8_t (alphabets of at most 31 symbols and
 // BITS <= 8: the distance and code-length codes): entry = sym << 3 | (len - 1), 0xFF => long code or invalid; halves the
 // table's shared memory.
-template <int LANES, int BITS, int MAXSYM, class E = uint16_t>
+// CAUX = 1: compact aux layout, only the entries a decoder with a BITS-wide LUT can ask for: [limit of length BITS+1 .. 15][offset of length
+// BITS+1 .. 15], 2 * (15 - BITS) entries per lane instead of 32 (the two-phase kernel fits seven CTAs per SM that way).
+template <int LANES, int BITS, int MAXSYM, class E = uint16_t, int CAUX = 0>
 struct Huff {
+  static constexpr int AUXN = 15 - BITS;
+  static IRF_HD int ai_lim(int l) { return CAUX ? l - (BITS + 1) : l; }
+  static IRF_HD int ai_off(int l) { return CAUX ? AUXN + l - (BITS + 1) : 16 + l; }
   static_assert(sizeof(E) == 2 || (MAXSYM <= 32 && BITS <= 7), "byte entries hold 5 symbol bits and 3 length bits; 0xFF is reserved");
   static IRF_HD E enc(int sym, int len) { return sizeof(E) == 2 ? (E)(sym << 4 | len) : (E)(sym << 3 | (len - 1)); }
   static IRF_HD E none() { return sizeof(E) == 2 ? (E)0 : (E)0xFF; }
@@ -165,7 +170,7 @@ struct Huff {
     for (int i = 0; i < 16; i++) count[i] = 0;
     for (int i = 0; i < n; i++) count[lens[i]]++;
     for (uint32_t i = 0; i < (1u << BITS); i++) lut.set(i, none());
-    for (int i = 0; i < 32; i++) aux.set(i, 0);
+    for (int i = 0; i < (CAUX ? 2 * AUXN : 32); i++) aux.set(i, 0);
     if (count[0] == n) return true;  // no codes: any use is an error later
     int left = 1;
     for (int l = 1; l < 16; l++) { left <<= 1; left -= count[l]; if (left < 0) return false; }
@@ -173,7 +178,7 @@ struct Huff {
     uint16_t offs[16], next_code[16]; offs[1] = 0;
     for (int l = 1; l < 15; l++) offs[l + 1] = offs[l] + count[l];
     { uint32_t code = 0; for (int l = 1; l < 16; l++) { code = (code + (l > 1 ? count[l - 1] : 0)) << 1; next_code[l] = (uint16_t)code;
-        aux.set(l, (uint16_t)((code + count[l]) << (15 - l) > 0xffffu ? 0xffffu : (code + count[l]) << (15 - l))); aux.set(16 + l, (uint16_t)(offs[l] - code)); } }
+        if (!CAUX || l > BITS) { aux.set(ai_lim(l), (uint16_t)((code + count[l]) << (15 - l) > 0xffffu ? 0xffffu : (code + count[l]) << (15 - l))); aux.set(ai_off(l), (uint16_t)(offs[l] - code)); } } }
     for (int s = 0; s < n; s++) {
       int l = lens[s]; if (!l) continue;
       symbol[offs[l]++] = (uint16_t)s;
@@ -194,12 +199,12 @@ struct Huff {
   IRF_HD int slow_index(BitReader& br, uint32_t code15) const {
     uint32_t lim[16];
 #pragma unroll
-    for (int l = BITS + 1; l < 16; l++) lim[l] = aux.get(l);
+    for (int l = BITS + 1; l < 16; l++) lim[l] = aux.get(ai_lim(l));
     int len = 0;
 #pragma unroll
     for (int l = 15; l > BITS; l--) if (code15 < lim[l]) len = l;
     if (!len) return -1;
-    uint32_t idx = (uint32_t)(uint16_t)((code15 >> (15 - len)) + aux.get(16 + len));
+    uint32_t idx = (uint32_t)(uint16_t)((code15 >> (15 - len)) + aux.get(ai_off(len)));
     if (idx >= (uint32_t)MAXSYM) return -1;
     br.drop(len);
     return (int)idx;

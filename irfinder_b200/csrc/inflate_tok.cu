@@ -61,21 +61,15 @@ __device__ __forceinline__ void resolve_batch(uint8_t* ob, uint32_t mstart, uint
       }
     }
     if (ready && ml <= TOK_LONG) {
-      uint8_t* dp = ob + mstart; const uint8_t* sp = dp - d;
-      if (d >= 4) {
-        // four source bytes per trip from two aligned word loads and a funnel shift (the words may reach a few bytes beyond the
-        // source: those bytes are dropped).  d >= 4: a trip never reads what the same trip writes; what an earlier trip of this
-        // lane wrote is read back in program order.
-        uint32_t rem = ml;
-        do {
-          const uint32_t* wa = (const uint32_t*)((uintptr_t)sp & ~(uintptr_t)3); const uint32_t v = __funnelshift_r(wa[0], wa[1], ((uint32_t)(uintptr_t)sp & 3u) * 8u);
-          dp[0] = (uint8_t)v; if (rem > 1) dp[1] = (uint8_t)(v >> 8); if (rem > 2) dp[2] = (uint8_t)(v >> 16); if (rem > 3) dp[3] = (uint8_t)(v >> 24);
-          sp += 4; dp += 4; rem = rem > 4 ? rem - 4 : 0;
-        } while (rem);
-      } else {                                           // run-length match (period 1..3): byte by byte, the source index wraps inside the period
-        uint32_t w = 0;
-        for (uint32_t k = 0; k < ml; k++) { dp[k] = sp[w]; w++; if (w == d) w = 0; }
-      }
+      uint8_t* dp = ob + mstart; const uint8_t* sp = dp - d; uint32_t w = 0, rem = ml;
+      do {                                               // 4 bytes per trip (most matches are 3 or 4 long): loads first, then stores; the source index
+        const uint32_t k = rem < 4 ? rem : 4; uint32_t v[4];   // wraps inside the period, so run-length matches only ever read the d final bytes
+#pragma unroll
+        for (int j = 0; j < 4; j++) { if ((uint32_t)j < k) v[j] = sp[w]; w++; if (w == d) w = 0; }
+#pragma unroll
+        for (int j = 0; j < 4; j++) if ((uint32_t)j < k) dp[j] = (uint8_t)v[j];
+        dp += k; rem -= k;
+      } while (rem);
     }
     if (ready) pending = false;
     __syncwarp();   // orders this round's stores before the next round's loads (and before the next batch)
@@ -89,8 +83,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uin
                                                                   const u32* __restrict__ list, uint32_t* tok_scratch) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // per warp: [lit LUT][dist LUT][2 x 32 canonical-limit entries], 16-bit entries interleaved by lane
-  constexpr size_t WARP_U16 = (size_t)((1 << LB) + (1 << DB) + 64) * 32;
+  // per warp: [lit LUT, 16-bit entries][dist LUT, byte entries][canonical-limit entries of both], interleaved by lane
+  constexpr size_t WARP_U16 = TokLane<32, LB, DB>::TABLE_U16;
   uint16_t* lit = smem_tables + (size_t)warp * WARP_U16;
   uint16_t* dst = lit + (1 << LB) * 32;
   uint16_t sym_store[320];
@@ -164,7 +158,7 @@ struct TokGeom { int ctas_per_sm, sms; size_t smem; int warps; };
 template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
 static TokGeom tok_geometry() {
   static int ctas[64] = {0}, sms[64] = {0};
-  const size_t smem = (size_t)WARPS * ((size_t)((1 << LB) + (1 << DB) + 64) * 32) * sizeof(uint16_t);
+  const size_t smem = (size_t)WARPS * TokLane<32, LB, DB>::TABLE_U16 * sizeof(uint16_t);
   int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");
   if (!ctas[dev]) {
     auto kern = inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB>;
@@ -190,10 +184,13 @@ static void tok_launch(const InflateArgs& a, cudaStream_t s) {
     fprintf(stderr, "[tok] <%d warps, %d/%d-bit LUTs> grid %d x %d CTAs/SM: phase A %.1f Mcycles/claim, phase B %.1f Mcycles/claim, %llu claims; per claim: %.0f votes, %.1f table builds, %.0f batches, %.2f rounds/batch\n", WARPS, LB, DB, grid, g.ctas_per_sm,
             z[0] / 1e6 / std::max(1ull, z[6]), z[1] / 1e6 / std::max(1ull, z[6]), z[6], (double)z[2] / std::max(1ull, z[6]), (double)z[3] / std::max(1ull, z[6]), (double)z[4] / std::max(1ull, z[6]), (double)z[5] / std::max(1ull, z[4])); }
 }
-// variants: literal/length and distance LUT width against warps per SM (shared memory per warp = (2^LB + 2^DB + 64) * 64 bytes)
-//   12: 6/5 bits, 20 warps per SM     13: 7/6 bits, 12 warps     14: 8/6 bits, 9 warps     15: 9/6 bits, 5 warps
+// variants: LUT width against warps per SM (shared memory per warp = TokLane::TABLE_U16 * 2 bytes; registers per thread follow from MINB)
+//   12: 6/5 bits, 5 CTAs x 4 warps = 20 warps per SM (96 registers; measured fastest: 124.9 ms on the 20M-pair file)
+//   13: 6/5 bits, 7 CTAs x 4 warps = 28 warps (72 registers, 140 bytes spilled: 143 ms - the kernel is bound by issue slots and L1
+//       wavefronts, not by latency, so more warps only add spills)
+//   14: 7/5 bits, 5 CTAs x 3 warps = 15 warps (174 ms: the wider LUT saves fewer instructions than the lost warps cost)     15: 8/6 bits, 9 warps
 #define IRF_TOK_DISPATCH(variant, CALL) \
-  switch (variant) { case 13: CALL(4, 7, 6, 24, 3); break; case 14: CALL(3, 8, 6, 24, 3); break; case 15: CALL(1, 9, 6, 24, 5); break; default: CALL(4, 6, 5, 24, 5); break; }
+  switch (variant) { case 13: CALL(4, 6, 5, 24, 7); break; case 14: CALL(3, 7, 5, 24, 5); break; case 15: CALL(3, 8, 6, 24, 3); break; default: CALL(4, 6, 5, 24, 5); break; }
 static TokGeom tok_geom_of(int variant) {
   TokGeom g{};
 #define IRF_TOK_GEOM(W, LB, DB, P, M) g = tok_geometry<W, LB, DB, P, M>()

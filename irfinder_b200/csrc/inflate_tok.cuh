@@ -40,7 +40,11 @@ IRF_HD uint32_t tok_dist(uint32_t t) { return (t & 32767u) + 1u; }
 template <int LANES, int LIT_BITS, int DIST_BITS>
 struct TokLane {
   BitReader br;
-  Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32> hd;
+  // shared-memory tables of a lane: literal/length LUT (16-bit entries), distance LUT (byte entries), compact canonical-limit tables
+  using HL = Huff<LANES, LIT_BITS, 288, uint16_t, 1>; using HD = Huff<LANES, DIST_BITS, 32, uint8_t, 1>;
+  static constexpr size_t DIST_LUT_U16 = ((size_t)(1u << DIST_BITS) * LANES + 1) / 2;          // the distance LUT's size in 16-bit units
+  static constexpr size_t TABLE_U16 = (size_t)(1u << LIT_BITS) * LANES + DIST_LUT_U16 + (size_t)(2 * HD::AUXN + 2 * HL::AUXN) * LANES;   // all tables of LANES lanes
+  HL hl; HD hd;
   uint8_t* out;                // start of this block's output
   uint32_t op, cap;            // bytes produced so far (literals written + match bytes left open), ISIZE
   uint32_t acc, sh;            // literal bytes of the current aligned 32-bit output word; bit position of output offset `op` inside it
@@ -56,9 +60,9 @@ struct TokLane {
     br.init(cdata, clen); out = o; op = 0; cap = isize; acc = 0; dirty = 0; mis = (uint32_t)((uintptr_t)o & 3); sh = mis * 8;
     lo_full = mis ? (int32_t)(4 - mis) : 0; hi_full = (int32_t)isize - (int32_t)(((uintptr_t)o + isize) & 3) - 3;   // first + 4 <= aligned end
     tok = tok_region; ntok = 0; last_end = 0;
-    hl.lut.bind(lit_lut_base, lane); hd.lut.bind(dist_lut_base, lane);
-    // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][dist aux (32)][lit aux (32)], all lane-interleaved
-    hd.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES, lane); hl.aux.bind(dist_lut_base + (size_t)(1u << DIST_BITS) * LANES + (size_t)32 * LANES, lane);
+    hl.lut.bind(lit_lut_base, lane); hd.lut.bind((uint8_t*)dist_lut_base, lane);
+    // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT (bytes)][dist aux][lit aux], all lane-interleaved
+    hd.aux.bind(dist_lut_base + DIST_LUT_U16, lane); hl.aux.bind(dist_lut_base + DIST_LUT_U16 + (size_t)(2 * HD::AUXN) * LANES, lane);
     state = LS_HEADER; status = INF_OK; bfinal = 0; bad = 0;
   }
   IRF_HD void idle() { state = LS_DONE; status = INF_OK; ntok = 0; op = 0; cap = 0; bad = 0; }
@@ -120,7 +124,8 @@ struct TokLane {
       for (int i = 0; i < 19; i++) lens[i] = 0;
       for (int i = 0; i < hclen; i++) { br.refill(); lens[order[i]] = (uint8_t)br.take(3); }
       // the code-length code (<= 7 bits) borrows the distance LUT region
-      Huff<LANES, (DIST_BITS < 7 ? DIST_BITS : 7), 19> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.aux.base = hd.aux.base;
+      static_assert(DIST_BITS <= 7, "the code-length code borrows the distance LUT (byte entries: at most 7 bits)");
+      Huff<LANES, DIST_BITS, 19, uint8_t, 1> hc; hc.symbol = hd.symbol; hc.lut.base = hd.lut.base; hc.aux.base = hd.aux.base;
       if (!hc.build(lens, 19)) return fail(INF_ERR_CODELEN);
       int idx = 0;
       while (idx < hlit + hdist) {
@@ -165,7 +170,7 @@ struct TokLane {
     const uint32_t xb = (s < 8u || s >= 28u) ? 0u : (s - 4u) >> 2;
     uint32_t len = s < 8u ? s + 3u : (s >= 28u ? 258u : ((4u + (s & 3u)) << xb) + 3u + br.take((int)xb));
     br.refill();
-    uint32_t ed = hd.lut.get(br.peek(DIST_BITS)); uint32_t ld = ed & 15u, ds = ed >> 4;
+    const uint8_t ed = hd.lut.get(br.peek(DIST_BITS)); const uint32_t ld = (uint32_t)HD::len_of(ed); uint32_t ds = (uint32_t)HD::sym_of(ed);
     if (ld) br.drop((int)ld);
     else { int idx = hd.slow_index(br, hd.head15(br)); if (idx < 0) { bad = INF_ERR_SYMBOL; return; } ds = hd.symbol[idx]; }
     const uint32_t xd = ds < 4u ? 0u : (ds >> 1) - 1u;
