@@ -18,6 +18,7 @@ constexpr u32 SPAN_OVERHANG_RIGHT = 4;     // [C-4]
 constexpr u32 EDGE_WINDOW_OFFSET = 5;      // [C-13]
 constexpr u32 EDGE_WINDOW_LEN = 50;        // [C-13]
 constexpr int BUCKET_SHIFT = 10;
+constexpr u32 REC_SLOTS = 65536 / 36 + 2;   // records that can START inside one BGZF block (a record has at least 36 bytes)
 
 // ---- junction key: 36-bit concatenated-genome coordinate of the left end, 28-bit gap (CIGAR op lengths are 28-bit)
 constexpr int JKEY_GAP_BITS = 28;

@@ -89,7 +89,7 @@ struct irf_ctx {
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
   DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
   // staged input
-  DevBuf d_tok, d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
+  DevBuf d_tok, d_slots, d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
   vector<Blk> blks; int nblk_own = 0; u64 Uend = 0; bool staged = false, staged_has_header = false, inflated_input = false;
   u64 pslots = 0, n_cand = 0, n_rec = 0, frame_entry0 = 0, frame_exit_rel = 0; bool sharded = false; u64 halo_leftover = 0;
@@ -337,23 +337,23 @@ struct irf_ctx {
   void plan_engines(int de_percent, int mode = 0) {
     sync();   // a fetch of the previous plan's lists may still be queued against the arena rewritten below
     const size_t nb = blks.size(), chunk = chunk_bytes;
-    sm_list.clear(); de_list.clear(); de_chunk_end.clear(); chunk_blk_end.clear();
+    sm_list.clear(); de_list.clear(); de_chunk_end.clear(); sm_chunk_end.clear(); chunk_blk_end.clear();
     const bool de_ok = de_percent > 0 && inflate_variant != 8 && g_drv.deflate_engine();
     const size_t nch = std::max<size_t>((src_total + chunk - 1) / chunk, 1);
     for (size_t c = 0, b1 = 0; c < nch; c++) { size_t hi = std::min(src_total, (c + 1) * chunk);
       while (b1 < nb && (blks[b1].c_off + blks[b1].c_len + 8 <= hi || c + 1 >= nch)) b1++;
       chunk_blk_end.push_back(b1); }
     size_t k_sm = 0;
-    if (mode == 1 && de_ok) {   // leading chunks for the kernel: its share of the blocks, cut back to whole waves of its grid when it exceeds one
-      size_t target = nb * (size_t)(100 - de_percent) / 100, lanes = overlap_lanes(), waves = (target + lanes / 4) / lanes, budget = waves ? waves * lanes : target;
-      while (k_sm + 1 < nch && chunk_blk_end[k_sm] <= budget) k_sm++;
+    if (mode == 1 && de_ok) {   // leading chunks for the kernel: its share of the blocks (count_streaming launches it one grid-full of blocks at a time)
+      size_t target = nb * (size_t)(100 - de_percent) / 100;
+      while (k_sm + 1 < nch && chunk_blk_end[k_sm] <= target) k_sm++;
     }
     k_de = nch - k_sm;
     for (size_t c = 0, b0 = 0; c < nch; c++) {
       size_t b1 = chunk_blk_end[c];
       size_t nde = !de_ok ? 0 : mode == 1 ? (c >= k_sm ? b1 - b0 : 0) : (b1 - b0) * (size_t)de_percent / 100;
       for (size_t b = b0; b < b1; b++) { if (blks[b].isize == 0) continue; if (b < b0 + nde) de_list.push_back((u32)b); else sm_list.push_back((u32)b); }
-      de_chunk_end.push_back(de_list.size()); b0 = b1;
+      de_chunk_end.push_back(de_list.size()); sm_chunk_end.push_back(sm_list.size()); b0 = b1;
     }
     de_params.resize(de_list.size()); d_de_act.ensure(nb * 4);
     for (size_t i = 0; i < de_list.size(); i++) { const Blk& k = blks[de_list[i]]; CUmemDecompressParams& q = de_params[i]; memset(&q, 0, sizeof q);
@@ -370,7 +370,7 @@ struct irf_ctx {
   bool crc_pending = false;
   void join_crc() { if (crc_pending) { IRF_CUDA(cudaStreamSynchronize(s_de)); crc_pending = false; } }
   size_t chunk_bytes = 256ull << 20; vector<size_t> chunk_blk_end; int stream_pipeline = 1;
-  vector<u32> sm_list, de_list; vector<size_t> de_chunk_end; vector<CUmemDecompressParams> de_params; bool engines_planned = false;
+  vector<u32> sm_list, de_list; vector<size_t> de_chunk_end, sm_chunk_end; vector<CUmemDecompressParams> de_params; bool engines_planned = false;
 
   // S1: BGZF inflate on two engines at once.  The Blackwell decompression engine (cuMemBatchDecompressAsync, raw DEFLATE,
   // no SM involved) takes its share of every chunk; one persistent launch of inflate_kernel takes the rest.  When the bytes
@@ -443,13 +443,13 @@ struct irf_ctx {
   int n_inflate_launches = 0;
 
   int dev_err() { int e = 0; IRF_CUDA(cudaMemcpyAsync(&e, d_err.p, 4, cudaMemcpyDeviceToHost, s_compute)); sync(); return e; }
-  void check_dev_err(const char* stage_name) {
-    int e = dev_err(); if (!e) return;
+  void check_dev_err(const char* stage_name) { int e = dev_err(); if (e) throw err_text(e, stage_name); }
+  static string err_text(int e, const char* stage_name) {
     string m = string(stage_name) + ":";
     if (e & DERR_INFLATE) m += " corrupt DEFLATE data in a BGZF block;"; if (e & DERR_TRUNCATED) m += " truncated BAM record stream;"; if (e & DERR_BAD_RECORD) m += " malformed BAM record / unframeable stream;";
     if (e & DERR_JUNC_FULL) m += " junction table full (raise junc_capacity_log2);"; if (e & DERR_JKEY_RANGE) m += " junction outside the supported key range;";
     if (e & DERR_PAIR_FULL) m += " pairing table full;"; if (e & DERR_REFID) m += " record refID beyond the header's reference list;"; if (e & DERR_DUMP_FULL) m += " fragment dump buffer full;"; if (e & DERR_STARVED) m += " inflate kernel starved of input (host copy stalled);"; if (e & DERR_CRC) m += " CRC-32 of an inflated BGZF block does not match its footer;";
-    throw m;
+    return m;
   }
 
   // BAM2blocks::readBamHeader on device-inflated bytes
@@ -539,7 +539,7 @@ struct irf_ctx {
     if (!bound) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s_compute));
     if (from_host) { if (!engines_planned || planned_percent != 100) plan_engines(100); }
     else if (!engines_planned || planned_percent != 1000 + de_percent_overlap) plan_engines(de_percent_overlap, 1);
-    if (!from_host && !sm_list.empty()) tok_scratch((int)sm_list.size());
+    if (!from_host && !sm_list.empty()) tok_scratch((int)std::min(sm_list.size(), overlap_lanes()));
     const size_t nb = blks.size(), nch = chunk_blk_end.size(); const bool sm_used = !from_host && !sm_list.empty(); const size_t ksm = sm_used ? nch - k_de : 0;   // chunks [0, ksm) are the SM kernel's
     cudaEvent_t k0 = nullptr, k1 = nullptr;
     int* errp = T.err ? T.err : d_err.as<int>();
@@ -570,18 +570,31 @@ struct irf_ctx {
     }
     for (size_t c = npre; c < pre_ev_copy.size(); c++) cudaEventDestroy(pre_ev_copy[c]);
     pre_ev_copy.clear(); pre_copied_bytes = 0;   // ownership of the first npre events moved to ev_copy
-    if (sm_used) {   // the SM kernel's share, one launch beside everything else
-      IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventCreate(&k1)); IRF_CUDA(cudaEventRecord(k0, s_copy));
-      InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)sm_list.size(), d_status.as<int>(),
-                    errp, (unsigned int*)(d_small.as<uint8_t>() + 160), nullptr, d_sm_list.as<u32>()};
-      a.tok_scratch = tok_scratch(a.nblk); a.tok_scratch_bytes = d_tok.cap;
-      launch_inflate(a, inflate_variant, s_copy); IRF_CUDA(cudaEventRecord(k1, s_copy));
-      if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)sm_list.size(), d_status.as<int>(), errp, s_copy, d_sm_list.as<u32>());
+    // The SM kernel's share, beside everything else: one launch per grid-full of blocks (a launch whose blocks do not fill the grid
+    // runs as long as a full one - each warp works through its 32 blocks at its own pace - so a share of 1.4 grids goes out as a full launch
+    // and a 0.4 one; while the second runs, the SM slots it leaves empty go to the counting kernels of the first launch's chunks).
+    vector<cudaEvent_t> k_ev; vector<size_t> k_chunk_end;   // event after launch g; chunks [k_chunk_end[g-1], k_chunk_end[g]) belong to it
+    if (sm_used) {
+      IRF_CUDA(cudaEventCreate(&k0)); IRF_CUDA(cudaEventRecord(k0, s_copy));
+      const size_t lanes = overlap_lanes();
+      for (size_t c0 = 0; c0 < ksm;) {
+        size_t c1 = c0 + 1; const size_t s0 = c0 ? sm_chunk_end[c0 - 1] : 0;
+        while (c1 < ksm && sm_chunk_end[c1] - s0 <= lanes) c1++;
+        const size_t s1 = sm_chunk_end[c1 - 1];
+        InflateArgs a{d_comp.as<uint8_t>(), d_c_off.as<u64>(), d_c_len.as<u32>(), d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), (int)(s1 - s0), d_status.as<int>(),
+                      errp, (unsigned int*)(d_small.as<uint8_t>() + 160), nullptr, d_sm_list.as<u32>() + s0};
+        a.tok_scratch = tok_scratch((int)(s1 - s0)); a.tok_scratch_bytes = d_tok.cap;
+        launch_inflate(a, inflate_variant, s_copy);
+        cudaEvent_t ev; IRF_CUDA(cudaEventCreate(&ev)); IRF_CUDA(cudaEventRecord(ev, s_copy)); k_ev.push_back(ev); k_chunk_end.push_back(c1);
+        if (verify_crc && s1 > s0) { IRF_CUDA(cudaStreamWaitEvent(s_chk, ev, 0)); launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(s1 - s0), d_status.as<int>(), errp, s_chk, d_sm_list.as<u32>() + s0); }
+        c0 = c1;
+      }
+      k1 = k_ev.back();
     }
-    auto cleanup = [&]() { if (fed) feed_stop(); else for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); if (k1) cudaEventDestroy(k1); };
+    auto cleanup = [&]() { if (fed) feed_stop(); else for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); for (auto e : k_ev) cudaEventDestroy(e); };
     try {
       // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
-      if (sm_used && staged_has_header) IRF_CUDA(cudaEventSynchronize(k1));   // the header lies in the kernel's share
+      if (sm_used && staged_has_header) IRF_CUDA(cudaEventSynchronize(k_ev[0]));   // the header lies in the kernel's first launch
       for (size_t c = 0; staged_has_header; c++) {
         IRF_CUDA(cudaEventSynchronize(ev_inf[c])); check_dev_err("inflate");
         u64 full = Uend; Uend = inf_end[c]; bool ok = true;
@@ -593,6 +606,8 @@ struct irf_ctx {
       u32* n_bad = d_small.as<u32>(); u64* totals = (u64*)(d_small.as<uint8_t>() + 16); u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192);
       // A shard of a larger file (multi-GPU) has no header and ends with look-ahead blocks that are inflated but not counted
       // here: its first record start is a guess unless the caller passed one ("entry0"), exactly as in count().
+      { size_t mx = 0, p0 = 0; for (size_t c = 0; c < nch; c++) { size_t p1 = std::min<size_t>(chunk_blk_end[c], (size_t)nblk_own); if (p1 > p0) { mx = std::max(mx, p1 - p0); p0 = p1; } }
+        if (mx * REC_SLOTS * 8 + 256 > d_slots.cap) { sync(); d_slots.ensure(mx * REC_SLOTS * 8); } }
       u64 entry_prev = rec0; int entry_valid = 1; n_rec = 0; n_cand = 0; frame_rounds = 0; size_t b0 = 0; u64 fe0 = rec0; bool first = true;
       if (!staged_has_header) { entry_valid = entry0_override >= 0; entry_prev = entry_valid ? (u64)entry0_override : 0; entry0_override = -1; }
       for (size_t c = 0; c < nch; c++) {
@@ -604,37 +619,39 @@ struct irf_ctx {
         size_t need = std::min(c + 1, nch - 1); while (need + 1 < nch && inf_end[need] - inf_end[c] < (8u << 20)) need++;
         if (last_own) need = nch - 1;
         IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[need], 0));
-        if (sm_used && c < ksm) IRF_CUDA(cudaStreamWaitEvent(s_compute, k1, 0));
+        if (sm_used && c < ksm) { size_t g = 0; while (k_chunk_end[g] <= std::min(need, ksm - 1)) g++; IRF_CUDA(cudaStreamWaitEvent(s_compute, k_ev[g], 0)); }   // the launch that inflates the last chunk this one needs
         const u64 visible = inf_end[need];
         FrameArgs fa{d_U.as<uint8_t>(), d_u_off.as<u64>() + b0, d_u_len.as<u32>() + b0, nbk, visible, entry_prev, entry_valid, T.n_ref, T.ref_len,
                      d_entry.as<u64>() + b0, d_exit.as<u64>() + b0, d_nrec.as<u32>() + b0, d_ncand.as<u32>() + b0, d_ferr.as<uint8_t>() + b0, T.err, (int*)(d_small.as<uint8_t>() + 48)};
+        fa.slots = d_slots.as<u64>();   // record starts per block, written by the walk (chunk-local block index)
         launch_frame_guess(fa, s_compute); launch_walk_count(fa, nullptr, s_compute);
+        // ONE host round trip per chunk in the usual case: the consistency check, the totals and the chunk's exit are queued together and
+        // read back at once; only a chunk with a wrong first-record guess (n_bad != 0) goes through repair rounds, each with its own read-back.
+        u64 ht[3] = {0, 0, 0}, ex = 0; u32 hb = 0;
         for (int rounds = 0;; rounds++) {
           IRF_CUDA(cudaMemsetAsync(n_bad, 0, 4, s_compute)); launch_frame_mark(fa, d_mism.as<uint8_t>() + b0, d_mask.as<uint8_t>() + b0, n_bad, s_compute);
-          u32 hb = 0; IRF_CUDA(cudaMemcpyAsync(&hb, n_bad, 4, cudaMemcpyDeviceToHost, s_compute)); sync();
+          IRF_CUDA(cudaMemcpyAsync(&hb, n_bad, 4, cudaMemcpyDeviceToHost, s_compute));
+          // the totals of a chain that may still be repaired are provisional: their error bits go to a word of their own and count only once the chain holds
+          IRF_CUDA(cudaMemsetAsync(totals, 0, 24, s_compute)); { FrameArgs ft = fa; ft.err = (int*)(totals + 2); launch_frame_totals(ft, totals, s_compute); }
+          IRF_CUDA(cudaMemcpyAsync(ht, totals, 24, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(&ex, d_exit.as<u64>() + (b1 - 1), 8, cudaMemcpyDeviceToHost, s_compute));
+          if (first) IRF_CUDA(cudaMemcpyAsync(&fe0, d_entry.as<u64>() + b0, 8, cudaMemcpyDeviceToHost, s_compute));
+          sync();
           if (!hb) break; if (rounds > nbk + 2) throw string("record framing did not converge"); frame_rounds++;
-          if (getenv("IRF_DEBUG_FRAMING") && (rounds < 3 || rounds % 100 == 0)) {
-            vector<uint8_t> hm(nbk); vector<u64> he(nbk), hx(nbk); IRF_CUDA(cudaMemcpy(hm.data(), d_mask.as<uint8_t>() + b0, nbk, cudaMemcpyDeviceToHost));
-            IRF_CUDA(cudaMemcpy(he.data(), d_entry.as<u64>() + b0, nbk * 8, cudaMemcpyDeviceToHost)); IRF_CUDA(cudaMemcpy(hx.data(), d_exit.as<u64>() + b0, nbk * 8, cudaMemcpyDeviceToHost));
-            size_t none = 0; for (int i = 0; i < nbk; i++) none += hx[i] == ~0ull;
-            fprintf(stderr, "[framing] chunk %zu (%d blocks from %zu): round %d repairs %u entries, %zu blocks without an exit;", c, nbk, b0, rounds, hb, none);
-            int shown = 0; for (int i = 0; i < nbk && shown < 4; i++) if (hm[i]) { fprintf(stderr, " block %d: entry now %llu (block starts at %llu), old exit of it %llu;", i, (unsigned long long)he[i], (unsigned long long)blks[b0 + i].isize, (unsigned long long)hx[i]); shown++; }
-            fprintf(stderr, "\n"); }
+          if (getenv("IRF_DEBUG_FRAMING") && (rounds < 3 || rounds % 100 == 0)) fprintf(stderr, "[framing] chunk %zu (%d blocks from %zu): round %d repairs %u entries\n", c, nbk, b0, rounds, hb);
           launch_walk_count(fa, d_mask.as<uint8_t>() + b0, s_compute);
         }
-        IRF_CUDA(cudaMemsetAsync(totals, 0, 16, s_compute)); launch_frame_totals(fa, totals, s_compute);
-        u64 ht[2] = {0, 0}, ex = 0; IRF_CUDA(cudaMemcpyAsync(ht, totals, 16, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(&ex, d_exit.as<u64>() + (b1 - 1), 8, cudaMemcpyDeviceToHost, s_compute));
-        if (first) IRF_CUDA(cudaMemcpyAsync(&fe0, d_entry.as<u64>() + b0, 8, cudaMemcpyDeviceToHost, s_compute));
-        sync(); check_dev_err("record framing");
+        if ((int)ht[2]) throw err_text((int)ht[2], "record framing");
+        check_dev_err("record framing");
         entry_prev = ex; entry_valid = 1; first = false; n_rec += ht[0]; n_cand += ht[1];
         if (ht[0]) {
+          // the lists keep their size from chunk to chunk (generous first allocation), so no allocation and no host wait separates the
+          // chunks: the pairing kernel leaves its counts on the device and the two counting kernels are launched over upper bounds
           d_rec_base.ensure((size_t)nbk * 8); d_rec_off.ensure((ht[0] + ht[0] / 2) * 8); d_pair_list.ensure((ht[1] + ht[1] / 2 + 16) * 16); d_single_list.ensure((ht[0] + ht[0] / 2 + 16) * 8);
-          launch_scan_counts(d_nrec.as<u32>() + b0, d_rec_base.as<u64>(), nbk, s_compute); launch_walk_list(fa, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
+          launch_scan_counts(d_nrec.as<u32>() + b0, d_rec_base.as<u64>(), nbk, s_compute); launch_gather_records(fa, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
           IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
           launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), ht[0], d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute);
-          u64 lc[2] = {0, 0}; IRF_CUDA(cudaMemcpyAsync(lc, list_counts, 16, cudaMemcpyDeviceToHost, s_compute)); sync();
-          launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), lc[0], s_compute); launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), lc[1], s_compute);
-          sync();   // the work lists are reused by the next chunk
+          launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), ht[1] + 1, s_compute, list_counts);   // every pair is completed by one candidate record of this chunk (its mate may have waited since an earlier chunk)
+          launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), ht[0] - ht[1] + 1, s_compute, list_counts + 1);
         }
         b0 = b1;
       }
@@ -646,7 +663,7 @@ struct irf_ctx {
       if (sm_used) { float t_sm = 0; IRF_CUDA(cudaEventElapsedTime(&t_sm, e0, k1)); inf = std::max(inf, t_sm); IRF_CUDA(cudaEventElapsedTime(&t_sm, k0, k1)); timing[10] = t_sm; timing[11] = sm_byte_share(); }
       if (getenv("IRF_DEBUG_TIMING")) { float t_de = 0, t_sm = 0; IRF_CUDA(cudaEventElapsedTime(&t_de, e0, ev_inf[nch - 1])); if (sm_used) IRF_CUDA(cudaEventElapsedTime(&t_sm, k0, k1));
         fprintf(stderr, "[pipeline] %s: %zu chunks (%zu DE), DE done at %.1f ms, SM inflate %.1f ms, all counted at %.1f ms\n", from_host ? "streamed" : "resident", nch, nch - ksm, t_de, t_sm, tot); }
-      timing[0] = inf; timing[1] = inf; timing[2] = 0; timing[3] = tot - inf; timing[5] = tot; n_inflate_launches = sm_used ? 1 : 0;
+      timing[0] = inf; timing[1] = inf; timing[2] = 0; timing[3] = tot - inf; timing[5] = tot; n_inflate_launches = sm_used ? (int)k_ev.size() : 0;
       { u64 own_end = 0; for (int i = 0; i < nblk_own; i++) own_end += blks[i].isize; frame_entry0 = fe0; frame_exit_rel = entry_prev >= own_end ? entry_prev - own_end : 0; }
     } catch (...) { cudaStreamSynchronize(s_copy); cudaStreamSynchronize(s_de); cudaStreamSynchronize(s_chk); cudaStreamSynchronize(s_compute); cleanup(); throw; }
     cleanup();
@@ -941,7 +958,7 @@ void irf_destroy(irf_ctx* c) {
   if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
-                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
+                   &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_slots, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
                    &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();

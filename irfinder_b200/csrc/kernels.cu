@@ -173,14 +173,24 @@ __host__ __device__ inline u32 crc_mulmod(u32 a, u32 b) {   // product of two po
   return p;
 }
 struct CrcMul { u32 x[5]; };
-__global__ void __launch_bounds__(256) crc_check_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, const u32* __restrict__ want,
-                                                         int nblk, CrcMul M, int* __restrict__ status, int* __restrict__ err, const u32* __restrict__ list) {
-  __shared__ u32 T[4][256];
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = (u32)i; for (int k = 0; k < 8; k++) c = (c & 1u) ? (c >> 1) ^ CRC_POLY : c >> 1; T[0][i] = c; }
+// Tables: slicing-by-4, one private copy per LANE in shared memory (entry (k, i) of lane l at ((k * 256 + i) * 32 + l): bank = lane),
+// so the 32 data-dependent look-ups of a warp never collide.  With one shared copy the look-ups of a warp hit ~3.5 entries per bank
+// on average and the kernel ran at 1.45 TB/s (20 ms per 50M-pair step, profiles/README.md round 1); the look-up, one per byte and
+// lane, is the unit of work here, so conflict-free look-ups are what lets the kernel follow HBM.  128 KB of tables: one 512-thread
+// CTA per SM, persistent, filled once per CTA.
+constexpr int CRC_THREADS = 512;
+__global__ void __maxnreg__(64) crc_check_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, const u32* __restrict__ want,
+                                                                   int nblk, CrcMul M, int* __restrict__ status, int* __restrict__ err, const u32* __restrict__ list) {
+  extern __shared__ u32 crc_tab[];   // [4][256][32]
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = (u32)i; for (int k = 0; k < 8; k++) c = (c & 1u) ? (c >> 1) ^ CRC_POLY : c >> 1; crc_tab[i * 32] = c; }
   __syncthreads();
-  for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = T[0][i]; for (int t = 1; t < 4; t++) { c = T[0][c & 255u] ^ (c >> 8); T[t][i] = c; } }
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) { u32 c = crc_tab[i * 32]; for (int t = 1; t < 4; t++) { c = crc_tab[(c & 255u) * 32] ^ (c >> 8); crc_tab[(t * 256 + i) * 32] = c; } }
+  __syncthreads();
+  for (int e = threadIdx.x; e < 1024 * 31; e += blockDim.x) { const int ent = e / 31, l = e % 31 + 1; crc_tab[ent * 32 + l] = crc_tab[ent * 32]; }   // the other 31 copies
   __syncthreads();
   const int lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
+  const u32* T0 = crc_tab + lane; const u32* T1 = T0 + 256 * 32; const u32* T2 = T1 + 256 * 32; const u32* T3 = T2 + 256 * 32;
+  auto word = [&](u32 w, u32 r) -> u32 { w ^= r; return T3[(w & 255u) * 32] ^ T2[((w >> 8) & 255u) * 32] ^ T1[((w >> 16) & 255u) * 32] ^ T0[(w >> 24) * 32]; };
   for (int bi = blockIdx.x * wpb + (threadIdx.x >> 5); bi < nblk; bi += gridDim.x * wpb) {
     const int b = list ? (int)list[bi] : bi;   // optional list of block indices (the blocks one engine produced)
     u32 len = u_len[b]; if (!len) continue;
@@ -191,17 +201,18 @@ __global__ void __launch_bounds__(256) crc_check_kernel(const uint8_t* __restric
     if (hi > 0) {
       if (lo == 0) r = 0xFFFFFFFFu;   // the lane holding the first byte carries the initial register
       const uint8_t* p = base + lo; const uint8_t* e = base + hi;
-      while (p < e && ((uintptr_t)p & 15)) { r = T[0][(r ^ *p++) & 255u] ^ (r >> 8); }
-      for (; p + 16 <= e; p += 16) {   // 128-bit loads: each lane streams its own slice, so wide loads keep the sector traffic down
-        uint4 q = *(const uint4*)p; u32 w;
-        w = q.x ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
-        w = q.y ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
-        w = q.z ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
-        w = q.w ^ r; r = T[3][w & 255u] ^ T[2][(w >> 8) & 255u] ^ T[1][(w >> 16) & 255u] ^ T[0][w >> 24];
+      while (p < e && ((uintptr_t)p & 15)) { r = T0[((r ^ *p++) & 255u) * 32] ^ (r >> 8); }
+      for (; p + 64 <= e; p += 64) {   // four 128-bit loads in flight per lane before the first is consumed
+        const uint4 q0 = *(const uint4*)p, q1 = *(const uint4*)(p + 16), q2 = *(const uint4*)(p + 32), q3 = *(const uint4*)(p + 48);
+        r = word(q0.x, r); r = word(q0.y, r); r = word(q0.z, r); r = word(q0.w, r);
+        r = word(q1.x, r); r = word(q1.y, r); r = word(q1.z, r); r = word(q1.w, r);
+        r = word(q2.x, r); r = word(q2.y, r); r = word(q2.z, r); r = word(q2.w, r);
+        r = word(q3.x, r); r = word(q3.y, r); r = word(q3.z, r); r = word(q3.w, r);
       }
-      while (p < e) { r = T[0][(r ^ *p++) & 255u] ^ (r >> 8); }
+      for (; p + 16 <= e; p += 16) { const uint4 q = *(const uint4*)p; r = word(q.x, r); r = word(q.y, r); r = word(q.z, r); r = word(q.w, r); }
+      while (p < e) { r = T0[((r ^ *p++) & 255u) * 32] ^ (r >> 8); }
     }
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < 5; k++) {
       u32 v = __shfl_xor_sync(0xffffffffu, r, 1 << k); bool upper = (lane >> k) & 1;
       u32 a = upper ? v : r, bb = upper ? r : v;   // a = the earlier bytes, bb = the later 2^k slices
@@ -229,11 +240,16 @@ void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, i
   if (n > 0) { de_check_kernel<<<(n + 255) / 256, 256, 0, s>>>(list, n, act, u_len, status, err); IRF_LAUNCHED(); }
 }
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list) {
-  static CrcMul M; static bool init = false;
+  static CrcMul M; static bool init = false; static int sms_of[64] = {0};
   if (!init) { u32 p = 0x40000000u;   // x^1; square up to x^(8 * 2048) = x^(2^14), then keep squaring
     for (int i = 0; i < 14; i++) p = crc_mulmod(p, p);
     for (int k = 0; k < 5; k++) { M.x[k] = p; p = crc_mulmod(p, p); } init = true; }
-  if (nblk > 0) { int grid = std::min((nblk + 7) / 8, 148 * 8); crc_check_kernel<<<grid, 256, 0, s>>>(U, u_off, u_len, crc_expected, nblk, M, status, err, list); IRF_LAUNCHED(); }
+  if (nblk <= 0) return;
+  constexpr int smem = 4 * 256 * 32 * 4;
+  int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");
+  if (!sms_of[dev]) { IRF_CUDA(cudaFuncSetAttribute(crc_check_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); IRF_CUDA(cudaDeviceGetAttribute(&sms_of[dev], cudaDevAttrMultiProcessorCount, dev)); }
+  const int wpb = CRC_THREADS / 32, grid = std::min((nblk + wpb - 1) / wpb, sms_of[dev]);
+  crc_check_kernel<<<grid, CRC_THREADS, smem, s>>>(U, u_off, u_len, crc_expected, nblk, M, status, err, list); IRF_LAUNCHED();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -279,12 +295,13 @@ __global__ void frame_guess_kernel(const uint8_t* __restrict__ U, const u64* __r
 }
 
 // Walks the records that start inside block b; exit = first record start at or beyond the block end.
-__device__ void walk_count_block(const uint8_t* U, u64 e, u64 blk_end, u64 Uend, u64& exit_off, u32& n_rec, u32& n_cand, int& ferr) {
+__device__ void walk_count_block(const uint8_t* U, u64 e, u64 blk_end, u64 Uend, u64& exit_off, u32& n_rec, u32& n_cand, int& ferr, u64* slots) {
   n_rec = 0; n_cand = 0; ferr = 0;
   while (e < blk_end) {
     if (e + 36 > Uend) { ferr = DERR_TRUNCATED; e = Uend; break; }
     Core c; load_core(U, e, c);
     if (c.block_size < 32 || e + 4 + (u64)c.block_size > Uend) { ferr = c.block_size < 32 ? DERR_BAD_RECORD : DERR_TRUNCATED; e = Uend; break; }
+    if (slots && n_rec < REC_SLOTS) slots[n_rec] = e;   // the record starts of this block, gathered into the dense list afterwards (no second walk)
     n_rec++;
     if (!(c.flag & 0x4) && c.refID >= 0 && (c.flag & 0x1) && !(c.flag & 0x8) && c.next_refID == c.refID) n_cand++;
     e += 4 + (u64)c.block_size;
@@ -293,12 +310,12 @@ __device__ void walk_count_block(const uint8_t* U, u64 e, u64 blk_end, u64 Uend,
 }
 __global__ void walk_count_kernel(const uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk, u64 Uend,
                                   const u64* __restrict__ entry, u64* __restrict__ exit_off, u32* __restrict__ n_rec, u32* __restrict__ n_cand,
-                                  const uint8_t* __restrict__ mask, uint8_t* __restrict__ ferr) {
+                                  const uint8_t* __restrict__ mask, uint8_t* __restrict__ ferr, u64* __restrict__ slots) {
   int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= nblk || (mask && !mask[b])) return;
   u64 e = entry[b];
   if (e == ~0ull) { exit_off[b] = ~0ull; n_rec[b] = 0; n_cand[b] = 0; ferr[b] = 0; return; }
-  u64 x; u32 nr, nc; int fe; walk_count_block(U, e, u_off[b] + u_len[b], Uend, x, nr, nc, fe);
+  u64 x; u32 nr, nc; int fe; walk_count_block(U, e, u_off[b] + u_len[b], Uend, x, nr, nc, fe, slots ? slots + (size_t)b * REC_SLOTS : nullptr);
   exit_off[b] = x; n_rec[b] = nr; n_cand[b] = nc; ferr[b] = (uint8_t)fe;
 }
 // Repair step, in two kernels so that no thread reads an entry another thread is rewriting.  Block b is "consistent" when
@@ -336,8 +353,19 @@ void launch_frame_guess(const FrameArgs& a, cudaStream_t s) {
   if (grid) { IRF_CUDA(cudaMemsetAsync(a.first, 0x7f, sizeof(int), s)); frame_guess_kernel<<<grid, 256, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.rec0, a.rec0_valid, a.n_ref, a.ref_len, a.entry, a.first); IRF_LAUNCHED(); }
 }
 void launch_walk_count(const FrameArgs& a, const uint8_t* mask, cudaStream_t s) {
-  int grid = (a.nblk + 127) / 128;
-  if (grid) { walk_count_kernel<<<grid, 128, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.entry, a.exit_off, a.n_rec, a.n_cand, mask, a.ferr); IRF_LAUNCHED(); }
+  int grid = (a.nblk + 63) / 64;   // 64-thread CTAs: a chunk has only a few thousand blocks, spread them over all SMs
+  if (grid) { walk_count_kernel<<<grid, 64, 0, s>>>(a.U, a.u_off, a.u_len, a.nblk, a.Uend, a.entry, a.exit_off, a.n_rec, a.n_cand, mask, a.ferr, a.slots); IRF_LAUNCHED(); }
+}
+// Dense record list from the per-block slot regions the walk filled: one warp per BGZF block, coalesced on both sides.
+__global__ void gather_records_kernel(const u64* __restrict__ slots, const u32* __restrict__ n_rec, const u64* __restrict__ rec_base, int nblk, u64* __restrict__ rec_off) {
+  const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (b >= nblk) return;
+  const u32 n = min(n_rec[b], REC_SLOTS); const u64 at = rec_base[b]; const u64* sp = slots + (size_t)b * REC_SLOTS;
+  for (u32 i = lane; i < n; i += 32) rec_off[at + i] = sp[i];
+}
+void launch_gather_records(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s) {
+  long threads = (long)a.nblk * 32; int grid = (int)((threads + 255) / 256);
+  if (grid) { gather_records_kernel<<<grid, 256, 0, s>>>(a.slots, a.n_rec, rec_base, a.nblk, rec_off); IRF_LAUNCHED(); }
 }
 void launch_frame_mark(const FrameArgs& a, uint8_t* mism, uint8_t* mask, u32* n_bad, cudaStream_t s) {
   int grid = (a.nblk + 255) / 256;
@@ -416,9 +444,14 @@ struct FragSink {
   __device__ void junction(u32 left, u32 right) {
     u64 base = T.chr_goff[chr]; u64 gl = base + left, gr = base + right; u64 gap = (u64)right - (u64)left;
     if (right < left || gap >= (1ull << JKEY_GAP_BITS) || gr >= (1ull << 36)) { atomicOr(T.err, DERR_JKEY_RANGE); return; }
-    u32 s = ht_upsert(T.jc_keys, T.jc_mask, jkey_make(gl, gap), T.err); if (s != 0xffffffffu) atomicAdd(&T.jc_cnt[2ull * s + dir], 1u);
-    s = ht_upsert(T.jl_keys, T.jl_mask, gl, T.err); if (s != 0xffffffffu) atomicAdd(&T.jl_cnt[2ull * s + dir], 1u);
-    s = ht_upsert(T.jr_keys, T.jr_mask, gr, T.err); if (s != 0xffffffffu) atomicAdd(&T.jr_cnt[2ull * s + dir], 1u);
+    // neighbouring fragments of a coordinate-sorted file cross the same junctions: the lanes of a warp that are here with the same
+    // key and strand elect one lane, which does the table look-up and adds the whole group's count (one atomic instead of up to 32)
+    const u64 key = jkey_make(gl, gap);
+    const u32 peers = __match_any_sync(__activemask(), key ^ ((u64)dir << 63)); const u32 n = (u32)__popc(peers);
+    if ((int)(threadIdx.x & 31) != __ffs(peers) - 1) return;
+    u32 s = ht_upsert(T.jc_keys, T.jc_mask, key, T.err); if (s != 0xffffffffu) atomicAdd(&T.jc_cnt[2ull * s + dir], n);
+    s = ht_upsert(T.jl_keys, T.jl_mask, gl, T.err); if (s != 0xffffffffu) atomicAdd(&T.jl_cnt[2ull * s + dir], n);
+    s = ht_upsert(T.jr_keys, T.jr_mask, gr, T.err); if (s != 0xffffffffu) atomicAdd(&T.jr_cnt[2ull * s + dir], n);
   }
   // SpansPoint::ProcessBlocks (row a8): points p with start < p < end
   __device__ void spans(u32 start, u32 end) {
@@ -602,8 +635,10 @@ __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const ui
   warp_add_stat(&T.stats[ST_SKIPPED], skipped); warp_add_stat(&T.stats[ST_CAND], cand);
   if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
 }
-__global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs) {
+__global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs, const u64* __restrict__ npairs_dev) {
+  if (npairs_dev) npairs = min(npairs, *npairs_dev);   // the grid was sized from an upper bound; the pairing kernel left the actual count on the device
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((u64)blockIdx.x * blockDim.x >= npairs) return;
   FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
   if (i < npairs) {
     u64 o1 = pair_list[2 * i], o2 = pair_list[2 * i + 1]; Core c1, c2; load_core(U, o1, c1); load_core(U, o2, c2);
@@ -612,8 +647,10 @@ __global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const u
   warp_add_stat(&T.stats[ST_PAIRED], st.paired); warp_add_stat(&T.stats[ST_SHORT], st.shortp); warp_add_stat(&T.stats[ST_INTERSECT], st.inter);
   warp_add_stat(&T.stats[ST_LONG], st.longp); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
 }
-__global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ single_list, u64 nsingles) {
+__global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ single_list, u64 nsingles, const u64* __restrict__ nsingles_dev) {
+  if (nsingles_dev) nsingles = min(nsingles, *nsingles_dev);
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  if ((u64)blockIdx.x * blockDim.x >= nsingles) return;
   FragSink sink(T); u32 n = 0;
   if (i < nsingles) { u64 e = single_list[i]; Core c; load_core(U, e, c); n = 1; process_single(T, U, e, c, sink); }
   warp_add_stat(&T.stats[ST_SINGLE], n); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
@@ -622,13 +659,13 @@ void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_of
   u64 grid = (nrec + 255) / 256;
   if (grid) { pair_records_kernel<<<(unsigned)grid, 256, 0, s>>>(T, U, rec_off, nrec, ptab, pmask, pair_list, single_list, list_counts); IRF_LAUNCHED(); }
 }
-void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s) {
-  u64 grid = (npairs + 127) / 128;
-  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs); IRF_LAUNCHED(); }
+void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s, const u64* npairs_dev) {
+  u64 grid = (npairs + 127) / 128;   // npairs_dev given: npairs is an upper bound and the kernel reads the count itself
+  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs, npairs_dev); IRF_LAUNCHED(); }
 }
-void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s) {
+void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s, const u64* nsingles_dev) {
   u64 grid = (nsingles + 127) / 128;
-  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, single_list, nsingles); IRF_LAUNCHED(); }
+  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, single_list, nsingles, nsingles_dev); IRF_LAUNCHED(); }
 }
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s) {
   int grid = (a.nblk + 127) / 128;

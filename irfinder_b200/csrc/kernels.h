@@ -17,6 +17,7 @@ struct FrameArgs {
   int n_ref; const int32_t* ref_len;
   u64* entry; u64* exit_off; u32* n_rec; u32* n_cand; uint8_t* ferr; int* err;  // ferr: per-block framing error of the latest walk
   int* first = nullptr;   // device scalar: index of the first block that has an entry (set by launch_frame_guess, read by launch_frame_mark)
+  u64* slots = nullptr;   // optional: REC_SLOTS record starts per block, filled by the walk (launch_gather_records turns them into the dense list)
 };
 
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s);
@@ -38,8 +39,9 @@ void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s);
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s);
 void launch_scan_counts(const u32* in, u64* out, int n, cudaStream_t s);
 void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s);
-void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s);
-void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s);
+void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s, const u64* npairs_dev = nullptr);
+void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s, const u64* nsingles_dev = nullptr);
+void launch_gather_records(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s);
 void launch_pair_leftover(const u64* ptab, u64 nslots, u64* n_left, u64* left_off, u64 left_cap, cudaStream_t s);
 void launch_halo_pack(const uint8_t* U, const u64* left_off, u64 n, uint8_t* out, u64* rec_off, u64* cursor, u64 cap, cudaStream_t s);
 unsigned long long launch_counter();
