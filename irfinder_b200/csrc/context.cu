@@ -120,7 +120,7 @@ struct irf_ctx {
     { std::ifstream f(rc); if (!f) throw string("cannot open ") + rc; sp.loadRef(f); }   // SpansPoint::setSpanLength(5,4) is compiled in (common.cuh)
     roi = RoiRef();
     if (roi_path && strcmp(roi_path, "NULL") != 0 && roi_path[0]) { std::ifstream f(roi_path); if (!f) throw string("cannot open ") + roi_path; roi.loadRef(f); }
-    refs_loaded = true; bound = false;
+    refs_loaded = true; bound = false; owner_key.clear();
     // chromosome-independent device tables
     upload(d_sp_pos, sp.pos, s_compute); upload(d_seg_start, cov.seg_start, s_compute); upload(d_seg_end, cov.seg_end, s_compute); upload(d_seg_coff, cov.seg_coff, s_compute);
     vector<u32> rs, re; for (auto& r : roi.rois) { rs.push_back(r.start); re.push_back(r.end); }
@@ -193,7 +193,7 @@ struct irf_ctx {
     T.jr_keys = d_jr_keys.as<u64>(); T.jr_cnt = d_jr_cnt.as<u32>(); T.jr_mask = jside_slots - 1;
     T.stats = d_stats.as<u64>(); T.err = d_err.as<int>();
     T.dump = dump_fragments ? d_dump.as<u32>() : nullptr; T.dump_cursor = dump_fragments ? d_dump_cursor.as<u64>() : nullptr; T.dump_cap = dump_cap;
-    bound = true; sync();
+    bound = true; owner_key.clear(); sync();
     reset(true);   // in the middle of a count: the inflate / CRC checks of this very run may already have raised the error flag
   }
 
@@ -736,7 +736,7 @@ struct irf_ctx {
   // (import_depth), and irf_finalize computes the statistics of the owned introns only; the rows of the other introns stay
   // zero on the device, so the caller merges the row tables with an integer SUM and then calls finalize_rows().
   bool owner_mode = false, rows_pending = false; int owner_me = 0, owner_world = 1; u32 n_own_introns = 0;
-  DevBuf d_seg_owner, d_own_introns, d_fidx, d_fval, d_rows_dir; u64 foreign_cap = 1ull << 20;
+  DevBuf d_seg_owner, d_own_introns, d_fidx, d_fval, d_rows_dir; u64 foreign_cap = 1ull << 20; vector<int64_t> owner_key;
   void first_record(int32_t& refid, int32_t& pos) {
     refid = -2; pos = 0; if (!counted) throw string("irf_count has not run");
     if (n_rec == 0 || frame_entry0 + 12 > Uend) return;
@@ -747,6 +747,9 @@ struct irf_ctx {
     if (!bound) throw string("irf_count has not run");
     if (world < 1 || world > 255 || me < 0 || me >= world) throw string("bad owner plan");
     const u32 nseg = (u32)cov.seg_start.size(); const int n = (int)chr_names.size();
+    { vector<int64_t> key; key.push_back(world); key.push_back(me); for (int r = 0; r < world; r++) { key.push_back(cut_refid[r]); key.push_back(cut_pos[r]); }
+      if (key == owner_key && d_seg_owner.p) { owner_mode = true; owner_me = me; owner_world = world; return; }   // same shards as last time (repeated runs on staged bytes): the plan stands
+      owner_key = key; }
     std::map<string, int> id; for (int i = n - 1; i >= 0; i--) id[chr_names[i]] = i;
     // cut keys (refID, pos); a rank without records (refID < 0) owns nothing: its cut is the next rank's
     vector<std::pair<int64_t, int64_t>> cut(world); const std::pair<int64_t, int64_t> INF{1ll << 40, 0};

@@ -247,8 +247,18 @@ def run_plan(core, plan, device=None, group=None, restage=True):
             core.set_option("stage_lazy", 1 if restage else 0)   # lazy: streamed to the GPU beside the inflate instead of copied first
         core.stage(data.ctypes.data, plan.n_own, data.size, has_header=(rank == 0))
         core._plan_staged_id = None if restage else id(plan)
+    import time as _time
+    _t = [_time.perf_counter()]
+    phases = {}
+
+    def _mark(name):
+        _sync(dev)
+        now = _time.perf_counter()
+        phases[name] = round((now - _t[0]) * 1e3, 2)
+        _t[0] = now
     core.count()
-    info = dict(cuts=plan.cuts, recount=0)
+    _mark("count")
+    info = dict(cuts=plan.cuts, recount=0, phase_ms=phases)
     if world > 1:
         # ---- frame handshake: my first record must be where my left neighbour's last record ends.  A recount changes the
         # exit a rank reports, so the values are exchanged again until nobody has to move (one round in practice).
@@ -267,6 +277,7 @@ def run_plan(core, plan, device=None, group=None, restage=True):
                 info["recount"] += 1
         else:
             raise RuntimeError("record framing of neighbouring shards does not agree")
+        _mark("handshake")
         # ---- 1. halo
         hb, hnb, ho, hnr = core.export_halo()
         _sync(dev)
@@ -278,6 +289,7 @@ def run_plan(core, plan, device=None, group=None, restage=True):
         _sync(dev)
         core.import_halo(all_bytes.data_ptr(), int(sum(blens)), all_offs.data_ptr() if all_offs.numel() else 0, int(all_offs.numel()), rank, world)
         info["halo_records"] = int(all_offs.numel())
+        _mark("halo")
         # ---- 2. junction tables: the three exports travel in ONE gather ([n0, n1, n2 | keys | counts as 64-bit words])
         exp = [core.export_junctions(which) for which in range(3)]
         _sync(dev)
@@ -298,11 +310,13 @@ def run_plan(core, plan, device=None, group=None, restage=True):
             k, c = torch.cat(ks).contiguous(), torch.cat(cs).contiguous()
             if k.numel():
                 core.import_junctions(which, k.data_ptr(), c.data_ptr(), int(k.numel()))
+        _mark("junctions")
         # ---- 3. small additive tables, in place on the library's buffers
         for name, typestr in (("spans", "<i4"), ("roi", "<i4"), ("chr", "<i4"), ("stats", "<i8")):
             p, cnt, _ = core.device_table(name)
             if cnt:
                 dist.all_reduce(_wrap(p, cnt, typestr, dev), op=dist.ReduceOp.SUM, group=group)
+        _mark("small_tables")
         # ---- 4. depth: region-owned
         rid, pos = core.first_record()
         mine = torch.tensor([rid, pos], dtype=torch.int64, device=dev)
@@ -323,8 +337,9 @@ def run_plan(core, plan, device=None, group=None, restage=True):
             _sync(dev)
             if ai.numel():
                 core.import_depth(ai.data_ptr(), av.data_ptr(), int(ai.numel()))
-        _sync(dev)
+        _mark("depth_exchange")
     core.finalize()
+    _mark("finalize")
     if world > 1:
         # ---- 5. rows of the owned introns -> every rank (integer SUM: exactly one rank holds a non-zero row)
         for name in ("rows_nondir",) + (("rows_dir",) if core.directionality != 0 else ()):
@@ -333,6 +348,7 @@ def run_plan(core, plan, device=None, group=None, restage=True):
                 dist.all_reduce(_wrap(p, cnt, "<i8", dev), op=dist.ReduceOp.SUM, group=group)
         _sync(dev)
         core.finalize_rows()
+        _mark("rows")
     return info
 
 

@@ -321,6 +321,8 @@ def test_region_sharded_run_is_byte_identical(tiny, tmp_path, world):
     info = run_sharded_local(cores, buf, bai=bai)
     if bai is None:      # index cuts sit where a 16 kb window begins, which in this small file can fall between read clusters
         assert info["halo_records"] > 0, "the cut points must split at least one pair for this test to mean anything"
+    if world == 5 and bai is None:   # region-owned depth: with five shards of this small genome some coverage must land in another rank's segments
+        assert info["foreign_depth_entries"] > 0, "no counter crossed an ownership boundary: the sparse depth exchange was not exercised"
     for r, c in enumerate(cores):
         out = str(tmp_path / f"g{r}")
         c.write_outputs(out)
