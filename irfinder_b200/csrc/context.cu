@@ -213,7 +213,7 @@ struct irf_ctx {
     IRF_CUDA(cudaMemsetAsync(d_stats.p, 0, ST_SLOTS * 8, s)); if (!keep_err) IRF_CUDA(cudaMemsetAsync(d_err.p, 0, 4, s));
     if (dump_fragments) IRF_CUDA(cudaMemsetAsync(d_dump_cursor.p, 0, 8, s));
     launch_ht_insert_keys(T.jc_keys, T.jc_mask, d_annot_keys.as<u64>(), n_annot, T.err, s);
-    counted = finalized = false; sharded = false; halo_leftover = 0; owner_mode = false; rows_pending = false; launches0 = launch_counter();
+    counted = finalized = false; sharded = false; halo_leftover = 0; owner_mode = false; rows_pending = false; n_carry = 0; carry_bytes = 0; launches0 = launch_counter();
   }
 
   // ---------------------------------------------------------------- BGZF scan (SAM v1 §4.1)
@@ -303,19 +303,23 @@ struct irf_ctx {
       auto fetch = [&](DevBuf& b, const void* src, size_t bytes) { b.ensure(bytes + 16); launch_host_fetch(b.p, h_tab.dev(src), bytes, s_compute); };
       fetch(d_c_off, c_off, nbk * 8); fetch(d_u_off, u_off, nbk * 8); fetch(d_c_len, c_len, nbk * 4); fetch(d_u_len, u_len, nbk * 4); fetch(d_crc, crcs, nbk * 4); }
     if (pre_ev_copy.empty() && !feed_active) d_comp.ensure(src_total + 64);
-    d_U.ensure(Uend + 64);
+    d_U.ensure(Uend + 64 + (seg_mode ? carry_bytes + 256 : 0));
     size_t nb = blks.size(); d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb); d_mism.ensure(nb);
     sync();  // allocation changes above settle before anything is queued against the buffers
     resident = false; staged = true; staged_has_header = has_header != 0; engines_planned = false;
     if (copy_now) { if (src_total) IRF_CUDA(cudaMemcpyAsync(d_comp.p, h_src, src_total, cudaMemcpyHostToDevice, s_compute)); sync(); resident = true; h_src = nullptr; }
   }
-  void stage_inflated(const void* src, size_t n) {  // reference stdin mode with an already-inflated stream
-    inflated_input = true; blks.clear(); const u32 CH = 65536; size_t nb = (n + CH - 1) / CH; vector<u64> u_off(nb); vector<u32> u_len(nb);
-    for (size_t i = 0; i < nb; i++) { u_off[i] = (u64)i * CH; u_len[i] = (u32)std::min<size_t>(CH, n - i * CH); blks.push_back(Blk{0, 0, u_len[i], 0}); }
-    nblk_own = (int)nb; Uend = n; upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute); d_U.ensure(n + 64);
-    IRF_CUDA(cudaMemcpyAsync(d_U.p, src, n, cudaMemcpyHostToDevice, s_compute));
+  // Reference stdin mode with an already-inflated stream (`gzip -cd | irfinder ... /dev/stdin`): the bytes are cut into 64 KiB
+  // pseudo-blocks so that record framing works as for BGZF input.  n_own < n_total: a segment of a longer stream with look-ahead
+  // bytes (n_own a multiple of 64 KiB); has_header = 0: a later segment.
+  void stage_inflated(const void* src, size_t n_own, size_t n_total, bool has_header) {
+    inflated_input = true; blks.clear(); const u32 CH = 65536; const size_t n = n_total; size_t nb = (n + CH - 1) / CH; vector<u64> u_off(nb); vector<u32> u_len(nb);
+    if (n_own < n_total && n_own % CH) throw string("internal: a segment of an inflated stream must end on a 64 KiB boundary");
+    for (size_t i = 0; i < nb; i++) { u_off[i] = (u64)i * CH; u_len[i] = (u32)std::min<size_t>(CH, n - i * CH); blks.push_back(Blk{0, 0, u_len[i], (u64)i * CH}); }
+    nblk_own = (int)((n_own + CH - 1) / CH); Uend = n; upload(d_u_off, u_off, s_compute); upload(d_u_len, u_len, s_compute); d_U.ensure(n + 64 + (seg_mode ? carry_bytes + 256 : 0));
+    IRF_CUDA(cudaMemcpyAsync(d_U.p, src, n, cudaMemcpyHostToDevice, s_compute)); IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + n, 0, 64, s_compute));
     d_status.ensure(nb * 4); d_entry.ensure(nb * 8); d_exit.ensure(nb * 8); d_nrec.ensure(nb * 4); d_ncand.ensure(nb * 4); d_ferr.ensure(nb); d_mask.ensure(nb); d_mism.ensure(nb);
-    sync(); staged = true; staged_has_header = true; resident = true;
+    sync(); staged = true; staged_has_header = has_header; resident = true;
   }
 
   // S1: one persistent inflate launch.  When the bytes are still on the host the copy runs beside it in 256 MB chunks on
@@ -602,7 +606,8 @@ struct irf_ctx {
         Uend = full; if (ok) break;
       }
       if (!bound) chr_map_update();
-      pslots = next_pow2(std::max<u64>(1024, Uend / 80)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
+      pslots = next_pow2(std::max<u64>(1024, Uend / 80 + 2 * n_carry)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
+      park_carry();
       u32* n_bad = d_small.as<u32>(); u64* totals = (u64*)(d_small.as<uint8_t>() + 16); u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192);
       // A shard of a larger file (multi-GPU) has no header and ends with look-ahead blocks that are inflated but not counted
       // here: its first record start is a guess unless the caller passed one ("entry0"), exactly as in count().
@@ -649,7 +654,7 @@ struct irf_ctx {
           d_rec_base.ensure((size_t)nbk * 8); d_rec_off.ensure((ht[0] + ht[0] / 2) * 8); d_pair_list.ensure((ht[1] + ht[1] / 2 + 16) * 16); d_single_list.ensure((ht[0] + ht[0] / 2 + 16) * 8);
           launch_scan_counts(d_nrec.as<u32>() + b0, d_rec_base.as<u64>(), nbk, s_compute); launch_gather_records(fa, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
           IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
-          launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), ht[0], d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute);
+          launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), ht[0], d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute, carry_base(), 1);
           launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), ht[1] + 1, s_compute, list_counts);   // every pair is completed by one candidate record of this chunk (its mate may have waited since an earlier chunk)
           launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), ht[0] - ht[1] + 1, s_compute, list_counts + 1);
         }
@@ -668,6 +673,7 @@ struct irf_ctx {
     } catch (...) { cudaStreamSynchronize(s_copy); cudaStreamSynchronize(s_de); cudaStreamSynchronize(s_chk); cudaStreamSynchronize(s_compute); cleanup(); throw; }
     cleanup();
     resident = true; counted = true; finalized = false;
+    collect_carry();
   }
 
   // S2 + S3
@@ -709,13 +715,14 @@ struct irf_ctx {
     check_dev_err("record framing");
     if (nblk_own == nb && nb > 0 && fe[1] != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
     IRF_CUDA(cudaEventRecord(e2, s_compute));
-    pslots = next_pow2(std::max<u64>(1024, n_cand + n_cand / 2)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
+    pslots = next_pow2(std::max<u64>(1024, n_cand + n_cand / 2 + 2 * n_carry)); d_ptab.ensure(pslots * 8); IRF_CUDA(cudaMemsetAsync(d_ptab.p, 0, pslots * 8, s_compute));
+    park_carry();
     d_rec_base.ensure((size_t)nblk_own * 8); d_rec_off.ensure(n_rec * 8);
     launch_scan_counts(d_nrec.as<u32>(), d_rec_base.as<u64>(), nblk_own, s_compute);
     launch_walk_list(own, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
     d_pair_list.ensure((n_cand / 2 + 1) * 16); d_single_list.ensure((n_rec - n_cand + 1) * 8);
     u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192); IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
-    launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute);
+    launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute, carry_base(), 1);
     u64 lc[2] = {0, 0}; IRF_CUDA(cudaMemcpyAsync(lc, list_counts, 16, cudaMemcpyDeviceToHost, s_compute)); sync();
     launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), lc[0], s_compute);
     launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), lc[1], s_compute);
@@ -726,6 +733,7 @@ struct irf_ctx {
     timing[0] = a; timing[2] = b; timing[3] = c; timing[5] = a + b + c;
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); cudaEventDestroy(e3);
     counted = true; finalized = false;
+    collect_carry();
   }
   int frame_rounds = 0;
 
@@ -793,6 +801,36 @@ struct irf_ctx {
     pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute));
     if (directionality != 0) { pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows_dir.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_compute)); }
     sync(); rows_pending = false; finalized = true;
+  }
+
+  // ---------------------------------------------------------------- segmented (streamed) runs
+  // A stream of unknown length (stdin behind STAR or `gzip -cd`) is counted segment by segment: each segment is
+  // staged and counted like a shard (own bytes + look-ahead, first record handed over from the previous segment's last one) on the
+  // same context without a reset in between.  Mates that are still waiting when a segment ends are trimmed to fixed part + name +
+  // CIGAR (the halo format) and carried into the next segment, where they are parked in the fresh pair table ahead of its records.
+  bool seg_mode = false; u64 n_carry = 0, carry_bytes = 0; DevBuf d_carry, d_carry_off; size_t stream_segment_bytes = 1ull << 30;
+  u64 carry_base() const { return seg_mode && n_carry ? ((Uend + 64 + 63) & ~63ull) : ~0ull; }
+  void park_carry() {   // called after the pair table has been cleared, before the segment's own records are paired
+    if (!seg_mode || !n_carry) return;
+    const u64 cb = carry_base();
+    IRF_CUDA(cudaMemcpyAsync(d_U.as<uint8_t>() + cb, d_carry.p, carry_bytes, cudaMemcpyDeviceToDevice, s_compute));
+    IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + cb + carry_bytes, 0, 64, s_compute));
+    launch_shift_offsets(d_carry_off.as<u64>(), n_carry, cb, s_compute);
+    u64* lc = (u64*)(d_small.as<uint8_t>() + 192); IRF_CUDA(cudaMemsetAsync(lc, 0, 16, s_compute));
+    d_pair_list.ensure((n_carry + 16) * 16); d_single_list.ensure((n_carry + 16) * 8);
+    launch_pair_records(T, d_U.as<uint8_t>(), d_carry_off.as<u64>(), n_carry, d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), lc, s_compute, cb, 0);
+  }
+  void collect_carry() {   // after a segment's count: the records still waiting for a mate
+    if (!seg_mode) return;
+    u64 n = count_leftovers(nullptr, 0); d_left.ensure(n * 8 + 8); if (n) count_leftovers(d_left.as<u64>(), n);
+    u64 cap = n * 320 + 1024; u64 used = 0;
+    for (;;) {
+      d_carry.ensure(cap + 64); d_carry_off.ensure(n * 8 + 8); u64* cur = (u64*)(d_small.as<uint8_t>() + 128); IRF_CUDA(cudaMemsetAsync(cur, 0, 8, s_compute));
+      launch_halo_pack(d_U.as<uint8_t>(), d_left.as<u64>(), n, d_carry.as<uint8_t>(), d_carry_off.as<u64>(), cur, cap, s_compute);
+      IRF_CUDA(cudaMemcpyAsync(&used, cur, 8, cudaMemcpyDeviceToHost, s_compute)); sync();
+      if (used <= cap) break; cap = used + 1024;
+    }
+    n_carry = n; carry_bytes = used;
   }
 
   u64 count_leftovers(u64* fill, u64 cap) {
@@ -928,6 +966,65 @@ struct irf_ctx {
     return " [blocks were being inflated by the hardware decompression engine, which reports malformed DEFLATE data as a CUDA fault: the input is probably corrupt;"
            " this process's CUDA context is lost; rerun with option safe_inflate=1 (IRF_SAFE_INFLATE=1 for the irfinder binary) to have the SM kernel name the damaged block]";
   }
+  // irf_run_stream: a pipe of unknown length, counted segment by segment with two page-locked buffers (a reader thread fills one
+  // while the GPU counts the other).  A segment = own bytes (ending on a BGZF block boundary, or a 64 KiB boundary of an inflated
+  // stream) + look-ahead bytes, which are also the first bytes of the next segment.
+  void run_stream(int fd, bool inflated) {
+    const size_t SEG = std::max<size_t>(stream_segment_bytes, 1u << 20), LA = std::min<size_t>(SEG, 8u << 20), SLOT = SEG + LA + (1u << 17);
+    struct Slot { uint8_t* p = nullptr; size_t own = 0, total = 0, filled = 0; bool last = false, ready = false; string err; } slot[2];
+    for (auto& sl : slot) IRF_CUDA(cudaMallocHost((void**)&sl.p, SLOT + 64));
+    std::mutex mu; std::condition_variable cv; bool stop = false;
+    auto boundary = [&](const uint8_t* p, size_t filled, size_t limit, bool eof) -> size_t {   // largest segment end <= limit
+      if (inflated) return eof && filled <= limit ? filled : (std::min(limit, filled) / 65536) * 65536;
+      size_t off = 0; Blk b; size_t tot = 0;
+      while (off + 18 <= filled && parse_block(p, off, filled, b, tot, nullptr) && off + tot <= limit) off += tot;
+      return off;
+    };
+    std::thread reader([&]() {
+      size_t keep = 0; int cur = 0; bool eof = false;
+      while (!eof) {
+        Slot& sl = slot[cur];
+        { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return stop || !sl.ready; }); if (stop) return; }
+        size_t filled = keep;   // the tail of the previous slot (its look-ahead and what followed) is already at the front
+        while (filled < SEG + LA) { ssize_t k = read(fd, sl.p + filled, std::min<size_t>(SEG + LA - filled, 1u << 26)); if (k < 0) { sl.err = "read error"; eof = true; break; } if (k == 0) { eof = true; break; } filled += (size_t)k; }
+        sl.filled = filled; sl.last = eof;
+        if (eof) { sl.total = boundary(sl.p, filled, filled, true); sl.own = sl.total; if (sl.err.empty() && sl.total != filled) sl.err = inflated ? "internal" : "truncated BGZF block at the end of the stream"; }
+        else { sl.own = boundary(sl.p, filled, SEG, false); sl.total = boundary(sl.p, filled, filled, false);
+          if (!sl.own) { sl.err = "no BGZF block boundary inside a segment (not a BGZF stream?)"; eof = true; }
+          else { Slot& nx = slot[cur ^ 1]; { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return stop || !nx.ready; }); if (stop) return; }
+            keep = filled - sl.own; memcpy(nx.p, sl.p + sl.own, keep); } }
+        { std::lock_guard<std::mutex> g(mu); sl.ready = true; } cv.notify_all();
+        cur ^= 1;
+      }
+    });
+    auto finish = [&]() { { std::lock_guard<std::mutex> g(mu); stop = true; } cv.notify_all(); reader.join(); for (auto& sl : slot) cudaFreeHost(sl.p); seg_mode = false; };
+    try {
+      if (bound) reset();
+      seg_mode = true; n_carry = 0; carry_bytes = 0; entry0_override = -1;
+      bool first = true; u64 n_rec_all = 0; double t_count = 0;
+      for (int cur = 0;; cur ^= 1) {
+        Slot& sl = slot[cur];
+        { std::unique_lock<std::mutex> lk(mu); cv.wait(lk, [&] { return sl.ready; }); }
+        if (!sl.err.empty()) throw sl.err;
+        if (first && sl.total == 0) throw string(inflated ? "empty input stream" : "not a BGZF stream (empty input)");
+        if (sl.total) {
+          if (inflated) stage_inflated(sl.p, sl.own, sl.total, first);
+          else { if (sl.last && require_eof) { Blk b; size_t tot = 0, off = 0, lastsz = 1; while (off < sl.total && parse_block(sl.p, off, sl.total, b, tot, nullptr)) { lastsz = b.isize; off += tot; } if (lastsz != 0) throw string("BGZF EOF marker missing (truncated stream?)"); }
+            bool req = require_eof; require_eof = false; try { stage(sl.p, sl.own, sl.total, first ? 1 : 0, false); } catch (...) { require_eof = req; throw; } require_eof = req; }
+          if (first && !bound && false) {}
+          count(); n_rec_all += n_rec; t_count += timing[5];
+          entry0_override = (long long)frame_exit_rel;   // where the next segment's first record starts, relative to its first inflated byte
+        }
+        const bool last = sl.last; first = false;
+        { std::lock_guard<std::mutex> g(mu); sl.ready = false; } cv.notify_all();
+        if (last) break;
+      }
+      if (n_carry) { /* mates that never came: counted as error reads through the candidate count in finalize */ }
+      n_rec = n_rec_all; timing[5] = t_count;
+      finish();
+      finalize();
+    } catch (...) { finish(); throw; }
+  }
   void* pinned_buf(size_t n) { if (n > pinned_cap) { if (pinned) cudaFreeHost(pinned); pinned = nullptr; IRF_CUDA(cudaMallocHost(&pinned, n + 64)); pinned_cap = n; } return pinned; }
   size_t read_fd_all(int fd, size_t hint) {
     size_t cap = std::max<size_t>(hint, 1 << 20), n = 0; vector<uint8_t> tmp; uint8_t* dst = (uint8_t*)pinned_buf(cap);
@@ -963,7 +1060,7 @@ void irf_destroy(irf_ctx* c) {
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_slots, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
-                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
@@ -987,6 +1084,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "verify_crc") c->verify_crc = v != 0;
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
   else if (k == "safe_inflate") { if (v) { c->de_percent = 0; c->de_percent_stream = 0; } else { c->de_percent = 70; c->de_percent_stream = 100; } c->engines_planned = false; }   // untrusted input: every block through the SM kernel, which answers malformed DEFLATE with IRF_EFORMAT and stays usable
+  else if (k == "stream_segment_mb") { if (v < 1 || v > 65536) return IRF_EINVAL; c->stream_segment_bytes = (size_t)v << 20; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements
   else if (k == "file_ring") { if (v < 0 || v > 2) return IRF_EINVAL; c->file_ring = (int)v; }
@@ -1029,13 +1127,7 @@ int irf_run_bam(irf_ctx* c, const char* path, const char* /*bai_path*/) {
     c->run_host_buffer(c->pinned, n);
   });
 }
-int irf_run_stream(irf_ctx* c, int fd, int inflated) {
-  IRF_TRY(c, {
-    size_t n = c->read_fd_all(fd, 64 << 20);
-    if (!inflated) c->run_host_buffer(c->pinned, n);
-    else { c->stage_inflated(c->pinned, n); if (c->bound) c->reset(); c->count(); c->finalize(); }
-  });
-}
+int irf_run_stream(irf_ctx* c, int fd, int inflated) { IRF_TRY(c, c->run_stream(fd, inflated != 0)); }
 int irf_write_outputs(irf_ctx* c, const char* outdir) { if (!outdir) return IRF_EINVAL; IRF_TRY(c, c->write_outputs(outdir)); }
 const char* irf_stdout_text(irf_ctx* c) { return c ? c->stdout_text.c_str() : ""; }
 int irf_directionality(irf_ctx* c) { return c ? c->directionality : 0; }

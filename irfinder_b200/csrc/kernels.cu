@@ -612,8 +612,11 @@ __device__ __forceinline__ void warp_add_stat(u64* slot, u64 v) {
   for (int o = 16; o; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
   if ((threadIdx.x & 31) == 0 && v) atomicAdd(slot, v);
 }
+// carry_base: records at offsets >= carry_base are waiting mates carried over from the previous segment of a segmented (streamed) run;
+// they come EARLIER in the file than every record of this segment (the tie-break for level mates) and were counted when first seen
+// (count_stats = 0 for the launch that parks them again).
 __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask,
-                                                            u64* __restrict__ pair_list, u64* __restrict__ single_list, u64* __restrict__ list_counts) {
+                                                            u64* __restrict__ pair_list, u64* __restrict__ single_list, u64* __restrict__ list_counts, u64 carry_base, int count_stats) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
   bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0, cand = 0;
   if (i < nrec) {
@@ -625,13 +628,16 @@ __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const ui
       u64 mo; Core m; cand = 1;
       if (pair_lookup_or_wait(T, ptab, pmask, U, e, c, mo, m)) {
         is_pair = true;
-        bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e < mo);       // read 1 = left mate; level starts: the earlier record
+        const bool e_carry = e >= carry_base, m_carry = mo >= carry_base;
+        const bool e_earlier = e_carry != m_carry ? e_carry : e < mo;
+        bool first_is_me = c.pos < m.pos || (c.pos == m.pos && e_earlier);    // read 1 = left mate; level starts: the earlier record
         o1 = first_is_me ? e : mo; o2 = first_is_me ? mo : e;
       }
     }
   }
   u64 at = warp_append(&list_counts[0], is_pair); if (is_pair) { pair_list[2 * at] = o1; pair_list[2 * at + 1] = o2; }
   at = warp_append(&list_counts[1], is_single); if (is_single) single_list[at] = e;
+  if (!count_stats) return;
   warp_add_stat(&T.stats[ST_SKIPPED], skipped); warp_add_stat(&T.stats[ST_CAND], cand);
   if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
 }
@@ -655,10 +661,12 @@ __global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const
   if (i < nsingles) { u64 e = single_list[i]; Core c; load_core(U, e, c); n = 1; process_single(T, U, e, c, sink); }
   warp_add_stat(&T.stats[ST_SINGLE], n); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
 }
-void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s) {
+void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s, u64 carry_base, int count_stats) {
   u64 grid = (nrec + 255) / 256;
-  if (grid) { pair_records_kernel<<<(unsigned)grid, 256, 0, s>>>(T, U, rec_off, nrec, ptab, pmask, pair_list, single_list, list_counts); IRF_LAUNCHED(); }
+  if (grid) { pair_records_kernel<<<(unsigned)grid, 256, 0, s>>>(T, U, rec_off, nrec, ptab, pmask, pair_list, single_list, list_counts, carry_base, count_stats); IRF_LAUNCHED(); }
 }
+__global__ void shift_offsets_kernel(u64* off, u64 n, u64 delta) { u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i < n) off[i] += delta; }
+void launch_shift_offsets(u64* off, u64 n, u64 delta, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { shift_offsets_kernel<<<(unsigned)g, 256, 0, s>>>(off, n, delta); IRF_LAUNCHED(); } }
 void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s, const u64* npairs_dev) {
   u64 grid = (npairs + 127) / 128;   // npairs_dev given: npairs is an upper bound and the kernel reads the count itself
   if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs, npairs_dev); IRF_LAUNCHED(); }

@@ -278,6 +278,44 @@ def test_cli_default_options_on_damaged_bams(built, tiny, tmp_path):
     assert_same_outputs(tiny["oracle_out"], out)
 
 
+@pytest.mark.parametrize("order", ["sorted", "collated"])
+@pytest.mark.parametrize("inflated", [0, 1])
+def test_stream_input_is_counted_segment_by_segment(built, tiny, tmp_path, order, inflated):
+    """irf_run_stream (the reference's /dev/stdin mode) reads a pipe of unknown length in bounded segments:
+    here 1 MB segments of a 7 MB file, so records straddle segment ends and (in the coordinate-sorted file) mates sit in different
+    segments and are carried over.  BGZF bytes and an already-inflated stream, both record orders; a stream cut short must fail."""
+    from bamutil import inflate_file
+    from irfinder_b200 import IRFError
+    path = tiny[order]
+    if inflated:
+        path = str(tmp_path / "raw.bam.bytes")
+        open(path, "wb").write(inflate_file(tiny[order]))
+    c = _core(stream_segment_mb=1)
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    for rep in range(2):                                   # twice on one context: nothing of the first run may leak into the second
+        r, w = os.pipe()
+        feeder = subprocess.Popen(["dd", "if=" + path, "bs=777777", "status=none"], stdout=w)   # a real pipe, fed in odd-sized pieces
+        os.close(w)
+        c.run_stream(r, inflated)
+        os.close(r)
+        assert feeder.wait() == 0
+        out = str(tmp_path / f"g{rep}")
+        c.write_outputs(out)
+        assert_same_outputs(tiny["oracle_out"], out)
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+    cut = str(tmp_path / "cut.bytes")
+    data = open(path, "rb").read()
+    open(cut, "wb").write(data[: len(data) * 2 // 3 + 11])
+    fd = os.open(cut, os.O_RDONLY)
+    with pytest.raises(IRFError):
+        c.run_stream(fd, inflated)
+    os.close(fd)
+    fd = os.open(path, os.O_RDONLY)
+    c.run_stream(fd, inflated)                             # the context stays usable
+    os.close(fd)
+    assert c.stats()["pairs"] > 0
+
+
 def test_micro_fixture_by_hand_on_gpu(tmp_path):
     """The hand-derived fixture of tests/micro_fixture.py (every cell computed by hand) through the CUDA path,
     in both record orders; BGZF blocks of 700-900 bytes make nearly every record straddle a block boundary."""
