@@ -8,7 +8,7 @@ pairing, every ProcessBlocks, depth scan and per-intron statistics.
   value : million read pairs / s with the compressed BAM already resident in HBM (irf_reset + irf_count + irf_finalize)
   e2e   : the same through the reference-facing call with HOST buffers: irf_run_buffer (pinned host BGZF bytes ->
           device in the timed region) + irf_write_outputs (result tables device -> host, six text tables formatted)
-  roofline : dominant kernel = inflate_kernel; algorithmic bytes = compressed in + inflated out
+  roofline : dominant kernel = inflate_tok_kernel; algorithmic bytes = compressed in + inflated out
   cpu_baseline : the CPU restatement in oracle/ (the mounted reference has no source) on one host core,
           bounded sample of the same workload
 Workload: BASELINE.json configs[1] (50M pairs 2x150, GRCh38-shaped, ~200k introns); inputs (10 GB) exceed L2.
@@ -408,8 +408,8 @@ def run_b200(a):
                        "merge_phase_ms": (merge_phases if world > 1 else None), "generation_s": round(gen_s, 1), "ref_load_s": round(ref_s, 2), "pairs_counted": stats["pairs"], "checks": "ok" if all(checks.values()) else {k: v for k, v in checks.items() if not v}, "stage_ms": {k: round(v, 3) for k, v in stage_t.items()}},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(comp_bytes), "d2h_bytes_per_step": int(d2h), "ms_per_step": round(dte / a.steps * 1e3, 3), "text_bytes_written": int(out_bytes), "stage_ms": {k: round(v, 3) for k, v in e2e_stage.items()}},
             "gpu_launches": launches,
-            "roofline": {"bound": "hbm", "kernel": "inflate_kernel: one persistent launch, %.0f %% of the inflate bytes; the hardware decompression engine inflates the other %.0f %% concurrently" % (sm_share * 100, 100 - sm_share * 100),
-                         "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic, "traffic_source": "profiles/inflate_traffic.json: DRAM bytes per algorithmic byte of this kernel from one ncu --set full capture (12M-pair input) x this launch's algorithmic bytes", "peak_source": peak_src,
+            "roofline": {"bound": "hbm", "kernel": "inflate_tok_kernel (two-phase DEFLATE: Huffman decode per lane, LZ77 resolve per warp): %.0f %% of the inflate bytes in %.0f persistent launch(es) per step; the hardware decompression engine inflates the other %.0f %% concurrently" % (sm_share * 100, inflate_launches / max(a.steps, 1), 100 - sm_share * 100),
+                         "achieved": round(achieved, 2), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic, "traffic_source": "profiles/inflate_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum per algorithmic byte from one ncu --set full capture of this very launch (tools/ncu_inflate_benched.sh: the first SM-inflate launch of `python bench.py` on this workload) x this launch's algorithmic bytes", "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(sm_bytes), "launches_per_step": inflate_launches / max(a.steps, 1), "avg_launch_ms": round(sm_ms, 3),
                          "both_engines": {"achieved": round(stage_achieved, 2), "frac": round(stage_achieved / peak, 5), "algorithmic_bytes_per_step": int(alg_bytes), "ms_until_all_inflated": round(avg_inflate_ms, 3)}},
             "cpu_baseline": cpu, "clocks": clocks}
