@@ -11,12 +11,17 @@ namespace irf {
 typedef unsigned long long u64;
 typedef uint32_t u32;
 
-// ---- disputed behavioural constants; the oracle holds its own copy on purpose
-constexpr int JUNC_MIN_FLANK = 5;          // [C-3]
-constexpr u32 SPAN_OVERHANG_LEFT = 5;      // [C-4]
-constexpr u32 SPAN_OVERHANG_RIGHT = 4;     // [C-4]
-constexpr u32 EDGE_WINDOW_OFFSET = 5;      // [C-13]
-constexpr u32 EDGE_WINDOW_LEN = 50;        // [C-13]
+// ---- disputed behaviours: every rule the recollected specification is unsure about is a RUN-TIME setting, on
+// this side (irf_set_option "rule_*") and, independently, in the oracle (environment IRF_RULE_*), so that the day the reference source
+// can be read a wrong guess is a configuration change and not a kernel edit.  Defaults = the resolutions listed in DESIGN.md §1.
+struct Rules {
+  int junc_min_flank = 5;                  // [C-3]  both blocks flanking a junction must be at least this long
+  u32 span_left = 5, span_right = 4;       // [C-4]  a span point p is counted when blockStart + left < p < blockEnd - right
+  u32 skip_flags = 0;                      // [C-6]  extra flag bits whose records are skipped (0x100 secondary, 0x800 supplementary); unmapped always are
+  int pct_tie_midpoint = 1;                // [C-12] cumulative count exactly on the percentile boundary: 1 = midpoint with the next depth, 0 = this depth
+  u32 edge_offset = 5, edge_len = 50;      // [C-13] first/last windows of an intron
+  double warn_lowcover = 10, warn_lowsplice = 4, warn_minor_ratio = 0.33333, warn_nonuniform_abs = 4, warn_nonuniform_ratio = 1.5;   // [C-14]
+};
 constexpr int BUCKET_SHIFT = 10;
 constexpr u32 REC_SLOTS = 65536 / 36 + 2;   // records that can START inside one BGZF block (a record has at least 36 bytes)
 
@@ -63,6 +68,7 @@ struct DevTables {
   int* err;
   // optional fragment dump (tests): words appended at dump[atomicAdd(dump_cursor, n)]
   u32* dump; u64* dump_cursor; u64 dump_cap;
+  Rules rules;
 };
 
 // One row of IRFinder-IR-*.txt in numeric form; text formatting happens on the host.

@@ -101,7 +101,7 @@ struct irf_ctx {
   bool counted = false, finalized = false;
   string err;
 
-  DevTables T{};
+  DevTables T{}; Rules rules;
 
   // ---------------------------------------------------------------- set-up
   void init(int dev) {
@@ -173,6 +173,7 @@ struct irf_ctx {
       IntronDesc d; d.blk_begin = (u32)ib.size();
       for (auto& b : rec.blocks) cov.pieces(rec.chrName, b.first, b.second, ib);
       d.blk_main_end = (u32)ib.size();
+      const u32 EDGE_WINDOW_OFFSET = rules.edge_offset, EDGE_WINDOW_LEN = rules.edge_len;   // [C-13]
       u32 ws = rec.start + EDGE_WINDOW_OFFSET, we = rec.end > EDGE_WINDOW_OFFSET ? rec.end - EDGE_WINDOW_OFFSET : 0;
       cov.pieces(rec.chrName, ws, std::min(ws + EDGE_WINDOW_LEN, rec.end), ib); d.blk_first_end = (u32)ib.size();
       cov.pieces(rec.chrName, (we > EDGE_WINDOW_LEN && we - EDGE_WINDOW_LEN > rec.start) ? we - EDGE_WINDOW_LEN : rec.start, we, ib); d.blk_last_end = (u32)ib.size();
@@ -192,6 +193,7 @@ struct irf_ctx {
     T.jl_keys = d_jl_keys.as<u64>(); T.jl_cnt = d_jl_cnt.as<u32>(); T.jl_mask = jside_slots - 1;
     T.jr_keys = d_jr_keys.as<u64>(); T.jr_cnt = d_jr_cnt.as<u32>(); T.jr_mask = jside_slots - 1;
     T.stats = d_stats.as<u64>(); T.err = d_err.as<int>();
+    T.rules = rules;
     T.dump = dump_fragments ? d_dump.as<u32>() : nullptr; T.dump_cursor = dump_fragments ? d_dump_cursor.as<u64>() : nullptr; T.dump_cap = dump_cap;
     bound = true; owner_key.clear(); sync();
     reset(true);   // in the middle of a count: the inflate / CRC checks of this very run may already have raised the error flag
@@ -1084,6 +1086,16 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "verify_crc") c->verify_crc = v != 0;
   else if (k == "de_percent") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent = (int)v; c->de_percent_stream = v == 0 ? 0 : c->de_percent_stream; c->engines_planned = false; }
   else if (k == "safe_inflate") { if (v) { c->de_percent = 0; c->de_percent_stream = 0; } else { c->de_percent = 70; c->de_percent_stream = 100; } c->engines_planned = false; }   // untrusted input: every block through the SM kernel, which answers malformed DEFLATE with IRF_EFORMAT and stays usable
+  else if (k.rfind("rule_", 0) == 0) {   // SURVEY.md Appendix C rules (see Rules in common.cuh); floating thresholds are given in millionths
+    Rules& R = c->rules; const string r = k.substr(5);
+    if (r == "junc_min_flank") R.junc_min_flank = (int)v; else if (r == "span_left") R.span_left = (u32)v; else if (r == "span_right") R.span_right = (u32)v;
+    else if (r == "skip_flags") R.skip_flags = (u32)v; else if (r == "pct_tie_midpoint") R.pct_tie_midpoint = v != 0;
+    else if (r == "edge_offset") R.edge_offset = (u32)v; else if (r == "edge_len") R.edge_len = (u32)v;
+    else if (r == "warn_lowcover_e6") R.warn_lowcover = v / 1e6; else if (r == "warn_lowsplice_e6") R.warn_lowsplice = v / 1e6; else if (r == "warn_minor_ratio_e6") R.warn_minor_ratio = v / 1e6;
+    else if (r == "warn_nonuniform_abs_e6") R.warn_nonuniform_abs = v / 1e6; else if (r == "warn_nonuniform_ratio_e6") R.warn_nonuniform_ratio = v / 1e6;
+    else { c->err = "unknown option " + k; return IRF_EINVAL; }
+    c->bound = false;   // the device tables carry the rules (and the edge windows are cut on the host): bind again
+  }
   else if (k == "stream_segment_mb") { if (v < 1 || v > 65536) return IRF_EINVAL; c->stream_segment_bytes = (size_t)v << 20; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements

@@ -474,9 +474,9 @@ struct FragSink {
   __device__ __noinline__ void block(int s, int l) {   // one body shared by every call site: the fully inlined version thrashed the instruction cache
     u32 a = read_start + (u32)s, e = a + (u32)l;
     nuc += (u32)l;
-    if (have_prev && prev_len >= JUNC_MIN_FLANK && l >= JUNC_MIN_FLANK) junction(prev_end, a);
+    if (have_prev && prev_len >= T.rules.junc_min_flank && l >= T.rules.junc_min_flank) junction(prev_end, a);
     have_prev = true; prev_end = e; prev_len = l;
-    if ((u32)l > SPAN_OVERHANG_LEFT + SPAN_OVERHANG_RIGHT) spans(a + SPAN_OVERHANG_LEFT, e - SPAN_OVERHANG_RIGHT);
+    if ((u32)l > T.rules.span_left + T.rules.span_right) spans(a + T.rules.span_left, e - T.rules.span_right);
     if (l > 0) coverage(a, e);
     if (dump_base && dump_n + 2 <= dump_base[0]) { dump_base[dump_n++] = a; dump_base[dump_n++] = e; dump_nb[dump_read]++; }
   }
@@ -621,7 +621,7 @@ __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const ui
   bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0, cand = 0;
   if (i < nrec) {
     e = rec_off[i]; Core c; load_core(U, e, c);
-    if ((c.flag & 0x4) || c.refID < 0) skipped = 1;                          // [C-6] only unmapped records are skipped
+    if ((c.flag & 0x4) || c.refID < 0 || (c.flag & T.rules.skip_flags)) skipped = 1;   // [C-6] unmapped records, and what rule_skip_flags adds
     else if (c.refID >= T.n_ref) atomicOr(T.err, DERR_REFID);
     else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) is_single = true;   // [C-7]
     else {
@@ -866,7 +866,7 @@ __global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, c
         for (int q = 0; q < 3; q++) if (pstate[q] == 1) { pct[q] = ((double)pdepth[q] + (double)d) / 2.0; pstate[q] = 2; }
         u64 a = max(cum, lo), b = min(cum + h, hi); if (b > a) total += (b - a) * d;
         cum += h;
-        for (int q = 0; q < 3; q++) if (pstate[q] == 0) { if (cum * 100 > n * pp[q]) { pct[q] = d; pstate[q] = 2; } else if (cum * 100 == n * pp[q]) { pdepth[q] = d; pct[q] = d; pstate[q] = 1; } }
+        for (int q = 0; q < 3; q++) if (pstate[q] == 0) { if (cum * 100 > n * pp[q]) { pct[q] = d; pstate[q] = 2; } else if (cum * 100 == n * pp[q]) { pdepth[q] = d; pct[q] = d; pstate[q] = T.rules.pct_tie_midpoint ? 1 : 2; } }
       }
       r.coverage = n ? (double)(n - hist[0]) / (double)n : 0.0;
       r.depth = (n && hi > lo) ? (double)total / (double)(hi - lo) : 0.0;
@@ -887,10 +887,11 @@ __global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, c
       r.irratio = (r.depth == 0 && jmax == 0) ? 0.0 : r.depth / (r.depth + (double)jmax);
       // warnings [C-14]
       double spmax = max(r.sp_left, r.sp_right), spmin = min(r.sp_left, r.sp_right);
-      if ((double)r.jc_exact + r.depth < 10) r.warning = W_LOWCOVER;
-      else if (r.jc_exact < 4) r.warning = W_LOWSPLICING;
-      else if ((double)r.jc_exact < (double)jmax * 0.33333) r.warning = W_MINORISOFORM;
-      else if ((spmax > r.depth + 4 && spmax > r.depth * 1.5) || (spmin + 4 < r.depth && spmin * 1.5 < r.depth)) r.warning = W_NONUNIFORM;
+      const Rules& R = T.rules;
+      if ((double)r.jc_exact + r.depth < R.warn_lowcover) r.warning = W_LOWCOVER;
+      else if ((double)r.jc_exact < R.warn_lowsplice) r.warning = W_LOWSPLICING;
+      else if ((double)r.jc_exact < (double)jmax * R.warn_minor_ratio) r.warning = W_MINORISOFORM;
+      else if ((spmax > r.depth + R.warn_nonuniform_abs && spmax > r.depth * R.warn_nonuniform_ratio) || (spmin + R.warn_nonuniform_abs < r.depth && spmin * R.warn_nonuniform_ratio < r.depth)) r.warning = W_NONUNIFORM;
       else r.warning = W_NONE;
       rows[it] = r;
     }

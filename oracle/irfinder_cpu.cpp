@@ -47,14 +47,17 @@ using std::vector;
 // ---------------------------------------------------------------------------------------------
 // Disputed constants.  One place each.
 static unsigned TRIM_CENTER_PERCENT = 40;        // [C-2] central band kept by the trimmed mean (40 => ranks 30%..70%)
-static const int JUNC_MIN_FLANK = 5;             // [C-3] both flanking blocks must be >= 5 bp
-static const unsigned SPAN_OVERHANG_LEFT = 5;    // [C-4]
-static const unsigned SPAN_OVERHANG_RIGHT = 4;   // [C-4]
+static int JUNC_MIN_FLANK = 5;                   // [C-3] both flanking blocks must be >= 5 bp          (env IRF_RULE_JUNC_MIN_FLANK)
+static unsigned SPAN_OVERHANG_LEFT = 5;          // [C-4]                                               (env IRF_RULE_SPAN_LEFT)
+static unsigned SPAN_OVERHANG_RIGHT = 4;         // [C-4]                                               (env IRF_RULE_SPAN_RIGHT)
 static const unsigned DIR_MIN_TOTAL = 8;         // [C-11] junction considered when total > 8
 static const unsigned DIR_RATIO = 4;             // [C-11] one strand > 4x the other
 static const unsigned DIR_DECISIVE = 100;        // [C-11] agree > 100x oppose
-static const unsigned EDGE_WINDOW_OFFSET = 5;    // [C-13] first/last-50bp windows start 5 bp inside the intron
-static const unsigned EDGE_WINDOW_LEN = 50;      // [C-13]
+static unsigned EDGE_WINDOW_OFFSET = 5;          // [C-13] first/last-50bp windows start 5 bp inside the intron (env IRF_RULE_EDGE_OFFSET)
+static unsigned EDGE_WINDOW_LEN = 50;            // [C-13]                                              (env IRF_RULE_EDGE_LEN)
+static unsigned SKIP_FLAGS = 0;                  // [C-6] extra flag bits whose records are skipped            (env IRF_RULE_SKIP_FLAGS)
+static bool PCT_TIE_MIDPOINT = true;             // [C-12]                                              (env IRF_RULE_PCT_TIE_MIDPOINT)
+static double WARN_LOWCOVER = 10, WARN_LOWSPLICE = 4, WARN_MINOR_RATIO = 0.33333, WARN_NONUNIFORM_ABS = 4, WARN_NONUNIFORM_RATIO = 1.5;   // [C-14] (env IRF_RULE_WARN_*_E6, millionths)
 static const char* HDR_IR = "Chr\tStart\tEnd\tName\tNull\tStrand\tExcludedBases\tCoverage\tIntronDepth\tIntronDepth25Percentile\tIntronDepth50Percentile\tIntronDepth75Percentile\tExonToIntronReadsLeft\tExonToIntronReadsRight\tIntronDepthFirst50bp\tIntronDepthLast50bp\tSpliceLeft\tSpliceRight\tSpliceExact\tIRratio\tWarnings\n";
 static const char* HDR_JC = "JC_seqname\tstart\tend\tstrand\ttotal\tpos\tneg\n";   // [C-15]
 static const char* HDR_SP = "SP_seqname\tcoord\ttotal\tpos\tneg\n";                 // [C-15]
@@ -344,7 +347,7 @@ class CoverageBlocks : public ReadBlockProcessor {
     for (auto it = h.begin(); it != h.end(); ++it) {
       cum += it->second;
       if (cum * 100 > target100) return it->first;
-      if (cum * 100 == target100) { auto nx = std::next(it); return nx == h.end() ? (double)it->first : ((double)it->first + (double)nx->first) / 2.0; }
+      if (cum * 100 == target100) { auto nx = std::next(it); return (nx == h.end() || !PCT_TIE_MIDPOINT) ? (double)it->first : ((double)it->first + (double)nx->first) / 2.0; }
     }
     return (double)h.rbegin()->first;
   }
@@ -389,10 +392,10 @@ class CoverageBlocksIRFinder : public CoverageBlocks {
   // [C-14]
   static const char* warning(double depth, unsigned JCexact, unsigned JCmax, unsigned SPleft, unsigned SPright) {
     double spmax = std::max(SPleft, SPright), spmin = std::min(SPleft, SPright);
-    if (JCexact + depth < 10) return "LowCover";
-    if (JCexact < 4) return "LowSplicing";
-    if (JCexact < JCmax * 0.33333) return "MinorIsoform";
-    if ((spmax > depth + 4 && spmax > depth * 1.5) || (spmin + 4 < depth && spmin * 1.5 < depth)) return "NonUniformIntronCover";
+    if (JCexact + depth < WARN_LOWCOVER) return "LowCover";
+    if (JCexact < WARN_LOWSPLICE) return "LowSplicing";
+    if (JCexact < JCmax * WARN_MINOR_RATIO) return "MinorIsoform";
+    if ((spmax > depth + WARN_NONUNIFORM_ABS && spmax > depth * WARN_NONUNIFORM_RATIO) || (spmin + WARN_NONUNIFORM_ABS < depth && spmin * WARN_NONUNIFORM_RATIO < depth)) return "NonUniformIntronCover";
     return "-";
   }
 };
@@ -516,7 +519,7 @@ class BAM2blocks {
       if (!readRecord(reads[idx], eof)) { cErrorReads++; std::cerr << "Input error: truncated or malformed BAM record\n"; return 1; }
       if (eof) break;
       const bam_read_core& c = reads[idx].core;
-      if ((c.flag & 0x4) || c.refID < 0) { cSkippedReads++; continue; }
+      if ((c.flag & 0x4) || c.refID < 0 || (c.flag & SKIP_FLAGS)) { cSkippedReads++; continue; }
       if (!pairCandidate(c)) { cSingleReads++; processSingle(reads[idx]); continue; }
       if (held < 0) { held = idx; continue; }
       BamRead& a = reads[held]; BamRead& b = reads[idx];
@@ -534,6 +537,12 @@ class BAM2blocks {
 int main(int argc, char** argv) {
   if (argc < 7) { std::cerr << "Usage: irfinder_cpu <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|-> [--dump-fragments FILE] [--dump-depth FILE] [--depth-digest FILE]\n"; return 1; }
   if (const char* t = getenv("IRF_TRIM_CENTER")) TRIM_CENTER_PERCENT = (unsigned)atoi(t);
+  { auto geti = [](const char* k, long long d) { const char* t = getenv(k); return t ? atoll(t) : d; };   // the Appendix-C rules, one environment variable each
+    JUNC_MIN_FLANK = (int)geti("IRF_RULE_JUNC_MIN_FLANK", JUNC_MIN_FLANK); SPAN_OVERHANG_LEFT = (unsigned)geti("IRF_RULE_SPAN_LEFT", SPAN_OVERHANG_LEFT); SPAN_OVERHANG_RIGHT = (unsigned)geti("IRF_RULE_SPAN_RIGHT", SPAN_OVERHANG_RIGHT);
+    EDGE_WINDOW_OFFSET = (unsigned)geti("IRF_RULE_EDGE_OFFSET", EDGE_WINDOW_OFFSET); EDGE_WINDOW_LEN = (unsigned)geti("IRF_RULE_EDGE_LEN", EDGE_WINDOW_LEN); SKIP_FLAGS = (unsigned)geti("IRF_RULE_SKIP_FLAGS", 0);
+    PCT_TIE_MIDPOINT = geti("IRF_RULE_PCT_TIE_MIDPOINT", 1) != 0;
+    WARN_LOWCOVER = geti("IRF_RULE_WARN_LOWCOVER_E6", 10000000) / 1e6; WARN_LOWSPLICE = geti("IRF_RULE_WARN_LOWSPLICE_E6", 4000000) / 1e6; WARN_MINOR_RATIO = geti("IRF_RULE_WARN_MINOR_RATIO_E6", 333330) / 1e6;
+    WARN_NONUNIFORM_ABS = geti("IRF_RULE_WARN_NONUNIFORM_ABS_E6", 4000000) / 1e6; WARN_NONUNIFORM_RATIO = geti("IRF_RULE_WARN_NONUNIFORM_RATIO_E6", 1500000) / 1e6; }
   string outdir = argv[1];
   CoverageBlocksIRFinder oCov; JunctionCount oJC; SpansPoint oSP; FragmentsInChr oChr; FragmentsInROI oROI; bool haveROI = strcmp(argv[5], "NULL") != 0;
   { std::ifstream f(argv[2]); if (!f) { std::cerr << "cannot open " << argv[2] << "\n"; return 1; } oCov.loadRef(f); }

@@ -316,6 +316,38 @@ def test_stream_input_is_counted_segment_by_segment(built, tiny, tmp_path, order
     assert c.stats()["pairs"] > 0
 
 
+_RULE_SETS = {
+    "junction_span_flags": dict(junc_min_flank=4, span_left=4, span_right=5, skip_flags=0x900),
+    "percentile_edge": dict(pct_tie_midpoint=0, edge_offset=3, edge_len=40),
+    "warnings": dict(warn_lowcover_e6=5_000_000, warn_lowsplice_e6=2_000_000, warn_minor_ratio_e6=250_000, warn_nonuniform_abs_e6=2_000_000, warn_nonuniform_ratio_e6=1_200_000),
+}
+
+
+@pytest.mark.parametrize("which", sorted(_RULE_SETS))
+def test_appendix_c_rules_are_run_time_settings_on_both_sides(built, tiny, tmp_path, which):
+    """SURVEY.md Appendix C / §8c "Mitigation": every behaviour the recollected specification is unsure about (junction flank, span
+    overhangs, secondary/supplementary handling, percentile tie rule, edge windows, warning thresholds) is a run-time setting in the
+    library (irf_set_option rule_*) and, independently, in the oracle (IRF_RULE_*).  A second setting of each must agree byte for
+    byte too, and must actually change the output (otherwise the knob is not wired)."""
+    rules = _RULE_SETS[which]
+    env = {"IRF_RULE_" + k.upper(): str(v) for k, v in rules.items()}
+    out_o = str(tmp_path / "o")
+    ostd = run_oracle(built, tiny, out_o, env=env)
+    c = _gpu_run(tiny, str(tmp_path / "g"), **{"rule_" + k: v for k, v in rules.items()})
+    assert_same_outputs(out_o, str(tmp_path / "g"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
+    changed = [n for n in ("IRFinder-IR-nondir.txt", "IRFinder-JuncCount.txt", "IRFinder-SpansPoint.txt")
+               if open(os.path.join(out_o, n), "rb").read() != open(os.path.join(tiny["oracle_out"], n), "rb").read()]
+    assert changed, "the alternative rules left every table unchanged"
+    c.set_option("rule_junc_min_flank", 5); c.set_option("rule_span_left", 5); c.set_option("rule_span_right", 4); c.set_option("rule_skip_flags", 0)
+    c.set_option("rule_pct_tie_midpoint", 1); c.set_option("rule_edge_offset", 5); c.set_option("rule_edge_len", 50)
+    for k, v in dict(warn_lowcover_e6=10_000_000, warn_lowsplice_e6=4_000_000, warn_minor_ratio_e6=333_330, warn_nonuniform_abs_e6=4_000_000, warn_nonuniform_ratio_e6=1_500_000).items():
+        c.set_option("rule_" + k, v)
+    c.run_bam(tiny["sorted"])                       # back to the defaults on the same context: the default tables again
+    c.write_outputs(str(tmp_path / "d"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "d"))
+
+
 def test_micro_fixture_by_hand_on_gpu(tmp_path):
     """The hand-derived fixture of tests/micro_fixture.py (every cell computed by hand) through the CUDA path,
     in both record orders; BGZF blocks of 700-900 bytes make nearly every record straddle a block boundary."""
