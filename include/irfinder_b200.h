@@ -28,7 +28,8 @@ enum {
   IRF_T_ROI = 2,          /* uint32[2][n_roi] (FragmentsInROI counts) */
   IRF_T_CHR = 3,          /* uint32[2][n_ref], BAM header order (FragmentsInChr counts) */
   IRF_T_JUNCTIONS = 4,    /* struct {int32 refid; uint32 start, end, neg, pos;}[n] counted junctions (JunctionCount map) */
-  IRF_T_DEPTH = 5,        /* int32[2][P] per-base depth over the compact measured space (CoverageBlock counters after scan) */
+  IRF_T_DEPTH = 5,        /* int32[2][P] per-base depth over the compact measured space (CoverageBlock counters after scan); after a region-owned
+                             sharded run (irf_owner_plan) only the segments this rank owns hold the merged depth */
   IRF_T_ROWS_NONDIR = 6,  /* irf_intron_row[n_introns], ref-cover.bed order (IRFinder-IR-nondir.txt, numeric) */
   IRF_T_ROWS_DIR = 7,     /* same for IRFinder-IR-dir.txt; n = 0 when the library is unstranded */
   IRF_T_FRAGMENTS = 8,    /* uint32 words of the FragmentBlocks dump (option dump_fragments=1): per fragment
@@ -60,7 +61,12 @@ const char* irf_last_error(irf_ctx* ctx);
  * NOTE: the engine answers malformed DEFLATE data with a sticky CUDA error (the process must restart), the SM kernel with IRF_EFORMAT.
  * "junc_capacity_log2" (default 24), "require_eof" (default 1), "verify_crc" (default 1: check every block's CRC-32 as gzip does), "stage_lazy" (default 0; 1 = irf_stage only records the host
  * buffer and irf_count streams it to the GPU beside the inflate kernel: the buffer must then stay valid until irf_count returns).
- * Must be set before irf_load_ref / the first run. */
+ * "stream_segment_mb" (default 1024): irf_run_stream reads its pipe in segments of this size (two page-locked buffers of it).
+ * "rule_*": the behaviours SURVEY.md Appendix C marks as uncertain, as run-time settings (defaults = DESIGN.md section 1): rule_junc_min_flank (5),
+ * rule_span_left (5), rule_span_right (4), rule_skip_flags (0; e.g. 0x900 skips secondary and supplementary records), rule_pct_tie_midpoint (1),
+ * rule_edge_offset (5), rule_edge_len (50), and in millionths rule_warn_lowcover_e6 (10000000), rule_warn_lowsplice_e6 (4000000),
+ * rule_warn_minor_ratio_e6 (333330), rule_warn_nonuniform_abs_e6 (4000000), rule_warn_nonuniform_ratio_e6 (1500000).
+ * Must be set before irf_load_ref / the first run (the rule_* and safe_inflate options may also be changed between runs). */
 int irf_set_option(irf_ctx* ctx, const char* key, const char* value);
 
 /* Replaces CoverageBlocksIRFinder::loadRef, JunctionCount::loadRef, SpansPoint::setSpanLength(5,4)+loadRef and
@@ -73,7 +79,9 @@ int irf_load_ref(irf_ctx* ctx, const char* cover_bed, const char* sj_ref, const 
 int irf_run_bam(irf_ctx* ctx, const char* bam_path, const char* bai_path);
 /* Same, from a host buffer holding the BGZF bytes (pinned memory copies fastest). */
 int irf_run_buffer(irf_ctx* ctx, const void* bgzf, size_t nbytes);
-/* Reference-compatible stdin mode: fd delivers BGZF/gzip bytes (inflated = 0) or an already-inflated BAM stream (inflated = 1). */
+/* Reference-compatible stdin mode (irfinder.cpp main reading /dev/stdin behind `gzip -cd` or STAR): fd delivers BGZF/gzip bytes (inflated = 0) or an
+ * already-inflated BAM stream (inflated = 1).  The stream is read and counted in bounded segments ("stream_segment_mb"), so its length is not limited
+ * by host memory; a record must fit into the 8 MB of look-ahead that follow a segment. */
 int irf_run_stream(irf_ctx* ctx, int fd, int inflated);
 
 /* Replaces the six file writers at the end of main(): IRFinder-IR-nondir.txt, IRFinder-IR-dir.txt (stranded libraries only),
