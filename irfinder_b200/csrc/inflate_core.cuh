@@ -11,9 +11,11 @@
 //    interleaved by lane (word index * LANES + lane) so a warp's 32 random lookups never bank-conflict.
 //    Codes longer than the LUT width (rare) fall back to a canonical bit-serial walk over the
 //    code-length histogram, held in per-lane local memory.
-//  * Output goes through a per-lane shared-memory ring (last 256 bytes): finished 32-byte sectors leave as 128-bit
-//    stores and short-distance LZ77 matches never touch L2; long-distance matches load up to 8 source bytes from
-//    global memory in one step and store them in the next, so the load latency hides behind decode work.
+//  * Output: bytes are stored to global memory one by one; long-distance LZ77 matches load up to 8 source bytes in one step and
+//    store them in the next, so the load latency hides behind decode work.  (A per-lane shared-memory output ring, RING_BITS > 0,
+//    was measured slower and is no longer offered by launch_inflate; the code path remains for the host emulation tests.)
+//  * This one-phase decoder is inflate_variant 0-11; the default kernel is the two-phase one in inflate_tok.cuh, which reuses
+//    BitReader, LaneTable and Huff from this file.
 //
 // The routine is __host__ __device__ so tests/emu can run the very same code on the CPU against
 // zlib; the shipped library only ever instantiates it inside kernels.
