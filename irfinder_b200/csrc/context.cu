@@ -480,7 +480,7 @@ struct irf_ctx {
   // in file order; a chunk's event is recorded behind its last piece.  Page-locking 14 GB for one run cost ~4 s (and as
   // long again to release); the ring is 128 MB, allocated once per context.
   struct Piece { size_t lo, hi; int chunk; bool last; };
-  static constexpr int FEED_SLOTS = 8; static constexpr size_t FEED_SLOT_BYTES = 16u << 20;
+  static constexpr int FEED_SLOTS = 16; static constexpr size_t FEED_SLOT_BYTES = 16u << 20; int feed_threads_n = 12;   // round 1: 8 slots, 4 threads -> ~17 GB/s from the page cache
   int feed_fd = -1; int file_ring = 1;   // option "file_ring": 0 never, 1 files above 64 MB, 2 always
   vector<Piece> feed_pieces; vector<cudaEvent_t> feed_ev_chunk; vector<char> feed_chunk_queued; cudaEvent_t feed_slot_ev[FEED_SLOTS] = {};
   uint8_t* feed_ring = nullptr; std::mutex feed_mu; std::condition_variable feed_cv; size_t feed_next = 0, feed_queued_upto = 0; bool feed_abort = false, feed_active = false; string feed_error; vector<std::thread> feed_threads;
@@ -512,7 +512,7 @@ struct irf_ctx {
       for (size_t o = lo; o < hi; o += sub) feed_pieces.push_back(Piece{o, std::min(hi, o + sub), (int)c, o + sub >= hi}); }
     feed_ev_chunk.resize(nch); for (auto& e : feed_ev_chunk) IRF_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     feed_chunk_queued.assign(nch, 0); feed_next = 0; feed_queued_upto = 0; feed_abort = false; feed_error.clear(); feed_active = true;
-    unsigned nt = std::min<unsigned>(4, std::max(1u, std::thread::hardware_concurrency()));
+    unsigned nt = std::min<unsigned>((unsigned)std::min(feed_threads_n, FEED_SLOTS - 2), std::max(1u, std::thread::hardware_concurrency()));
     for (unsigned t = 0; t < nt; t++) feed_threads.emplace_back([this]() { feed_worker(); });
   }
   cudaEvent_t feed_wait_chunk(size_t c) {   // returns once every copy of chunk c has been queued on the copy stream
@@ -1099,6 +1099,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "stream_segment_mb") { if (v < 1 || v > 65536) return IRF_EINVAL; c->stream_segment_bytes = (size_t)v << 20; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements
+  else if (k == "file_ring_threads") { if (v < 1 || v > 64) return IRF_EINVAL; c->feed_threads_n = (int)v; }
   else if (k == "file_ring") { if (v < 0 || v > 2) return IRF_EINVAL; c->file_ring = (int)v; }
   else if (k == "stream_pipeline") c->stream_pipeline = v != 0;
   else if (k == "resident_pipeline") { if (v < 0 || v > 2) return IRF_EINVAL; c->resident_pipeline = (int)v; }
