@@ -1,11 +1,11 @@
 // inflate_tok.cu — the two-phase SM inflate kernel (see inflate_tok.cuh for the format and the reasons).
 //
 // One persistent launch, 148 SMs x resident CTAs; every warp claims 32 consecutive BGZF blocks from a global counter and runs
-//   phase A  lane per block: Huffman decode, literals stored at their final place as aligned 32-bit words, one 4-byte token per
-//            LZ77 match appended to the lane's scratch region;
-//   phase B  warp per block, for each of the 32 blocks in turn: tokens are read 32 at a time (coalesced), a warp scan turns their
-//            lengths into output positions, and the matches are copied — in parallel when their source bytes are final, in order
-//            otherwise (a match may read what an earlier match of the same batch writes);
+//   phase A  lane per block: Huffman decode into the lane's scratch region: one 4-byte token per LZ77 match (literal count, length,
+//            distance) from the bottom, the literal bytes packed four to a word from the top; nothing is written to the output;
+//   phase B  warp per block, for each of the 32 blocks in turn: tokens are read 32 at a time (coalesced), two warp scans turn their
+//            lengths into output and literal-stream positions, the literals are placed, and the matches are copied — in parallel
+//            when their source bytes are final, in order otherwise (a match may read what an earlier match of the same batch writes);
 // then claims the next 32.  Replaces `gzip -cd` of the reference pipeline; RFC 1951.
 #include <algorithm>
 #include <cstdio>
@@ -31,8 +31,33 @@ __device__ unsigned long long g_tok_prof[8];
 // match of the batch overlaps its source bytes.  Holes are ordered like the tokens, so the matches that can overlap lane i's
 // source [src, need) form a range of lanes [lo, hi) found by two binary searches over the warp (shuffles); a round then costs one
 // ballot and one AND per lane, and the number of rounds is the depth of the dependency chains, not the number of dependent matches.
-constexpr uint32_t TOK_LONG = 16;   // matches longer than this are copied by the whole warp
-__device__ __forceinline__ void resolve_batch(uint8_t* ob, uint32_t mstart, uint32_t ml, uint32_t d, int lane, uint32_t& rounds) {
+// tok_long (kernel argument, default 16; IRF_TOK_LONG for experiments): matches longer than this are copied by the whole warp
+constexpr uint32_t LIT_LONG = 4;    // literal runs longer than this are placed by the whole warp
+// lstart / lit / lq: output offset, length and literal-stream offset of the literal run in front of lane i's match; lits: the block's
+// literal stream (word j at lits[-j], bytes in little-endian order)
+__device__ __forceinline__ uint8_t lit_byte(const uint32_t* lits, uint32_t q) { return (uint8_t)(lits[-(int)(q >> 2)] >> (8 * (q & 3))); }
+// lwin / wq: the 32 words of the literal stream from word wq on, one per lane, loaded a batch ahead (the short runs of a batch are
+// served from this window by shuffles instead of dependent loads from the scratch region)
+__device__ __forceinline__ void resolve_batch(uint8_t* ob, const uint32_t* lits, uint32_t lwin, uint32_t wq, uint32_t lstart, uint32_t lit, uint32_t lq, uint32_t mstart, uint32_t ml, uint32_t d, int lane, uint32_t& rounds, const uint32_t TOK_LONG) {
+  // ---- literals first: they depend on nothing, and the matches of this batch may read them
+  {
+    const uint32_t w0 = (lq >> 2) - wq;                  // window word that holds the run's first byte (garbage for lanes without a short run)
+    const uint32_t a = __shfl_sync(0xffffffffu, lwin, (int)(w0 & 31u)), b = __shfl_sync(0xffffffffu, lwin, (int)((w0 + 1) & 31u));
+    if (lit && lit <= LIT_LONG) {
+      uint32_t v;
+      if (w0 < 31u) v = __funnelshift_r(a, b, (lq & 3u) * 8u);
+      else { v = 0; for (uint32_t k = 0; k < lit; k++) v |= (uint32_t)lit_byte(lits, lq + k) << (8 * k); }   // run beyond the window (a batch with many literals)
+      uint8_t* dp = ob + lstart;
+      dp[0] = (uint8_t)v; if (lit > 1) dp[1] = (uint8_t)(v >> 8); if (lit > 2) dp[2] = (uint8_t)(v >> 16); if (lit > 3) dp[3] = (uint8_t)(v >> 24);
+    }
+  }
+  unsigned ll = __ballot_sync(0xffffffffu, lit > LIT_LONG);
+  while (ll) {                                           // long runs: 32 consecutive bytes per trip (warp-uniform loop)
+    const int f = __ffs(ll) - 1; ll &= ll - 1;
+    const uint32_t fs = __shfl_sync(0xffffffffu, lstart, f), fn = __shfl_sync(0xffffffffu, lit, f), fq = __shfl_sync(0xffffffffu, lq, f);
+    for (uint32_t k = lane; k < fn; k += 32) ob[fs + k] = lit_byte(lits, fq + k);
+  }
+  __syncwarp();
   const uint32_t mend = mstart + ml, src = mstart - d, need = src + min(ml, d);   // source bytes [src, need) must be final before this match may be copied
   uint32_t lo = 0, hi = 0;   // lo = lanes whose hole ends at or before src; hi = lanes whose hole starts before need
 #pragma unroll
@@ -80,7 +105,7 @@ template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                                   uint8_t* U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                                   int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark,
-                                                                  const u32* __restrict__ list, uint32_t* tok_scratch) {
+                                                                  const u32* __restrict__ list, uint32_t* tok_scratch, uint32_t tok_long) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // per warp: [lit LUT, 16-bit entries][dist LUT, byte entries][canonical-limit entries of both], interleaved by lane
@@ -107,7 +132,8 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uin
     int b = (int)base + lane; const bool in_range = b < nblk; if (list && in_range) b = (int)list[b];
     TokLane<32, LB, DB> L;
     const bool work = in_range && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
-    if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, my_tok); else L.idle();
+    if (work) L.start(comp + c_off[b], c_len[b], u_len[b], lit, dst, lane, sym_store, my_tok); else L.idle();
+    uint8_t* const my_out = work ? U + u_off[b] : nullptr;
     // ---- phase A.  One vote per four decode iterations.  A table build (thousands of instructions that every lane of the warp
     // pays for) starts only when no lane is left decoding, half the warp is waiting for one, or the waiting lanes have waited
     // PATIENCE votes; zlib closes a DEFLATE block after a fixed number of symbols, so lanes mostly arrive together anyway.
@@ -133,18 +159,22 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uin
     for (int j = 0; j < 32; j++) {
       const uint32_t n = __shfl_sync(0xffffffffu, L.ntok, j); const int st = __shfl_sync(0xffffffffu, L.status, j);
       if (n == 0 || st != 0) continue;
-      const uint32_t* tp = (const uint32_t*)shfl_ptr(my_tok, j); uint8_t* ob = (uint8_t*)shfl_ptr(L.out, j);
-      uint32_t pos = 0;
+      const uint32_t* tp = (const uint32_t*)shfl_ptr(my_tok, j); uint8_t* ob = (uint8_t*)shfl_ptr(my_out, j);
+      const uint32_t* lits = tp + (TOK_CAP - 1);
+      uint32_t pos = 0, qpos = 0;
       uint32_t t_next = lane < n ? tp[lane] : 0;
+      const uint32_t nlw = __shfl_sync(0xffffffffu, L.nlw, j);               // literal words of this block
+      uint32_t lwin = (uint32_t)lane < nlw ? lits[-lane] : 0u;
       for (uint32_t tb = 0; tb < n; tb += 32) {
-        const uint32_t t = t_next;
+        const uint32_t t = t_next, win = lwin, wq = qpos >> 2;
         t_next = tb + 32 + lane < n ? tp[tb + 32 + lane] : 0;   // the next batch's tokens are on their way while this one is resolved
-        const uint32_t ml = tok_mlen(t), tot = tok_lit(t) + ml; uint32_t incl = tot;
+        const uint32_t ml = tok_mlen(t), nl = tok_lit(t); uint32_t incl = nl + ml, linc = nl;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { uint32_t v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
-        const uint32_t mstart = pos + incl - ml;
-        pos += __shfl_sync(0xffffffffu, incl, 31);
-        resolve_batch(ob, mstart, ml, tok_dist(t), lane, rounds); batches++;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o), w = __shfl_up_sync(0xffffffffu, linc, o); if (lane >= o) { incl += v; linc += w; } }
+        const uint32_t mstart = pos + incl - ml, lstart = mstart - nl, lq = qpos + linc - nl;
+        pos += __shfl_sync(0xffffffffu, incl, 31); qpos += __shfl_sync(0xffffffffu, linc, 31);
+        { const uint32_t nw = (qpos >> 2) + (uint32_t)lane; lwin = nw < nlw ? lits[-(int)nw] : 0u; }   // ... and so is the next batch's window of the literal stream
+        resolve_batch(ob, lits, win, wq, lstart, nl, lq, mstart, ml, tok_dist(t), lane, rounds, tok_long); batches++;
       }
     }
     __syncwarp();
@@ -175,10 +205,11 @@ static void tok_launch(const InflateArgs& a, cudaStream_t s) {
   const int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, g.ctas_per_sm * g.sms);
   if (grid <= 0) return;
   if (!a.tok_scratch || a.tok_scratch_bytes < (size_t)grid * WARPS * 32 * TOK_CAP * sizeof(uint32_t)) throw std::string("inflate: token scratch missing or too small");
+  const uint32_t tok_long = getenv("IRF_TOK_LONG") ? (uint32_t)atoi(getenv("IRF_TOK_LONG")) : 16u;
   const bool prof = getenv("IRF_TOK_PROF") != nullptr;
   if (prof) { unsigned long long z[8] = {0}; IRF_CUDA(cudaMemcpyToSymbol(g_tok_prof, z, sizeof z)); }
   IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch);
+  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch, tok_long);
   note_launch();
   if (prof) { IRF_CUDA(cudaStreamSynchronize(s)); unsigned long long z[8]; IRF_CUDA(cudaMemcpyFromSymbol(z, g_tok_prof, sizeof z));
     fprintf(stderr, "[tok] <%d warps, %d/%d-bit LUTs> grid %d x %d CTAs/SM: phase A %.1f Mcycles/claim, phase B %.1f Mcycles/claim, %llu claims; per claim: %.0f votes, %.1f table builds, %.0f batches, %.2f rounds/batch\n", WARPS, LB, DB, grid, g.ctas_per_sm,

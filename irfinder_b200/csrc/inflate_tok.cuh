@@ -12,10 +12,15 @@
 // 4-byte tokens that the warp resolves later with all 32 lanes working on ONE block (64 KiB working set per warp, not per lane).
 //
 // Token (32 bits):  lit_len << 24 | match_len << 15 | (dist - 1)
-//   lit_len   0..255  literal bytes since the end of the previous match (they are already in the output)
-//   match_len 0, 3..258; 0 = no match: the token only carries 255 literals of a long literal run
+//   lit_len   0..255  literal bytes that precede the match (taken from the literal stream in order)
+//   match_len 0, 3..258; 0 = no match: the token only carries literals (a run longer than 255, or the tail of the block)
 //   dist      1..32768
-// Literals after the last match need no token.  At most isize/3 + isize/255 + 2 tokens per block (TOK_CAP).
+// Literal stream: the literal bytes of a block in order, packed four to a word.  Tokens grow from the bottom of the lane's scratch
+// region, literal words from its top (word j of the stream at index TOK_CAP - 1 - j): a block never needs more than isize/3 + 2
+// words for both (a literal costs a quarter of a word, a match at least three output bytes per word).
+// Phase A therefore writes nothing to the output: every output byte is stored by the resolve phase, whole blocks at a time, so
+// sectors reach DRAM once and complete (the first version stored literals in place during decode; the match bytes filled in later
+// re-opened sectors that had long left L2: 5.1 DRAM bytes per algorithmic byte).
 //
 // __host__ __device__ like inflate_core.cuh: tests/emu runs this very routine on the CPU against zlib.
 #pragma once
@@ -45,55 +50,38 @@ struct TokLane {
   static constexpr size_t DIST_LUT_U16 = ((size_t)(1u << DIST_BITS) * LANES + 1) / 2;          // the distance LUT's size in 16-bit units
   static constexpr size_t TABLE_U16 = (size_t)(1u << LIT_BITS) * LANES + DIST_LUT_U16 + (size_t)(2 * HD::AUXN + 2 * HL::AUXN) * LANES;   // all tables of LANES lanes
   HL hl; HD hd;
-  uint8_t* out;                // start of this block's output
-  uint32_t op, cap;            // bytes produced so far (literals written + match bytes left open), ISIZE
-  uint32_t acc, sh;            // literal bytes of the current aligned 32-bit output word; bit position of output offset `op` inside it
-  uint32_t dirty;              // the current word holds literal bytes that have not been stored yet (acc alone cannot tell: a literal may be 0)
-  int32_t lo_full, hi_full;    // words whose first byte lies at output offset [lo_full, hi_full) belong to this block alone
-  uint32_t mis;                // (address of out) & 3
-  uint32_t* tok; uint32_t ntok, last_end;   // last_end: output offset where the previous match ended
+  uint32_t op, cap;            // output bytes accounted for so far (literals + matches), ISIZE
+  uint32_t acc, sh;            // literal bytes of the current word of the literal stream; bit position of the next byte in it
+  uint32_t* tok; uint32_t ntok, nlw, last_end;   // tokens written, literal words written (from the top), output offset where the previous match ended
   int state, status, bfinal; uint32_t bad;   // bad: an InflateStatus noticed inside iter(); turned into a failure by check()
 
   // sym_store: 320 uint16 of lane-private scratch (288 literal/length symbols + 32 distance symbols); tok_region: TOK_CAP words
-  IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* o, uint32_t isize, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store, uint32_t* tok_region) {
+  IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint32_t isize, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store, uint32_t* tok_region) {
     hl.symbol = sym_store; hd.symbol = sym_store + 288;
-    br.init(cdata, clen); out = o; op = 0; cap = isize; acc = 0; dirty = 0; mis = (uint32_t)((uintptr_t)o & 3); sh = mis * 8;
-    lo_full = mis ? (int32_t)(4 - mis) : 0; hi_full = (int32_t)isize - (int32_t)(((uintptr_t)o + isize) & 3) - 3;   // first + 4 <= aligned end
-    tok = tok_region; ntok = 0; last_end = 0;
+    br.init(cdata, clen); op = 0; cap = isize; acc = 0; sh = 0;
+    tok = tok_region; ntok = 0; nlw = 0; last_end = 0;
     hl.lut.bind(lit_lut_base, lane); hd.lut.bind((uint8_t*)dist_lut_base, lane);
     // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT (bytes)][dist aux][lit aux], all lane-interleaved
     hd.aux.bind(dist_lut_base + DIST_LUT_U16, lane); hl.aux.bind(dist_lut_base + DIST_LUT_U16 + (size_t)(2 * HD::AUXN) * LANES, lane);
     state = LS_HEADER; status = INF_OK; bfinal = 0; bad = 0;
   }
-  IRF_HD void idle() { state = LS_DONE; status = INF_OK; ntok = 0; op = 0; cap = 0; bad = 0; }
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; ntok = 0; nlw = 0; op = 0; cap = 0; bad = 0; }
   IRF_HD bool done() const { return state == LS_DONE; }
   IRF_HD void fail(int code) { status = code; state = LS_DONE; }
 
-  // Stores the word that holds output offset `o` (its literal bytes are in acc; bytes of open matches are zero and are filled in
-  // by the resolve phase): one aligned store when the word lies wholly inside this block, byte by byte otherwise (the first and
-  // the last word can be shared with the neighbouring blocks, which other warps write).
-  IRF_HD void flush_word_at(uint32_t o) {
-    const int32_t first = (int32_t)((o + mis) & ~3u) - (int32_t)mis;   // output offset of the word's first byte (negative: it starts before the block)
-    uint8_t* wp = out + first;
-    if (first >= lo_full && first < hi_full) *(uint32_t*)wp = acc;
-    else { for (int j = 0; j < 4; j++) { int32_t q = first + j; if (q >= 0 && q < (int32_t)cap) wp[j] = (uint8_t)(acc >> (8 * j)); } }
-    acc = 0; dirty = 0;
-  }
   IRF_HD void put_literal(uint32_t byte) {   // caller has checked op < cap
-    acc |= byte << sh; sh += 8; dirty = 1;
-    if (sh == 32) { flush_word_at(op); sh = 0; }
-    op++;
+    acc |= byte << sh; sh += 8; op++;
+    if (sh == 32) { tok[TOK_CAP - 1 - nlw] = acc; nlw++; acc = 0; sh = 0; }
   }
-  IRF_HD void put_match(uint32_t len, uint32_t dist) {   // caller has checked the ranges
+  IRF_HD void put_token(uint32_t len, uint32_t dist) {   // the literals since the previous match, then the match (len = 0: literals only)
     uint32_t lit = op - last_end;
     while (lit > 255) { tok[ntok++] = tok_make(255, 0, 1); lit -= 255; }   // a literal run longer than a token can say (rare)
-    tok[ntok++] = tok_make(lit, len, dist);
-    if (sh + 8 * len < 32) { sh += 8 * len; op += len; last_end = op; return; }   // the match ends inside the current word: its bytes stay zero in acc
-    if (dirty) flush_word_at(op);                                      // literal bytes before the match in this word
-    op += len; last_end = op; sh = ((op + mis) & 3u) * 8; acc = 0;
+    if (lit | len) tok[ntok++] = tok_make(lit, len, dist);
+    op += len; last_end = op;
   }
   IRF_HD void finish() {
-    if (dirty) flush_word_at(op);   // dirty implies 0 < sh < 32: offset `op` (even when it equals cap) still lies in the started word
+    put_token(0, 1);                                  // the literals behind the last match
+    if (sh) { tok[TOK_CAP - 1 - nlw] = acc; nlw++; }
     status = op == cap ? INF_OK : INF_ERR_ISIZE; state = LS_DONE;
   }
 
@@ -178,7 +166,7 @@ struct TokLane {
     if ((s > 28u) | (ds > 29u)) { bad = INF_ERR_SYMBOL; return; }
     if (dist > op) { bad = INF_ERR_DIST; return; }
     if (op + len > cap) { bad = INF_ERR_OVERRUN_OUT; return; }
-    put_match(len, dist);
+    put_token(len, dist);
   }
   // once per vote of the driver loop: turn a noticed error into a failure, catch a bit reader that ran past its input
   IRF_HD void check() {
@@ -194,24 +182,28 @@ struct TokLane {
   }
 };
 
-// Scalar resolve of one block's tokens (the reference semantics of the warp-wide resolve in kernels.cu; used by tests/emu).
-IRF_HD bool tok_resolve_scalar(uint8_t* out, uint32_t isize, const uint32_t* tok, uint32_t ntok) {
-  uint32_t pos = 0;
+// Scalar resolve of one block (the reference semantics of the warp-wide resolve in inflate_tok.cu; used by tests/emu): literals from the
+// stream at the top of the region, matches from the output itself.
+IRF_HD bool tok_resolve_scalar(uint8_t* out, uint32_t isize, const uint32_t* region, uint32_t ntok) {
+  uint32_t pos = 0, q = 0;
   for (uint32_t i = 0; i < ntok; i++) {
-    uint32_t t = tok[i], lit = tok_lit(t), ml = tok_mlen(t), d = tok_dist(t);
-    pos += lit; if (pos + ml > isize || (ml && d > pos)) return false;
+    uint32_t t = region[i], lit = tok_lit(t), ml = tok_mlen(t), d = tok_dist(t);
+    if (pos + lit + ml > isize || (ml && d > pos + lit)) return false;
+    for (uint32_t k = 0; k < lit; k++, q++) out[pos + k] = (uint8_t)(region[TOK_CAP - 1 - (q >> 2)] >> (8 * (q & 3)));
+    pos += lit;
     for (uint32_t k = 0; k < ml; k++) out[pos + k] = out[pos + k - d];
     pos += ml;
   }
-  return pos <= isize;
+  return pos == isize;
 }
 template <int LANES, int LIT_BITS, int DIST_BITS>
 IRF_HD int inflate_block_tok(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint32_t* tok_region, uint32_t* ntok_out = nullptr) {
   TokLane<LANES, LIT_BITS, DIST_BITS> L; uint16_t sym_store[320];
-  L.start(cdata, clen, out, isize, lit_lut_base, dist_lut_base, lane, sym_store, tok_region);
+  L.start(cdata, clen, isize, lit_lut_base, dist_lut_base, lane, sym_store, tok_region);
   while (!L.done()) L.step();
-  if (ntok_out) *ntok_out = L.ntok;
+  if (ntok_out) *ntok_out = L.ntok + L.nlw;
   if (L.status) return L.status;
+  if (L.ntok + L.nlw > TOK_CAP) return INF_ERR_OVERRUN_OUT;
   return tok_resolve_scalar(out, isize, tok_region, L.ntok) ? INF_OK : INF_ERR_DIST;
 }
 

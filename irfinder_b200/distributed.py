@@ -318,11 +318,14 @@ def run_plan(core, plan, device=None, group=None, restage=True):
                 dist.all_reduce(_wrap(p, cnt, typestr, dev), op=dist.ReduceOp.SUM, group=group)
         _mark("small_tables")
         # ---- 4. depth: region-owned
-        rid, pos = core.first_record()
-        mine = torch.tensor([rid, pos], dtype=torch.int64, device=dev)
-        firsts = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(firsts, mine, group=group)
-        core.owner_plan([int(f[0]) for f in firsts], [int(f[1]) for f in firsts], rank)
+        firsts = getattr(plan, "_firsts", None)          # the first record of every shard: a property of the plan's bytes, gathered once
+        if firsts is None or info["recount"]:
+            rid, pos = core.first_record()
+            mine = torch.tensor([rid, pos], dtype=torch.int64, device=dev)
+            got = [torch.zeros_like(mine) for _ in range(world)]
+            dist.all_gather(got, mine, group=group)
+            firsts = plan._firsts = [(int(f[0]), int(f[1])) for f in got]
+        core.owner_plan([f[0] for f in firsts], [f[1] for f in firsts], rank)
         ip, vp, nf = core.export_foreign_depth()
         nfs = torch.tensor([nf], dtype=torch.int64, device=dev)
         dist.all_reduce(nfs, op=dist.ReduceOp.SUM, group=group)
@@ -330,10 +333,11 @@ def run_plan(core, plan, device=None, group=None, restage=True):
         if info["foreign_depth_entries"] > FOREIGN_DENSE_LIMIT:     # not region-shaped shards: the dense merge is cheaper
             p, cnt, _ = core.device_table("diff")
             dist.all_reduce(_wrap(p, cnt, "<i4", dev), op=dist.ReduceOp.SUM, group=group)
-        else:
-            idx, _ = _all_gather_var(_wrap(ip, nf, "<i8", dev), group, dist)
-            val, _ = _all_gather_var(_wrap(vp, nf, "<i4", dev), group, dist)
-            ai, av = torch.cat(idx).contiguous(), torch.cat(val).contiguous()
+        elif info["foreign_depth_entries"]:                         # (nothing to exchange when no counter crossed an ownership boundary)
+            packed = torch.cat([_wrap(ip, nf, "<i8", dev), _wrap(vp, nf, "<i4", dev).to(torch.int64)])   # one gather: [indices | values]
+            got, _ = _all_gather_var(packed, group, dist)
+            ai = torch.cat([g[: g.numel() // 2] for g in got]).contiguous()
+            av = torch.cat([g[g.numel() // 2:] for g in got]).to(torch.int32).contiguous()
             _sync(dev)
             if ai.numel():
                 core.import_depth(ai.data_ptr(), av.data_ptr(), int(ai.numel()))
