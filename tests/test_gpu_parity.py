@@ -366,6 +366,32 @@ def test_micro_fixture_by_hand_on_gpu(tmp_path):
             assert st[k] == v, (key, k)
 
 
+def test_rule_probe_fixture_by_hand_on_gpu(tmp_path):
+    """tests/micro_fixture2.py through the CUDA path: the default table cell for cell as derived by hand, then every alternative rule
+    (irf_set_option rule_*) changes exactly the hand-derived cells.  Independent of the oracle: the expectations are literals."""
+    import micro_fixture2
+    from test_oracle_cpu import _check_rule_probe
+    p = micro_fixture2.write(str(tmp_path / "m"))
+    for key in ("collated", "sorted"):
+        c = _core()
+        c.load_ref(p["cover"], p["sj"], p["rc"], p["roi"])
+        c.run_bam(p[key])
+        out = str(tmp_path / ("g_" + key))
+        c.write_outputs(out)
+        for name, want in micro_fixture2.EXPECT.items():
+            assert open(os.path.join(out, name)).read() == want, (key, name)
+        st = _stats_from_stdout(c.stdout_text)
+        for k, v in micro_fixture2.EXPECT_STATS.items():
+            assert st[k] == v, (key, k)
+    for which, (rules, _) in micro_fixture2.RULE_PROBES.items():
+        c = _core(**{"rule_" + k: v for k, v in rules.items()})
+        c.load_ref(p["cover"], p["sj"], p["rc"], p["roi"])
+        c.run_bam(p["sorted"])
+        out = str(tmp_path / ("r_" + which))
+        c.write_outputs(out)
+        _check_rule_probe(open(os.path.join(out, "IRFinder-IR-nondir.txt")).read(), which)
+
+
 def test_golden_vectors_on_gpu(built, tmp_path):
     meta = _gen(tmp_path, "w", genome="tiny", introns=120, pairs=4000, readlen=100, seed=21, chunks=3)
     _gpu_run(meta, str(tmp_path / "g"))

@@ -8,6 +8,7 @@ import subprocess
 import pytest
 
 import micro_fixture
+import micro_fixture2
 from bamutil import inflate_file, read_records, write_bam
 from conftest import OUT_FILES, ROOT, run_oracle
 
@@ -29,6 +30,35 @@ def test_micro_fixture_by_hand(built, tmp_path):
     for k, v in micro_fixture.EXPECT_STATS.items():
         assert st[k] == v, k
     assert st["Directionality:"] == "0"
+
+
+def _check_rule_probe(ir_text, which):
+    """The hand-derived cells of one alternative rule, and that every other cell kept its default value."""
+    base = micro_fixture2.parse_ir(micro_fixture2.EXPECT["IRFinder-IR-nondir.txt"])
+    got = micro_fixture2.parse_ir(ir_text)
+    cells = micro_fixture2.RULE_PROBES[which][1]
+    for intron, row in base.items():
+        for col, dflt in row.items():
+            want = cells.get(intron, {}).get(col, dflt)
+            assert got[intron][col] == want, (which, intron, col, got[intron][col], want)
+
+
+def test_rule_probe_fixture_by_hand(built, tmp_path):
+    """tests/micro_fixture2.py: seven introns whose cells are decided by the Appendix-C rules (flank 4 vs 5, span point exactly at
+    start+5 / end-4, percentile ties, edge windows, one intron per warning label), every cell derived by hand; then each rule is set
+    to its alternative (IRF_RULE_*) and exactly the hand-derived cells change."""
+    p = micro_fixture2.write(str(tmp_path / "m"))
+    for key in ("collated", "sorted"):        # all reads are single-end, so the record order does not matter to the oracle either
+        out = run_oracle(built, p, str(tmp_path / ("o_" + key)), bam=p[key])
+        for name, want in micro_fixture2.EXPECT.items():
+            assert open(os.path.join(str(tmp_path / ("o_" + key)), name)).read() == want, (key, name)
+        st = _stats(out)
+        for k, v in micro_fixture2.EXPECT_STATS.items():
+            assert st[k] == v, (key, k)
+    for which, (rules, _) in micro_fixture2.RULE_PROBES.items():
+        d = str(tmp_path / ("r_" + which))
+        run_oracle(built, p, d, env={"IRF_RULE_" + k.upper(): str(v) for k, v in rules.items()})
+        _check_rule_probe(open(os.path.join(d, "IRFinder-IR-nondir.txt")).read(), which)
 
 
 def test_inflated_stdin_equals_bgzf_file(built, tmp_path):
