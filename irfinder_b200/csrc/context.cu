@@ -746,7 +746,7 @@ struct irf_ctx {
   // (import_depth), and irf_finalize computes the statistics of the owned introns only; the rows of the other introns stay
   // zero on the device, so the caller merges the row tables with an integer SUM and then calls finalize_rows().
   bool owner_mode = false, rows_pending = false; int owner_me = 0, owner_world = 1; u32 n_own_introns = 0;
-  DevBuf d_seg_owner, d_own_introns, d_fidx, d_fval, d_rows_dir; u64 foreign_cap = 1ull << 20; vector<int64_t> owner_key;
+  DevBuf d_seg_owner, d_tile_state, d_own_introns, d_fidx, d_fval, d_rows_dir; u64 foreign_cap = 1ull << 20; vector<int64_t> owner_key;
   void first_record(int32_t& refid, int32_t& pos) {
     refid = -2; pos = 0; if (!counted) throw string("irf_count has not run");
     if (n_rec == 0 || frame_entry0 + 12 > Uend) return;
@@ -779,6 +779,12 @@ struct irf_ctx {
     vector<uint8_t> group(nseg, 255); for (u32 i = 0; i < nseg; i++) { u32 r = find(i); group[r] = std::min(group[r], want[i]); }
     vector<uint8_t> owner(nseg); for (u32 i = 0; i < nseg; i++) owner[i] = group[find(i)];
     vector<u32> mine; for (size_t k = 0; k < cov.BEDrecords.size(); k++) { int o = first_seg[k] == 0xffffffffu ? 0 : owner[first_seg[k]]; if (o == me) mine.push_back((u32)k); }
+    // ownership per 1024-slot tile of the compact space, for the kernel that lists the foreign counters
+    { const u64 ntiles = (cov.P + 1023) / 1024; vector<uint8_t> ts(ntiles, 3);   // 3 = nothing seen yet
+      for (u32 i = 0; i < nseg; i++) { const u64 c0 = cov.seg_coff[i], c1 = c0 + (u64)(cov.seg_end[i] - cov.seg_start[i]); const uint8_t v = owner[i] == me ? 1 : 2;
+        for (u64 t = c0 / 1024; t <= c1 / 1024; t++) ts[t] = ts[t] == 3 ? v : (ts[t] == v ? v : 0); }
+      for (auto& x : ts) if (x == 3) x = 1;
+      upload(d_tile_state, ts, s_compute); }
     upload(d_seg_owner, owner, s_compute); upload(d_own_introns, mine, s_compute); sync();
     n_own_introns = (u32)mine.size(); owner_mode = true; owner_me = me; owner_world = world;
   }
@@ -787,7 +793,7 @@ struct irf_ctx {
     u64* cur = (u64*)(d_small.as<uint8_t>() + 104);
     for (;;) {
       d_fidx.ensure(foreign_cap * 8); d_fval.ensure(foreign_cap * 4); IRF_CUDA(cudaMemsetAsync(cur, 0, 8, s_compute));
-      launch_foreign_depth(T, (u32)cov.seg_start.size(), d_seg_owner.as<uint8_t>(), (u32)owner_me, d_fidx.as<u64>(), d_fval.as<int32_t>(), cur, foreign_cap, s_compute);
+      launch_foreign_depth(T, (u32)cov.seg_start.size(), d_seg_owner.as<uint8_t>(), (u32)owner_me, d_tile_state.as<uint8_t>(), d_fidx.as<u64>(), d_fval.as<int32_t>(), cur, foreign_cap, s_compute);
       u64 n = 0; IRF_CUDA(cudaMemcpyAsync(&n, cur, 8, cudaMemcpyDeviceToHost, s_compute)); sync();
       if (n <= foreign_cap) return n;
       foreign_cap = n + n / 4;   // rare: grow and list again
@@ -868,12 +874,14 @@ struct irf_ctx {
     // Directional(); the side stream takes the per-intron statistics (maximum depth, histogram kernel, row read-back), which
     // need the scanned depth and the junction hash tables but not the exported rows.
     cudaEvent_t ev_scan, ev_side; IRF_CUDA(cudaEventCreateWithFlags(&ev_scan, cudaEventDisableTiming)); IRF_CUDA(cudaEventCreateWithFlags(&ev_side, cudaEventDisableTiming));
-    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute); IRF_CUDA(cudaEventRecord(ev_scan, s_compute));
-    u32* dmax = d_small.as<u32>() + 2; u32 hmax = 0;
-    IRF_CUDA(cudaStreamWaitEvent(s_copy, ev_scan, 0)); IRF_CUDA(cudaMemsetAsync(dmax, 0, 4, s_copy)); launch_max_depth(T.diff, cov.P, dmax, s_copy);
-    IRF_CUDA(cudaMemcpyAsync(&hmax, dmax, 4, cudaMemcpyDeviceToHost, s_copy));
+    u32* dmax = d_small.as<u32>() + 10; u32 hm[2] = {0, 0};   // bytes 40..47 of the scratch words: the largest depth of each strand, found by the scan itself
+    IRF_CUDA(cudaMemsetAsync(dmax, 0, 8, s_compute));
+    launch_depth_scan(T.diff, cov.P * 2, d_tile_sums.as<int32_t>(), s_compute, cov.P, dmax); IRF_CUDA(cudaEventRecord(ev_scan, s_compute));
+    IRF_CUDA(cudaStreamWaitEvent(s_copy, ev_scan, 0));
+    IRF_CUDA(cudaMemcpyAsync(hm, dmax, 8, cudaMemcpyDeviceToHost, s_copy));
     mark("scan");
     IRF_CUDA(cudaStreamSynchronize(s_copy));
+    const u32 hmax = hm[0] + hm[1];   // an upper bound of the largest combined depth: it only chooses the histogram layout
     // shared-memory histograms (the usual case): one short-lived CTA per intron, so the export kernels of the other stream
     // get SM slots as CTAs retire; deep data needs a global scratch histogram per CTA, hence a fixed number of looping CTAs
     u32 n_in = (u32)cov.BEDrecords.size(); u32 bins = hmax >= 8192 ? hmax + 1 : 1;
@@ -1062,7 +1070,7 @@ void irf_destroy(irf_ctx* c) {
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_slots, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
-                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_tile_state, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
   for (auto b : all) b->release();
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);

@@ -783,7 +783,9 @@ __global__ void __launch_bounds__(1024) scan_sums_kernel(int32_t* sums, u64 nt) 
     if (threadIdx.x == 1023) carry = c + incl; __syncthreads();
   }
 }
-__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(int32_t* __restrict__ d, u64 n, const int32_t* __restrict__ sums) {
+// P / dmax: when given, the largest depth of either strand (elements below / from P) is folded into this pass (dmax[0], dmax[1]); their sum
+// bounds the largest combined depth, which only sizes the per-intron histograms (a separate 1.1 ms pass over the table in round 1).
+__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(int32_t* __restrict__ d, u64 n, const int32_t* __restrict__ sums, u64 P, u32* __restrict__ dmax) {
   // each thread owns SCAN_ITEMS consecutive elements (vector loads), warp + CTA prefix over thread totals
   u64 base = (u64)blockIdx.x * SCAN_TILE + (u64)threadIdx.x * SCAN_ITEMS; int v[SCAN_ITEMS]; int tot = 0;
   if (base + SCAN_ITEMS <= n) { const int4* p = (const int4*)(d + base);
@@ -801,12 +803,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(int32_t* __res
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS / 4; k++) p[k] = make_int4(v[4 * k] + off, v[4 * k + 1] + off, v[4 * k + 2] + off, v[4 * k + 3] + off); }
   else { for (int k = 0; k < SCAN_ITEMS; k++) if (base + k < n) d[base + k] = v[k] + off; }
+  if (dmax) {
+    int m0 = 0, m1 = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) if (base + k < n) { const int x = v[k] + off; if (base + k < P) m0 = max(m0, x); else m1 = max(m1, x); }
+    for (int o = 16; o; o >>= 1) { m0 = max(m0, __shfl_down_sync(0xffffffffu, m0, o)); m1 = max(m1, __shfl_down_sync(0xffffffffu, m1, o)); }
+    if (lane == 0) { if (m0 > 0) atomicMax(&dmax[0], (u32)m0); if (m1 > 0) atomicMax(&dmax[1], (u32)m1); }
+  }
 }
-void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s) {
+void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s, u64 P, u32* dmax) {
   if (!n) return; u64 nt = (n + SCAN_TILE - 1) / SCAN_TILE;
   { scan_tile_sums_kernel<<<(unsigned)nt, SCAN_THREADS, 0, s>>>(d, n, tile_sums); IRF_LAUNCHED(); }
   { scan_sums_kernel<<<1, 1024, 0, s>>>(tile_sums, nt); IRF_LAUNCHED(); }
-  { scan_apply_kernel<<<(unsigned)nt, SCAN_THREADS, 0, s>>>(d, n, tile_sums); IRF_LAUNCHED(); }
+  { scan_apply_kernel<<<(unsigned)nt, SCAN_THREADS, 0, s>>>(d, n, tile_sums, P, dmax); IRF_LAUNCHED(); }
 }
 u64 depth_scan_tiles(u64 n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
 
@@ -908,19 +917,24 @@ void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronD
 // owning rank; a rank's difference counters outside its own segments are almost all zero (a coordinate-sorted shard covers
 // its own region plus the reads that reach over the cut), so instead of all-reducing the whole table each rank lists its
 // non-zero foreign counters as (index, value) and the owners add them.
-__global__ void __launch_bounds__(256) foreign_depth_kernel(const int32_t* __restrict__ diff, u64 P, const u32* __restrict__ seg_start, const u32* __restrict__ seg_end, const u64* __restrict__ seg_coff,
-                                                             const uint8_t* __restrict__ seg_owner, u32 nseg, u32 me, u64* __restrict__ out_idx, int32_t* __restrict__ out_val, u64* __restrict__ cursor, u64 cap) {
-  const u32 lane = threadIdx.x & 31, wpb = blockDim.x >> 5;
-  for (u32 s = blockIdx.x * wpb + (threadIdx.x >> 5); s < nseg; s += gridDim.x * wpb) {
-    if (seg_owner[s] == me) continue;
-    const u64 c0 = seg_coff[s]; const u32 n = seg_end[s] - seg_start[s] + 1;
+// tile_state: one byte per 1024 consecutive slots of the compact space: 1 = every slot owned by this rank (skipped), 2 = none owned
+// (every non-zero counter is listed), 0 = mixed (the owner of a non-zero slot is looked up).  The table is streamed once at HBM speed;
+// the first version walked segment by segment (one warp per segment, ~60 dependent loads each: 4 ms per step at 8 GPUs).
+constexpr int FOREIGN_TILE = 1024;
+__global__ void __launch_bounds__(256) foreign_depth_kernel(const int32_t* __restrict__ diff, u64 P, const u64* __restrict__ seg_coff, const uint8_t* __restrict__ seg_owner, u32 nseg, u32 me,
+                                                             const uint8_t* __restrict__ tile_state, u64 ntiles, u64* __restrict__ out_idx, int32_t* __restrict__ out_val, u64* __restrict__ cursor, u64 cap) {
+  const u32 lane = threadIdx.x & 31;
+  for (u64 t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const uint8_t st = tile_state[t]; if (st == 1) continue;
     for (int dir = 0; dir < 2; dir++) {
-      const u64 base = (u64)dir * P + c0;
-      for (u32 o = 0; o < n; o += 32) {
-        const u32 i = o + lane; const int32_t v = i < n ? diff[base + i] : 0;
-        const u32 m = __ballot_sync(0xffffffffu, v != 0); if (!m) continue;
-        u64 at = 0; if (lane == 0) at = atomicAdd(cursor, (u64)__popc(m)); at = __shfl_sync(0xffffffffu, at, 0) + __popc(m & ((1u << lane) - 1u));
-        if (v != 0 && at < cap) { out_idx[at] = base + i; out_val[at] = v; }
+#pragma unroll
+      for (int k = 0; k < FOREIGN_TILE / 256; k++) {
+        const u64 c = t * FOREIGN_TILE + (u64)k * 256 + threadIdx.x; const int32_t v = c < P ? diff[(u64)dir * P + c] : 0;
+        bool emit = v != 0;
+        if (emit && st == 0) { u32 lo = 0, hi = nseg; while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (seg_coff[mid] <= c) lo = mid; else hi = mid; } emit = seg_owner[lo] != me; }
+        const u32 m = __ballot_sync(0xffffffffu, emit); if (!m) continue;
+        u64 at = 0; if (lane == (u32)(__ffs(m) - 1)) at = atomicAdd(cursor, (u64)__popc(m)); at = __shfl_sync(0xffffffffu, at, __ffs(m) - 1) + __popc(m & ((1u << lane) - 1u));
+        if (emit && at < cap) { out_idx[at] = (u64)dir * P + c; out_val[at] = v; }
       }
     }
   }
@@ -933,8 +947,9 @@ __global__ void import_depth_kernel(int32_t* __restrict__ diff, u64 P, const u64
   while (hi - lo > 1) { u32 mid = (lo + hi) >> 1; if (seg_coff[mid] <= c) lo = mid; else hi = mid; }
   if (seg_owner[lo] == me) atomicAdd(&diff[g], val[i]);
 }
-void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s) {
-  if (nseg) { foreign_depth_kernel<<<148 * 8, 256, 0, s>>>(T.diff, T.P, T.seg_start, T.seg_end, T.seg_coff, seg_owner, nseg, me, out_idx, out_val, cursor, cap); IRF_LAUNCHED(); }
+void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const uint8_t* tile_state, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s) {
+  const u64 ntiles = (T.P + FOREIGN_TILE - 1) / FOREIGN_TILE;
+  if (nseg && ntiles) { foreign_depth_kernel<<<(unsigned)std::min<u64>(ntiles, 148 * 16), 256, 0, s>>>(T.diff, T.P, T.seg_coff, seg_owner, nseg, me, tile_state, ntiles, out_idx, out_val, cursor, cap); IRF_LAUNCHED(); }
 }
 void launch_import_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const u64* idx, const int32_t* val, u64 n, cudaStream_t s) {
   u64 g = (n + 255) / 256; if (g && nseg) { import_depth_kernel<<<(unsigned)g, 256, 0, s>>>(T.diff, T.P, T.seg_coff, seg_owner, nseg, me, idx, val, n); IRF_LAUNCHED(); }

@@ -52,12 +52,12 @@ void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32*
 void launch_ht_compact(const u64* keys, const u32* cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted, cudaStream_t s);
 size_t junction_sort_temp_bytes(u64 n);
 void launch_junction_sort(void* temp, size_t temp_bytes, const u64* keys_in, u64* keys_out, const u64* cnt_in, u64* cnt_out, u64 n, cudaStream_t s);
-void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s);
+void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s, u64 P = 0, u32* dmax = nullptr);   // dmax: two words, zeroed by the caller, receive the largest depth below / from element P
 u64 depth_scan_tiles(u64 n);
 void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s);
 void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
                          u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list = nullptr);
-void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s);
+void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const uint8_t* tile_state, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s);   // tile_state: per 1024 slots, 1 all mine / 2 none mine / 0 mixed
 void launch_import_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const u64* idx, const int32_t* val, u64 n, cudaStream_t s);
 
 }  // namespace irf
