@@ -480,7 +480,7 @@ struct irf_ctx {
   // in file order; a chunk's event is recorded behind its last piece.  Page-locking 14 GB for one run cost ~4 s (and as
   // long again to release); the ring is 128 MB, allocated once per context.
   struct Piece { size_t lo, hi; int chunk; bool last; };
-  static constexpr int FEED_SLOTS = 16; static constexpr size_t FEED_SLOT_BYTES = 16u << 20; int feed_threads_n = 12;   // round 1: 8 slots, 4 threads -> ~17 GB/s from the page cache
+  static constexpr int FEED_SLOTS = 24; static constexpr size_t FEED_SLOT_BYTES = 16u << 20; int feed_threads_n = 16;   // round 1: 8 slots, 4 threads -> ~17 GB/s from the page cache
   int feed_fd = -1; int file_ring = 1;   // option "file_ring": 0 never, 1 files above 64 MB, 2 always
   vector<Piece> feed_pieces; vector<cudaEvent_t> feed_ev_chunk; vector<char> feed_chunk_queued; cudaEvent_t feed_slot_ev[FEED_SLOTS] = {};
   uint8_t* feed_ring = nullptr; std::mutex feed_mu; std::condition_variable feed_cv; size_t feed_next = 0, feed_queued_upto = 0; bool feed_abort = false, feed_active = false; string feed_error; vector<std::thread> feed_threads;
@@ -552,12 +552,16 @@ struct irf_ctx {
     IRF_CUDA(cudaMemsetAsync(d_U.as<uint8_t>() + Uend, 0, 64, s_compute));
     cudaEvent_t ready; IRF_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming)); IRF_CUDA(cudaEventRecord(ready, s_compute));
     IRF_CUDA(cudaStreamWaitEvent(s_copy, ready, 0)); IRF_CUDA(cudaStreamWaitEvent(s_de, ready, 0));
-    vector<cudaEvent_t> ev_copy(nch), ev_inf(nch); vector<u64> inf_end(nch);   // inflated offset where each chunk ends
+    vector<cudaEvent_t> ev_copy(nch, nullptr), ev_inf(nch, nullptr); vector<u64> inf_end(nch);   // inflated offset where each chunk ends
     { u64 u = 0; size_t b = 0; for (size_t c = 0; c < nch; c++) { for (; b < chunk_blk_end[c]; b++) u += blks[b].isize; inf_end[c] = u; } }
     const size_t npre = std::min(pre_ev_copy.size(), nch);   // chunks whose copy stage() already queued (same chunking)
     const bool fed = from_host && feed_active;                 // file input: the feeder threads queue the copies (same chunking)
     if (fed && feed_ev_chunk.size() < nch) throw string("internal: file ring and pipeline disagree on the chunk count");
-    for (size_t c = 0; c < nch; c++) {
+    // Copy (unless queued already), engine batch and checks of chunk c.  Everything is queued up front, except for file input: there a
+    // chunk can only be submitted once the reader threads have queued its copies, so submission is interleaved with the counting loop
+    // (submit_upto) - round 1 waited here for the whole file to be read before the first chunk was counted.
+    size_t submitted = 0;
+    auto submit_chunk = [&](size_t c) {
       size_t lo = c * chunk_bytes, hi = std::min(src_total, lo + chunk_bytes);
       if (!from_host) { IRF_CUDA(cudaEventCreateWithFlags(&ev_copy[c], cudaEventDisableTiming)); }
       else if (fed) { ev_copy[c] = feed_wait_chunk(c); }
@@ -573,7 +577,10 @@ struct irf_ctx {
       // the SMs are busy; a mismatch raises the error flag, which is read after the last chunk
       if (f1 > f0) { IRF_CUDA(cudaStreamWaitEvent(s_chk, ev_inf[c], 0)); launch_de_check(d_de_list.as<u32>() + f0, (int)(f1 - f0), d_de_act.as<u32>(), d_u_len.as<u32>(), d_status.as<int>(), errp, s_chk);
         if (verify_crc) launch_crc_check(d_U.as<uint8_t>(), d_u_off.as<u64>(), d_u_len.as<u32>(), d_crc.as<u32>(), (int)(f1 - f0), d_status.as<int>(), errp, s_chk, d_de_list.as<u32>() + f0); }
-    }
+    };
+    auto chunk_ready = [&](size_t c) { if (!fed) return true; std::lock_guard<std::mutex> g(feed_mu); return feed_abort || feed_chunk_queued[c] != 0; };
+    auto submit_upto = [&](size_t last, bool block) { for (; submitted < nch && submitted <= last; submitted++) { if (!block && !chunk_ready(submitted)) return; submit_chunk(submitted); } };
+    if (!fed) submit_upto(nch - 1, true);
     for (size_t c = npre; c < pre_ev_copy.size(); c++) cudaEventDestroy(pre_ev_copy[c]);
     pre_ev_copy.clear(); pre_copied_bytes = 0;   // ownership of the first npre events moved to ev_copy
     // The SM kernel's share, beside everything else: one launch per grid-full of blocks (a launch whose blocks do not fill the grid
@@ -597,11 +604,12 @@ struct irf_ctx {
       }
       k1 = k_ev.back();
     }
-    auto cleanup = [&]() { if (fed) feed_stop(); else for (auto e : ev_copy) cudaEventDestroy(e); for (auto e : ev_inf) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); for (auto e : k_ev) cudaEventDestroy(e); };
+    auto cleanup = [&]() { if (fed) feed_stop(); else for (auto e : ev_copy) if (e) cudaEventDestroy(e); for (auto e : ev_inf) if (e) cudaEventDestroy(e); cudaEventDestroy(ready); cudaEventDestroy(e0); cudaEventDestroy(e3); if (k0) cudaEventDestroy(k0); for (auto e : k_ev) cudaEventDestroy(e); };
     try {
       // BAM2blocks::readBamHeader as soon as the first chunk is there (a header larger than one chunk waits for more)
       if (sm_used && staged_has_header) IRF_CUDA(cudaEventSynchronize(k_ev[0]));   // the header lies in the kernel's first launch
       for (size_t c = 0; staged_has_header; c++) {
+        submit_upto(c, true);
         IRF_CUDA(cudaEventSynchronize(ev_inf[c])); check_dev_err("inflate");
         u64 full = Uend; Uend = inf_end[c]; bool ok = true;
         try { parse_header_from_device(); } catch (const string& e) { ok = false; if (e.find("truncated") == string::npos || c + 1 == nch) { Uend = full; throw; } }
@@ -625,6 +633,7 @@ struct irf_ctx {
         // realistic record, however many small chunks it spans, is complete)
         size_t need = std::min(c + 1, nch - 1); while (need + 1 < nch && inf_end[need] - inf_end[c] < (8u << 20)) need++;
         if (last_own) need = nch - 1;
+        submit_upto(need, true); submit_upto(need + 3, false);   // file input: what this chunk needs (waiting for the readers if necessary), and whatever else has been read by now
         IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_inf[need], 0));
         if (sm_used && c < ksm) { size_t g = 0; while (k_chunk_end[g] <= std::min(need, ksm - 1)) g++; IRF_CUDA(cudaStreamWaitEvent(s_compute, k_ev[g], 0)); }   // the launch that inflates the last chunk this one needs
         const u64 visible = inf_end[need];
@@ -662,6 +671,7 @@ struct irf_ctx {
         }
         b0 = b1;
       }
+      submit_upto(nch - 1, true);
       if (nblk_own == (int)nb && entry_prev != Uend) throw string("record framing: last record does not end at the end of the stream (truncated BAM)");
       IRF_CUDA(cudaEventRecord(e3, s_compute)); IRF_CUDA(cudaStreamSynchronize(s_copy)); IRF_CUDA(cudaStreamSynchronize(s_de)); IRF_CUDA(cudaStreamSynchronize(s_chk)); sync();
       check_dev_err("fragment counting");
