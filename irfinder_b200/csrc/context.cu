@@ -87,7 +87,7 @@ struct irf_ctx {
   DevBuf d_jc_keys, d_jc_cnt, d_jl_keys, d_jl_cnt, d_jr_keys, d_jr_cnt, d_annot_keys; u64 n_annot = 0; u32 jc_slots = 0, jside_slots = 0;
   DevBuf d_bucket_base, d_bucket_n, d_sp_bidx, d_seg_bidx, d_roi_bidx;
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
-  DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt;
+  DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt, d_junc_rows;
   // staged input
   DevBuf d_tok, d_slots, d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
@@ -96,7 +96,6 @@ struct irf_ctx {
   void* pinned = nullptr; size_t pinned_cap = 0;
   // results
   vector<u64> h_stats; vector<u32> h_sp, h_roi, h_chr, h_dump; vector<JuncEntry> h_junc; vector<IntronRow> rows_nondir, rows_dir; vector<int32_t> h_depth;
-  struct JuncOut { int32_t refid; u32 start, end, neg, pos; }; vector<JuncOut> h_junc_out;
   int directionality = 0; string stdout_text, dir_log; double timing[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
   bool counted = false, finalized = false;
   string err;
@@ -903,16 +902,15 @@ struct irf_ctx {
     launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy, do_list);
     if (!owner_mode) { pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); }
     // junctions -> host (JunctionCount map contents)
-    u64 nj = export_table(0); vector<u64> k(nj); vector<u32> c(nj * 2);
-    if (nj) {   // sort by key on the device: key order == (refID, start, end) order
-      size_t tb = junction_sort_temp_bytes(nj); d_sort_tmp.ensure(tb); d_sort_keys.ensure(nj * 8); d_sort_cnt.ensure(nj * 8);
+    u64 nj = export_table(0);
+    static_assert(sizeof(JuncEntry) == 20, "JuncEntry is the 20-byte row the device writes and IRF_T_JUNCTIONS exposes");
+    if (h_junc.size() != nj) { if (!h_junc.empty()) cudaHostUnregister(h_junc.data()); h_junc.clear(); h_junc.resize(nj); if (nj && cudaHostRegister(h_junc.data(), nj * sizeof(JuncEntry), cudaHostRegisterDefault) != cudaSuccess) cudaGetLastError(); }
+    if (nj) {   // sort by key on the device (key order == (refID, start, end) order), turn the pairs into rows there, one read-back into page-locked memory
+      size_t tb = junction_sort_temp_bytes(nj); d_sort_tmp.ensure(tb); d_sort_keys.ensure(nj * 8); d_sort_cnt.ensure(nj * 8); d_junc_rows.ensure(nj * sizeof(JuncEntry));
       launch_junction_sort(d_sort_tmp.p, tb, d_exp_keys[0].as<u64>(), d_sort_keys.as<u64>(), d_exp_cnt[0].as<u64>(), d_sort_cnt.as<u64>(), nj, s_compute);
-      IRF_CUDA(cudaMemcpyAsync(k.data(), d_sort_keys.p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); IRF_CUDA(cudaMemcpyAsync(c.data(), d_sort_cnt.p, nj * 8, cudaMemcpyDeviceToHost, s_compute)); sync();
+      launch_junction_rows(d_sort_keys.as<u64>(), d_sort_cnt.as<u64>(), nj, T.chr_goff, T.n_ref, d_junc_rows.p, s_compute);
+      IRF_CUDA(cudaMemcpyAsync(h_junc.data(), d_junc_rows.p, nj * sizeof(JuncEntry), cudaMemcpyDeviceToHost, s_compute)); sync();
     }
-    h_junc.resize(nj);
-    { int rid = 0; for (u64 i = 0; i < nj; i++) { u64 gl = k[i] >> JKEY_GAP_BITS, gap = k[i] & ((1ull << JKEY_GAP_BITS) - 1); while (rid + 1 < (int)chr_goff.size() - 1 && gl >= chr_goff[rid + 1]) rid++;
-        h_junc[i] = JuncEntry{rid, (u32)(gl - chr_goff[rid]), (u32)(gl - chr_goff[rid] + gap), {c[2 * i], c[2 * i + 1]}}; } }
-    h_junc_out.resize(nj); for (u64 i = 0; i < nj; i++) h_junc_out[i] = JuncOut{h_junc[i].refid, h_junc[i].start, h_junc[i].end, h_junc[i].cnt[0], h_junc[i].cnt[1]};
     mark("junction export+sort"); dir_log.clear(); directionality = directional(jref, chr_names, h_junc, dir_log); mark("directional");
     IRF_CUDA(cudaStreamSynchronize(s_copy)); mark("intron stats nondir (side stream)");
     if (directionality == 0 && !rows_dir.empty()) { cudaHostUnregister(rows_dir.data()); vector<IntronRow>().swap(rows_dir); }
@@ -1080,8 +1078,9 @@ void irf_destroy(irf_ctx* c) {
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_slots, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
-                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_tile_state, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt};
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_tile_state, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt, &c->d_junc_rows};
   for (auto b : all) b->release();
+  if (!c->h_junc.empty()) cudaHostUnregister(c->h_junc.data());
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->wm_host) cudaFreeHost(c->wm_host);
@@ -1174,7 +1173,7 @@ int irf_get_table(irf_ctx* c, int which, const void** p, size_t* n) {
         case IRF_T_SPANS: *p = c->h_sp.data(); *n = c->h_sp.size(); break;
         case IRF_T_ROI: *p = c->h_roi.data(); *n = c->h_roi.size(); break;
         case IRF_T_CHR: *p = c->h_chr.data(); *n = c->h_chr.size(); break;
-        case IRF_T_JUNCTIONS: *p = c->h_junc_out.data(); *n = c->h_junc_out.size(); break;
+        case IRF_T_JUNCTIONS: *p = c->h_junc.data(); *n = c->h_junc.size(); break;
         case IRF_T_ROWS_NONDIR: *p = c->rows_nondir.data(); *n = c->rows_nondir.size(); break;
         case IRF_T_ROWS_DIR: *p = c->rows_dir.data(); *n = c->rows_dir.size(); break;
         case IRF_T_FRAGMENTS: *p = c->h_dump.data(); *n = c->h_dump.size(); break;

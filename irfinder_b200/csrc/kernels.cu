@@ -755,6 +755,18 @@ size_t junction_sort_temp_bytes(u64 n) { size_t b = 0; cub::DeviceRadixSort::Sor
 void launch_junction_sort(void* temp, size_t temp_bytes, const u64* keys_in, u64* keys_out, const u64* cnt_in, u64* cnt_out, u64 n, cudaStream_t s) {
   if (n) { cub::DeviceRadixSort::SortPairs(temp, temp_bytes, keys_in, keys_out, cnt_in, cnt_out, (int)n, 0, 64, s); IRF_LAUNCHED(); }
 }
+// Sorted (key, counts) pairs -> the rows the host works with {refID, start, end, count[0], count[1]} (the JuncEntry / IRF_T_JUNCTIONS layout).
+struct JuncRow { int refid; u32 start, end, c0, c1; };
+__global__ void junction_rows_kernel(const u64* __restrict__ keys, const u64* __restrict__ cnt, u64 n, const u64* __restrict__ chr_goff, int n_ref, JuncRow* __restrict__ out) {
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+  const u64 k = keys[i], gl = k >> JKEY_GAP_BITS, gap = k & ((1ull << JKEY_GAP_BITS) - 1), c = cnt[i];
+  int lo = 0, hi = n_ref;                                   // last reference whose offset is <= gl
+  while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (chr_goff[mid] <= gl) lo = mid; else hi = mid; }
+  out[i] = JuncRow{lo, (u32)(gl - chr_goff[lo]), (u32)(gl - chr_goff[lo] + gap), (u32)c, (u32)(c >> 32)};
+}
+void launch_junction_rows(const u64* keys, const u64* cnt, u64 n, const u64* chr_goff, int n_ref, void* out, cudaStream_t s) {
+  u64 g = (n + 255) / 256; if (g) { junction_rows_kernel<<<(unsigned)g, 256, 0, s>>>(keys, cnt, n, chr_goff, n_ref, (JuncRow*)out); IRF_LAUNCHED(); }
+}
 void launch_ht_insert_keys(u64* keys, u32 mask, const u64* in, u64 n, int* err, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { ht_insert_keys_kernel<<<(unsigned)g, 256, 0, s>>>(keys, mask, in, n, err); IRF_LAUNCHED(); } }
 void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32* in_cnt, u64 n, int* err, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { ht_add_kernel<<<(unsigned)g, 256, 0, s>>>(keys, cnt, mask, in_keys, in_cnt, n, err); IRF_LAUNCHED(); } }
 void launch_ht_compact(const u64* keys, const u32* cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted, cudaStream_t s) {

@@ -51,6 +51,7 @@ void launch_ht_insert_keys(u64* keys, u32 mask, const u64* in, u64 n, int* err, 
 void launch_ht_add(u64* keys, u32* cnt, u32 mask, const u64* in_keys, const u32* in_cnt, u64 n, int* err, cudaStream_t s);
 void launch_ht_compact(const u64* keys, const u32* cnt, u64 nslots, u64* out_keys, u32* out_cnt, u64* cursor, u64 cap, int only_counted, cudaStream_t s);
 size_t junction_sort_temp_bytes(u64 n);
+void launch_junction_rows(const u64* keys, const u64* cnt, u64 n, const u64* chr_goff, int n_ref, void* out_rows, cudaStream_t s);   // 20-byte rows {refID, start, end, count[0], count[1]}
 void launch_junction_sort(void* temp, size_t temp_bytes, const u64* keys_in, u64* keys_out, const u64* cnt_in, u64* cnt_out, u64 n, cudaStream_t s);
 void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s, u64 P = 0, u32* dmax = nullptr);   // dmax: two words, zeroed by the caller, receive the largest depth below / from element P
 u64 depth_scan_tiles(u64 n);
