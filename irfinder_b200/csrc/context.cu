@@ -87,7 +87,7 @@ struct irf_ctx {
   DevBuf d_jc_keys, d_jc_cnt, d_jl_keys, d_jl_cnt, d_jr_keys, d_jr_cnt, d_annot_keys; u64 n_annot = 0; u32 jc_slots = 0, jside_slots = 0;
   DevBuf d_bucket_base, d_bucket_n, d_sp_bidx, d_seg_bidx, d_roi_bidx;
   DevBuf d_stats, d_err, d_introns, d_iblocks, d_rows, d_scratch, d_tile_sums, d_small, d_dump, d_dump_cursor; u64 dump_cap = 0;
-  DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt, d_junc_rows;
+  DevBuf d_exp_keys[3], d_exp_cnt[3], d_sort_tmp, d_sort_keys, d_sort_cnt, d_junc_rows, d_overflow;
   // staged input
   DevBuf d_tok, d_slots, d_sm_list, d_de_list, d_de_act, d_crc, d_comp, d_U, d_c_off, d_c_len, d_u_off, d_u_len, d_status, d_entry, d_exit, d_nrec, d_ncand, d_ferr, d_mask, d_mism, d_ptab, d_left, d_halo, d_halo_off, d_hptab, d_rec_base, d_rec_off, d_pair_list, d_single_list;
   const uint8_t* h_src = nullptr; size_t src_total = 0; bool resident = false;
@@ -896,10 +896,18 @@ struct irf_ctx {
     u32 n_in = (u32)cov.BEDrecords.size(); u32 bins = hmax >= 8192 ? hmax + 1 : 1;
     // region-owned run: this rank computes the rows of its own introns only (the others stay zero and are merged by the caller)
     const u32 n_do = owner_mode ? n_own_introns : n_in; const u32* do_list = owner_mode ? d_own_introns.as<u32>() : nullptr;
-    int grid = (int)std::min<u32>(std::max<u32>(n_do, 1), bins == 1 ? (1u << 20) : 148 * 4);
-    d_scratch.ensure((u64)grid * bins * 4);
+    // one-pass fast kernel for every intron (2048-bin shared-memory histogram); the few introns with a deeper position land in an
+    // overflow list and go through the general two-pass kernel (looping CTAs; global scratch histograms when the depth exceeds 8192)
+    int grid = (int)std::min<u32>(std::max<u32>(n_do, 1), bins == 1 ? 148 * 8 : 148 * 4);
+    d_scratch.ensure((u64)grid * bins * 4); d_overflow.ensure((u64)n_do * 4 + 4);
+    u32* n_over = d_small.as<u32>() + 14;
+    auto stats = [&](int dir_mode, IntronRow* out) {
+      IRF_CUDA(cudaMemsetAsync(n_over, 0, 4, s_copy));
+      launch_intron_stats_fast(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, dir_mode, trim_center, out, s_copy, do_list, d_overflow.as<u32>(), n_over);
+      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, dir_mode, trim_center, d_scratch.as<u32>(), bins, grid, out, s_copy, d_overflow.as<u32>(), n_over);
+    };
     if (owner_mode) { d_rows_dir.ensure(n_in * sizeof(IntronRow)); IRF_CUDA(cudaMemsetAsync(d_rows.p, 0, n_in * sizeof(IntronRow), s_copy)); IRF_CUDA(cudaMemsetAsync(d_rows_dir.p, 0, n_in * sizeof(IntronRow), s_copy)); }
-    launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, 0, trim_center, d_scratch.as<u32>(), bins, grid, d_rows.as<IntronRow>(), s_copy, do_list);
+    stats(0, d_rows.as<IntronRow>());
     if (!owner_mode) { pin_rows(rows_nondir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_nondir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); }
     // junctions -> host (JunctionCount map contents)
     u64 nj = export_table(0);
@@ -915,7 +923,7 @@ struct irf_ctx {
     IRF_CUDA(cudaStreamSynchronize(s_copy)); mark("intron stats nondir (side stream)");
     if (directionality == 0 && !rows_dir.empty()) { cudaHostUnregister(rows_dir.data()); vector<IntronRow>().swap(rows_dir); }
     if (directionality != 0) {
-      launch_intron_stats(T, T.diff, d_introns.as<IntronDesc>(), d_iblocks.as<IntronBlock>(), n_do, directionality, trim_center, d_scratch.as<u32>(), bins, grid, owner_mode ? d_rows_dir.as<IntronRow>() : d_rows.as<IntronRow>(), s_copy, do_list);
+      stats(directionality, owner_mode ? d_rows_dir.as<IntronRow>() : d_rows.as<IntronRow>());
       if (!owner_mode) { pin_rows(rows_dir, n_in); if (n_in) IRF_CUDA(cudaMemcpyAsync(rows_dir.data(), d_rows.p, n_in * sizeof(IntronRow), cudaMemcpyDeviceToHost, s_copy)); } IRF_CUDA(cudaStreamSynchronize(s_copy));
     }
     IRF_CUDA(cudaEventRecord(ev_side, s_copy)); IRF_CUDA(cudaStreamWaitEvent(s_compute, ev_side, 0)); cudaEventDestroy(ev_scan); cudaEventDestroy(ev_side);
@@ -1078,7 +1086,7 @@ void irf_destroy(irf_ctx* c) {
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_slots, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
                    &c->d_entry, &c->d_exit, &c->d_nrec, &c->d_ncand, &c->d_ferr, &c->d_mask, &c->d_mism, &c->d_ptab, &c->d_left, &c->d_halo, &c->d_halo_off, &c->d_hptab, &c->d_rec_base, &c->d_rec_off, &c->d_pair_list, &c->d_single_list, &c->d_exp_keys[0], &c->d_exp_keys[1], &c->d_exp_keys[2],
-                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_tile_state, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt, &c->d_junc_rows};
+                   &c->d_exp_cnt[0], &c->d_exp_cnt[1], &c->d_exp_cnt[2], &c->d_seg_owner, &c->d_tile_state, &c->d_own_introns, &c->d_fidx, &c->d_fval, &c->d_rows_dir, &c->d_carry, &c->d_carry_off, &c->d_sort_tmp, &c->d_sort_keys, &c->d_sort_cnt, &c->d_junc_rows, &c->d_overflow};
   for (auto b : all) b->release();
   if (!c->h_junc.empty()) cudaHostUnregister(c->h_junc.data());
   if (!c->rows_nondir.empty()) cudaHostUnregister(c->rows_nondir.data()); if (!c->rows_dir.empty()) cudaHostUnregister(c->rows_dir.data());

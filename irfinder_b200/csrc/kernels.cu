@@ -846,38 +846,9 @@ void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s) { i
 constexpr int IS_THREADS = 256, IS_SMEM_BINS = 8192;
 __device__ __forceinline__ u32 depth_at(const int32_t* depth, u64 P, u64 c, int sel) { return sel < 0 ? (u32)(depth[c] + depth[P + c]) : (u32)depth[(u64)sel * P + c]; }
 
-__global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, const int32_t* __restrict__ depth, const IntronDesc* __restrict__ introns, const IntronBlock* __restrict__ blocks,
-                                                                   u32 n_introns, int directionality, u32 trim_center, u32* __restrict__ scratch, u32 scratch_bins, IntronRow* __restrict__ rows,
-                                                                   const u32* __restrict__ list) {   // list: optional indices of the introns to compute (region-owned multi-GPU runs); n_introns entries
-  __shared__ u32 sh_hist[IS_SMEM_BINS]; __shared__ u32 sh_red[IS_THREADS / 32]; __shared__ u32 sh_max; __shared__ u64 sh_edge[4];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  u32* ghist = scratch + (u64)blockIdx.x * scratch_bins;
-  for (u32 li = blockIdx.x; li < n_introns; li += gridDim.x) {
-    const u32 it = list ? list[li] : li;
-    const IntronDesc in = introns[it];
-    int sel = -1;
-    if (directionality != 0) { bool measureDir = in.plus != 0; if (directionality < 0) measureDir = !measureDir; sel = measureDir ? 1 : 0; }
-    // pass 1: maximum depth and number of positions
-    u32 mx = 0; u64 npos = 0;
-    for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { IntronBlock bl = blocks[b]; npos += bl.len; for (u32 p = tid; p < bl.len; p += IS_THREADS) mx = max(mx, depth_at(depth, T.P, bl.c0 + p, sel)); }
-    for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_down_sync(0xffffffffu, mx, o));
-    if (lane == 0) sh_red[warp] = mx; __syncthreads();
-    if (tid == 0) { u32 m = 0; for (int w = 0; w < IS_THREADS / 32; w++) m = max(m, sh_red[w]); sh_max = m; } __syncthreads();
-    mx = sh_max; const bool in_smem = mx < IS_SMEM_BINS; u32* hist = in_smem ? sh_hist : ghist;
-    if (!in_smem && mx >= scratch_bins) { if (tid == 0) atomicOr(T.err, DERR_BAD_RECORD); __syncthreads(); continue; }
-    for (u32 i = tid; i <= mx; i += IS_THREADS) hist[i] = 0;
-    __syncthreads();
-    // pass 2: histogram
-    for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { IntronBlock bl = blocks[b]; for (u32 p = tid; p < bl.len; p += IS_THREADS) atomicAdd(&hist[depth_at(depth, T.P, bl.c0 + p, sel)], 1u); }
-    // edge windows (mean depth over measured positions): warps 1 and 2
-    if (warp == 1 || warp == 2) {
-      u32 b0 = warp == 1 ? in.blk_main_end : in.blk_first_end, b1 = warp == 1 ? in.blk_first_end : in.blk_last_end; u64 tot = 0, cnt = 0;
-      for (u32 b = b0; b < b1; b++) { IntronBlock bl = blocks[b]; cnt += bl.len; for (u32 p = lane; p < bl.len; p += 32) tot += depth_at(depth, T.P, bl.c0 + p, sel); }
-      for (int o = 16; o; o >>= 1) tot += __shfl_down_sync(0xffffffffu, tot, o);
-      if (lane == 0) { sh_edge[(warp - 1) * 2] = tot; sh_edge[(warp - 1) * 2 + 1] = cnt; }
-    }
-    __syncthreads();
-    if (tid == 0) {
+// coverageFromHist / percentileFromHist / trimmedMeanFromHist in one ascending walk ([C-2][C-12]), the edge-window means, SpansPoint::lookup and
+// JunctionCount::lookup{Left,Right,}, IRratio and the warning: everything of one IRFinder-IR row that follows the depth histogram.  One thread.
+__device__ void intron_row_from_hist(const DevTables& T, const IntronDesc& in, const u32* hist, u32 mx, u64 npos, const u64* sh_edge, int sel, u32 trim_center, IntronRow* out) {
       IntronRow r; r.positions = npos; r.excluded = (long long)(in.end - in.start) - (long long)npos;
       // coverageFromHist / percentileFromHist / trimmedMeanFromHist, one ascending walk ([C-2][C-12])
       u64 n = npos, lo = n * (100 - trim_center) / 200, hi = n - lo, cum = 0, total = 0; double pct[3] = {0, 0, 0}; int pstate[3] = {0, 0, 0}; u32 pdepth[3] = {0, 0, 0};
@@ -914,14 +885,87 @@ __global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, c
       else if ((double)r.jc_exact < (double)jmax * R.warn_minor_ratio) r.warning = W_MINORISOFORM;
       else if ((spmax > r.depth + R.warn_nonuniform_abs && spmax > r.depth * R.warn_nonuniform_ratio) || (spmin + R.warn_nonuniform_abs < r.depth && spmin * R.warn_nonuniform_ratio < r.depth)) r.warning = W_NONUNIFORM;
       else r.warning = W_NONE;
-      rows[it] = r;
+  *out = r;
+}
+
+
+__global__ void __launch_bounds__(IS_THREADS) intron_stats_kernel(DevTables T, const int32_t* __restrict__ depth, const IntronDesc* __restrict__ introns, const IntronBlock* __restrict__ blocks,
+                                                                   u32 n_introns, int directionality, u32 trim_center, u32* __restrict__ scratch, u32 scratch_bins, IntronRow* __restrict__ rows,
+                                                                   const u32* __restrict__ list, const u32* __restrict__ n_dev) {   // list: optional indices of the introns to compute (owned introns, or the fast path's overflow list); n_dev: their number when only the device knows it
+  __shared__ u32 sh_hist[IS_SMEM_BINS]; __shared__ u32 sh_red[IS_THREADS / 32]; __shared__ u32 sh_max; __shared__ u64 sh_edge[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  u32* ghist = scratch + (u64)blockIdx.x * scratch_bins;
+  if (n_dev) n_introns = min(n_introns, *n_dev);
+  for (u32 li = blockIdx.x; li < n_introns; li += gridDim.x) {
+    const u32 it = list ? list[li] : li;
+    const IntronDesc in = introns[it];
+    int sel = -1;
+    if (directionality != 0) { bool measureDir = in.plus != 0; if (directionality < 0) measureDir = !measureDir; sel = measureDir ? 1 : 0; }
+    // pass 1: maximum depth and number of positions
+    u32 mx = 0; u64 npos = 0;
+    for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { IntronBlock bl = blocks[b]; npos += bl.len; for (u32 p = tid; p < bl.len; p += IS_THREADS) mx = max(mx, depth_at(depth, T.P, bl.c0 + p, sel)); }
+    for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_down_sync(0xffffffffu, mx, o));
+    if (lane == 0) sh_red[warp] = mx; __syncthreads();
+    if (tid == 0) { u32 m = 0; for (int w = 0; w < IS_THREADS / 32; w++) m = max(m, sh_red[w]); sh_max = m; } __syncthreads();
+    mx = sh_max; const bool in_smem = mx < IS_SMEM_BINS; u32* hist = in_smem ? sh_hist : ghist;
+    if (!in_smem && mx >= scratch_bins) { if (tid == 0) atomicOr(T.err, DERR_BAD_RECORD); __syncthreads(); continue; }
+    for (u32 i = tid; i <= mx; i += IS_THREADS) hist[i] = 0;
+    __syncthreads();
+    // pass 2: histogram
+    for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { IntronBlock bl = blocks[b]; for (u32 p = tid; p < bl.len; p += IS_THREADS) atomicAdd(&hist[depth_at(depth, T.P, bl.c0 + p, sel)], 1u); }
+    // edge windows (mean depth over measured positions): warps 1 and 2
+    if (warp == 1 || warp == 2) {
+      u32 b0 = warp == 1 ? in.blk_main_end : in.blk_first_end, b1 = warp == 1 ? in.blk_first_end : in.blk_last_end; u64 tot = 0, cnt = 0;
+      for (u32 b = b0; b < b1; b++) { IntronBlock bl = blocks[b]; cnt += bl.len; for (u32 p = lane; p < bl.len; p += 32) tot += depth_at(depth, T.P, bl.c0 + p, sel); }
+      for (int o = 16; o; o >>= 1) tot += __shfl_down_sync(0xffffffffu, tot, o);
+      if (lane == 0) { sh_edge[(warp - 1) * 2] = tot; sh_edge[(warp - 1) * 2 + 1] = cnt; }
     }
+    __syncthreads();
+    if (tid == 0) intron_row_from_hist(T, in, hist, mx, npos, sh_edge, sel, trim_center, &rows[it]);
     __syncthreads();
   }
 }
+// Fast path of the same: ONE pass over the intron's depth values (round 1 read them twice: maximum first, then histogram) into a
+// 2048-bin shared-memory histogram; an intron with a deeper position is appended to `overflow` and done by intron_stats_kernel.
+constexpr int ISF_BINS = 2048;
+__global__ void __launch_bounds__(IS_THREADS) intron_stats_fast_kernel(DevTables T, const int32_t* __restrict__ depth, const IntronDesc* __restrict__ introns, const IntronBlock* __restrict__ blocks,
+                                                                        u32 n_introns, int directionality, u32 trim_center, IntronRow* __restrict__ rows, const u32* __restrict__ list,
+                                                                        u32* __restrict__ overflow, u32* __restrict__ n_overflow) {
+  __shared__ u32 sh_hist[ISF_BINS]; __shared__ u32 sh_max, sh_over; __shared__ u64 sh_edge[4];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const u32 li = blockIdx.x; if (li >= n_introns) return;
+  const u32 it = list ? list[li] : li;
+  const IntronDesc in = introns[it];
+  int sel = -1;
+  if (directionality != 0) { bool measureDir = in.plus != 0; if (directionality < 0) measureDir = !measureDir; sel = measureDir ? 1 : 0; }
+  for (int i = tid; i < ISF_BINS; i += IS_THREADS) sh_hist[i] = 0;
+  if (tid == 0) { sh_max = 0; sh_over = 0; }
+  __syncthreads();
+  u32 mx = 0; u64 npos = 0; bool over = false;
+  for (u32 b = in.blk_begin; b < in.blk_main_end; b++) { const IntronBlock bl = blocks[b]; npos += bl.len;
+    for (u32 p = tid; p < bl.len; p += IS_THREADS) { const u32 d = depth_at(depth, T.P, bl.c0 + p, sel); if (d < (u32)ISF_BINS) { atomicAdd(&sh_hist[d], 1u); mx = max(mx, d); } else over = true; } }
+  for (int o = 16; o; o >>= 1) mx = max(mx, __shfl_down_sync(0xffffffffu, mx, o));
+  if (lane == 0 && mx) atomicMax(&sh_max, mx);
+  if (over) sh_over = 1;
+  if (warp == 1 || warp == 2) {   // edge windows (mean depth over measured positions)
+    u32 b0 = warp == 1 ? in.blk_main_end : in.blk_first_end, b1 = warp == 1 ? in.blk_first_end : in.blk_last_end; u64 tot = 0, cnt = 0;
+    for (u32 b = b0; b < b1; b++) { const IntronBlock bl = blocks[b]; cnt += bl.len; for (u32 p = lane; p < bl.len; p += 32) tot += depth_at(depth, T.P, bl.c0 + p, sel); }
+    for (int o = 16; o; o >>= 1) tot += __shfl_down_sync(0xffffffffu, tot, o);
+    if (lane == 0) { sh_edge[(warp - 1) * 2] = tot; sh_edge[(warp - 1) * 2 + 1] = cnt; }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    if (sh_over) overflow[atomicAdd(n_overflow, 1u)] = it;
+    else intron_row_from_hist(T, in, sh_hist, sh_max, npos, sh_edge, sel, trim_center, &rows[it]);
+  }
+}
 void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
-                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list) {
-  if (n_introns) { intron_stats_kernel<<<grid, IS_THREADS, 0, s>>>(T, depth, introns, blocks, n_introns, directionality, trim_center, scratch, scratch_bins, rows, list); IRF_LAUNCHED(); }
+                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list, const u32* n_dev) {
+  if (n_introns) { intron_stats_kernel<<<grid, IS_THREADS, 0, s>>>(T, depth, introns, blocks, n_introns, directionality, trim_center, scratch, scratch_bins, rows, list, n_dev); IRF_LAUNCHED(); }
+}
+void launch_intron_stats_fast(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
+                              IntronRow* rows, cudaStream_t s, const u32* list, u32* overflow, u32* n_overflow) {
+  if (n_introns) { intron_stats_fast_kernel<<<n_introns, IS_THREADS, 0, s>>>(T, depth, introns, blocks, n_introns, directionality, trim_center, rows, list, overflow, n_overflow); IRF_LAUNCHED(); }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -57,7 +57,10 @@ void launch_depth_scan(int32_t* d, u64 n, int32_t* tile_sums, cudaStream_t s, u6
 u64 depth_scan_tiles(u64 n);
 void launch_max_depth(const int32_t* depth, u64 P, u32* out, cudaStream_t s);
 void launch_intron_stats(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
-                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list = nullptr);
+                         u32* scratch, u32 scratch_bins, int grid, IntronRow* rows, cudaStream_t s, const u32* list = nullptr, const u32* n_dev = nullptr);
+// one-pass fast path (depth < 2048 everywhere in the intron); deeper introns are appended to overflow[*n_overflow++] for launch_intron_stats
+void launch_intron_stats_fast(const DevTables& T, const int32_t* depth, const IntronDesc* introns, const IntronBlock* blocks, u32 n_introns, int directionality, u32 trim_center,
+                              IntronRow* rows, cudaStream_t s, const u32* list, u32* overflow, u32* n_overflow);
 void launch_foreign_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const uint8_t* tile_state, u64* out_idx, int32_t* out_val, u64* cursor, u64 cap, cudaStream_t s);   // tile_state: per 1024 slots, 1 all mine / 2 none mine / 0 mixed
 void launch_import_depth(const DevTables& T, u32 nseg, const uint8_t* seg_owner, u32 me, const u64* idx, const int32_t* val, u64 n, cudaStream_t s);
 
