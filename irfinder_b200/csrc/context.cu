@@ -5,6 +5,9 @@
 // (binding name-keyed reference tables to BAM refIDs), kernel orchestration and result download.
 // There is no CPU implementation of any counting step in this library: without a CUDA device every entry
 // point fails with IRF_ECUDA.
+#ifndef _GNU_SOURCE
+#define _GNU_SOURCE
+#endif
 #include <cuda.h>
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -997,6 +1000,9 @@ struct irf_ctx {
   // stream) + look-ahead bytes, which are also the first bytes of the next segment.
   void run_stream(int fd, bool inflated) {
     const size_t SEG = std::max<size_t>(stream_segment_bytes, 1u << 20), LA = std::min<size_t>(SEG, 8u << 20), SLOT = SEG + LA + (1u << 17);
+#ifdef F_SETPIPE_SZ
+    fcntl(fd, F_SETPIPE_SZ, 1 << 20);   // a pipe: the largest buffer an unprivileged process may ask for (best effort; fewer wake-ups per GB)
+#endif
     struct Slot { uint8_t* p = nullptr; size_t own = 0, total = 0, filled = 0; bool last = false, ready = false; string err; } slot[2];
     for (auto& sl : slot) IRF_CUDA(cudaMallocHost((void**)&sl.p, SLOT + 64));
     std::mutex mu; std::condition_variable cv; bool stop = false;
