@@ -12,8 +12,7 @@
 //    Codes longer than the LUT width (rare) fall back to a canonical bit-serial walk over the
 //    code-length histogram, held in per-lane local memory.
 //  * Output: bytes are stored to global memory one by one; long-distance LZ77 matches load up to 8 source bytes in one step and
-//    store them in the next, so the load latency hides behind decode work.  (A per-lane shared-memory output ring, RING_BITS > 0,
-//    was measured slower and is no longer offered by launch_inflate; the code path remains for the host emulation tests.)
+//    store them in the next, so the load latency hides behind decode work.
 //  * This one-phase decoder is inflate_variant 0-11; the default kernel is the two-phase one in inflate_tok.cuh, which reuses
 //    BitReader, LaneTable and Huff from this file.
 //
@@ -82,52 +81,23 @@ struct BitReader {
   IRF_HD bool overrun() const { return (const uint8_t*)wp - 16 - (half ? 4 : 8) - (bc >> 3) > end + 4; }
 };
 
-// Output cursor.  RING_BITS == 0: bytes are stored to global memory one by one.  RING_BITS > 0: the last 2^RING_BITS output
-// bytes of each lane live in a shared-memory ring (word-interleaved by lane, conflict-free); finished 32-byte sectors
-// leave as two 128-bit stores, and LZ77 matches whose distance fits inside the ring are served from shared memory.
-// Why: with ~100k streams in flight the byte stores of the plain version reach L2 as 1-byte partial-sector writes, about
-// half of which miss and make L2 fetch the sector from DRAM first (profiles/r1: 16x the algorithmic DRAM traffic).
-template <int LANES, int RING_BITS>
+// Output cursor: bytes are stored to global memory one by one.  (Round 1 also had a mode that kept each lane's last 2^k output bytes in a
+// shared-memory ring and flushed whole sectors; it lost more to occupancy than it won and its flush faulted on some output alignments, so it
+// was removed in round 2.  The two-phase kernel in inflate_tok.cuh solves the same problem - partial-sector writes - by writing every output
+// byte in its resolve phase.)
+template <int LANES>
 struct OutCursor {
-  static constexpr uint32_t R = RING_BITS ? (1u << RING_BITS) : 1u;
   uint8_t* out;      // start of this block's output
   uint32_t op;       // bytes produced so far
   uint32_t cap;      // ISIZE
-  uint32_t fl;       // bytes already written to global memory (ring mode)
-  uintptr_t pz;      // plain mode: output sectors below this address have been pre-written (see prezero)
-  uint8_t* ring;     // this lane's view of the warp's ring region (ring mode)
-  IRF_HD void init(uint8_t* o, uint32_t c, uint8_t* ring_region, int lane) { out = o; op = 0; cap = c; fl = 0; ring = ring_region ? ring_region + lane * 4 : nullptr; pz = ((uintptr_t)o + 31) & ~(uintptr_t)31; }
-  IRF_HD static uint32_t ridx(uintptr_t g) { uint32_t i = (uint32_t)g & (R - 1); return (i >> 2) * (LANES * 4) + (i & 3); }
-  IRF_HD void emit(uint32_t byte) {
-    if (RING_BITS) ring[ridx((uintptr_t)out + op)] = (uint8_t)byte; else out[op] = (uint8_t)byte;
-    op++;
-  }
-  IRF_HD uint8_t ring_at(uint32_t pos) const { return ring[ridx((uintptr_t)out + pos)]; }
-  // writes every complete 32-byte sector (in address space) that is still only in the ring
-  IRF_HD void flush_sectors() {
-    if (!RING_BITS) return;
-    for (;;) {
-      uintptr_t g = (uintptr_t)out + fl; uint32_t room = 32u - ((uint32_t)g & 31u);
-      if (op - fl < room) break;
-      if (room == 32u) {
-        const uint32_t* w = (const uint32_t*)(ring + ridx(g)); uint32_t v[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) v[j] = w[j * LANES];
-#ifdef __CUDA_ARCH__
-        uint4* d = (uint4*)g; d[0] = make_uint4(v[0], v[1], v[2], v[3]); d[1] = make_uint4(v[4], v[5], v[6], v[7]);
-#else
-        for (int j = 0; j < 8; j++) ((uint32_t*)g)[j] = v[j];
-#endif
-      } else { for (uint32_t j = 0; j < room; j++) ((uint8_t*)g)[j] = ring[ridx(g + j)]; }   // head of a block that starts mid-sector
-      fl += room;
-    }
-  }
-  // Plain mode: a 1-byte store that misses in L2 makes L2 fetch the whole 32-byte sector from DRAM first.  Writing
-  // whole sectors of zeros a little ahead of the byte stores creates those sectors in L2 without a fetch, so the byte
-  // stores that follow hit.  Only sectors that lie wholly inside this block's output are touched (the first and last
-  // partial sectors are shared with the neighbouring blocks, i.e. with other lanes).
+  uintptr_t pz;      // output sectors below this address have been pre-written (see prezero)
+  IRF_HD void init(uint8_t* o, uint32_t c) { out = o; op = 0; cap = c; pz = ((uintptr_t)o + 31) & ~(uintptr_t)31; }
+  IRF_HD void emit(uint32_t byte) { out[op] = (uint8_t)byte; op++; }
+  // A 1-byte store that misses in L2 makes L2 fetch the whole 32-byte sector from DRAM first.  Writing whole sectors of zeros a
+  // little ahead of the byte stores creates those sectors in L2 without a fetch, so the byte stores that follow hit.  Only sectors
+  // that lie wholly inside this block's output are touched (the first and last partial sectors are shared with the neighbouring
+  // blocks, i.e. with other lanes).
   IRF_HD void prezero(uint32_t lead) {
-    if (RING_BITS) return;
     uintptr_t want = (uintptr_t)out + op + lead, last = ((uintptr_t)out + cap) & ~(uintptr_t)31;
     if (want > last) want = last;
     while (pz + 32 <= want) {
@@ -139,7 +109,6 @@ struct OutCursor {
       pz += 32;
     }
   }
-  IRF_HD void flush_all() { if (!RING_BITS) return; flush_sectors(); for (; fl < op; fl++) out[fl] = ring_at(fl); }
 };
 
 // Per-lane Huffman set: a BITS-wide LUT plus, for the rare longer codes, the canonical-code limits.
@@ -237,12 +206,11 @@ struct Huff {
 enum LaneState : int { LS_HEADER = 0, LS_SYMBOL = 1, LS_COPY = 2, LS_FINISH = 3, LS_DONE = 4, LS_SLOWLIT = 5, LS_SLOWDIST = 6 };
 
 // DIST8: the distance LUT (and the code-length LUT that borrows its storage) uses byte entries (see Huff).
-template <int LANES, int LIT_BITS, int DIST_BITS, int RING_BITS = 0, int PREZERO = 0, int DIST8 = 0>
+template <int LANES, int LIT_BITS, int DIST_BITS, int PREZERO = 0, int DIST8 = 0>
 struct InflateLane {
   using DistEntry = typename std::conditional<DIST8 != 0, uint8_t, uint16_t>::type;
   static constexpr size_t DIST_LUT_U16 = DIST8 ? (size_t)(1u << DIST_BITS) * LANES / 2 + ((size_t)(1u << DIST_BITS) * LANES & 1) : (size_t)(1u << DIST_BITS) * LANES;   // the distance LUT's size in 16-bit units
-  static constexpr uint32_t NEAR = RING_BITS ? (1u << RING_BITS) - 8u : 0u;   // matches up to this distance are copied inside the ring
-  BitReader br; OutCursor<LANES, RING_BITS> oc; uint32_t tick;
+  BitReader br; OutCursor<LANES> oc; uint32_t tick;
   Huff<LANES, LIT_BITS, 288> hl; Huff<LANES, DIST_BITS, 32, DistEntry> hd;
   int state, status, bfinal; uint32_t copy_len, copy_dist, isize;
   uint32_t pend_n; uint32_t pend[8];  // bytes of a match chunk loaded in the previous step, one register each so nothing has to
@@ -250,15 +218,15 @@ struct InflateLane {
   uint16_t slow_sym;   // long-code symbol fetched from local memory in the previous step
 
   // sym_store: 320 uint16 of lane-private scratch (288 literal/length symbols + 32 distance symbols)
-  IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize_, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store, uint8_t* ring_region = nullptr) {
+  IRF_HD void start(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize_, uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint16_t* sym_store) {
     hl.symbol = sym_store; hd.symbol = sym_store + 288; tick = 0;
-    br.init(cdata, clen); oc.init(out, isize_, ring_region, lane); isize = isize_; if (PREZERO) oc.prezero(256);
+    br.init(cdata, clen); oc.init(out, isize_); isize = isize_; if (PREZERO) oc.prezero(256);
     hl.lut.bind(lit_lut_base, lane); hd.lut.bind((DistEntry*)dist_lut_base, lane);
     // canonical-limit tables sit behind the two LUTs: [lit LUT][dist LUT][lit aux (32)][dist aux (32)], all lane-interleaved
     hd.aux.bind(dist_lut_base + DIST_LUT_U16, lane); hl.aux.bind(dist_lut_base + DIST_LUT_U16 + (size_t)32 * LANES, lane);
     state = LS_HEADER; status = INF_OK; bfinal = 0; copy_len = copy_dist = 0; pend_n = 0; slow_sym = 0;
   }
-  IRF_HD void idle() { state = LS_DONE; status = INF_OK; pend_n = 0; tick = 0; oc.init(nullptr, 0, nullptr, 0); }   // the driver loop keeps stepping idle lanes: their cursor must be inert
+  IRF_HD void idle() { state = LS_DONE; status = INF_OK; pend_n = 0; tick = 0; oc.init(nullptr, 0); }   // the driver loop keeps stepping idle lanes: their cursor must be inert
   IRF_HD bool done() const { return state == LS_DONE; }
   IRF_HD void fail(int code) { status = code; state = LS_DONE; }
 
@@ -271,8 +239,7 @@ struct InflateLane {
       uint32_t len = br.take(16); br.refill(); uint32_t nlen = br.take(16);
       if ((len ^ nlen) != 0xffffu) return fail(INF_ERR_STORED);
       if (oc.op + len > oc.cap) return fail(INF_ERR_OVERRUN_OUT);
-      for (uint32_t i = 0; i < len; i++) { br.refill(); if (PREZERO && (i & 31u) == 0) oc.prezero(64); oc.emit(br.take(8)); if ((i & 31u) == 31u) oc.flush_sectors(); if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); }
-      oc.flush_sectors();
+      for (uint32_t i = 0; i < len; i++) { br.refill(); if (PREZERO && (i & 31u) == 0) oc.prezero(64); oc.emit(br.take(8)); if (br.overrun()) return fail(INF_ERR_OVERRUN_IN); }
       state = bfinal ? LS_FINISH : LS_HEADER; return;
     }
     if (btype == 3) return fail(INF_ERR_BTYPE);
@@ -365,32 +332,16 @@ struct InflateLane {
   // copy_store() at the top of the NEXT step stores them, so the L2 latency of the loads hides behind the other lanes'
   // (and this lane's) decode work instead of stalling the warp.  For dist < 8 the source index wraps inside the period,
   // which makes overlapping (run-length) matches correct without reloading.
-  IRF_HD void copy_store() {   // far match: bytes fetched from global memory in the previous step
-    if (RING_BITS) {
+  IRF_HD void copy_store() {   // bytes fetched from global memory in the previous step
+    uint8_t* dst = oc.out + oc.op;
 #pragma unroll
-      for (int j = 0; j < 8; j++) if ((uint32_t)j < pend_n) oc.emit(pend[j]);
-    } else {
-      uint8_t* dst = oc.out + oc.op;
-#pragma unroll
-      for (int j = 0; j < 8; j++) if ((uint32_t)j < pend_n) dst[j] = (uint8_t)pend[j];
-      oc.op += pend_n;
-    }
+    for (int j = 0; j < 8; j++) if ((uint32_t)j < pend_n) dst[j] = (uint8_t)pend[j];
+    oc.op += pend_n;
     pend_n = 0;
     if (!copy_len) state = LS_SYMBOL;
   }
-  IRF_HD void copy_load() {
+  IRF_HD void copy_load() {   // consumed by copy_store() in the next step
     uint32_t k = copy_len < 8 ? copy_len : 8, w = 0;
-    if (RING_BITS && copy_dist <= NEAR) {   // near match: source and destination are both in the ring, done within this step
-      uint8_t t[8]; uint32_t from = oc.op - copy_dist;
-#pragma unroll
-      for (int j = 0; j < 8; j++) { if ((uint32_t)j < k) t[j] = oc.ring_at(from + w); w++; if (w == copy_dist) w = 0; }
-#pragma unroll
-      for (int j = 0; j < 8; j++) if ((uint32_t)j < k) oc.emit(t[j]);
-      copy_len -= k;
-      if (!copy_len) state = LS_SYMBOL;
-      return;
-    }
-    // far match: the source was flushed to global memory long ago (the flush lag is below NEAR); consumed by copy_store()
     const uint8_t* src = oc.out + oc.op - copy_dist;
 #pragma unroll
     for (int j = 0; j < 8; j++) {
@@ -409,18 +360,18 @@ struct InflateLane {
     if (state == LS_HEADER && allow_header) header();
     if (state == LS_SYMBOL) symbol();
     if (state == LS_COPY) copy_load();
-    if (state == LS_FINISH) { oc.flush_all(); status = oc.op == isize ? INF_OK : INF_ERR_ISIZE; state = LS_DONE; }
-    if ((++tick & 7u) == 0) { if (RING_BITS) oc.flush_sectors(); else if (PREZERO) oc.prezero(256); }   // every lane, every 8th step (ring: keeps the unflushed tail below NEAR bytes)
+    if (state == LS_FINISH) { status = oc.op == isize ? INF_OK : INF_ERR_ISIZE; state = LS_DONE; }
+    if (PREZERO && (++tick & 7u) == 0) oc.prezero(256);   // every lane, every 8th step
   }
 };
 
 // Decodes one raw DEFLATE stream of `clen` bytes at `cdata` into exactly `isize` bytes at `out` (scalar driver,
 // used by the host emulation in tests/emu).  Both buffers need 8 readable bytes of slack after their ends.
-template <int LANES, int LIT_BITS, int DIST_BITS, int RING_BITS = 0, int PREZERO = 0, int DIST8 = 0>
+template <int LANES, int LIT_BITS, int DIST_BITS, int PREZERO = 0, int DIST8 = 0>
 IRF_HD int inflate_block(const uint8_t* cdata, uint32_t clen, uint8_t* out, uint32_t isize,
-                         uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane, uint8_t* ring_region = nullptr) {
-  InflateLane<LANES, LIT_BITS, DIST_BITS, RING_BITS, PREZERO, DIST8> L; uint16_t sym_store[320];
-  L.start(cdata, clen, out, isize, lit_lut_base, dist_lut_base, lane, sym_store, ring_region);
+                         uint16_t* lit_lut_base, uint16_t* dist_lut_base, int lane) {
+  InflateLane<LANES, LIT_BITS, DIST_BITS, PREZERO, DIST8> L; uint16_t sym_store[320];
+  L.start(cdata, clen, out, isize, lit_lut_base, dist_lut_base, lane, sym_store);
   while (!L.done()) L.step();
   return L.status;
 }

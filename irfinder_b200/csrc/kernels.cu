@@ -1,8 +1,9 @@
 // kernels.cu — sm_100a kernels of the BAM -> intron-retention counting path.
 //
-// Stage map:  S1 inflate_kernel  ->  S2 frame_guess / walk_count / frame_mark+rewalk (record
-// framing)  ->  S3 walk_process_kernel (record decode, CIGAR -> blocks, mate pairing by device hash,
-// FragmentBlocks formation and every ReadBlockProcessor's ProcessBlocks)  ->  S4 scan + intron_stats_kernel.
+// Stage map:  S1 inflate (inflate_tok.cu: the default two-phase kernel; inflate_kernel below: the one-phase variants 0-11) and
+// crc_check_kernel  ->  S2 frame_guess / walk_count / frame_mismatch+mark / gather_records (record framing)  ->  S3 pair_records_kernel (skip /
+// single / pair decision, mate pairing by device hash), process_pairs / process_singles (CIGAR -> blocks, FragmentBlocks formation and every
+// ReadBlockProcessor's ProcessBlocks)  ->  S4 depth scan + intron_stats kernels; plus the table maintenance of the multi-GPU merge.
 // Each device function that restates a reference routine names it (upstream file per SURVEY.md §8a; the
 // mounted /root/reference has no source to cite by line).
 #include <algorithm>
@@ -46,19 +47,18 @@ __device__ __forceinline__ void load_core(const uint8_t* U, u64 off, Core& c) {
 // S1: BGZF / DEFLATE inflate, one lane per BGZF block.  Persistent CTAs: every warp claims the next 32 blocks from a
 // global counter until none are left, so a launch has one short tail instead of one per wave.
 // D8: byte entries in the distance LUT (1 KB less shared memory per warp); MINB: CTAs per SM the register allocation must allow.
-template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM, int RB, int PZ, int D8 = 0, int MINB = 0>
+template <int WARPS, int LB, int DB, int HEADER_BATCH, int LANE_CLAIM, int PZ, int D8 = 0, int MINB = 0>
 __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                              uint8_t* __restrict__ U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                              int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark,
                                                              const u32* __restrict__ list) {   // list: optional indices of the blocks this kernel owns (the rest go to the decompression engine)
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // per warp: [lit LUT][dist LUT][2 x 32 canonical-limit entries] (16-bit, lane-interleaved) [output ring: 2^RB bytes per lane]
+  // per warp: [lit LUT][dist LUT][2 x 32 canonical-limit entries] (16-bit, lane-interleaved)
   constexpr size_t DIST_U16 = D8 ? (1 << DB) * 16 : (1 << DB) * 32;
-  constexpr size_t WARP_U16 = (size_t)((1 << LB) + 64) * 32 + DIST_U16 + (RB ? ((1 << RB) * 32) / 2 : 0);
+  constexpr size_t WARP_U16 = (size_t)((1 << LB) + 64) * 32 + DIST_U16;
   uint16_t* lit = smem_tables + (size_t)warp * WARP_U16;
   uint16_t* dst = lit + (1 << LB) * 32;
-  uint8_t* ring = RB ? (uint8_t*)(lit + (size_t)((1 << LB) + 64) * 32 + DIST_U16) : nullptr;
   uint16_t sym_store[320];
   if (!LANE_CLAIM) {   // warp-granular claims: 32 consecutive blocks per warp, all lanes start together
     for (;;) {
@@ -81,15 +81,15 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_kernel(const uint8_t
         if (starved) { if (lane == 0) atomicOr(err, DERR_STARVED); break; }
       }
       int b = (int)base + lane; const bool in_range = b < nblk; if (list && in_range) b = (int)list[b];
-      InflateLane<32, LB, DB, RB, PZ, D8> L;
+      InflateLane<32, LB, DB, PZ, D8> L;
       bool work = in_range && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
-      if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, ring); else L.idle();
+      if (work) L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); else L.idle();
       while (__any_sync(0xffffffffu, !L.done())) L.step();   // the vote keeps the warp converged (see InflateLane)
       if (work && L.status) { status[b] = L.status; atomicOr(err, DERR_INFLATE); }
     }
     return;
   }
-  InflateLane<32, LB, DB, RB, PZ, D8> L; L.idle();
+  InflateLane<32, LB, DB, PZ, D8> L; L.idle();
   int b = -1; bool exhausted = false;
   // HEADER_BATCH: lanes that must be waiting for a block header before the warp pays for one
   for (;;) {
@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_kernel(const uint8_t
       base = __shfl_sync(0xffffffffu, base, leader);
       if (need) {
         unsigned int nb = base + (unsigned int)__popc(m & ((1u << lane) - 1u));
-        if (nb < (unsigned int)nblk) { b = (int)nb; if (u_len[b] == 0 && c_len[b] <= 2) L.idle(); else L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store, ring); }
+        if (nb < (unsigned int)nblk) { b = (int)nb; if (u_len[b] == 0 && c_len[b] <= 2) L.idle(); else L.start(comp + c_off[b], c_len[b], U + u_off[b], u_len[b], lit, dst, lane, sym_store); }
         else { b = -1; exhausted = true; }
       }
     }
@@ -121,16 +121,16 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_kernel(const uint8_t
 static int g_inflate_lanes = 0, g_inflate_cta_cap = 0;
 void set_inflate_cta_cap(int ctas_per_sm) { g_inflate_cta_cap = ctas_per_sm; }   // 0 = as many CTAs per SM as fit
 int inflate_resident_lanes() { return g_inflate_lanes; }   // lanes (= BGZF blocks in flight) of the last inflate launch's full grid; 0 before the first launch
-template <int WARPS, int LB, int DB, int HB = 1, int LC = 0, int RB = 0, int PZ = 0, int D8 = 0, int MINB = 0>
+template <int WARPS, int LB, int DB, int HB = 1, int LC = 0, int PZ = 0, int D8 = 0, int MINB = 0>
 static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
-  size_t smem = (size_t)WARPS * (((size_t)((1 << LB) + 64) * 32 + (D8 ? (1 << DB) * 16 : (1 << DB) * 32)) * sizeof(uint16_t) + (RB ? (size_t)(1 << RB) * 32 : 0));
+  size_t smem = (size_t)WARPS * (((size_t)((1 << LB) + 64) * 32 + (D8 ? (1 << DB) * 16 : (1 << DB) * 32)) * sizeof(uint16_t));
   // the shared-memory opt-in and the occupancy are per device: one cache slot per device ordinal
   static int ctas_cache[64] = {0}, sms_cache[64] = {0};
   int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");
   int& ctas_per_sm = ctas_cache[dev]; int& sms = sms_cache[dev];
   if (!ctas_per_sm) {
-    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB>, WARPS * 32, smem));
+    IRF_CUDA(cudaFuncSetAttribute(inflate_kernel<WARPS, LB, DB, HB, LC, PZ, D8, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, inflate_kernel<WARPS, LB, DB, HB, LC, PZ, D8, MINB>, WARPS * 32, smem));
     IRF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (ctas_per_sm < 1) ctas_per_sm = 1;
   }
@@ -139,25 +139,21 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
   int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, sms * per_sm);   // 148 SMs x resident CTAs
   if (grid > 0) {
     IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-    inflate_kernel<WARPS, LB, DB, HB, LC, RB, PZ, D8, MINB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();
+    inflate_kernel<WARPS, LB, DB, HB, LC, PZ, D8, MINB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();
   }
 }
 size_t inflate_scratch_bytes(int variant, int nblk) { return variant >= 12 && variant <= 15 && nblk > 0 ? inflate_tok_scratch_bytes(variant, nblk) : 0; }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
-  // The shared-memory output-ring variants (1, 6, 9: RB > 0) are not offered any more: their sector flush raised a misaligned-address
-  // fault for some output alignments (seen once the test suite ran them after other tests), and they measured slower anyway.
-  if (variant == 1 || variant == 6 || variant == 9) throw std::string("inflate_variant ") + std::to_string(variant) + " (shared-memory output ring) is disabled: its sector flush faults on some output alignments";
-  if (variant >= 12 && variant <= 15) { launch_inflate_tok(a, variant, s); g_inflate_lanes = inflate_tok_lanes(variant); return; }   // two-phase kernel: token decode per lane, then warp-wide match resolve (inflate_tok.cu)
-  switch (variant) {   // <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, output ring bits>
-    case 2: launch_inflate_t<4, 6, 5, 1, 0, 0, 1>(a, s); break;   // pre-written output sectors
-    case 3: launch_inflate_t<4, 6, 6, 1, 0, 0, 1>(a, s); break;
+  switch (variant) {   // one-phase kernel: <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, pre-written sectors, byte distance LUT, CTAs per SM>
+    case 2: launch_inflate_t<4, 6, 5, 1, 0, 1>(a, s); break;   // pre-written output sectors
+    case 3: launch_inflate_t<4, 6, 6, 1, 0, 1>(a, s); break;
     case 4: launch_inflate_t<4, 6, 6, 1, 0, 0>(a, s); break;
-    case 5: launch_inflate_t<4, 7, 6, 1, 0, 0, 1>(a, s); break;
+    case 5: launch_inflate_t<4, 7, 6, 1, 0, 1>(a, s); break;
     case 7: launch_inflate_t<4, 7, 6, 1, 0, 0>(a, s); break;
     case 8: launch_inflate_t<4, 6, 5, 4, 1, 0>(a, s); break;    // lane-granular claims + header batching (measured slower, kept for A/B)
-    case 10: launch_inflate_t<4, 6, 5, 1, 0, 0, 0, 1, 6>(a, s); break;   // byte distance LUT: 36 KB per CTA and <= 80 registers, six CTAs per SM (NOT YET MEASURED)
-    case 11: launch_inflate_t<4, 6, 5, 1, 0, 0, 0, 1, 0>(a, s); break;   // byte distance LUT only (five CTAs; isolates the table change from the occupancy change)
-    default: launch_inflate_t<4, 6, 5, 1, 0, 0>(a, s); break;
+    case 10: launch_inflate_t<4, 6, 5, 1, 0, 0, 1, 6>(a, s); break;   // byte distance LUT: 36 KB per CTA and <= 80 registers, six CTAs per SM
+    case 11: launch_inflate_t<4, 6, 5, 1, 0, 0, 1, 0>(a, s); break;   // byte distance LUT only (five CTAs; isolates the table change from the occupancy change)
+    default: launch_inflate_t<4, 6, 5, 1, 0, 0>(a, s); break;   // variants 0, 1, 6, 9 (the last three were the removed output-ring versions)
   }
 }
 

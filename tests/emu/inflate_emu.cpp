@@ -9,9 +9,8 @@
 #include "../../irfinder_b200/csrc/inflate_core.cuh"
 #include "../../irfinder_b200/csrc/inflate_tok.cuh"
 
-template <int LB, int DB, int RB = 0, int PZ = 0, int D8 = 0>
+template <int LB, int DB, int PZ = 0, int D8 = 0>
 static int run(const std::vector<uint8_t>& f) {
-  std::vector<uint32_t> ringw((1 << (RB ? RB : 2)) / 4 + 4); uint8_t* ring = RB ? (uint8_t*)ringw.data() : nullptr;
   std::vector<uint16_t> lit(1 << LB), dist((1 << DB) + 64);  // dist LUT + the two 32-entry aux tables behind it
   size_t off = 0; long nblk = 0, bad = 0; std::vector<uint8_t> a(65536 + 64), b(65536 + 64);
   while (off + 18 <= f.size()) {
@@ -19,7 +18,7 @@ static int run(const std::vector<uint8_t>& f) {
     if (h[0] != 31 || h[1] != 139 || h[12] != 'B' || h[13] != 'C') { fprintf(stderr, "bad BGZF header at %zu\n", off); return 2; }
     uint32_t bsize = (h[16] | h[17] << 8) + 1u, clen = bsize - 26, isize; memcpy(&isize, &f[off + bsize - 4], 4);
     std::fill(a.begin(), a.end(), 0xAA);
-    int st = irf::inflate_block<1, LB, DB, RB, PZ, D8>(&f[off + 18], clen, a.data() + (nblk % 37), isize, lit.data(), dist.data(), 0, ring);  // vary output alignment
+    int st = irf::inflate_block<1, LB, DB, PZ, D8>(&f[off + 18], clen, a.data() + (nblk % 37), isize, lit.data(), dist.data(), 0);  // vary output alignment
     z_stream zs; memset(&zs, 0, sizeof zs); inflateInit2(&zs, -15); zs.next_in = (Bytef*)&f[off + 18]; zs.avail_in = clen; zs.next_out = b.data(); zs.avail_out = 65536;
     int zr = inflate(&zs, Z_FINISH); inflateEnd(&zs);
     if (st != 0 || zr != Z_STREAM_END || zs.total_out != isize || memcmp(a.data() + (nblk % 37), b.data(), isize) != 0 || a[(nblk % 37) + isize] != 0xAA || (nblk % 37 && a[(nblk % 37) - 1] != 0xAA)) {
@@ -56,6 +55,6 @@ int main(int argc, char** argv) {
   int v = argc > 2 ? atoi(argv[2]) : 9;
   if (v == 406) return run_tok<6, 5>(f); if (v == 407) return run_tok<7, 5>(f); if (v == 408) return run_tok<8, 6>(f); if (v == 409) return run_tok<9, 6>(f);
   if (v == 8) return run<8, 6>(f); if (v == 10) return run<10, 7>(f); if (v == 7) return run<7, 5>(f); if (v == 6) return run<6, 5>(f);
-  if (v == 306) return run<6, 5, 0, 0, 1>(f); if (v == 307) return run<7, 7, 0, 0, 1>(f);   // byte entries in the distance / code-length LUT
-  if (v == 206) return run<6, 5, 0, 1>(f); if (v == 108) return run<6, 5, 8>(f); if (v == 109) return run<7, 6, 9>(f); return run<9, 6>(f);
+  if (v == 306) return run<6, 5, 0, 1>(f); if (v == 307) return run<7, 7, 0, 1>(f);   // byte entries in the distance / code-length LUT
+  if (v == 206) return run<6, 5, 1>(f); return run<9, 6>(f);
 }
