@@ -61,6 +61,8 @@ const char* irf_last_error(irf_ctx* ctx);
  * NOTE: the engine answers malformed DEFLATE data with a sticky CUDA error (the process must restart), the SM kernel with IRF_EFORMAT.
  * "junc_capacity_log2" (default 24), "require_eof" (default 1), "verify_crc" (default 1: check every block's CRC-32 as gzip does), "stage_lazy" (default 0; 1 = irf_stage only records the host
  * buffer and irf_count streams it to the GPU beside the inflate kernel: the buffer must then stay valid until irf_count returns).
+ * "depth_tile" (default 0): 1 / 2 = CoverageBlocks counters of a CTA are summed in a shared-memory tile and flushed with red.global / by one TMA
+ * bulk reduce per strand (measured slower than the plain global atomics of 0 on the benchmark shapes; kept selectable).
  * "stream_segment_mb" (default 1024): irf_run_stream reads its pipe in segments of this size (two page-locked buffers of it).
  * "rule_*": the behaviours SURVEY.md Appendix C marks as uncertain, as run-time settings (defaults = DESIGN.md section 1): rule_junc_min_flank (5),
  * rule_span_left (5), rule_span_right (4), rule_skip_flags (0; e.g. 0x900 skips secondary and supplementary records), rule_pct_tie_midpoint (1),

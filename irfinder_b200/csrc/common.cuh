@@ -23,6 +23,7 @@ struct Rules {
   double warn_lowcover = 10, warn_lowsplice = 4, warn_minor_ratio = 0.33333, warn_nonuniform_abs = 4, warn_nonuniform_ratio = 1.5;   // [C-14]
 };
 constexpr int BUCKET_SHIFT = 10;
+constexpr int DEPTH_TILE = 2048;            // counters per strand in a CTA's shared-memory depth tile (a 2048-aligned window of the [2][P] difference table)
 constexpr u32 REC_SLOTS = 65536 / 36 + 2;   // records that can START inside one BGZF block (a record has at least 36 bytes)
 
 // ---- junction key: 36-bit concatenated-genome coordinate of the left end, 28-bit gap (CIGAR op lengths are 28-bit)
@@ -69,6 +70,8 @@ struct DevTables {
   // optional fragment dump (tests): words appended at dump[atomicAdd(dump_cursor, n)]
   u32* dump; u64* dump_cursor; u64 dump_cap;
   Rules rules;
+  int depth_tile;           // CoverageBlocks counters of a CTA's fragments are first summed in a shared-memory tile: 0 = off (global atomics), 1 = tile flushed with
+                            // one red.global per non-zero counter, 2 = tile flushed by one TMA bulk reduce per strand (cp.reduce.async.bulk ... add.s32)
 };
 
 // One row of IRFinder-IR-*.txt in numeric form; text formatting happens on the host.

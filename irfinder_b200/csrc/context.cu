@@ -1127,6 +1127,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
     else { c->err = "unknown option " + k; return IRF_EINVAL; }
     c->bound = false;   // the device tables carry the rules (and the edge windows are cut on the host): bind again
   }
+  else if (k == "depth_tile") { if (v < 0 || v > 2) return IRF_EINVAL; c->T.depth_tile = (int)v; }
   else if (k == "stream_segment_mb") { if (v < 1 || v > 65536) return IRF_EINVAL; c->stream_segment_bytes = (size_t)v << 20; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
   else if (k == "inflate_ctas") { if (v < 0 || v > 32) return IRF_EINVAL; set_inflate_cta_cap((int)v); }   // process-wide, for A/B measurements

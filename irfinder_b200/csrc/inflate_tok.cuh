@@ -1,15 +1,14 @@
-// inflate_tok.cuh — two-phase DEFLATE for BGZF blocks: a lane decodes the Huffman stream of one block into literal bytes
-// (stored at their final place) and a list of LZ77 match tokens; afterwards the whole warp fills in the matches of each of
-// its 32 blocks (kernels.cu, inflate_tok_kernel).  Replaces `gzip -cd` of the reference's pipeline;
-// format authority RFC 1951.
+// inflate_tok.cuh — two-phase DEFLATE for BGZF blocks: a lane decodes the Huffman stream of one block into a literal stream and a
+// list of LZ77 match tokens (phase A); afterwards the whole warp writes the output of each of its 32 blocks, literals and matches
+// (phase B, inflate_tok.cu).  Replaces `gzip -cd` of the reference's pipeline; format authority RFC 1951.
 //
 // Why two phases (measured on the one-phase kernel of round 1, profiles/README.md): with the LZ77 copies inside the decode
 // loop a warp's lanes sat in different states (table build / symbol / copy) and only ~11 of 32 were active per instruction; each
 // copy was a dependent load from a 64 KiB-per-lane working set that missed L2 (13.6 DRAM bytes per algorithmic byte); every
 // output byte was one store instruction.  Here the decode loop does ONE thing per iteration in every lane — one literal/length
 // symbol (plus its distance symbol) — so lanes stay converged and, because zlib closes a DEFLATE block after a fixed number of
-// symbols, reach their next table build in nearly the same iteration; literals leave as aligned 32-bit words; matches become
-// 4-byte tokens that the warp resolves later with all 32 lanes working on ONE block (64 KiB working set per warp, not per lane).
+// symbols, reach their next table build in nearly the same iteration; matches become 4-byte tokens that the warp resolves later
+// with all 32 lanes working on ONE block (64 KiB working set per warp, not per lane).
 //
 // Token (32 bits):  lit_len << 24 | match_len << 15 | (dist - 1)
 //   lit_len   0..255  literal bytes that precede the match (taken from the literal stream in order)

@@ -423,7 +423,8 @@ __device__ void cigar_scan(const uint8_t* cig, u32 n, int& genome_len, int& firs
 struct FragSink {
   const DevTables& T; int chr, dir; u32 read_start; bool have_prev; u32 prev_end; int prev_len; u64 nuc;
   u32* dump_base; u32 dump_n, dump_nb[2]; int dump_read;
-  __device__ FragSink(const DevTables& t) : T(t), nuc(0), dump_base(nullptr) {}
+  int32_t* tile; unsigned long long* tile_base;   // the CTA's shared-memory depth tile ([2][DEPTH_TILE]) and the table index each strand's window starts at; null = no tile
+  __device__ FragSink(const DevTables& t) : T(t), nuc(0), dump_base(nullptr), tile(nullptr), tile_base(nullptr) {}
   __device__ void begin_fragment(int chr_, int dir_, u32 reserve_blocks) {
     chr = chr_; dir = dir_; dump_base = nullptr;
     if (T.dump) {
@@ -464,8 +465,20 @@ struct FragSink {
     for (; lo < r.end; lo++) {
       u32 ss = T.seg_start[lo]; if (ss >= end) break;
       u32 a = max(start, ss), b = min(end, T.seg_end[lo]);
-      if (a < b) { int32_t* d = T.diff + (u64)dir * T.P + T.seg_coff[lo]; atomicAdd(d + (a - ss), 1); atomicAdd(d + (b - ss), -1); }
+      if (a < b) { const u64 g = (u64)dir * T.P + T.seg_coff[lo]; depth_add(g + (a - ss), 1); depth_add(g + (b - ss), -1); }
     }
+  }
+  // One +1 / -1 of the difference table (index g into the [2][P] table).  With a tile, the first counter a CTA touches on a strand fixes that
+  // strand's window (the 2048-aligned block of the table around it: the input is coordinate-sorted, so the CTA's other fragments land in or
+  // next to it); counters inside the window are summed in shared memory and reach the table once, in the flush at the end of the kernel,
+  // counters outside go to the table directly.
+  __device__ __forceinline__ void depth_add(u64 g, int v) {
+    if (tile) {
+      const u64 G = g & ~(u64)(DEPTH_TILE - 1); unsigned long long cur = tile_base[dir];
+      if (cur == ~0ull) { const unsigned long long old = atomicCAS(&tile_base[dir], ~0ull, (unsigned long long)G); cur = old == ~0ull ? G : old; }
+      if (cur == G) { atomicAdd(&tile[dir * DEPTH_TILE + (int)(g & (DEPTH_TILE - 1))], v); return; }
+    }
+    atomicAdd(T.diff + g, v);
   }
   __device__ __noinline__ void block(int s, int l) {   // one body shared by every call site: the fully inlined version thrashed the instruction cache
     u32 a = read_start + (u32)s, e = a + (u32)l;
@@ -637,24 +650,70 @@ __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const ui
   warp_add_stat(&T.stats[ST_SKIPPED], skipped); warp_add_stat(&T.stats[ST_CAND], cand);
   if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
 }
-__global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs, const u64* __restrict__ npairs_dev) {
-  if (npairs_dev) npairs = min(npairs, *npairs_dev);   // the grid was sized from an upper bound; the pairing kernel left the actual count on the device
-  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  if ((u64)blockIdx.x * blockDim.x >= npairs) return;
-  FragSink sink(T); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
-  if (i < npairs) {
-    u64 o1 = pair_list[2 * i], o2 = pair_list[2 * i + 1]; Core c1, c2; load_core(U, o1, c1); load_core(U, o2, c2);
-    st.paired = 1; process_pair(T, U, o1, c1, o2, c2, sink, st);
+// Shared-memory depth tile of a counting CTA (DevTables::depth_tile): zeroed at the start, flushed at the end - with one red.global per non-zero
+// counter, or by the TMA unit (one bulk reduce per strand: the "TMA-staged spill" of the difference array).
+struct DepthTile {
+  int32_t* tile; unsigned long long* base;
+  __device__ void begin(const DevTables& T, int32_t* sh_tile, unsigned long long* sh_base) {
+    tile = T.depth_tile ? sh_tile : nullptr; base = sh_base;
+    if (!tile) return;
+    for (int i = threadIdx.x; i < 2 * DEPTH_TILE; i += blockDim.x) tile[i] = 0;
+    if (threadIdx.x < 2) base[threadIdx.x] = ~0ull;
+    __syncthreads();
   }
+  __device__ void attach(FragSink& s) const { s.tile = tile; s.tile_base = base; }
+  __device__ void flush(const DevTables& T) {
+    if (!tile) return;
+    __syncthreads();
+    if (T.depth_tile == 2) {
+      if (threadIdx.x == 0) {
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tile was written through the generic proxy; the bulk reduce reads it through the async proxy
+        for (int d = 0; d < 2; d++) {
+          const unsigned long long G = base[d]; if (G == ~0ull) continue;
+          const u64 left = 2 * T.P - G; const uint32_t bytes = (uint32_t)(((left < (u64)DEPTH_TILE ? left : (u64)DEPTH_TILE) * 4 + 15) & ~15ull);   // the table has 256 bytes of slack behind it
+          const uint32_t src = (uint32_t)__cvta_generic_to_shared(tile + d * DEPTH_TILE);
+          asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.s32 [%0], [%1], %2;" :: "l"(T.diff + G), "r"(src), "r"(bytes) : "memory");
+        }
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the shared memory may go once the TMA unit has read it
+      }
+    } else {
+      for (int d = 0; d < 2; d++) {
+        const unsigned long long G = base[d]; if (G == ~0ull) continue;
+        for (int i = threadIdx.x; i < DEPTH_TILE; i += blockDim.x) { const int v = tile[d * DEPTH_TILE + i]; if (v) atomicAdd(T.diff + G + i, v); }
+      }
+    }
+  }
+};
+// fr: fragments per thread (a CTA with a depth tile takes several consecutive 128-fragment slices so that zeroing and flushing the tile pay off)
+__global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs, const u64* __restrict__ npairs_dev, int fr) {
+  __shared__ __align__(16) int32_t sh_tile[2 * DEPTH_TILE]; __shared__ unsigned long long sh_base[2];
+  if (npairs_dev) npairs = min(npairs, *npairs_dev);   // the grid was sized from an upper bound; the pairing kernel left the actual count on the device
+  if ((u64)blockIdx.x * fr * blockDim.x >= npairs) return;
+  DepthTile dt; dt.begin(T, sh_tile, sh_base);
+  FragSink sink(T); dt.attach(sink); LocalStats st = {0, 0, 0, 0, 0, 0, 0};
+  for (int k = 0; k < fr; k++) {
+    const u64 i = ((u64)blockIdx.x * fr + k) * blockDim.x + threadIdx.x;
+    if (i < npairs) {
+      u64 o1 = pair_list[2 * i], o2 = pair_list[2 * i + 1]; Core c1, c2; load_core(U, o1, c1); load_core(U, o2, c2);
+      st.paired++; process_pair(T, U, o1, c1, o2, c2, sink, st);
+    }
+  }
+  dt.flush(T);
   warp_add_stat(&T.stats[ST_PAIRED], st.paired); warp_add_stat(&T.stats[ST_SHORT], st.shortp); warp_add_stat(&T.stats[ST_INTERSECT], st.inter);
   warp_add_stat(&T.stats[ST_LONG], st.longp); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
 }
-__global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ single_list, u64 nsingles, const u64* __restrict__ nsingles_dev) {
+__global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ single_list, u64 nsingles, const u64* __restrict__ nsingles_dev, int fr) {
+  __shared__ __align__(16) int32_t sh_tile[2 * DEPTH_TILE]; __shared__ unsigned long long sh_base[2];
   if (nsingles_dev) nsingles = min(nsingles, *nsingles_dev);
-  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  if ((u64)blockIdx.x * blockDim.x >= nsingles) return;
-  FragSink sink(T); u32 n = 0;
-  if (i < nsingles) { u64 e = single_list[i]; Core c; load_core(U, e, c); n = 1; process_single(T, U, e, c, sink); }
+  if ((u64)blockIdx.x * fr * blockDim.x >= nsingles) return;
+  DepthTile dt; dt.begin(T, sh_tile, sh_base);
+  FragSink sink(T); dt.attach(sink); u32 n = 0;
+  for (int k = 0; k < fr; k++) {
+    const u64 i = ((u64)blockIdx.x * fr + k) * blockDim.x + threadIdx.x;
+    if (i < nsingles) { u64 e = single_list[i]; Core c; load_core(U, e, c); n++; process_single(T, U, e, c, sink); }
+  }
+  dt.flush(T);
   warp_add_stat(&T.stats[ST_SINGLE], n); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
 }
 void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s, u64 carry_base, int count_stats) {
@@ -664,12 +723,12 @@ void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_of
 __global__ void shift_offsets_kernel(u64* off, u64 n, u64 delta) { u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i < n) off[i] += delta; }
 void launch_shift_offsets(u64* off, u64 n, u64 delta, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { shift_offsets_kernel<<<(unsigned)g, 256, 0, s>>>(off, n, delta); IRF_LAUNCHED(); } }
 void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s, const u64* npairs_dev) {
-  u64 grid = (npairs + 127) / 128;   // npairs_dev given: npairs is an upper bound and the kernel reads the count itself
-  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs, npairs_dev); IRF_LAUNCHED(); }
+  const int fr = T.depth_tile ? 4 : 1; u64 grid = (npairs + 128ull * fr - 1) / (128ull * fr);   // npairs_dev given: npairs is an upper bound and the kernel reads the count itself
+  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs, npairs_dev, fr); IRF_LAUNCHED(); }
 }
 void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s, const u64* nsingles_dev) {
-  u64 grid = (nsingles + 127) / 128;
-  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, single_list, nsingles, nsingles_dev); IRF_LAUNCHED(); }
+  const int fr = T.depth_tile ? 4 : 1; u64 grid = (nsingles + 128ull * fr - 1) / (128ull * fr);
+  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, single_list, nsingles, nsingles_dev, fr); IRF_LAUNCHED(); }
 }
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s) {
   int grid = (a.nblk + 127) / 128;

@@ -348,6 +348,25 @@ def test_appendix_c_rules_are_run_time_settings_on_both_sides(built, tiny, tmp_p
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "d"))
 
 
+@pytest.mark.parametrize("mode", [1, 2])
+def test_depth_tile_modes_are_bit_exact(built, tiny, tmp_path, mode):
+    """CoverageBlocks counters summed in a shared-memory tile per CTA before they reach the difference table (option depth_tile: 1 = tile
+    flushed with one red per non-zero counter, 2 = flushed by the TMA unit, cp.reduce.async.bulk add.s32): the per-base depth must be
+    bit-identical to the oracle's on a paired and on a dense single-end workload, through the staged path and the chunk pipeline."""
+    c = _core(depth_tile=mode)
+    c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    for bam in (tiny["sorted"], tiny["collated"]):
+        c.run_bam(bam)
+        assert np.array_equal(c.table("depth"), np.fromfile(tiny["oracle_depth"], dtype="<i4"))
+    c.write_outputs(str(tmp_path / "g"))
+    assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
+    meta = _gen(tmp_path, "se", genome="tiny", introns=200, pairs=60000, readlen=75, seed=14, single=True, intronic=0.4, hot_introns=50, chunks=3)
+    run_oracle(built, meta, str(tmp_path / "o2"), depth=str(tmp_path / "d2.i32"))
+    c2 = _gpu_run(meta, str(tmp_path / "g2"), depth_tile=mode, stream_chunk_kb=256)
+    assert_same_outputs(str(tmp_path / "o2"), str(tmp_path / "g2"))
+    assert np.array_equal(c2.table("depth"), np.fromfile(str(tmp_path / "d2.i32"), dtype="<i4"))
+
+
 def test_micro_fixture_by_hand_on_gpu(tmp_path):
     """The hand-derived fixture of tests/micro_fixture.py (every cell computed by hand) through the CUDA path,
     in both record orders; BGZF blocks of 700-900 bytes make nearly every record straddle a block boundary."""
