@@ -34,7 +34,7 @@ enum {
   IRF_T_ROWS_DIR = 7,     /* same for IRFinder-IR-dir.txt; n = 0 when the library is unstranded */
   IRF_T_FRAGMENTS = 8,    /* uint32 words of the FragmentBlocks dump (option dump_fragments=1): per fragment
                              [n_words, chr, dir, readCount, nblk0, nblk1, (start,end)*] */
-  IRF_T_TIMING = 9,       /* double[12] of the last run: ms h2d+inflate, ms inflate kernels, ms framing, ms counting, ms finalize, ms count total, ms host BGZF scan, ms output formatting, kernels launched since irf_reset, inflate launches, ms of the inflate_kernel launch alone, share of the algorithmic bytes it inflated */
+  IRF_T_TIMING = 9,       /* double[13] of the last run: ms h2d+inflate, ms inflate kernels, ms framing, ms counting, ms finalize, ms count total, ms host BGZF scan, ms output formatting, kernels launched since irf_reset, inflate launches, ms of the SM inflate launch(es) alone, share of the algorithmic bytes they inflated, launches of the two-phase inflate kernel by this process so far */
   IRF_T_DIFF = 10         /* device only: int32[2][P] difference counters before irf_finalize */
 };
 

@@ -99,7 +99,7 @@ struct irf_ctx {
   void* pinned = nullptr; size_t pinned_cap = 0;
   // results
   vector<u64> h_stats; vector<u32> h_sp, h_roi, h_chr, h_dump; vector<JuncEntry> h_junc; vector<IntronRow> rows_nondir, rows_dir; vector<int32_t> h_depth;
-  int directionality = 0; string stdout_text, dir_log; double timing[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
+  int directionality = 0; string stdout_text, dir_log; double timing[13] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
   bool counted = false, finalized = false;
   string err;
 
@@ -1180,7 +1180,7 @@ int irf_directionality(irf_ctx* c) { return c ? c->directionality : 0; }
 int irf_get_table(irf_ctx* c, int which, const void** p, size_t* n) {
   if (!c || !p || !n) return IRF_EINVAL;
   IRF_TRY(c, {
-    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; *p = c->timing; *n = 12; }
+    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; c->timing[12] = (double)tok_launch_counter(); *p = c->timing; *n = 13; }
     else {
       if (!c->finalized) throw string("no finished run to read tables from");
       switch (which) {

@@ -31,14 +31,14 @@ __device__ unsigned long long g_tok_prof[8];
 // match of the batch overlaps its source bytes.  Holes are ordered like the tokens, so the matches that can overlap lane i's
 // source [src, need) form a range of lanes [lo, hi) found by two binary searches over the warp (shuffles); a round then costs one
 // ballot and one AND per lane, and the number of rounds is the depth of the dependency chains, not the number of dependent matches.
-// tok_long (kernel argument, default 16; IRF_TOK_LONG for experiments): matches longer than this are copied by the whole warp
+constexpr uint32_t TOK_LONG = 16;   // matches longer than this are copied by the whole warp (4 / 8 / 16 / 32 / 64 measured: 184 / 143 / 131 / 132 / 136 ms)
 constexpr uint32_t LIT_LONG = 4;    // literal runs longer than this are placed by the whole warp
 // lstart / lit / lq: output offset, length and literal-stream offset of the literal run in front of lane i's match; lits: the block's
 // literal stream (word j at lits[-j], bytes in little-endian order)
 __device__ __forceinline__ uint8_t lit_byte(const uint32_t* lits, uint32_t q) { return (uint8_t)(lits[-(int)(q >> 2)] >> (8 * (q & 3))); }
 // lwin / wq: the 32 words of the literal stream from word wq on, one per lane, loaded a batch ahead (the short runs of a batch are
 // served from this window by shuffles instead of dependent loads from the scratch region)
-__device__ __forceinline__ void resolve_batch(uint8_t* ob, const uint32_t* lits, uint32_t lwin, uint32_t wq, uint32_t lstart, uint32_t lit, uint32_t lq, uint32_t mstart, uint32_t ml, uint32_t d, int lane, uint32_t& rounds, const uint32_t TOK_LONG) {
+__device__ __forceinline__ void resolve_batch(uint8_t* ob, const uint32_t* lits, uint32_t lwin, uint32_t wq, uint32_t lstart, uint32_t lit, uint32_t lq, uint32_t mstart, uint32_t ml, uint32_t d, int lane, uint32_t& rounds) {
   // ---- literals first: they depend on nothing, and the matches of this batch may read them
   {
     const uint32_t w0 = (lq >> 2) - wq;                  // window word that holds the run's first byte (garbage for lanes without a short run)
@@ -105,7 +105,7 @@ template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
 __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                                   uint8_t* U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                                   int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark,
-                                                                  const u32* __restrict__ list, uint32_t* tok_scratch, uint32_t tok_long) {
+                                                                  const u32* __restrict__ list, uint32_t* tok_scratch) {
   extern __shared__ uint16_t smem_tables[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // per warp: [lit LUT, 16-bit entries][dist LUT, byte entries][canonical-limit entries of both], interleaved by lane
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uin
         const uint32_t mstart = pos + incl - ml, lstart = mstart - nl, lq = qpos + linc - nl;
         pos += __shfl_sync(0xffffffffu, incl, 31); qpos += __shfl_sync(0xffffffffu, linc, 31);
         { const uint32_t nw = (qpos >> 2) + (uint32_t)lane; lwin = nw < nlw ? lits[-(int)nw] : 0u; }   // ... and so is the next batch's window of the literal stream
-        resolve_batch(ob, lits, win, wq, lstart, nl, lq, mstart, ml, tok_dist(t), lane, rounds, tok_long); batches++;
+        resolve_batch(ob, lits, win, wq, lstart, nl, lq, mstart, ml, tok_dist(t), lane, rounds); batches++;
       }
     }
     __syncwarp();
@@ -205,11 +205,10 @@ static void tok_launch(const InflateArgs& a, cudaStream_t s) {
   const int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, g.ctas_per_sm * g.sms);
   if (grid <= 0) return;
   if (!a.tok_scratch || a.tok_scratch_bytes < (size_t)grid * WARPS * 32 * TOK_CAP * sizeof(uint32_t)) throw std::string("inflate: token scratch missing or too small");
-  const uint32_t tok_long = getenv("IRF_TOK_LONG") ? (uint32_t)atoi(getenv("IRF_TOK_LONG")) : 16u;
   const bool prof = getenv("IRF_TOK_PROF") != nullptr;
   if (prof) { unsigned long long z[8] = {0}; IRF_CUDA(cudaMemcpyToSymbol(g_tok_prof, z, sizeof z)); }
   IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch, tok_long);
+  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch);
   note_launch();
   if (prof) { IRF_CUDA(cudaStreamSynchronize(s)); unsigned long long z[8]; IRF_CUDA(cudaMemcpyFromSymbol(z, g_tok_prof, sizeof z));
     fprintf(stderr, "[tok] <%d warps, %d/%d-bit LUTs> grid %d x %d CTAs/SM: phase A %.1f Mcycles/claim, phase B %.1f Mcycles/claim, %llu claims; per claim: %.0f votes, %.1f table builds, %.0f batches, %.2f rounds/batch\n", WARPS, LB, DB, grid, g.ctas_per_sm,
@@ -235,7 +234,10 @@ size_t inflate_tok_scratch_bytes(int variant, int nblk) {
   const int per = g.warps * 32, need = (nblk + per - 1) / per, grid = std::max(1, std::min(need, g.ctas_per_sm * g.sms));
   return (size_t)grid * per * TOK_CAP * sizeof(uint32_t);
 }
+static unsigned long long g_tok_launches = 0;
+unsigned long long tok_launch_counter() { return g_tok_launches; }   // launches of the two-phase kernel by this process (tests check that the default path really runs it)
 void launch_inflate_tok(const InflateArgs& a, int variant, cudaStream_t s) {
+  ++g_tok_launches;
 #define IRF_TOK_LAUNCH(W, LB, DB, P, M) tok_launch<W, LB, DB, P, M>(a, s)
   IRF_TOK_DISPATCH(variant, IRF_TOK_LAUNCH)
 }

@@ -144,6 +144,7 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
 }
 size_t inflate_scratch_bytes(int variant, int nblk) { return variant >= 12 && variant <= 15 && nblk > 0 ? inflate_tok_scratch_bytes(variant, nblk) : 0; }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
+  if (variant >= 12 && variant <= 15) { launch_inflate_tok(a, variant, s); g_inflate_lanes = inflate_tok_lanes(variant); return; }   // two-phase kernel: token decode per lane, then warp-wide resolve (inflate_tok.cu)
   switch (variant) {   // one-phase kernel: <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, pre-written sectors, byte distance LUT, CTAs per SM>
     case 2: launch_inflate_t<4, 6, 5, 1, 0, 1>(a, s); break;   // pre-written output sectors
     case 3: launch_inflate_t<4, 6, 6, 1, 0, 1>(a, s); break;
@@ -153,7 +154,8 @@ void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
     case 8: launch_inflate_t<4, 6, 5, 4, 1, 0>(a, s); break;    // lane-granular claims + header batching (measured slower, kept for A/B)
     case 10: launch_inflate_t<4, 6, 5, 1, 0, 0, 1, 6>(a, s); break;   // byte distance LUT: 36 KB per CTA and <= 80 registers, six CTAs per SM
     case 11: launch_inflate_t<4, 6, 5, 1, 0, 0, 1, 0>(a, s); break;   // byte distance LUT only (five CTAs; isolates the table change from the occupancy change)
-    default: launch_inflate_t<4, 6, 5, 1, 0, 0>(a, s); break;   // variants 0, 1, 6, 9 (the last three were the removed output-ring versions)
+    case 0: launch_inflate_t<4, 6, 5, 1, 0, 0>(a, s); break;    // the round-1 default
+    default: throw std::string("unknown inflate_variant ") + std::to_string(variant) + " (12-15: two-phase kernel, 0, 2-5, 7, 8, 10, 11: one-phase kernel)";
   }
 }
 
@@ -687,7 +689,8 @@ struct DepthTile {
 };
 // fr: fragments per thread (a CTA with a depth tile takes several consecutive 128-fragment slices so that zeroing and flushing the tile pay off)
 __global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ pair_list, u64 npairs, const u64* __restrict__ npairs_dev, int fr) {
-  __shared__ __align__(16) int32_t sh_tile[2 * DEPTH_TILE]; __shared__ unsigned long long sh_base[2];
+  extern __shared__ __align__(16) int32_t sh_tile[];   // [2][DEPTH_TILE] when the depth tile is on, nothing otherwise (16 KB of static shared memory cost the default path 10 %)
+  __shared__ unsigned long long sh_base[2];
   if (npairs_dev) npairs = min(npairs, *npairs_dev);   // the grid was sized from an upper bound; the pairing kernel left the actual count on the device
   if ((u64)blockIdx.x * fr * blockDim.x >= npairs) return;
   DepthTile dt; dt.begin(T, sh_tile, sh_base);
@@ -704,7 +707,7 @@ __global__ void __launch_bounds__(128) process_pairs_kernel(DevTables T, const u
   warp_add_stat(&T.stats[ST_LONG], st.longp); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
 }
 __global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ single_list, u64 nsingles, const u64* __restrict__ nsingles_dev, int fr) {
-  __shared__ __align__(16) int32_t sh_tile[2 * DEPTH_TILE]; __shared__ unsigned long long sh_base[2];
+  extern __shared__ __align__(16) int32_t sh_tile[]; __shared__ unsigned long long sh_base[2];
   if (nsingles_dev) nsingles = min(nsingles, *nsingles_dev);
   if ((u64)blockIdx.x * fr * blockDim.x >= nsingles) return;
   DepthTile dt; dt.begin(T, sh_tile, sh_base);
@@ -724,11 +727,11 @@ __global__ void shift_offsets_kernel(u64* off, u64 n, u64 delta) { u64 i = (u64)
 void launch_shift_offsets(u64* off, u64 n, u64 delta, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { shift_offsets_kernel<<<(unsigned)g, 256, 0, s>>>(off, n, delta); IRF_LAUNCHED(); } }
 void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s, const u64* npairs_dev) {
   const int fr = T.depth_tile ? 4 : 1; u64 grid = (npairs + 128ull * fr - 1) / (128ull * fr);   // npairs_dev given: npairs is an upper bound and the kernel reads the count itself
-  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, pair_list, npairs, npairs_dev, fr); IRF_LAUNCHED(); }
+  if (grid) { process_pairs_kernel<<<(unsigned)grid, 128, T.depth_tile ? 2 * DEPTH_TILE * sizeof(int32_t) : 0, s>>>(T, U, pair_list, npairs, npairs_dev, fr); IRF_LAUNCHED(); }
 }
 void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s, const u64* nsingles_dev) {
   const int fr = T.depth_tile ? 4 : 1; u64 grid = (nsingles + 128ull * fr - 1) / (128ull * fr);
-  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, 0, s>>>(T, U, single_list, nsingles, nsingles_dev, fr); IRF_LAUNCHED(); }
+  if (grid) { process_singles_kernel<<<(unsigned)grid, 128, T.depth_tile ? 2 * DEPTH_TILE * sizeof(int32_t) : 0, s>>>(T, U, single_list, nsingles, nsingles_dev, fr); IRF_LAUNCHED(); }
 }
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s) {
   int grid = (a.nblk + 127) / 128;

@@ -25,6 +25,7 @@ size_t inflate_scratch_bytes(int variant, int nblk);   // device scratch the cho
 void launch_inflate_tok(const InflateArgs& a, int variant, cudaStream_t s);   // inflate_tok.cu; variants 12-15 differ in LUT width / warps per SM
 size_t inflate_tok_scratch_bytes(int variant, int nblk);
 int inflate_tok_lanes(int variant);
+unsigned long long tok_launch_counter();
 void note_launch();                                     // bumps the library's kernel-launch counter (launchers outside kernels.cu)
 int inflate_resident_lanes();
 void set_inflate_cta_cap(int ctas_per_sm);

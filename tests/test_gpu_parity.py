@@ -776,6 +776,24 @@ def test_inflate_kernel_variants_agree(tiny, tmp_path, variant):
     assert c.timing()["inflate_launches"] >= 1 and c.timing()["sm_inflate_share"] == 1.0
 
 
+def test_default_sm_inflate_is_the_two_phase_kernel(tiny, tmp_path):
+    """The default inflate_variant must launch inflate_tok_kernel (a dispatch slip once sent it to the one-phase kernel: same bytes, 25 % slower,
+    and no parity test can see that), variant 0 must not, and an unknown variant is refused."""
+    from irfinder_b200 import IRFError
+    c = _gpu_run(tiny, str(tmp_path / "g"), de_percent=0, de_percent_stream=0)
+    before = c.timing()["tok_launches_total"]
+    c.run_bam(tiny["sorted"])
+    assert c.timing()["tok_launches_total"] > before
+    c0 = _gpu_run(tiny, str(tmp_path / "g0"), inflate_variant=0, de_percent=0, de_percent_stream=0)
+    mid = c0.timing()["tok_launches_total"]
+    c0.run_bam(tiny["sorted"])
+    assert c0.timing()["tok_launches_total"] == mid
+    bad = _core(inflate_variant=99, de_percent=0, de_percent_stream=0)
+    bad.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+    with pytest.raises(IRFError):
+        bad.run_bam(tiny["sorted"])
+
+
 @pytest.mark.parametrize("level,block", [(0, 65280), (6, 65280), (9, 65280), (6, 1500), (1, 20000)])
 def test_two_phase_inflate_on_other_encoders(built, tiny, tmp_path, level, block):
     """The two-phase SM kernel (token decode per lane, warp-wide match resolve) on BGZF written by other encoder settings than the

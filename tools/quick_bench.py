@@ -16,7 +16,7 @@ meta = synth.generate(a.out, genome=a.genome, introns=a.introns, pairs=a.pairs, 
 print("generated in %.1fs" % (time.time() - t0), {k: meta[k] for k in ("records", "inflated_bytes", "compressed_bytes")}, flush=True)
 data = np.fromfile(meta["sorted"], dtype=np.uint8)
 for v, ctas, dtile in [(int(x), int(y), int(z)) for x in a.variants.split(",") for y in a.ctas.split(",") for z in a.depth_tiles.split(",")]:
-    c = IRFinderCore(0, inflate_variant=v, inflate_ctas=ctas, de_percent=a.de_percent, resident_pipeline=0, depth_tile=dtile)
+    c = IRFinderCore(0, inflate_variant=v, inflate_ctas=ctas, de_percent=a.de_percent, resident_pipeline=0, **({"depth_tile": dtile} if dtile else {}))
     c.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])
     c.stage(data.ctypes.data, data.size)
     best = None
