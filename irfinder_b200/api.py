@@ -88,10 +88,14 @@ class IRFinderCore:
     """Host mirror of the reference's `irfinder` main: loadRef x4 -> processAll -> WriteOutput x6."""
 
     def __init__(self, device=0, **options):
+        """`device`: one GPU ordinal, or a list of them (an ordinal may repeat): irf_run_bam / irf_run_buffer then cut the BAM into one
+        byte range per entry, count them side by side inside this process and merge into the first context (csrc/multi.cu)."""
         self.lib = load_library()
         self.h = _vp()
-        dev = _i(device)
-        rc = self.lib.irf_create(C.byref(self.h), C.byref(dev), 1)
+        ids = [int(d) for d in device] if isinstance(device, (list, tuple)) else [int(device)]
+        self.devices = ids
+        dev = (_i * len(ids))(*ids)
+        rc = self.lib.irf_create(C.byref(self.h), dev, len(ids))
         if rc != 0:
             raise IRFError(rc, "irf_create failed: no usable CUDA device (this library has no CPU path)")
         for k, v in options.items():

@@ -2,20 +2,31 @@
 //   irfinder <outdir> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam|/dev/stdin|->
 // Same six positional arguments, same output files, counters and directionality on stdout, non-zero exit on error.
 // Extras go in the environment so the reference invocation works unchanged:
-//   IRF_DEVICE (GPU ordinal, default 0), IRF_TRIM_CENTER, IRF_SAFE_INFLATE=1 (no hardware decompression engine), IRF_STDIN_INFLATED=1 (stdin carries inflated BAM
+//   IRF_DEVICE (GPU ordinal, default 0) or IRF_DEVICES (a list such as 0,1,2,3 or 0-7: the BAM file is cut into one byte range per device and
+//   counted by all of them inside this process; an ordinal may repeat; stdin input uses the first device only), IRF_TRIM_CENTER, IRF_SAFE_INFLATE=1 (no hardware decompression engine), IRF_STDIN_INFLATED=1 (stdin carries inflated BAM
 //   bytes, as the reference's `gzip -cd |` pipe does; default: auto-detect from the gzip magic).
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fcntl.h>
 #include <unistd.h>
+#include <vector>
 #include "irfinder_b200.h"
 
 int main(int argc, char** argv) {
   if (argc != 7) { fprintf(stderr, "Usage: irfinder <outputDirectory> <ref-cover.bed> <ref-sj.ref> <ref-read-continues.ref> <ref-ROI.bed|NULL> <bam-file|/dev/stdin>\n"); return 1; }
-  int dev = getenv("IRF_DEVICE") ? atoi(getenv("IRF_DEVICE")) : 0;
+  std::vector<int> devs;
+  if (const char* l = getenv("IRF_DEVICES")) {   // "0,1,2" and ranges "0-7", mixed freely
+    for (const char* p = l; *p;) {
+      char* e; long a = strtol(p, &e, 10); if (e == p || a < 0) { fprintf(stderr, "irfinder: cannot parse IRF_DEVICES=%s\n", l); return 1; }
+      long b = a; if (*e == '-') { const char* q = e + 1; b = strtol(q, &e, 10); if (e == q || b < a) { fprintf(stderr, "irfinder: cannot parse IRF_DEVICES=%s\n", l); return 1; } }
+      for (long d = a; d <= b && devs.size() < 64; d++) devs.push_back((int)d);
+      p = e; if (*p == ',') p++; else if (*p) { fprintf(stderr, "irfinder: cannot parse IRF_DEVICES=%s\n", l); return 1; }
+    }
+  }
+  if (devs.empty()) devs.push_back(getenv("IRF_DEVICE") ? atoi(getenv("IRF_DEVICE")) : 0);
   irf_ctx* ctx = nullptr;
-  if (irf_create(&ctx, &dev, 1) != IRF_OK) { fprintf(stderr, "irfinder: cannot initialise CUDA device %d\n", dev); return 2; }
+  if (irf_create(&ctx, devs.data(), (int)devs.size()) != IRF_OK) { fprintf(stderr, "irfinder: cannot initialise CUDA device %d%s\n", devs[0], devs.size() > 1 ? " (or another of IRF_DEVICES)" : ""); return 2; }
   if (const char* t = getenv("IRF_TRIM_CENTER")) irf_set_option(ctx, "trim_center", t);
   if (const char* t = getenv("IRF_SAFE_INFLATE")) irf_set_option(ctx, "safe_inflate", t);   // untrusted input: SM inflate kernel only (recoverable errors that name the problem)
   int rc = irf_load_ref(ctx, argv[2], argv[3], argv[4], argv[5]);

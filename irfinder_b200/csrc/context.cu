@@ -30,6 +30,7 @@
 #include "../../include/irfinder_b200.h"
 #include "common.cuh"
 #include "kernels.h"
+#include "multi.h"
 #include "refs.h"
 
 using namespace irf;
@@ -85,6 +86,7 @@ struct irf_ctx {
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
   vector<string> chr_names; vector<int32_t> chr_lens; vector<u64> chr_goff; bool have_header = false, bound = false; u64 rec0 = 0;
+  u64 records_coff = 0;   // irf_read_header: file offset of the first BGZF block that starts at or after the first record (no header bytes from there on)
   // device reference tables
   DevBuf d_ref_len, d_chr_goff, d_sp_pos, d_sp_range, d_sp_count, d_seg_start, d_seg_end, d_seg_coff, d_seg_range, d_diff, d_roi_start, d_roi_end, d_roi_range, d_roi_count, d_chr_count;
   DevBuf d_jc_keys, d_jc_cnt, d_jl_keys, d_jl_cnt, d_jr_keys, d_jr_cnt, d_annot_keys; u64 n_annot = 0; u32 jc_slots = 0, jside_slots = 0;
@@ -102,6 +104,8 @@ struct irf_ctx {
   int directionality = 0; string stdout_text, dir_log; double timing[13] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
   bool counted = false, finalized = false;
   string err;
+  vector<irf_ctx*> all_ranks() { vector<irf_ctx*> v{this}; v.insert(v.end(), peers.begin(), peers.end()); return v; }
+  vector<irf_ctx*> peers;   // irf_create with n_devices > 1: the contexts of device_ids[1..]; this context is shard 0 and holds the merged tables after a run (multi.cu)
 
   DevTables T{}; Rules rules;
 
@@ -282,7 +286,7 @@ struct irf_ctx {
     double t0 = now_ms();
     inflated_input = false;
     feed_stop();
-    if (feed_fd >= 0 && !copy_now && has_header && n_own == n_total && n_total > 0 && feed_capable()) { d_comp.ensure(n_total + 64); feed_start(n_total); }
+    if (feed_fd >= 0 && !copy_now && ((has_header && n_own == n_total) || have_header) && n_total > 0 && feed_capable()) { d_comp.ensure(n_total + 64); feed_start(n_total); }
     else if (!copy_now && stream_pipeline && has_header && n_own == n_total && n_total > 0 && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine()) {
       // end-to-end path: the bytes can start crossing PCIe before the host has even walked the BGZF block chain
       d_comp.ensure(n_total + 64);
@@ -484,6 +488,7 @@ struct irf_ctx {
   struct Piece { size_t lo, hi; int chunk; bool last; };
   static constexpr int FEED_SLOTS = 24; static constexpr size_t FEED_SLOT_BYTES = 16u << 20; int feed_threads_n = 16;   // round 1: 8 slots, 4 threads -> ~17 GB/s from the page cache
   int feed_fd = -1; int file_ring = 1;   // option "file_ring": 0 never, 1 files above 64 MB, 2 always
+  u64 feed_base = 0;                     // file offset of the staged bytes' first byte (a shard of an in-process multi-device run)
   vector<Piece> feed_pieces; vector<cudaEvent_t> feed_ev_chunk; vector<char> feed_chunk_queued; cudaEvent_t feed_slot_ev[FEED_SLOTS] = {};
   uint8_t* feed_ring = nullptr; std::mutex feed_mu; std::condition_variable feed_cv; size_t feed_next = 0, feed_queued_upto = 0; bool feed_abort = false, feed_active = false; string feed_error; vector<std::thread> feed_threads;
   bool feed_capable() { return file_ring && stream_pipeline && de_percent_stream == 100 && inflate_variant != 8 && g_drv.deflate_engine(); }
@@ -496,7 +501,7 @@ struct irf_ctx {
       { std::unique_lock<std::mutex> lk(feed_mu); feed_cv.wait(lk, [&] { return feed_abort || feed_queued_upto + FEED_SLOTS > i; }); if (feed_abort) return; }   // piece i - FEED_SLOTS has been queued
       bool ok = true;
       if (i >= (size_t)FEED_SLOTS) ok = cudaEventSynchronize(feed_slot_ev[slot]) == cudaSuccess;                                                                  // ... and its copy has left the slot
-      for (size_t off = pc.lo; ok && off < pc.hi;) { ssize_t k = pread(feed_fd, buf + (off - pc.lo), pc.hi - off, (off_t)off); if (k <= 0) ok = false; else off += (size_t)k; }
+      for (size_t off = pc.lo; ok && off < pc.hi;) { ssize_t k = pread(feed_fd, buf + (off - pc.lo), pc.hi - off, (off_t)(feed_base + off)); if (k <= 0) ok = false; else off += (size_t)k; }
       std::unique_lock<std::mutex> lk(feed_mu); feed_cv.wait(lk, [&] { return feed_abort || feed_queued_upto == i; }); if (feed_abort) return;
       if (ok) ok = cudaMemcpyAsync(d_comp.as<uint8_t>() + pc.lo, buf, pc.hi - pc.lo, cudaMemcpyHostToDevice, s_copy) == cudaSuccess && cudaEventRecord(feed_slot_ev[slot], s_copy) == cudaSuccess;
       if (ok && pc.last) ok = cudaEventRecord(feed_ev_chunk[pc.chunk], s_copy) == cudaSuccess;
@@ -1081,13 +1086,19 @@ static int classify(const string& e) {
 extern "C" {
 
 int irf_create(irf_ctx** out, const int* device_ids, int n_devices) {
-  if (!out || n_devices != 1 || !device_ids) return IRF_EINVAL;
-  irf_ctx* c = new irf_ctx();
-  try { c->init(device_ids[0]); } catch (const string& e) { fprintf(stderr, "irf_create: %s\n", e.c_str()); delete c; *out = nullptr; return IRF_ECUDA; }
-  *out = c; return IRF_OK;
+  if (!out || n_devices < 1 || n_devices > 64 || !device_ids) return IRF_EINVAL;
+  *out = nullptr; vector<irf_ctx*> made;
+  for (int k = 0; k < n_devices; k++) {   // one context per entry; an ordinal may repeat (several shards on one GPU)
+    irf_ctx* c = new irf_ctx();
+    try { c->init(device_ids[k]); } catch (const string& e) { fprintf(stderr, "irf_create: device %d: %s\n", device_ids[k], e.c_str()); delete c; for (auto m : made) irf_destroy(m); return IRF_ECUDA; }
+    made.push_back(c);
+  }
+  made[0]->peers.assign(made.begin() + 1, made.end());
+  *out = made[0]; return IRF_OK;
 }
 void irf_destroy(irf_ctx* c) {
-  if (!c) return; cudaSetDevice(c->device); cudaDeviceSynchronize();
+  if (!c) return; for (auto p : c->peers) irf_destroy(p); c->peers.clear();
+  cudaSetDevice(c->device); cudaDeviceSynchronize();
   DevBuf* all[] = {&c->d_ref_len, &c->d_chr_goff, &c->d_sp_pos, &c->d_sp_range, &c->d_sp_count, &c->d_seg_start, &c->d_seg_end, &c->d_seg_coff, &c->d_seg_range, &c->d_diff, &c->d_roi_start, &c->d_roi_end,
                    &c->d_roi_range, &c->d_roi_count, &c->d_chr_count, &c->d_jc_keys, &c->d_jc_cnt, &c->d_jl_keys, &c->d_jl_cnt, &c->d_jr_keys, &c->d_jr_cnt, &c->d_annot_keys, &c->d_bucket_base, &c->d_bucket_n, &c->d_sp_bidx, &c->d_seg_bidx, &c->d_roi_bidx, &c->d_stats, &c->d_err, &c->d_introns,
                    &c->d_iblocks, &c->d_rows, &c->d_scratch, &c->d_tile_sums, &c->d_small, &c->d_dump, &c->d_dump_cursor, &c->d_tok, &c->d_slots, &c->d_sm_list, &c->d_de_list, &c->d_de_act, &c->d_crc, &c->d_comp, &c->d_U, &c->d_c_off, &c->d_c_len, &c->d_u_off, &c->d_u_len, &c->d_status,
@@ -1138,17 +1149,43 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
   else if (k == "de_percent_overlap") { if (v < 1 || v > 100) return IRF_EINVAL; c->de_percent_overlap = (int)v; }
   else if (k == "de_percent_stream") { if (v < 0 || v > 100) return IRF_EINVAL; c->de_percent_stream = (int)v; c->engines_planned = false; }
   else { c->err = "unknown option " + k; return IRF_EINVAL; }
+  for (auto p : c->peers) { int rc = irf_set_option(p, key, value); if (rc != IRF_OK) { c->err = p->err; return rc; } }   // every device of a multi-device context runs with the same options
   return IRF_OK;
 }
-int irf_load_ref(irf_ctx* c, const char* cover, const char* sj, const char* rc, const char* roi) { if (!cover || !sj || !rc) return IRF_EINVAL; IRF_TRY(c, c->load_ref(cover, sj, rc, roi)); }
+int irf_load_ref(irf_ctx* c, const char* cover, const char* sj, const char* rc, const char* roi) {
+  if (!cover || !sj || !rc) return IRF_EINVAL;
+  if (c && !c->peers.empty()) {   // the references are loaded on every device, side by side
+    vector<irf_ctx*> all = c->all_ranks(); vector<int> rcs(all.size(), IRF_OK); vector<std::thread> th;
+    for (size_t k = 1; k < all.size(); k++) th.emplace_back([&, k]() { rcs[k] = irf_load_ref(all[k], cover, sj, rc, roi); });
+    irf_ctx* self = c; auto one = [&]() -> int { IRF_TRY(self, self->load_ref(cover, sj, rc, roi)); }; rcs[0] = one();
+    for (auto& t : th) t.join();
+    for (size_t k = 0; k < all.size(); k++) if (rcs[k] != IRF_OK) { if (k) c->err = all[k]->err; return rcs[k]; }
+    return IRF_OK;
+  }
+  IRF_TRY(c, c->load_ref(cover, sj, rc, roi));
+}
 
-int irf_run_buffer(irf_ctx* c, const void* bgzf, size_t n) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->run_host_buffer(bgzf, n)); }
+int irf_run_buffer(irf_ctx* c, const void* bgzf, size_t n) {
+  if (!bgzf) return IRF_EINVAL;
+  if (c && !c->peers.empty()) IRF_TRY(c, irf::multi_run(c->all_ranks(), (const uint8_t*)bgzf, n, -1));
+  IRF_TRY(c, c->run_host_buffer(bgzf, n));
+}
 int irf_run_bam(irf_ctx* c, const char* path, const char* /*bai_path*/) {
   if (!path) return IRF_EINVAL;
   IRF_TRY(c, {
     int fd = open(path, O_RDONLY); if (fd < 0) throw string("cannot open ") + path;
     struct stat st; size_t hint = 0; if (fstat(fd, &st) == 0 && st.st_size > 0) hint = (size_t)st.st_size + 1;
     const size_t size = hint ? hint - 1 : 0;
+    if (!c->peers.empty()) {   // several devices: the file is mapped, cut into one byte range per device, and every device reads its own range
+      void* map = size && S_ISREG(st.st_mode) ? mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0) : MAP_FAILED;
+      if (map != MAP_FAILED) {
+        madvise(map, size, MADV_RANDOM);
+        try { irf::multi_run(c->all_ranks(), (const uint8_t*)map, size, fd); } catch (...) { munmap(map, size); close(fd); throw; }
+        munmap(map, size); close(fd); return IRF_OK;
+      }
+      size_t n = 0; try { n = c->read_fd_all(fd, hint); } catch (...) { close(fd); throw; } close(fd);
+      irf::multi_run(c->all_ranks(), (const uint8_t*)c->pinned, n, -1); return IRF_OK;
+    }
     if (size && S_ISREG(st.st_mode) && c->feed_capable() && (c->file_ring == 2 || size > (64u << 20))) {
       // regular file: mapped for the BGZF block scan, its bytes go to the GPU through the ring of page-locked buffers
       void* map = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
@@ -1210,6 +1247,7 @@ int irf_read_header(irf_ctx* c, const void* prefix, size_t n) {
     try { c->stage(prefix, 0, n, 1, false); } catch (...) { c->require_eof = req; throw; } c->require_eof = req;
     IRF_CUDA(cudaMemsetAsync(c->d_err.p, 0, 4, c->s_compute));   // a failed earlier run must not fail this one
     c->inflate_all(); c->join_crc(); c->check_dev_err("inflate"); c->parse_header_from_device(); c->staged = false;
+    { u64 u = 0; c->records_coff = c->blks.empty() ? 0 : c->blks.back().c_off + c->blks.back().c_len + 8; for (auto& b : c->blks) { if (u >= c->rec0) { c->records_coff = b.file_off; break; } u += b.isize; } }
   });
 }
 int irf_stage(irf_ctx* c, const void* bgzf, size_t own, size_t total, int has_header) { if (!bgzf) return IRF_EINVAL; IRF_TRY(c, c->stage(bgzf, own, total, has_header, !c->stage_lazy)); }
@@ -1281,3 +1319,19 @@ int irf_import_halo(irf_ctx* c, const void* bytes, size_t nbytes, const void* of
 }
 
 }  // extern "C"
+
+// ---- hooks of the in-process multi-device run (multi.h)
+namespace irf {
+int ctx_device(const irf_ctx* c) { return c->device; }
+bool ctx_require_eof(const irf_ctx* c) { return c->require_eof != 0; }
+uint64_t ctx_records_offset(const irf_ctx* c) { return c->records_coff; }
+int ctx_count_shard(irf_ctx* c, const uint8_t* src, size_t own, size_t total, bool has_header, int fd, uint64_t file_off) {
+  IRF_TRY(c, {
+    c->reset();
+    c->feed_fd = fd >= 0 && c->feed_capable() && (c->file_ring == 2 || total > (64u << 20)) ? fd : -1; c->feed_base = file_off;
+    const bool req = c->require_eof; c->require_eof = false;   // the EOF block is checked once for the whole file (multi_run), not per shard
+    try { c->stage(src, own, total, has_header ? 1 : 0, false); c->count(); } catch (...) { c->require_eof = req; c->feed_stop(); c->feed_fd = -1; c->feed_base = 0; c->h_src = nullptr; throw; }
+    c->require_eof = req; c->feed_stop(); c->feed_fd = -1; c->feed_base = 0; c->h_src = nullptr;
+  });
+}
+}  // namespace irf

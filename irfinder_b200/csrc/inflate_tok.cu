@@ -7,6 +7,7 @@
 //            lengths into output and literal-stream positions, the literals are placed, and the matches are copied — in parallel
 //            when their source bytes are final, in order otherwise (a match may read what an earlier match of the same batch writes);
 // then claims the next 32.  Replaces `gzip -cd` of the reference pipeline; RFC 1951.
+#include <atomic>
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -234,10 +235,10 @@ size_t inflate_tok_scratch_bytes(int variant, int nblk) {
   const int per = g.warps * 32, need = (nblk + per - 1) / per, grid = std::max(1, std::min(need, g.ctas_per_sm * g.sms));
   return (size_t)grid * per * TOK_CAP * sizeof(uint32_t);
 }
-static unsigned long long g_tok_launches = 0;
-unsigned long long tok_launch_counter() { return g_tok_launches; }   // launches of the two-phase kernel by this process (tests check that the default path really runs it)
+static std::atomic<unsigned long long> g_tok_launches{0};
+unsigned long long tok_launch_counter() { return g_tok_launches.load(std::memory_order_relaxed); }   // launches of the two-phase kernel by this process (tests check that the default path really runs it)
 void launch_inflate_tok(const InflateArgs& a, int variant, cudaStream_t s) {
-  ++g_tok_launches;
+  g_tok_launches.fetch_add(1, std::memory_order_relaxed);
 #define IRF_TOK_LAUNCH(W, LB, DB, P, M) tok_launch<W, LB, DB, P, M>(a, s)
   IRF_TOK_DISPATCH(variant, IRF_TOK_LAUNCH)
 }

@@ -7,6 +7,7 @@
 // Each device function that restates a reference routine names it (upstream file per SURVEY.md §8a; the
 // mounted /root/reference has no source to cite by line).
 #include <algorithm>
+#include <atomic>
 #include <cub/device/device_radix_sort.cuh>
 #include "common.cuh"
 #include "inflate_core.cuh"
@@ -14,9 +15,9 @@
 
 namespace irf {
 
-static unsigned long long g_launches = 0;  // kernels launched by this library (bench.py reports it as gpu_launches)
-unsigned long long launch_counter() { return g_launches; }
-#define IRF_LAUNCHED() (++g_launches)
+static std::atomic<unsigned long long> g_launches{0};  // kernels launched by this library (bench.py reports it as gpu_launches); contexts of several devices launch from their own host threads
+unsigned long long launch_counter() { return g_launches.load(std::memory_order_relaxed); }
+#define IRF_LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
 void note_launch() { IRF_LAUNCHED(); }
 
 // ------------------------------------------------------------------------------------------------
@@ -238,10 +239,10 @@ void launch_de_check(const u32* list, int n, const u32* act, const u32* u_len, i
   if (n > 0) { de_check_kernel<<<(n + 255) / 256, 256, 0, s>>>(list, n, act, u_len, status, err); IRF_LAUNCHED(); }
 }
 void launch_crc_check(const uint8_t* U, const u64* u_off, const u32* u_len, const u32* crc_expected, int nblk, int* status, int* err, cudaStream_t s, const u32* list) {
-  static CrcMul M; static bool init = false; static int sms_of[64] = {0};
-  if (!init) { u32 p = 0x40000000u;   // x^1; square up to x^(8 * 2048) = x^(2^14), then keep squaring
+  static int sms_of[64] = {0};
+  static const CrcMul M = [] { CrcMul m; u32 p = 0x40000000u;   // x^1; square up to x^(8 * 2048) = x^(2^14), then keep squaring
     for (int i = 0; i < 14; i++) p = crc_mulmod(p, p);
-    for (int k = 0; k < 5; k++) { M.x[k] = p; p = crc_mulmod(p, p); } init = true; }
+    for (int k = 0; k < 5; k++) { m.x[k] = p; p = crc_mulmod(p, p); } return m; }();
   if (nblk <= 0) return;
   constexpr int smem = 4 * 256 * 32 * 4;
   int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");

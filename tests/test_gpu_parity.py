@@ -807,3 +807,109 @@ def test_two_phase_inflate_on_other_encoders(built, tiny, tmp_path, level, block
     c = _gpu_run(tiny, str(tmp_path / "g"), bam=bam, inflate_variant=12, de_percent=0, de_percent_stream=0)
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "g"))
     assert c.timing()["sm_inflate_share"] == 1.0
+
+
+# ---- in-process multi-device context (irf_create with n_devices > 1, csrc/multi.cu; SURVEY.md §8b "one ctx drives all its GPUs") ----
+
+def _device_lists():
+    """Several shards on GPU 0 always; real device lists as far as the box has GPUs."""
+    import torch
+    n = torch.cuda.device_count()
+    lists = [[0, 0], [0, 0, 0], [0] * 5]
+    if n >= 2:
+        lists += [[0, 1], list(range(n))]
+    return lists
+
+
+@pytest.mark.parametrize("ring", [0, 2])
+def test_one_context_drives_several_devices(built, tiny, tmp_path, ring):
+    """irf_create(device_ids, n > 1): irf_run_bam / irf_run_buffer cut the BAM into one byte range per entry, count them side by side on
+    host threads, merge (hand-shake, halo, junctions, counters, region-owned depth, rows) and leave the complete tables in the
+    context - byte-identical to the oracle, for files read through the page-locked ring (ring=2) and through the mapping (ring=0)."""
+    from irfinder_b200 import IRFinderCore, IRFError
+    for k, devs in enumerate(_device_lists()):
+        c = IRFinderCore(devs, file_ring=ring, stream_chunk_kb=64)
+        c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+        for i, bam in enumerate([tiny["sorted"], tiny["collated"]]):
+            c.run_bam(bam)
+            out = str(tmp_path / f"g{k}_{i}")
+            c.write_outputs(out)
+            assert_same_outputs(tiny["oracle_out"], out)
+            assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(tiny["oracle_stdout"])
+        buf = np.fromfile(tiny["sorted"], dtype=np.uint8)
+        c.run_buffer(buf.ctypes.data, buf.size)
+        c.write_outputs(str(tmp_path / f"b{k}"))
+        assert_same_outputs(tiny["oracle_out"], str(tmp_path / f"b{k}"))
+        cut = str(tmp_path / "cut.bam")
+        open(cut, "wb").write(buf.tobytes()[: buf.size // 2])
+        with pytest.raises(IRFError):          # truncated file: refused as by a single-device context, and the context stays usable
+            c.run_bam(cut)
+        bad = bytearray(buf.tobytes())
+        offs = _bgzf_block_offsets(bad)
+        nxt = offs[len(offs) * 9 // 10 + 1]
+        bad[nxt - 8] ^= 0x40                   # wrong CRC-32 footer in a block of the last shard: reported with the shard it was found in
+        with pytest.raises(IRFError) as ei:
+            c.run_bytes(bytes(bad))
+        assert "CRC" in str(ei.value) and (len(devs) == 1 or "shard" in str(ei.value)), str(ei.value)
+        c.run_bam(tiny["sorted"])
+        c.write_outputs(str(tmp_path / f"again{k}"))
+        assert_same_outputs(tiny["oracle_out"], str(tmp_path / f"again{k}"))
+        c.close()
+
+
+def test_multi_device_context_stranded_and_ragged_inputs(built, tiny, tmp_path):
+    """The IR-dir table of a stranded library is merged like the nondir one; a header that spans several BGZF blocks is never cut;
+    a BAM without alignments and a BAM with fewer blocks than devices run on fewer devices."""
+    from bamutil import record, write_bam
+    from irfinder_b200 import IRFinderCore
+    meta = _gen(tmp_path, "s", genome="tiny", introns=300, pairs=40000, readlen=100, seed=12, stranded=-1, chunks=5)
+    ostd = run_oracle(built, meta, str(tmp_path / "o"))
+    c = IRFinderCore([0, 0, 0], stream_chunk_kb=64)
+    c.load_ref(meta["cover"], meta["sj"], meta["rc"], meta["roi"])
+    c.run_bam(meta["sorted"])
+    c.write_outputs(str(tmp_path / "g"))
+    assert c.directionality == -1
+    assert_same_outputs(str(tmp_path / "o"), str(tmp_path / "g"))
+    assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
+    c.close()
+
+    refs = [("chrA", 400000), ("chrB", 300000), ("chrEmpty", 50000)]
+    many = refs + [("scaffold_%04d_random_with_a_long_name" % i, 1000 + i) for i in range(4000)]
+    junc = [l.split("\t") for l in open(tiny["sj"]).read().split("\n") if l][:200]
+    recs = []
+    for i, j in enumerate(junc):
+        ref, s, e = (0 if j[0] == "chrA" else 1), int(j[1]), int(j[2])
+        recs.append(record("m%04d" % i, ref, s - 40, f"40M{e - s}N40M", 16 * (i & 1)))
+        recs.append(record("s%04d" % i, 3 + (i * 19) % 4000, 10, "50M", 0))
+    big = str(tmp_path / "many.bam")
+    raw = write_bam(big, many, recs, level=1, block=3000)
+    assert raw.index(b"m0000\0") > 2 * 3000
+    empty = str(tmp_path / "empty.bam")
+    write_bam(empty, refs, [], level=1)
+    for name, bam in (("many", big), ("empty", empty)):
+        m2 = dict(tiny, sorted=bam, collated=bam)
+        ostd = run_oracle(built, m2, str(tmp_path / f"o_{name}"))
+        c = IRFinderCore([0] * 4)
+        c.load_ref(tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"])
+        c.run_bam(bam)
+        c.write_outputs(str(tmp_path / f"g_{name}"))
+        assert_same_outputs(str(tmp_path / f"o_{name}"), str(tmp_path / f"g_{name}"))
+        assert _stats_from_stdout(c.stdout_text) == _stats_from_stdout(ostd)
+        c.close()
+
+
+def test_cli_with_a_device_list(built, tiny, tmp_path):
+    """IRF_DEVICES makes the reference invocation use several devices (here: three shards on GPU 0, and every GPU of the box)."""
+    import torch
+    exe = os.path.join(ROOT, "bin", "irfinder")
+    lists = ["0,0,0", "0-%d" % (torch.cuda.device_count() - 1)]
+    for k, devs in enumerate(lists):
+        out = str(tmp_path / f"cli{k}")
+        os.makedirs(out)
+        r = subprocess.run([exe, out, tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"], tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                           env=dict(os.environ, IRF_DEVICES=devs), timeout=300)
+        assert r.returncode == 0, r.stderr
+        assert_same_outputs(tiny["oracle_out"], out)
+        assert _stats_from_stdout(r.stdout) == _stats_from_stdout(tiny["oracle_stdout"])
+    bad = subprocess.run([exe, str(tmp_path), tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"], tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=dict(os.environ, IRF_DEVICES="0;1"))
+    assert bad.returncode != 0
