@@ -6,8 +6,9 @@
  * file:line inside it can be cited — SURVEY.md §0).  Each entry point below names the reference routine it
  * stands in for.  Conventions: every call returns 0 or a negative IRF_E* code; no C++ exception crosses
  * the ABI; the caller owns every pointer it passes; memory returned by irf_get_table belongs to the
- * context until the next run or irf_destroy; one context drives ONE GPU and is used from one host thread
- * at a time (multi-GPU = one process and one context per GPU).
+ * context until the next run or irf_destroy; a context is used from one host thread at a time.  Multi-GPU:
+ * either one context created over several devices (irf_create with n_devices > 1: the library shards, merges
+ * and finalizes inside the process), or one process and one context per GPU driven over NCCL.
  */
 #ifndef IRFINDER_B200_H
 #define IRFINDER_B200_H
@@ -44,7 +45,15 @@ typedef struct irf_intron_row {
   uint32_t sp_left, sp_right, jc_left, jc_right, jc_exact; int32_t warning; /* 0 -, 1 LowCover, 2 LowSplicing, 3 MinorIsoform, 4 NonUniformIntronCover */
 } irf_intron_row;
 
-/* Creates a context on device_ids[0] (n_devices must be 1).  Stands in for process start of `irfinder`. */
+/* Creates a context.  Stands in for process start of `irfinder`.
+ * n_devices == 1: everything runs on device_ids[0].
+ * n_devices > 1 (at most 64; an ordinal may repeat = several shards on one GPU): irf_run_bam and irf_run_buffer cut the BAM into one
+ * BGZF byte range per entry (never inside the header; fewer ranges when the file has fewer blocks), count the ranges side by side
+ * (one host thread per device), exchange what the reference's single set of processors would have seen together - frame hand-shake,
+ * cross-range mates, junction tables, span / ROI / chromosome / read counters, region-owned depth - and leave the complete, finalized
+ * tables in this context: irf_write_outputs, irf_get_table, irf_stdout_text work as after a single-device run and give the same
+ * bytes.  irf_set_option and irf_load_ref apply to every device; irf_run_stream (a pipe) and the staged calls below use
+ * device_ids[0] only.  (csrc/multi.cu; the irfinder binary takes the list from IRF_DEVICES=0,1,... or 0-7.) */
 int irf_create(irf_ctx** out, const int* device_ids, int n_devices);
 void irf_destroy(irf_ctx* ctx);
 const char* irf_last_error(irf_ctx* ctx);
