@@ -35,7 +35,7 @@ enum {
   IRF_T_ROWS_DIR = 7,     /* same for IRFinder-IR-dir.txt; n = 0 when the library is unstranded */
   IRF_T_FRAGMENTS = 8,    /* uint32 words of the FragmentBlocks dump (option dump_fragments=1): per fragment
                              [n_words, chr, dir, readCount, nblk0, nblk1, (start,end)*] */
-  IRF_T_TIMING = 9,       /* double[13] of the last run: ms h2d+inflate, ms inflate kernels, ms framing, ms counting, ms finalize, ms count total, ms host BGZF scan, ms output formatting, kernels launched since irf_reset, inflate launches, ms of the SM inflate launch(es) alone, share of the algorithmic bytes they inflated, launches of the two-phase inflate kernel by this process so far */
+  IRF_T_TIMING = 9,       /* double[14] of the last run: ms h2d+inflate, ms inflate kernels, ms framing, ms counting, ms finalize, ms count total, ms host BGZF scan, ms output formatting, kernels launched since irf_reset, inflate launches, ms of the SM inflate launch(es) alone, share of the algorithmic bytes they inflated, launches of the two-phase inflate kernel by this process so far, pairs formed by the adjacent-mate path */
   IRF_T_DIFF = 10         /* device only: int32[2][P] difference counters before irf_finalize */
 };
 
@@ -72,6 +72,8 @@ const char* irf_last_error(irf_ctx* ctx);
  * buffer and irf_count streams it to the GPU beside the inflate kernel: the buffer must then stay valid until irf_count returns).
  * "depth_tile" (default 0): 1 / 2 = CoverageBlocks counters of a CTA are summed in a shared-memory tile and flushed with red.global / by one TMA
  * bulk reduce per strand (measured slower than the plain global atomics of 0 on the benchmark shapes; kept selectable).
+ * "adjacent_pairs" (default -1): mates that follow each other in the file (name-collated input, STAR's pipe) are paired without the hash table;
+ * -1 = on unless the header says @HD SO:coordinate, 0 = off, 1 = on.  A matter of speed only: the pairs are the same either way.
  * "stream_segment_mb" (default 1024): irf_run_stream reads its pipe in segments of this size (two page-locked buffers of it).
  * "rule_*": the behaviours SURVEY.md Appendix C marks as uncertain, as run-time settings (defaults = DESIGN.md section 1): rule_junc_min_flank (5),
  * rule_span_left (5), rule_span_right (4), rule_skip_flags (0; e.g. 0x900 skips secondary and supplementary records), rule_pct_tie_midpoint (1),

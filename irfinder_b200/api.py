@@ -164,7 +164,7 @@ class IRFinderCore:
 
     def timing(self):
         t = self.table("timing")
-        keys = ["inflate_wall_ms", "inflate_kernel_ms", "framing_ms", "counting_ms", "finalize_ms", "count_total_ms", "host_scan_ms", "output_ms", "launches", "inflate_launches", "sm_inflate_ms", "sm_inflate_share", "tok_launches_total"]
+        keys = ["inflate_wall_ms", "inflate_kernel_ms", "framing_ms", "counting_ms", "finalize_ms", "count_total_ms", "host_scan_ms", "output_ms", "launches", "inflate_launches", "sm_inflate_ms", "sm_inflate_share", "tok_launches_total", "adjacent_pairs"]
         return dict(zip(keys, (float(x) for x in t)))
 
     # ---- staged / sharded operation

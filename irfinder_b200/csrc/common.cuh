@@ -39,7 +39,7 @@ enum DevErr : int {
 
 // ---- counters (the reference prints these on stdout; SURVEY.md §5 "Metrics")
 enum Stat : int { ST_SINGLE = 0, ST_PAIRED, ST_SHORT, ST_INTERSECT, ST_LONG, ST_SKIPPED, ST_ERROR, ST_NUCLEOTIDES, ST_RECORDS, ST_COUNT };
-constexpr int ST_CAND = ST_COUNT, ST_SLOTS = ST_COUNT + 1;   // internal: pair-candidate records seen (orphans = candidates - 2 x pairs); not part of the public table
+constexpr int ST_CAND = ST_COUNT, ST_ADJ = ST_COUNT + 1, ST_SLOTS = ST_COUNT + 2;   // internal: pair-candidate records seen (orphans = candidates - 2 x pairs) and pairs formed by the adjacent-mate path; not part of the public table
 
 struct Range { u32 begin, end; };
 

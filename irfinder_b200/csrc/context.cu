@@ -86,6 +86,8 @@ struct irf_ctx {
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
   vector<string> chr_names; vector<int32_t> chr_lens; vector<u64> chr_goff; bool have_header = false, bound = false; u64 rec0 = 0;
+  int adjacent_pairs = -1; bool hdr_coordinate_sorted = false;   // option "adjacent_pairs": -1 = from the header's @HD SO: tag (on unless SO:coordinate), 0 off, 1 on
+  int adjacent_on() const { return adjacent_pairs < 0 ? !hdr_coordinate_sorted : adjacent_pairs != 0; }
   u64 records_coff = 0;   // irf_read_header: file offset of the first BGZF block that starts at or after the first record (no header bytes from there on)
   // device reference tables
   DevBuf d_ref_len, d_chr_goff, d_sp_pos, d_sp_range, d_sp_count, d_seg_start, d_seg_end, d_seg_coff, d_seg_range, d_diff, d_roi_start, d_roi_end, d_roi_range, d_roi_count, d_chr_count;
@@ -101,7 +103,7 @@ struct irf_ctx {
   void* pinned = nullptr; size_t pinned_cap = 0;
   // results
   vector<u64> h_stats; vector<u32> h_sp, h_roi, h_chr, h_dump; vector<JuncEntry> h_junc; vector<IntronRow> rows_nondir, rows_dir; vector<int32_t> h_depth;
-  int directionality = 0; string stdout_text, dir_log; double timing[13] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
+  int directionality = 0; string stdout_text, dir_log; double timing[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}; unsigned long long launches0 = 0;
   bool counted = false, finalized = false;
   string err;
   vector<irf_ctx*> all_ranks() { vector<irf_ctx*> v{this}; v.insert(v.end(), peers.begin(), peers.end()); return v; }
@@ -472,7 +474,9 @@ struct irf_ctx {
     auto need = [&](size_t n) { if (n > have) fetch(std::max(n, have * 2)); if (n > have) throw string("BAM header truncated"); };
     need(12); if (memcmp(h.data(), "BAM\1", 4) != 0) throw string("not a BAM stream (bad magic)");
     int32_t l_text; memcpy(&l_text, &h[4], 4); if (l_text < 0) throw string("bad BAM header");
-    size_t p = 8 + (size_t)l_text; need(p + 4); int32_t n_ref; memcpy(&n_ref, &h[p], 4); p += 4; if (n_ref < 0) throw string("bad BAM header");
+    size_t p = 8 + (size_t)l_text; need(p + 4);
+    { const char* t = (const char*)h.data() + 8; const size_t first_line = (size_t)(std::find(t, t + l_text, '\n') - t); const string hd(t, first_line);   // @HD	VN:1.6	SO:coordinate
+      hdr_coordinate_sorted = hd.compare(0, 3, "@HD") == 0 && hd.find("SO:coordinate") != string::npos; } int32_t n_ref; memcpy(&n_ref, &h[p], 4); p += 4; if (n_ref < 0) throw string("bad BAM header");
     vector<string> names; vector<int32_t> lens;
     for (int i = 0; i < n_ref; i++) { need(p + 4); int32_t l_name; memcpy(&l_name, &h[p], 4); p += 4; if (l_name < 1) throw string("bad BAM header"); need(p + l_name + 4);
       names.emplace_back((const char*)&h[p], (size_t)l_name - 1); p += l_name; int32_t l_ref; memcpy(&l_ref, &h[p], 4); p += 4; lens.push_back(l_ref); }
@@ -672,7 +676,7 @@ struct irf_ctx {
           d_rec_base.ensure((size_t)nbk * 8); d_rec_off.ensure((ht[0] + ht[0] / 2) * 8); d_pair_list.ensure((ht[1] + ht[1] / 2 + 16) * 16); d_single_list.ensure((ht[0] + ht[0] / 2 + 16) * 8);
           launch_scan_counts(d_nrec.as<u32>() + b0, d_rec_base.as<u64>(), nbk, s_compute); launch_gather_records(fa, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
           IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
-          launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), ht[0], d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute, carry_base(), 1);
+          launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), ht[0], d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute, carry_base(), 1, adjacent_on());
           launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), ht[1] + 1, s_compute, list_counts);   // every pair is completed by one candidate record of this chunk (its mate may have waited since an earlier chunk)
           launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), ht[0] - ht[1] + 1, s_compute, list_counts + 1);
         }
@@ -741,7 +745,7 @@ struct irf_ctx {
     launch_walk_list(own, d_rec_base.as<u64>(), d_rec_off.as<u64>(), s_compute);
     d_pair_list.ensure((n_cand / 2 + 1) * 16); d_single_list.ensure((n_rec - n_cand + 1) * 8);
     u64* list_counts = (u64*)(d_small.as<uint8_t>() + 192); IRF_CUDA(cudaMemsetAsync(list_counts, 0, 16, s_compute));
-    launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute, carry_base(), 1);
+    launch_pair_records(T, d_U.as<uint8_t>(), d_rec_off.as<u64>(), n_rec, d_ptab.as<u64>(), (u32)(pslots - 1), d_pair_list.as<u64>(), d_single_list.as<u64>(), list_counts, s_compute, carry_base(), 1, adjacent_on());
     u64 lc[2] = {0, 0}; IRF_CUDA(cudaMemcpyAsync(lc, list_counts, 16, cudaMemcpyDeviceToHost, s_compute)); sync();
     launch_process_pairs(T, d_U.as<uint8_t>(), d_pair_list.as<u64>(), lc[0], s_compute);
     launch_process_singles(T, d_U.as<uint8_t>(), d_single_list.as<u64>(), lc[1], s_compute);
@@ -944,6 +948,7 @@ struct irf_ctx {
     check_dev_err("finalize"); mark("tables d2h");
     // orphans (pair candidates whose mate never came) = candidates - 2 x pairs; a sharded run counted them during the halo exchange
     h_stats[ST_ERROR] += sharded ? halo_leftover : h_stats[ST_CAND] - 2 * h_stats[ST_PAIRED];
+    timing[13] = (double)h_stats[ST_ADJ];
     h_stats.resize(ST_COUNT);
     float ms; IRF_CUDA(cudaEventElapsedTime(&ms, e0, e1)); timing[4] = ms; cudaEventDestroy(e0); cudaEventDestroy(e1);
     h_dump.clear(); h_depth.clear();
@@ -1138,6 +1143,7 @@ int irf_set_option(irf_ctx* c, const char* key, const char* value) {
     else { c->err = "unknown option " + k; return IRF_EINVAL; }
     c->bound = false;   // the device tables carry the rules (and the edge windows are cut on the host): bind again
   }
+  else if (k == "adjacent_pairs") { if (v < -1 || v > 1) return IRF_EINVAL; c->adjacent_pairs = (int)v; }
   else if (k == "depth_tile") { if (v < 0 || v > 2) return IRF_EINVAL; c->T.depth_tile = (int)v; }
   else if (k == "stream_segment_mb") { if (v < 1 || v > 65536) return IRF_EINVAL; c->stream_segment_bytes = (size_t)v << 20; }
   else if (k == "stream_chunk_kb") { if (v < 64) return IRF_EINVAL; c->chunk_bytes = (size_t)v << 10; c->engines_planned = false; }
@@ -1217,7 +1223,7 @@ int irf_directionality(irf_ctx* c) { return c ? c->directionality : 0; }
 int irf_get_table(irf_ctx* c, int which, const void** p, size_t* n) {
   if (!c || !p || !n) return IRF_EINVAL;
   IRF_TRY(c, {
-    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; c->timing[12] = (double)tok_launch_counter(); *p = c->timing; *n = 13; }
+    if (which == IRF_T_TIMING) { c->timing[8] = (double)(launch_counter() - c->launches0); c->timing[9] = c->n_inflate_launches; c->timing[12] = (double)tok_launch_counter(); *p = c->timing; *n = 14; }
     else {
       if (!c->finalized) throw string("no finished run to read tables from");
       switch (which) {

@@ -627,15 +627,42 @@ __device__ __forceinline__ void warp_add_stat(u64* slot, u64 v) {
 // carry_base: records at offsets >= carry_base are waiting mates carried over from the previous segment of a segmented (streamed) run;
 // they come EARLIER in the file than every record of this segment (the tie-break for level mates) and were counted when first seen
 // (count_stats = 0 for the launch that parks them again).
+// Adjacent-mate path (name-collated input, STAR's pipe).  L(i) = records i and i+1 are both pairing candidates and mates of
+// each other.  Record i is the LEFT half of an adjacent pair when L(i) && !L(i-1), the RIGHT half when L(i-1) && !L(i-2); the two rules
+// name the same pairs from both sides, so the left lane emits the pair and the right lane does nothing, and neither touches the hash
+// table.  Everything else (mates apart, the third and later records of a run of mutual mates) pairs through the table as before, so the
+// result does not depend on whether this path is on: it is a matter of speed only.
+__device__ __forceinline__ bool pair_candidate(const DevTables& T, const Core& c) {
+  return !(c.flag & 0x4) && c.refID >= 0 && !(c.flag & T.rules.skip_flags) && c.refID < T.n_ref && (c.flag & 0x1) && !(c.flag & 0x8) && c.next_refID == c.refID;
+}
+__device__ bool adjacent_mates(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64 i) {   // L(i); i may be "negative" (wrapped)
+  if (i >= nrec || i + 1 >= nrec) return false;
+  const u64 a = rec_off[i], b = rec_off[i + 1]; Core ca, cb; load_core(U, a, ca);
+  if (!pair_candidate(T, ca)) return false;
+  return is_mate(U, a, ca, b, cb) && pair_candidate(T, cb);
+}
 __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const uint8_t* __restrict__ U, const u64* __restrict__ rec_off, u64 nrec, u64* __restrict__ ptab, u32 pmask,
-                                                            u64* __restrict__ pair_list, u64* __restrict__ single_list, u64* __restrict__ list_counts, u64 carry_base, int count_stats) {
+                                                            u64* __restrict__ pair_list, u64* __restrict__ single_list, u64* __restrict__ list_counts, u64 carry_base, int count_stats, int adjacent) {
   u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-  bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0, cand = 0;
+  bool is_single = false, is_pair = false; u64 e = 0, o1 = 0, o2 = 0; u32 skipped = 0, cand = 0, adj = 0;
+  bool Li = false, Lm1 = false, Lm2 = false;
+  if (adjacent) {   // (uniform across the grid) L of this lane's record; the two to the left come from the neighbouring lanes
+    const u32 lane = threadIdx.x & 31;
+    Li = adjacent_mates(T, U, rec_off, nrec, i);
+    bool a = false, b = false; if (lane == 0) { a = adjacent_mates(T, U, rec_off, nrec, i - 1); b = adjacent_mates(T, U, rec_off, nrec, i - 2); }   // i - 1 / i - 2 wrap for i < 2: out of range, false
+    const bool up1 = __shfl_up_sync(0xffffffffu, Li, 1), up2 = __shfl_up_sync(0xffffffffu, Li, 2), a0 = __shfl_sync(0xffffffffu, a, 0);
+    Lm1 = lane == 0 ? a : up1; Lm2 = lane == 0 ? b : lane == 1 ? a0 : up2;
+  }
   if (i < nrec) {
     e = rec_off[i]; Core c; load_core(U, e, c);
     if ((c.flag & 0x4) || c.refID < 0 || (c.flag & T.rules.skip_flags)) skipped = 1;   // [C-6] unmapped records, and what rule_skip_flags adds
     else if (c.refID >= T.n_ref) atomicOr(T.err, DERR_REFID);
     else if (!(c.flag & 0x1) || (c.flag & 0x8) || c.next_refID != c.refID) is_single = true;   // [C-7]
+    else if (Li && !Lm1) {   // left half of an adjacent pair: the mate is the next record (later in the file: it wins only with the smaller pos)
+      cand = 1; adj = 1; is_pair = true; const u64 mo = rec_off[i + 1]; Core m; load_core(U, mo, m);
+      const bool first_is_me = c.pos <= m.pos; o1 = first_is_me ? e : mo; o2 = first_is_me ? mo : e;
+    }
+    else if (Lm1 && !Lm2) cand = 1;   // right half: emitted by the lane to the left
     else {
       u64 mo; Core m; cand = 1;
       if (pair_lookup_or_wait(T, ptab, pmask, U, e, c, mo, m)) {
@@ -650,7 +677,7 @@ __global__ void __launch_bounds__(256) pair_records_kernel(DevTables T, const ui
   u64 at = warp_append(&list_counts[0], is_pair); if (is_pair) { pair_list[2 * at] = o1; pair_list[2 * at + 1] = o2; }
   at = warp_append(&list_counts[1], is_single); if (is_single) single_list[at] = e;
   if (!count_stats) return;
-  warp_add_stat(&T.stats[ST_SKIPPED], skipped); warp_add_stat(&T.stats[ST_CAND], cand);
+  warp_add_stat(&T.stats[ST_SKIPPED], skipped); warp_add_stat(&T.stats[ST_CAND], cand); if (adjacent) warp_add_stat(&T.stats[ST_ADJ], adj);
   if (threadIdx.x == 0) { u64 base = (u64)blockIdx.x * blockDim.x; u64 n = nrec > base ? min((u64)blockDim.x, nrec - base) : 0; if (n) atomicAdd(&T.stats[ST_RECORDS], n); }
 }
 // Shared-memory depth tile of a counting CTA (DevTables::depth_tile): zeroed at the start, flushed at the end - with one red.global per non-zero
@@ -720,9 +747,9 @@ __global__ void __launch_bounds__(128) process_singles_kernel(DevTables T, const
   dt.flush(T);
   warp_add_stat(&T.stats[ST_SINGLE], n); warp_add_stat(&T.stats[ST_NUCLEOTIDES], sink.nuc);
 }
-void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s, u64 carry_base, int count_stats) {
+void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s, u64 carry_base, int count_stats, int adjacent) {
   u64 grid = (nrec + 255) / 256;
-  if (grid) { pair_records_kernel<<<(unsigned)grid, 256, 0, s>>>(T, U, rec_off, nrec, ptab, pmask, pair_list, single_list, list_counts, carry_base, count_stats); IRF_LAUNCHED(); }
+  if (grid) { pair_records_kernel<<<(unsigned)grid, 256, 0, s>>>(T, U, rec_off, nrec, ptab, pmask, pair_list, single_list, list_counts, carry_base, count_stats, adjacent); IRF_LAUNCHED(); }
 }
 __global__ void shift_offsets_kernel(u64* off, u64 n, u64 delta) { u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; if (i < n) off[i] += delta; }
 void launch_shift_offsets(u64* off, u64 n, u64 delta, cudaStream_t s) { u64 g = (n + 255) / 256; if (g) { shift_offsets_kernel<<<(unsigned)g, 256, 0, s>>>(off, n, delta); IRF_LAUNCHED(); } }

@@ -39,7 +39,7 @@ void launch_frame_mark(const FrameArgs& a, uint8_t* mism_scratch, uint8_t* mask,
 void launch_frame_totals(const FrameArgs& a, u64* totals, cudaStream_t s);
 void launch_walk_list(const FrameArgs& a, const u64* rec_base, u64* rec_off, cudaStream_t s);
 void launch_scan_counts(const u32* in, u64* out, int n, cudaStream_t s);
-void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s, u64 carry_base = ~0ull, int count_stats = 1);
+void launch_pair_records(const DevTables& T, const uint8_t* U, const u64* rec_off, u64 nrec, u64* ptab, u32 pmask, u64* pair_list, u64* single_list, u64* list_counts, cudaStream_t s, u64 carry_base = ~0ull, int count_stats = 1, int adjacent = 0);
 void launch_shift_offsets(u64* off, u64 n, u64 delta, cudaStream_t s);
 void launch_process_pairs(const DevTables& T, const uint8_t* U, const u64* pair_list, u64 npairs, cudaStream_t s, const u64* npairs_dev = nullptr);
 void launch_process_singles(const DevTables& T, const uint8_t* U, const u64* single_list, u64 nsingles, cudaStream_t s, const u64* nsingles_dev = nullptr);

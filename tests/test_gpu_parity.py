@@ -913,3 +913,59 @@ def test_cli_with_a_device_list(built, tiny, tmp_path):
         assert _stats_from_stdout(r.stdout) == _stats_from_stdout(tiny["oracle_stdout"])
     bad = subprocess.run([exe, str(tmp_path), tiny["cover"], tiny["sj"], tiny["rc"], tiny["roi"], tiny["sorted"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=dict(os.environ, IRF_DEVICES="0;1"))
     assert bad.returncode != 0
+
+
+# ---- adjacent-mate path (name-collated input / STAR's pipe pairs without the hash table) ----
+
+def test_adjacent_mates_pair_without_the_hash_table(built, tiny, tmp_path):
+    """Name-collated input (header not SO:coordinate) takes the adjacent-mate path by default: nearly every pair is formed from two
+    neighbouring records (only mates split by a chunk boundary go through the table); switching the path off, forcing it on for the
+    coordinate-sorted copy (where only overlapping mates happen to be neighbours) and cutting the file into many small chunks all
+    give the oracle's bytes - the path is a matter of speed, never of result."""
+    want = _stats_from_stdout(tiny["oracle_stdout"])
+    pairs = int(want["Total pairs processed"])
+    runs = [("collated", {}, lambda a: a > 0.95 * pairs),
+            ("collated", dict(adjacent_pairs=0), lambda a: a == 0),
+            ("collated", dict(stream_chunk_kb=64), lambda a: 0.8 * pairs < a <= pairs),
+            ("collated", dict(stream_pipeline=0), lambda a: a > 0.95 * pairs),
+            ("sorted", {}, lambda a: a == 0),
+            ("sorted", dict(adjacent_pairs=1), lambda a: 0 < a < pairs),
+            ("sorted", dict(adjacent_pairs=1, stream_chunk_kb=64), lambda a: 0 < a < pairs)]
+    for i, (which, opts, ok) in enumerate(runs):
+        c = _gpu_run(tiny, str(tmp_path / f"g{i}"), bam=tiny[which], **opts)
+        assert_same_outputs(tiny["oracle_out"], str(tmp_path / f"g{i}"))
+        assert _stats_from_stdout(c.stdout_text) == want
+        adj = c.timing()["adjacent_pairs"]
+        assert ok(adj), (which, opts, adj, pairs)
+
+
+def test_adjacent_path_on_runs_of_identical_mates(built, tiny, tmp_path):
+    """Runs of 2, 3, 4 and 5 records that are all mates of each other (same name, mirrored positions - duplicates as some pipelines emit
+    them): the first two pair as neighbours, the rest through the table, an odd one is left over as an error read, exactly as the
+    reference's one-at-a-time loop does with identical records.  Also a pair whose halves are separated by one unrelated record."""
+    from bamutil import record, write_bam
+    refs = [("chrA", 400000), ("chrB", 300000), ("chrEmpty", 50000)]
+    junc = [l.split("\t") for l in open(tiny["sj"]).read().split("\n") if l]
+    junc = [(0 if j[0] == "chrA" else 1, int(j[1]), int(j[2])) for j in junc if j[0] in ("chrA", "chrB")][:40]
+    P, PROPER, REV, MREV, R1, R2 = 0x1, 0x2, 0x10, 0x20, 0x40, 0x80
+    recs = []
+    for i, (ref, s, e) in enumerate(junc):
+        gap = e - s
+        a = record("run%03d" % i, ref, s - 30, f"30M{gap}N40M", P | PROPER | R1 | MREV, ref, s - 30, 0)      # level mates: pos == next_pos, so every copy is a mate of every other
+        n = 2 + i % 4
+        recs += [a] * n
+        l = record("gap%03d" % i, ref, s - 60, "50M", P | PROPER | R1 | MREV, ref, e + 5, 300)
+        r = record("gap%03d" % i, ref, e + 5, "50M", P | PROPER | R2 | REV, ref, s - 60, -300)
+        recs += [l, record("mid%03d" % i, ref, s - 10, "10M", 0), r]
+    bam = str(tmp_path / "runs.bam")
+    write_bam(bam, refs, recs, level=1, block=2000)
+    meta = dict(tiny, sorted=bam, collated=bam)
+    ostd = run_oracle(built, meta, str(tmp_path / "o"))
+    want = _stats_from_stdout(ostd)
+    assert int(want["Error reads"]) == sum(1 for i in range(len(junc)) if (2 + i % 4) % 2), want
+    for i, opts in enumerate([{}, dict(adjacent_pairs=0), dict(stream_chunk_kb=64)]):
+        c = _gpu_run(meta, str(tmp_path / f"g{i}"), **opts)
+        assert_same_outputs(str(tmp_path / "o"), str(tmp_path / f"g{i}"))
+        assert _stats_from_stdout(c.stdout_text) == want
+        if opts.get("adjacent_pairs", -1) != 0:
+            assert c.timing()["adjacent_pairs"] >= len(junc)
