@@ -64,7 +64,7 @@ const char* irf_last_error(irf_ctx* ctx);
  * "de_percent" (default 70) / "de_percent_stream" (default 100): share of the BGZF blocks inflated by the Blackwell hardware
  * decompression engine when the bytes are resident / streamed from the host; the rest go to the SM kernel; 0 = SM kernel only.
  * "resident_pipeline" (default 1): large resident inputs are counted by the overlapped chunk pipeline, in which the engine takes the
- * trailing "de_percent_overlap" % (default 79) of the file's chunks and the kernel the leading part; 0 = always stage by stage, 2 = always
+ * trailing "de_percent_overlap" % (default 71; the kernel's share is rounded down to whole grid-fulls of blocks) of the file's chunks and the kernel the leading part; 0 = always stage by stage, 2 = always
  * pipelined when structurally possible.  "file_ring" (default 1): irf_run_bam sends files above 64 MB through a ring of page-locked
  * buffers instead of page-locking a copy of the file; 0 = never, 2 = always.  "stream_pipeline" (default 1) / "stream_chunk_kb" (default 262144): chunk pipeline for host bytes.
  * NOTE: the engine answers malformed DEFLATE data with a sticky CUDA error (the process must restart), the SM kernel with IRF_EFORMAT.

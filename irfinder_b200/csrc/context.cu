@@ -81,7 +81,7 @@ static u32 next_pow2(u64 v) { u64 p = 1; while (p < v) p <<= 1; return (u32)std:
 struct irf_ctx {
   int device = 0; cudaStream_t s_compute = nullptr, s_copy = nullptr, s_de = nullptr, s_chk = nullptr;
   // options
-  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 12, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1, de_percent_overlap = 79, resident_pipeline = 1;
+  u32 trim_center = 40; int dump_fragments = 0, inflate_variant = 12, junc_cap_log2 = 24, require_eof = 1; long long entry0_override = -1; int stage_lazy = 0, verify_crc = 1, de_percent = 70, de_percent_stream = 100, planned_percent = -1, de_percent_overlap = 71, resident_pipeline = 1;
   // references (host)
   CoverageRef cov; JunctionRef jref; SpansPointRef sp; RoiRef roi; bool refs_loaded = false;
   // BAM header
@@ -347,7 +347,8 @@ struct irf_ctx {
     for (u32 i : sm_list) sm += (double)blks[i].c_len + blks[i].isize;
     return all > 0 ? sm / all : 0.0;
   }
-  static size_t overlap_lanes() { int l = inflate_resident_lanes(); return l > 0 ? (size_t)l : 94720; }   // 148 SMs x 5 CTAs x 128 lanes before the first launch
+  // BGZF blocks one full grid of the SM inflate kernel holds: the two-phase kernel's geometry for this device (148 SMs x 7 CTAs x 128 lanes), else what the last launch used
+  size_t overlap_lanes() const { if (inflate_variant >= 12 && inflate_variant <= 17) return (size_t)inflate_tok_lanes(inflate_variant); int l = inflate_resident_lanes(); return l > 0 ? (size_t)l : 94720; }
   void plan_engines(int de_percent, int mode = 0) {
     sync();   // a fetch of the previous plan's lists may still be queued against the arena rewritten below
     const size_t nb = blks.size(), chunk = chunk_bytes;
@@ -360,6 +361,7 @@ struct irf_ctx {
     size_t k_sm = 0;
     if (mode == 1 && de_ok) {   // leading chunks for the kernel: its share of the blocks (count_streaming launches it one grid-full of blocks at a time)
       size_t target = nb * (size_t)(100 - de_percent) / 100;
+      { const size_t lanes = overlap_lanes(); if (target >= lanes) target = target / lanes * lanes; }   // whole grid-fulls: a launch over a fraction of the grid takes as long as a full one
       while (k_sm + 1 < nch && chunk_blk_end[k_sm] <= target) k_sm++;
     }
     k_de = nch - k_sm;

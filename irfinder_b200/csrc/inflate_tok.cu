@@ -102,7 +102,7 @@ __device__ __forceinline__ void resolve_batch(uint8_t* ob, const uint32_t* lits,
   }
 }
 
-template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
+template <int WARPS, int LB, int DB, int PATIENCE, int MINB, int FUSE>
 __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uint8_t* __restrict__ comp, const u64* __restrict__ c_off, const u32* __restrict__ c_len,
                                                                   uint8_t* U, const u64* __restrict__ u_off, const u32* __restrict__ u_len, int nblk,
                                                                   int* __restrict__ status, int* __restrict__ err, unsigned int* __restrict__ next_block, const unsigned long long* watermark,
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uin
       if (starved) { if (lane == 0) atomicOr(err, DERR_STARVED); break; }
     }
     int b = (int)base + lane; const bool in_range = b < nblk; if (list && in_range) b = (int)list[b];
-    TokLane<32, LB, DB> L;
+    TokLane<32, LB, DB, FUSE> L;
     const bool work = in_range && !(u_len[b] == 0 && c_len[b] <= 2);  // skip the 28-byte EOF marker / empty blocks
     if (work) L.start(comp + c_off[b], c_len[b], u_len[b], lit, dst, lane, sym_store, my_tok); else L.idle();
     uint8_t* const my_out = work ? U + u_off[b] : nullptr;
@@ -186,13 +186,13 @@ __global__ void __launch_bounds__(WARPS * 32, MINB) inflate_tok_kernel(const uin
 
 // One geometry record per kernel instantiation and device (the shared-memory opt-in and the occupancy are per device).
 struct TokGeom { int ctas_per_sm, sms; size_t smem; int warps; };
-template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
+template <int WARPS, int LB, int DB, int PATIENCE, int MINB, int FUSE>
 static TokGeom tok_geometry() {
   static int ctas[64] = {0}, sms[64] = {0};
   const size_t smem = (size_t)WARPS * TokLane<32, LB, DB>::TABLE_U16 * sizeof(uint16_t);
   int dev = 0; IRF_CUDA(cudaGetDevice(&dev)); if (dev < 0 || dev >= 64) throw std::string("device ordinal beyond 63 is not supported");
   if (!ctas[dev]) {
-    auto kern = inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB>;
+    auto kern = inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB, FUSE>;
     IRF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     IRF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas[dev], kern, WARPS * 32, smem));
     IRF_CUDA(cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev));
@@ -200,31 +200,35 @@ static TokGeom tok_geometry() {
   }
   return TokGeom{ctas[dev], sms[dev], smem, WARPS};
 }
-template <int WARPS, int LB, int DB, int PATIENCE, int MINB>
+template <int WARPS, int LB, int DB, int PATIENCE, int MINB, int FUSE>
 static void tok_launch(const InflateArgs& a, cudaStream_t s) {
-  const TokGeom g = tok_geometry<WARPS, LB, DB, PATIENCE, MINB>();
+  const TokGeom g = tok_geometry<WARPS, LB, DB, PATIENCE, MINB, FUSE>();
   const int need = (a.nblk + WARPS * 32 - 1) / (WARPS * 32), grid = std::min(need, g.ctas_per_sm * g.sms);
   if (grid <= 0) return;
   if (!a.tok_scratch || a.tok_scratch_bytes < (size_t)grid * WARPS * 32 * TOK_CAP * sizeof(uint32_t)) throw std::string("inflate: token scratch missing or too small");
   const bool prof = getenv("IRF_TOK_PROF") != nullptr;
   if (prof) { unsigned long long z[8] = {0}; IRF_CUDA(cudaMemcpyToSymbol(g_tok_prof, z, sizeof z)); }
   IRF_CUDA(cudaMemsetAsync(a.next_block, 0, sizeof(unsigned int), s));
-  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch);
+  inflate_tok_kernel<WARPS, LB, DB, PATIENCE, MINB, FUSE><<<grid, WARPS * 32, g.smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, a.watermark, a.list, a.tok_scratch);
   note_launch();
   if (prof) { IRF_CUDA(cudaStreamSynchronize(s)); unsigned long long z[8]; IRF_CUDA(cudaMemcpyFromSymbol(z, g_tok_prof, sizeof z));
-    fprintf(stderr, "[tok] <%d warps, %d/%d-bit LUTs> grid %d x %d CTAs/SM: phase A %.1f Mcycles/claim, phase B %.1f Mcycles/claim, %llu claims; per claim: %.0f votes, %.1f table builds, %.0f batches, %.2f rounds/batch\n", WARPS, LB, DB, grid, g.ctas_per_sm,
+    fprintf(stderr, "[tok] <%d warps, %d/%d-bit LUTs, fuse %d> grid %d x %d CTAs/SM: phase A %.1f Mcycles/claim, phase B %.1f Mcycles/claim, %llu claims; per claim: %.0f votes, %.1f table builds, %.0f batches, %.2f rounds/batch\n", WARPS, LB, DB, FUSE, grid, g.ctas_per_sm,
             z[0] / 1e6 / std::max(1ull, z[6]), z[1] / 1e6 / std::max(1ull, z[6]), z[6], (double)z[2] / std::max(1ull, z[6]), (double)z[3] / std::max(1ull, z[6]), (double)z[4] / std::max(1ull, z[6]), (double)z[5] / std::max(1ull, z[4])); }
 }
-// variants: LUT width against warps per SM (shared memory per warp = TokLane::TABLE_U16 * 2 bytes; registers per thread follow from MINB)
-//   12: 6/5 bits, 5 CTAs x 4 warps = 20 warps per SM (96 registers; measured fastest: 124.9 ms on the 20M-pair file)
-//   13: 6/5 bits, 7 CTAs x 4 warps = 28 warps (72 registers, 140 bytes spilled: 143 ms - the kernel is bound by issue slots and L1
-//       wavefronts, not by latency, so more warps only add spills)
-//   14: 7/5 bits, 5 CTAs x 3 warps = 15 warps (174 ms: the wider LUT saves fewer instructions than the lost warps cost)     15: 8/6 bits, 9 warps
+// variants: fused iteration, warps per SM (registers per thread follow from MINB), LUT width (shared memory per warp = TokLane::TABLE_U16 * 2 bytes).
+// What counts is the steady state of a full grid, blocks per cycle = resident warps / cycles per claim of 32 blocks (IRF_TOK_PROF=1), because
+// the pipeline launches the kernel one grid-full of blocks at a time; the time for a whole file also depends on how its block count
+// divides into grid-fulls (5651 claims are 1.91 rounds of 2960 warps but 1.36 rounds of 4144, which hid this for a round).
+//   12: fused, 6/5 bits, 7 CTAs x 4 warps = 28 warps per SM (72 registers, 60 bytes spilled): 137.7 Mcycles per claim -> 0.203 claims per Mcycle and SM
+//   17: fused, 24 warps (80 registers): 125.0 Mcycles -> 0.192        13: fused, 20 warps (95 registers, no spill): 117.8 Mcycles -> 0.170
+//   16: not fused, 20 warps (the kernel as first committed in round 2): 123.0 Mcycles -> 0.163
+//   14: 7/5 bits, 15 warps; 15: 8/6 bits, 9 warps (not fused: the wider LUT leaves too few bits per refill; both far slower)
 #define IRF_TOK_DISPATCH(variant, CALL) \
-  switch (variant) { case 13: CALL(4, 6, 5, 24, 7); break; case 14: CALL(3, 7, 5, 24, 5); break; case 15: CALL(3, 8, 6, 24, 3); break; default: CALL(4, 6, 5, 24, 5); break; }
+  switch (variant) { case 13: CALL(4, 6, 5, 24, 5, 1); break; case 14: CALL(3, 7, 5, 24, 5, 0); break; case 15: CALL(3, 8, 6, 24, 3, 0); break; case 16: CALL(4, 6, 5, 24, 5, 0); break; \
+                     case 17: CALL(4, 6, 5, 24, 6, 1); break; default: CALL(4, 6, 5, 24, 7, 1); break; }
 static TokGeom tok_geom_of(int variant) {
   TokGeom g{};
-#define IRF_TOK_GEOM(W, LB, DB, P, M) g = tok_geometry<W, LB, DB, P, M>()
+#define IRF_TOK_GEOM(W, LB, DB, P, M, F) g = tok_geometry<W, LB, DB, P, M, F>()
   IRF_TOK_DISPATCH(variant, IRF_TOK_GEOM)
   return g;
 }
@@ -239,7 +243,7 @@ static std::atomic<unsigned long long> g_tok_launches{0};
 unsigned long long tok_launch_counter() { return g_tok_launches.load(std::memory_order_relaxed); }   // launches of the two-phase kernel by this process (tests check that the default path really runs it)
 void launch_inflate_tok(const InflateArgs& a, int variant, cudaStream_t s) {
   g_tok_launches.fetch_add(1, std::memory_order_relaxed);
-#define IRF_TOK_LAUNCH(W, LB, DB, P, M) tok_launch<W, LB, DB, P, M>(a, s)
+#define IRF_TOK_LAUNCH(W, LB, DB, P, M, F) tok_launch<W, LB, DB, P, M, F>(a, s)
   IRF_TOK_DISPATCH(variant, IRF_TOK_LAUNCH)
 }
 

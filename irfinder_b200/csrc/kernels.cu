@@ -143,9 +143,9 @@ static void launch_inflate_t(const InflateArgs& a, cudaStream_t s) {
     inflate_kernel<WARPS, LB, DB, HB, LC, PZ, D8, MINB><<<grid, WARPS * 32, smem, s>>>(a.comp, a.c_off, a.c_len, a.U, a.u_off, a.u_len, a.nblk, a.status, a.err, a.next_block, LC ? nullptr : a.watermark, LC ? nullptr : a.list); IRF_LAUNCHED();
   }
 }
-size_t inflate_scratch_bytes(int variant, int nblk) { return variant >= 12 && variant <= 15 && nblk > 0 ? inflate_tok_scratch_bytes(variant, nblk) : 0; }
+size_t inflate_scratch_bytes(int variant, int nblk) { return variant >= 12 && variant <= 17 && nblk > 0 ? inflate_tok_scratch_bytes(variant, nblk) : 0; }
 void launch_inflate(const InflateArgs& a, int variant, cudaStream_t s) {
-  if (variant >= 12 && variant <= 15) { launch_inflate_tok(a, variant, s); g_inflate_lanes = inflate_tok_lanes(variant); return; }   // two-phase kernel: token decode per lane, then warp-wide resolve (inflate_tok.cu)
+  if (variant >= 12 && variant <= 17) { launch_inflate_tok(a, variant, s); g_inflate_lanes = inflate_tok_lanes(variant); return; }   // two-phase kernel: token decode per lane, then warp-wide resolve (inflate_tok.cu)
   switch (variant) {   // one-phase kernel: <warps per CTA, literal LUT bits, distance LUT bits, header batch, lane-granular claims, pre-written sectors, byte distance LUT, CTAs per SM>
     case 2: launch_inflate_t<4, 6, 5, 1, 0, 1>(a, s); break;   // pre-written output sectors
     case 3: launch_inflate_t<4, 6, 6, 1, 0, 1>(a, s); break;

@@ -766,7 +766,7 @@ def test_file_input_through_the_page_locked_ring(tiny, tmp_path, chunk_kb):
     assert_same_outputs(tiny["oracle_out"], str(tmp_path / "recount"))
 
 
-@pytest.mark.parametrize("variant", [0, 12, 13, 14, 15, 10, 11, 7, 2])
+@pytest.mark.parametrize("variant", [0, 12, 13, 14, 15, 16, 17, 10, 11, 7, 2])
 def test_inflate_kernel_variants_agree(tiny, tmp_path, variant):
     """The A/B variants of the SM inflate kernel (pre-written sectors, wider LUTs, byte-entry distance LUT with five or six
     CTAs per SM; the shared-memory output-ring variants are disabled, see launch_inflate) must produce the same bytes as the default: outputs equal the oracle's with the

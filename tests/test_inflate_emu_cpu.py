@@ -29,7 +29,7 @@ def _bgzf(data, level):
     return out
 
 
-@pytest.mark.parametrize("bits", [7, 8, 9, 10, 306, 307, 406, 407, 409])   # 4xx: the two-phase token decoder (inflate_tok.cuh)
+@pytest.mark.parametrize("bits", [7, 8, 9, 10, 306, 307, 406, 407, 409, 416])   # 4xx: the two-phase token decoder (inflate_tok.cuh)
 def test_generated_bam_blocks(built, emu, tmp_path, bits):
     from irfinder_b200 import synth
     meta = synth.generate(str(tmp_path / "w"), genome="tiny", introns=80, pairs=6000, readlen=100, seed=31, chunks=2, collated=False)
@@ -47,6 +47,6 @@ def test_other_encoders_and_edge_streams(emu, tmp_path):
         c = zlib.compressobj(9, zlib.DEFLATED, -15, 9, zlib.Z_FIXED)   # fixed-Huffman blocks
         f.write(b"".join(_bgzf(blob[i:i + 3000], 9) for i in range(0, 30000, 3000)))
         f.write(_bgzf(b"", 6) if False else b"")
-    for bits in (7, 9, 306, 406, 408):
+    for bits in (7, 9, 306, 406, 408, 416):
         r = subprocess.run([emu, p, str(bits)], stdout=subprocess.PIPE, text=True)
         assert r.returncode == 0 and " bad 0" in r.stdout, r.stdout
