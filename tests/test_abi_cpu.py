@@ -73,3 +73,21 @@ def test_cli_reports_usage_and_missing_gpu(built):
     if not torch.cuda.is_available():
         r = subprocess.run([exe, "/tmp", "a", "b", "c", "NULL", "x.bam"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
         assert r.returncode == 2 and "cannot initialise CUDA device" in r.stderr and r.stdout == ""
+
+
+def test_cli_device_list_is_parsed_before_cuda(built):
+    """IRF_DEVICES (the in-process multi-device context): a list that cannot be parsed is refused with exit code 1 before any
+    device is touched; well-formed lists ("0,1", ranges "0-3", repeats "0,0") get as far as device initialisation, which on a box
+    without a GPU is the 'cannot initialise' failure that names the list."""
+    exe = os.path.join(ROOT, "bin", "irfinder")
+    if not os.path.exists(exe):
+        pytest.skip("CLI not built")
+    args = [exe, "/tmp", "a", "b", "c", "NULL", "x.bam"]
+    for bad in ("0;1", "a", "3-1", "0,,1", "-1", "0-"):
+        r = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=dict(os.environ, IRF_DEVICES=bad))
+        assert r.returncode == 1 and "cannot parse IRF_DEVICES" in r.stderr, (bad, r.returncode, r.stderr)
+    import torch
+    if not torch.cuda.is_available():
+        for good in ("0,1", "0-3", "0,0", "2"):
+            r = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=dict(os.environ, IRF_DEVICES=good))
+            assert r.returncode == 2 and "cannot initialise CUDA device" in r.stderr, (good, r.returncode, r.stderr)
